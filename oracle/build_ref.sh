@@ -1,0 +1,25 @@
+#!/usr/bin/env bash
+# TEST INFRASTRUCTURE.  Builds the UNMODIFIED reference VQ path (src/vq_encoder.cpp,
+# src/bcn_compressor.cpp + vendored Compressonator static libs) from where it lies under
+# $YUP_REFERENCE (default /root/reference) into oracle/_ref/libyupref.so, behind the C-ABI shim
+# oracle/ref_harness.cpp.  Flags follow the reference's CMakeLists.txt:142 (-mavx2 -mfma, OpenMP);
+# the reference's own CMake is not run (zstd submodule and TBB are missing).
+# No reference source is copied; all outputs go to oracle/_ref/ (git-ignored, travels with gpurun).
+set -euo pipefail
+HERE="$(cd "$(dirname "$0")" && pwd)"
+R="${YUP_REFERENCE:-/root/reference}"
+OUT="$HERE/_ref"
+if [ ! -d "$R/src" ]; then
+  echo "build_ref: $R not present; keeping any prebuilt $OUT/libyupref.so" >&2
+  exit 0
+fi
+mkdir -p "$OUT"
+L="$R/thirdparty/Compressonator/linux/lib/x64"
+CXXFLAGS="-std=c++17 -O2 -fopenmp -mavx2 -mfma -fPIC -I$R/include -I$R/thirdparty/colorm/include -I$R/thirdparty/Compressonator/include"
+g++ $CXXFLAGS -c "$R/src/vq_encoder.cpp" -o "$OUT/vq_encoder.o"
+g++ $CXXFLAGS -c "$R/src/bcn_compressor.cpp" -o "$OUT/bcn_compressor.o"
+g++ $CXXFLAGS -c "$HERE/ref_harness.cpp" -o "$OUT/ref_harness.o"
+g++ -shared -fopenmp -o "$OUT/libyupref.so" "$OUT/ref_harness.o" "$OUT/vq_encoder.o" "$OUT/bcn_compressor.o" \
+  -Wl,--start-group "$L/libCMP_Compressonator.a" "$L/libCMP_Common.a" "$L/libCMP_Core.a" \
+  "$L/libCMP_Core_SSE.a" "$L/libCMP_Core_AVX.a" "$L/libCMP_Core_AVX512.a" -Wl,--end-group -lpthread -ldl
+echo "build_ref: built $OUT/libyupref.so"
