@@ -1,0 +1,196 @@
+/*
+ * yupvq.h -- C ABI of the B200-native YupTexture vector-quantisation hot path.
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no C++ or torch types.
+ * Every entry point names the reference interface it replaces (paths relative to the reference
+ * repository, YupCore/YupTexture @ 7c8d4366).  The C++ classes in include/vq_encoder.h and
+ * include/vq_bcn_compressor.h (same names/signatures as the reference's) are thin wrappers over
+ * these calls; INTEGRATION.md shows the binding a reference maintainer would add.
+ *
+ * Conventions
+ *   - All functions return 0 on success, non-zero on failure; yupvq_last_error(ctx) gives the text
+ *     (the C++ wrapper rethrows it as std::runtime_error, the reference's convention,
+ *     src/vq_bcn_compressor.cpp:99).
+ *   - Data pointers may be host OR device pointers (detected with cudaPointerGetAttributes);
+ *     host buffers are staged through pinned memory owned by the context.  Outputs are caller-owned.
+ *   - A context is bound to one CUDA device and is not safe for concurrent calls (same contract as
+ *     one VQBCnCompressor instance, include/vq_bcn_compressor.h:16-25).
+ *   - There is no CPU fallback: without a CUDA device yupvq_create fails.
+ *   - Block order is row-major over 4x4 tiles, pixel order row-major inside a tile, channels
+ *     interleaved -- the layout of src/vq_bcn_compressor.cpp:142-146 / :235-252.
+ */
+#ifndef YUPVQ_H
+#define YUPVQ_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define YUPVQ_API __attribute__((visibility("default")))
+#else
+#define YUPVQ_API
+#endif
+
+typedef struct yupvq_ctx yupvq_ctx;
+
+/* BCFormat values of include/vq_bcn_types.h:27-36. */
+enum { YUPVQ_BC1 = 1, YUPVQ_BC2 = 2, YUPVQ_BC3 = 3, YUPVQ_BC4 = 4, YUPVQ_BC5 = 5, YUPVQ_BC6H = 6, YUPVQ_BC7 = 7 };
+/* DistanceMetric values of include/vq_bcn_types.h:105-108. */
+enum { YUPVQ_METRIC_SAD = 0, YUPVQ_METRIC_OKLAB = 1 };
+/* Assignment engine: AUTO picks the tcgen05 front-end + exact re-rank when the shape allows it. */
+enum { YUPVQ_ASSIGN_AUTO = 0, YUPVQ_ASSIGN_EXACT = 1, YUPVQ_ASSIGN_TENSOR = 2 };
+
+/* Mirrors CompressionConfig (include/vq_encoder.h:22-41) + the seed the reference lacks
+ * (src/vq_encoder.cpp:24-26 seeds std::mt19937 from std::random_device). */
+typedef struct yupvq_config {
+    uint32_t codebook_size;   /* K; use yupvq_codebook_size(quality) for the reference mapping      */
+    uint32_t max_iterations;  /* CompressionConfig::maxIterations (32)                              */
+    int32_t  metric;          /* YUPVQ_METRIC_*  (HDR ignores it: always Oklab)                     */
+    float    sample_ratio;    /* CompressionConfig::fastModeSampleRatio; >=1 or <=0 -> all blocks   */
+    uint64_t seed;            /* std::mt19937 seed; 0 -> std::random_device (reference behaviour)   */
+    int32_t  assign_mode;     /* YUPVQ_ASSIGN_*                                                     */
+    int32_t  reserved;
+} yupvq_config;
+
+typedef struct yupvq_stats {
+    uint32_t n_blocks;        /* blocks clustered (after sampling)                                  */
+    uint32_t codebook_size;
+    uint32_t lloyd_passes;    /* assignment passes run inside BuildCodebook                         */
+    uint32_t seed_rounds;     /* K-Means++ rounds that drew a sample                                */
+    uint32_t reseeds;         /* empty clusters re-seeded over all passes                           */
+    uint32_t rerank_blocks;   /* blocks sent to the exact re-rank over all passes (tensor mode)     */
+    float ms_h2d, ms_decode, ms_seed, ms_lloyd, ms_finalize, ms_quantize, ms_d2h, ms_total;
+    uint32_t gpu_launches;    /* kernels launched by this call                                      */
+    uint32_t reserved;
+} yupvq_stats;
+
+/* ---- lifetime ------------------------------------------------------------------------------ */
+YUPVQ_API int yupvq_create(int device, yupvq_ctx** out);
+YUPVQ_API void yupvq_destroy(yupvq_ctx* ctx);
+YUPVQ_API const char* yupvq_last_error(const yupvq_ctx* ctx); /* ctx may be NULL: creation error */
+YUPVQ_API const char* yupvq_version(void);
+
+/* Device-side stopwatch on the context's stream (CUDA events): brackets any sequence of calls.
+ * The reference wraps its calls in std::chrono (example/example.cpp:293-304); this is the
+ * device-clock equivalent the bench uses. */
+YUPVQ_API int yupvq_timer_start(yupvq_ctx* ctx);
+YUPVQ_API int yupvq_timer_stop(yupvq_ctx* ctx, float* out_ms);
+
+/* CompressionConfig::SetQuality, src/vq_encoder.cpp:12-18 (powers hard-wired 4..10). */
+YUPVQ_API uint32_t yupvq_codebook_size(float quality);
+/* Fill cfg the way VQBCnCompressor::Compress does from CompressionParams,
+ * src/vq_bcn_compressor.cpp:128-134. */
+YUPVQ_API void yupvq_config_init(yupvq_config* cfg, float quality, uint32_t max_iterations, int metric,
+                                 float sample_ratio, uint64_t seed);
+
+/* ---- whole-path entry points ----------------------------------------------------------------- */
+
+/* LDR VQ from BCn bytes: the three starred lines of VQBCnCompressor::Compress
+ * (src/vq_bcn_compressor.cpp:142-150): per-block BCn decode, BuildCodebook (up to, not including,
+ * the Compressonator centroid encode of src/vq_encoder.cpp:434-439) and QuantizeBlocks.
+ *   bc_blocks           n_blocks * blockSize bytes (8 for BC1/BC4, else 16)
+ *   out_pixel_centroids K * 16*channels bytes   (outPixelCentroids of BuildCodebook)
+ *   out_indices         n_blocks uint32         (QuantizeBlocks result)                          */
+YUPVQ_API int yupvq_encode_bcn(yupvq_ctx* ctx, const uint8_t* bc_blocks, size_t n_blocks, int bc_format,
+                               int channels, const yupvq_config* cfg, uint8_t* out_pixel_centroids,
+                               uint32_t* out_indices, yupvq_stats* stats);
+
+/* HDR VQ from the raw float image: VQBCnCompressor::CompressHDR, src/vq_bcn_compressor.cpp:230-256
+ * (edge-clamped 4x4 tile gather, BuildCodebookHDR up to the BC6H encode, QuantizeBlocksHDR).
+ *   image               height*width*channels floats, row-major
+ *   out_float_centroids K * 16*channels floats                                                    */
+YUPVQ_API int yupvq_encode_hdr(yupvq_ctx* ctx, const float* image, uint32_t width, uint32_t height,
+                               int channels, const yupvq_config* cfg, float* out_float_centroids,
+                               uint32_t* out_indices, yupvq_stats* stats);
+
+/* Batch of independent same-shape BC textures run in lock-step (BASELINE config 5).  Each texture
+ * gets its own codebook; seeds are cfg->seed + t.  Pointers are arrays of n_textures pointers.  */
+YUPVQ_API int yupvq_encode_bcn_batch(yupvq_ctx* ctx, const uint8_t* const* bc_blocks, size_t n_textures,
+                                     size_t n_blocks, int bc_format, int channels, const yupvq_config* cfg,
+                                     uint8_t* const* out_pixel_centroids, uint32_t* const* out_indices,
+                                     yupvq_stats* stats);
+
+/* ---- the reference's four public VQEncoder calls, on decoded blocks --------------------------- */
+
+/* VQEncoder::BuildCodebook, src/vq_encoder.cpp:260-433 (pixel blocks already decoded). */
+YUPVQ_API int yupvq_build_codebook(yupvq_ctx* ctx, const uint8_t* pixel_blocks, size_t n_blocks, int channels,
+                                   const yupvq_config* cfg, uint8_t* out_pixel_centroids, yupvq_stats* stats);
+/* VQEncoder::QuantizeBlocks, src/vq_encoder.cpp:447-486. */
+YUPVQ_API int yupvq_quantize_blocks(yupvq_ctx* ctx, const uint8_t* pixel_blocks, size_t n_blocks, int channels,
+                                    const uint8_t* pixel_centroids, uint32_t codebook_size, int metric,
+                                    int assign_mode, uint32_t* out_indices, yupvq_stats* stats);
+/* VQEncoder::BuildCodebookHDR, src/vq_encoder.cpp:493-613. */
+YUPVQ_API int yupvq_build_codebook_hdr(yupvq_ctx* ctx, const float* float_blocks, size_t n_blocks, int channels,
+                                       const yupvq_config* cfg, float* out_float_centroids, yupvq_stats* stats);
+/* VQEncoder::QuantizeBlocksHDR, src/vq_encoder.cpp:629-658. */
+YUPVQ_API int yupvq_quantize_blocks_hdr(yupvq_ctx* ctx, const float* float_blocks, size_t n_blocks, int channels,
+                                        const float* float_centroids, uint32_t codebook_size, int assign_mode,
+                                        uint32_t* out_indices, yupvq_stats* stats);
+
+/* ---- kernel-level entry points (unit parity; each is one stage of the path) ------------------- */
+
+/* BCnCompressor::Decompress of one 4x4 block, src/bcn_compressor.cpp:191-227, for n blocks. */
+YUPVQ_API int yupvq_decode_bcn(yupvq_ctx* ctx, const uint8_t* bc_blocks, size_t n_blocks, int bc_format,
+                               int channels, uint8_t* out_pixel_blocks);
+/* VQEncoder::PixelBlockToOklabBlock, src/vq_encoder.cpp:96-102 (out: n * 64 floats). */
+YUPVQ_API int yupvq_pixels_to_oklab(yupvq_ctx* ctx, const uint8_t* pixel_blocks, size_t n_blocks, int channels,
+                                    float* out_oklab);
+/* VQEncoder::OklabBlockToPixelBlock, src/vq_encoder.cpp:105-111. */
+YUPVQ_API int yupvq_oklab_to_pixels(yupvq_ctx* ctx, const float* oklab, size_t n_blocks, int channels,
+                                    uint8_t* out_pixel_blocks);
+/* VQEncoder::RgbaFloatBlockToOklabBlock, src/vq_encoder.cpp:179-185. */
+YUPVQ_API int yupvq_floats_to_oklab(yupvq_ctx* ctx, const float* float_blocks, size_t n_blocks, int channels,
+                                    float* out_oklab);
+/* VQEncoder::OklabBlockToRgbaFloatBlock, src/vq_encoder.cpp:188-194. */
+YUPVQ_API int yupvq_oklab_to_floats(yupvq_ctx* ctx, const float* oklab, size_t n_blocks, int channels,
+                                    float* out_float_blocks);
+/* The 4x4 tile gather of src/vq_bcn_compressor.cpp:235-252 (out: n_blocks * 16*channels floats). */
+YUPVQ_API int yupvq_gather_tiles(yupvq_ctx* ctx, const float* image, uint32_t width, uint32_t height,
+                                 int channels, float* out_float_blocks);
+/* The assignment loop of src/vq_encoder.cpp:330-340 on Oklab features: argmin with strict '<'
+ * (lowest index wins) and errors[i] = min distance (OklabBlockDistanceSq_SIMD, :212-237).
+ * out_errors may be NULL. */
+YUPVQ_API int yupvq_assign(yupvq_ctx* ctx, const float* features, size_t n_blocks, const float* centroids,
+                           uint32_t codebook_size, int assign_mode, uint32_t* out_indices, float* out_errors,
+                           yupvq_stats* stats);
+/* K-Means++ seeding of src/vq_encoder.cpp:287-313 (LDR, SAD^2 on pixels): out_seed_blocks[k] is the
+ * index of the block chosen as seed k.  Returns through *out_rounds the rounds that drew a sample. */
+YUPVQ_API int yupvq_seed_ldr(yupvq_ctx* ctx, const uint8_t* pixel_blocks, size_t n_blocks, int channels,
+                             uint32_t codebook_size, uint64_t seed, uint32_t* out_seed_blocks, uint32_t* out_rounds);
+/* K-Means++ seeding of src/vq_encoder.cpp:526-554 (HDR, weighted L2 on Oklab features). */
+YUPVQ_API int yupvq_seed_hdr(yupvq_ctx* ctx, const float* features, size_t n_blocks, uint32_t codebook_size,
+                             uint64_t seed, uint32_t* out_seed_blocks, uint32_t* out_rounds);
+/* One Lloyd update of src/vq_encoder.cpp:343-375: sums/counts, c = sum * (1.0f / count), empty
+ * clusters re-seeded with serial semantics from `errors` (modified in place on the device copy). */
+YUPVQ_API int yupvq_update_centroids(yupvq_ctx* ctx, const float* features, size_t n_blocks,
+                                     const uint32_t* assignments, const float* errors, uint32_t codebook_size,
+                                     float* inout_centroids, uint32_t* out_counts);
+/* VQBCnCompressor::DecompressToBCn gather, src/vq_bcn_compressor.cpp:350-358:
+ * out[i] = codebook[indices[i]] (blocks with an out-of-range index are left zero, as the reference
+ * leaves them default-initialised). */
+YUPVQ_API int yupvq_gather_codebook(yupvq_ctx* ctx, const uint8_t* codebook, uint32_t n_entries, uint32_t block_size,
+                                    const uint32_t* indices, size_t n_blocks, uint8_t* out_bc_blocks);
+
+/* ---- multi-GPU (one process per GPU) -------------------------------------------- */
+
+/* NCCL bootstrap: rank 0 calls yupvq_comm_unique_id, the host runtime (torch.distributed, MPI, a
+ * file) hands the 128 bytes to every rank, then every rank calls yupvq_comm_init. */
+YUPVQ_API int yupvq_comm_unique_id(yupvq_ctx* ctx, uint8_t out_id[128]);
+YUPVQ_API int yupvq_comm_init(yupvq_ctx* ctx, const uint8_t id[128], int n_ranks, int rank);
+/* Block-sharded LDR VQ: this rank holds blocks [first_block, first_block + n_local) of a texture
+ * of n_total blocks; the whole texture's BCn bytes are passed on every rank (seeding is replicated
+ * and integer-exact, so every rank draws the same seeds with no communication).  Per Lloyd pass
+ * the K x 64 fixed-point sums, K counts and the changed flag are all-reduced over NCCL.
+ * out_indices receives this rank's n_local indices. */
+YUPVQ_API int yupvq_encode_bcn_sharded(yupvq_ctx* ctx, const uint8_t* bc_blocks, size_t n_total, size_t first_block,
+                                       size_t n_local, int bc_format, int channels, const yupvq_config* cfg,
+                                       uint8_t* out_pixel_centroids, uint32_t* out_indices, yupvq_stats* stats);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* YUPVQ_H */

@@ -1,0 +1,1162 @@
+// C ABI (include/yupvq.h) and host orchestration of the VQ hot path.
+// Replaces, behind plain C entry points, the three starred lines of the reference's
+// VQBCnCompressor::Compress (src/vq_bcn_compressor.cpp:142-150) / CompressHDR (:230-256) and the
+// four public VQEncoder calls (include/vq_encoder.h:76-103).  All arithmetic runs in CUDA kernels
+// on the context's device; there is no CPU path.
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <numeric>
+#include <random>
+#include <string>
+#include <vector>
+
+#include "../../include/yupvq.h"
+#include "kernels.h"
+#include "nccl_dyn.h"
+
+using namespace yupvq;
+
+namespace {
+
+thread_local std::string g_create_error;
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        // round up so repeated slightly-larger requests do not thrash the allocator
+        size_t want = (bytes + (1u << 20) - 1) & ~(size_t)((1u << 20) - 1);
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+    template <typename T>
+    T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+}  // namespace
+
+struct yupvq_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    cudaEvent_t ev[10] = {};
+    cudaEvent_t ev_user[2] = {};
+    uint32_t launches = 0;
+    uint32_t reseeds_sharded = 0;
+
+    // device arena (grow-only, reused across calls)
+    DevBuf in_bytes;    // staged input (BCn bytes / pixel blocks / float image or blocks)
+    DevBuf planes;      // uint8 pixel planes (ch planes of uint4)
+    DevBuf feat;        // N x 64 fp32 features
+    DevBuf s_planes, s_feat, s_rows;  // fast-mode sampled subset
+    DevBuf min_dist, partial, seed_idx, canon, small;  // seeding
+    DevBuf assign, errors, cent, acc;                  // Lloyd
+    DevBuf cent_px, cent_feat, out_idx;                // finalize / quantize
+    uint32_t* h_small = nullptr;                       // pinned: flags + status readback
+
+    // multi-GPU
+    NcclApi nccl;
+    void* comm = nullptr;
+    int n_ranks = 1, rank = 0;
+
+    int fail(const char* fmt, ...) {
+        char buf[512];
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(buf, sizeof(buf), fmt, ap);
+        va_end(ap);
+        err = buf;
+        return 1;
+    }
+};
+
+#define CK(call)                                                                                        \
+    do {                                                                                                \
+        cudaError_t e_ = (call);                                                                        \
+        if (e_ != cudaSuccess) return ctx->fail("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), \
+                                                __FILE__, __LINE__);                                    \
+    } while (0)
+#define LAUNCH(call)     \
+    do {                 \
+        CK(call);        \
+        ++ctx->launches; \
+    } while (0)
+
+namespace {
+
+// small device scratch layout (uint32 words)
+enum { F_CHANGED = 0, F_EMPTY = 1, F_RESEEDS = 2, F_SPARE = 3, F_SEED_STATUS = 4 /*2 words*/, F_COUNTER = 6, F_MAXABS = 7, F_WORDS = 16 };
+
+bool is_device_ptr(const void* p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+// Returns a device pointer for `src` (staging host memory through `stage`).
+int to_device(yupvq_ctx* ctx, const void* src, size_t bytes, DevBuf& stage, const void** out) {
+    if (is_device_ptr(src)) {
+        *out = src;
+        return 0;
+    }
+    CK(stage.ensure(bytes));
+    CK(cudaMemcpyAsync(stage.p, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    *out = stage.p;
+    return 0;
+}
+
+int from_device(yupvq_ctx* ctx, void* dst, const void* src_dev, size_t bytes) {
+    if (!dst || bytes == 0) return 0;
+    CK(cudaMemcpyAsync(dst, src_dev, bytes, is_device_ptr(dst) ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost,
+                       ctx->stream));
+    return 0;
+}
+
+size_t bc_block_bytes(int fmt) { return (fmt == YUPVQ_BC1 || fmt == YUPVQ_BC4) ? 8 : 16; }
+
+bool bc_supported(int fmt) {
+    return fmt == YUPVQ_BC1 || fmt == YUPVQ_BC3 || fmt == YUPVQ_BC4 || fmt == YUPVQ_BC5 || fmt == YUPVQ_BC7;
+}
+
+struct Timer {
+    yupvq_ctx* ctx;
+    int next = 0;
+    explicit Timer(yupvq_ctx* c) : ctx(c) {}
+    int mark() {
+        cudaEventRecord(ctx->ev[next], ctx->stream);
+        return next++;
+    }
+    float ms(int a, int b) {
+        float v = 0.f;
+        cudaEventElapsedTime(&v, ctx->ev[a], ctx->ev[b]);
+        return v;
+    }
+};
+
+// The RNG stream of BuildCodebook: optional shuffle, one uniform_int draw,
+// then one canonical double per seeding round.  Host code uses the same libstdc++ <random> as the
+// reference, so the draws are bit-identical for the same seed.
+struct Draws {
+    std::vector<uint32_t> sample;  // empty -> all blocks in order
+    uint32_t first = 0;
+    std::vector<double> canon;
+};
+
+Draws make_draws(size_t n_all, uint32_t K, float ratio, uint64_t seed, size_t* n_used) {
+    Draws d;
+    std::mt19937 rng;
+    if (seed == 0) rng.seed(std::random_device{}());
+    else rng.seed((uint32_t)seed);
+    size_t n = n_all;
+    if (ratio < 1.0f && ratio > 0.0f) {  // src/vq_encoder.cpp:263-276
+        size_t m = (size_t)(n_all * ratio);
+        m = std::max((size_t)K, m);
+        m = std::min(m, n_all);
+        std::vector<size_t> idx(n_all);
+        std::iota(idx.begin(), idx.end(), (size_t)0);
+        std::shuffle(idx.begin(), idx.end(), rng);
+        d.sample.resize(m);
+        for (size_t i = 0; i < m; ++i) d.sample[i] = (uint32_t)idx[i];
+        n = m;
+    }
+    std::uniform_int_distribution<size_t> distrib(0, n - 1);  // :289-290
+    d.first = (uint32_t)distrib(rng);
+    d.canon.resize(K > 1 ? K - 1 : 0);
+    std::uniform_real_distribution<double> unit(0.0, 1.0);    // p = u * S + 0.0 (:303-304)
+    for (auto& u : d.canon) u = unit(rng);
+    *n_used = n;
+    return d;
+}
+
+struct Blocks {        // device-resident block set
+    size_t n = 0;
+    int ch = 0;
+    const uint4* planes = nullptr;  // null for HDR
+    size_t stride = 0;
+    const float* feat = nullptr;
+};
+
+int fixed_shift(size_t n_total, float max_abs) {
+    // sum of n_total values of magnitude <= max_abs must stay below 2^62
+    int bits_n = 1;
+    while (((size_t)1 << bits_n) < n_total && bits_n < 40) ++bits_n;
+    int e = 0;
+    if (max_abs > 0.f && std::isfinite(max_abs)) {
+        (void)std::frexp(max_abs, &e);  // max_abs < 2^e
+    } else if (!std::isfinite(max_abs)) {
+        e = 128;
+    }
+    int shift = 62 - bits_n - std::max(e, 0);
+    return std::max(-60, std::min(shift, 40));
+}
+
+// ---- K2: seeding -----------------------------------------------------------------------------------
+int run_seeding(yupvq_ctx* ctx, const Blocks& b, uint32_t K, const Draws& dr, bool hdr, uint32_t* out_rounds) {
+    const size_t n = b.n;
+    const int grid = (int)seed_grid_for(n);
+    CK(ctx->min_dist.ensure(n * sizeof(float)));
+    CK(ctx->partial.ensure((size_t)grid * 8));
+    CK(ctx->seed_idx.ensure((size_t)K * 4));
+    CK(ctx->canon.ensure(std::max<size_t>(1, dr.canon.size()) * 8));
+    if (!dr.canon.empty())
+        CK(cudaMemcpyAsync(ctx->canon.p, dr.canon.data(), dr.canon.size() * 8, cudaMemcpyHostToDevice, ctx->stream));
+    SeedState st;
+    st.min_dist = ctx->min_dist.as<float>();
+    st.partial = ctx->partial.as<unsigned long long>();
+    st.counter = ctx->small.as<unsigned int>() + F_COUNTER;
+    st.seed_idx = ctx->seed_idx.as<uint32_t>();
+    st.canon = ctx->canon.as<double>();
+    st.status = ctx->small.as<uint32_t>() + F_SEED_STATUS;
+    st.grid = grid;
+    LAUNCH(launch_seed_init(st, n, dr.first, ctx->stream));
+    for (uint32_t i = 1; i < K; ++i) {
+        if (hdr) LAUNCH(launch_seed_round_hdr(st, b.feat, n, i, K, ctx->stream));
+        else LAUNCH(launch_seed_round_ldr(st, b.planes, b.stride, n, b.ch, i, K, ctx->stream));
+    }
+    if (out_rounds) {
+        CK(cudaMemcpyAsync(ctx->h_small, st.status, 8, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+        *out_rounds = ctx->h_small[1];
+    }
+    return 0;
+}
+
+// Empty-cluster reseed when blocks are sharded (rare path, host-driven): for every empty cluster in
+// ascending order each rank proposes its local (max error, first index); the global winner is the
+// largest error with the lowest global index -- exactly the single-GPU std::max_element result --
+// and its owner broadcasts the feature row and zeroes that error.
+int reseed_sharded(yupvq_ctx* ctx, const Blocks& b, size_t first_block, uint32_t K, float* cent, float* errors,
+                   const long long* acc, uint32_t* flags) {
+    CK(cudaMemcpyAsync(ctx->h_small, flags + F_EMPTY, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (ctx->h_small[0] == 0) return 0;
+    std::vector<long long> counts(K);
+    CK(cudaMemcpyAsync(counts.data(), acc + (size_t)K * 64, (size_t)K * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    const int R = ctx->n_ranks;
+    CK(ctx->s_rows.ensure((size_t)(R + 1) * 16 + 256));
+    uint32_t* prop = ctx->s_rows.as<uint32_t>();          // [R+1][4]: slot R is this rank's proposal
+    float* row = reinterpret_cast<float*>(prop + (size_t)(R + 1) * 4);
+    std::vector<uint32_t> h((size_t)R * 4);
+    for (uint32_t c = 0; c < K; ++c) {
+        if (counts[c] != 0) continue;
+        uint32_t mine[4] = {0, 0xffffffffu, 0, 0};        // value bits, global index, valid, pad
+        if (b.n > 0) {
+            LAUNCH(launch_argmax_error(errors, b.n, prop + (size_t)R * 4, ctx->stream));
+            CK(cudaMemcpyAsync(mine, prop + (size_t)R * 4, 8, cudaMemcpyDeviceToHost, ctx->stream));
+            CK(cudaStreamSynchronize(ctx->stream));
+            mine[1] += (uint32_t)first_block;
+            mine[2] = 1;
+        }
+        CK(cudaMemcpyAsync(prop + (size_t)R * 4, mine, 16, cudaMemcpyHostToDevice, ctx->stream));
+        if (ctx->nccl.all_gather_bytes(ctx->comm, prop + (size_t)R * 4, prop, 16, ctx->stream)) return ctx->fail("ncclAllGather failed");
+        CK(cudaMemcpyAsync(h.data(), prop, (size_t)R * 16, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+        int owner = -1;
+        float bv = 0.f;
+        uint32_t bi = 0;
+        for (int r = 0; r < R; ++r) {
+            if (!h[(size_t)r * 4 + 2]) continue;
+            float v;
+            std::memcpy(&v, &h[(size_t)r * 4], 4);
+            const uint32_t gi = h[(size_t)r * 4 + 1];
+            if (owner < 0 || v > bv || (v == bv && gi < bi)) {
+                owner = r;
+                bv = v;
+                bi = gi;
+            }
+        }
+        if (owner < 0) return ctx->fail("reseed: no rank holds any block");
+        if (owner == ctx->rank) {
+            const size_t local = (size_t)bi - first_block;
+            CK(cudaMemcpyAsync(row, b.feat + local * 64, 256, cudaMemcpyDeviceToDevice, ctx->stream));
+            CK(cudaMemsetAsync(errors + local, 0, 4, ctx->stream));  // errors[worst] = 0.0f
+        }
+        if (ctx->nccl.broadcast_bytes(ctx->comm, row, 256, owner, ctx->stream)) return ctx->fail("ncclBroadcast failed");
+        CK(cudaMemcpyAsync(cent + (size_t)c * 64, row, 256, cudaMemcpyDeviceToDevice, ctx->stream));
+        ctx->reseeds_sharded++;
+    }
+    return 0;
+}
+
+// ---- K3..K5: Lloyd iterations ----------------------------------------------------------------------
+// break_after: LDR breaks on (!changed && iter > 0), HDR on (!changed && iter > 1)
+// (src/vq_encoder.cpp:341 vs :572).  cent (device, K x 64) holds the seeds on entry.
+int run_lloyd(yupvq_ctx* ctx, const Blocks& b, size_t n_total, size_t first_block, uint32_t K, uint32_t max_iter,
+              uint32_t break_after, int assign_mode, float* cent, yupvq_stats* stats) {
+    (void)assign_mode;
+    const size_t n = b.n;
+    CK(ctx->assign.ensure(std::max<size_t>(1, n) * 4));
+    CK(ctx->errors.ensure(std::max<size_t>(1, n) * 4));
+    const size_t acc_words = (size_t)K * 65 + 1;  // [K*64 sums | K counts | changed]
+    CK(ctx->acc.ensure(acc_words * 8));
+    uint32_t* flags = ctx->small.as<uint32_t>();
+    uint32_t* assign = ctx->assign.as<uint32_t>();
+    float* errors = ctx->errors.as<float>();
+    long long* acc = ctx->acc.as<long long>();
+    CK(cudaMemsetAsync(assign, 0, n * 4, ctx->stream));  // assignments(numBlocks, 0), :316
+    CK(cudaMemsetAsync(flags + F_RESEEDS, 0, 4, ctx->stream));
+    ctx->reseeds_sharded = 0;
+
+    // fixed-point scale from the data range (deterministic function of the data)
+    CK(cudaMemsetAsync(flags + F_MAXABS, 0, 4, ctx->stream));
+    LAUNCH(launch_max_abs(b.feat, n * 64, flags + F_MAXABS, ctx->stream));
+    CK(cudaMemcpyAsync(ctx->h_small, flags + F_MAXABS, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    float max_abs;
+    std::memcpy(&max_abs, ctx->h_small, 4);
+    if (ctx->comm) {
+        // the scale must be identical on every rank: use the global maximum
+        CK(cudaMemcpyAsync(flags + F_SPARE, ctx->h_small, 4, cudaMemcpyHostToDevice, ctx->stream));
+        if (ctx->nccl.all_reduce_max_u32(ctx->comm, flags + F_SPARE, 1, ctx->stream)) return ctx->fail("ncclAllReduce(max) failed");
+        CK(cudaMemcpyAsync(ctx->h_small, flags + F_SPARE, 4, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+        std::memcpy(&max_abs, ctx->h_small, 4);
+    }
+    const int shift = fixed_shift(n_total, max_abs);
+
+    uint32_t passes = 0;
+    for (uint32_t iter = 0; iter < max_iter; ++iter) {
+        CK(cudaMemsetAsync(flags, 0, 8, ctx->stream));  // changed, empty
+        LAUNCH(launch_assign_exact(b.feat, n, cent, K, assign, errors, flags, ctx->stream));
+        ++passes;
+        // The reference checks hasChanged between assign and update; the update is launched
+        // speculatively so one sync (and, sharded, one all-reduce) per pass carries both.
+        CK(cudaMemsetAsync(acc, 0, acc_words * 8, ctx->stream));
+        LAUNCH(launch_accumulate(b.feat, n, assign, K, shift, acc, flags, ctx->stream));
+        if (ctx->comm) {
+            if (ctx->nccl.all_reduce_sum_i64(ctx->comm, acc, acc_words, ctx->stream)) return ctx->fail("ncclAllReduce(sum) failed");
+        }
+        CK(cudaMemcpyAsync(ctx->h_small, acc + (size_t)K * 65, 8, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+        long long changed;
+        std::memcpy(&changed, ctx->h_small, 8);
+        if (!changed && iter > break_after) break;
+        LAUNCH(launch_finalize_centroids(acc, K, shift, cent, flags, ctx->stream));
+        if (!ctx->comm) {
+            LAUNCH(launch_reseed_empty(b.feat, n, errors, acc, K, cent, flags, ctx->stream));
+        } else if (reseed_sharded(ctx, b, first_block, K, cent, errors, acc, flags)) {
+            return 1;
+        }
+    }
+    CK(cudaMemcpyAsync(ctx->h_small, flags + F_RESEEDS, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (stats) {
+        stats->lloyd_passes = passes;
+        stats->reseeds = ctx->h_small[0] + ctx->reseeds_sharded;
+    }
+    return 0;
+}
+
+void init_stats(yupvq_stats* s) {
+    if (s) std::memset(s, 0, sizeof(*s));
+}
+
+// Shared tail of the LDR paths: seeding + Lloyd + centroid -> pixel conversion on a device block set.
+// `all` is the full block set; when sampling is active the subset is gathered first.
+// Leaves K x 16*ch uint8 pixel centroids in ctx->cent_px.
+int build_codebook_device(yupvq_ctx* ctx, const Blocks& all, size_t n_total, const yupvq_config* cfg, bool hdr,
+                          yupvq_stats* stats, Timer& tm, int* t_seed0, int* t_seed1, int* t_lloyd1, int* t_fin1) {
+    const uint32_t K = cfg->codebook_size;
+    size_t n_used = 0;
+    Draws dr = make_draws(all.n, K, cfg->sample_ratio, cfg->seed, &n_used);
+    Blocks b = all;
+    if (!dr.sample.empty()) {
+        CK(ctx->s_rows.ensure(n_used * 4));
+        CK(cudaMemcpyAsync(ctx->s_rows.p, dr.sample.data(), n_used * 4, cudaMemcpyHostToDevice, ctx->stream));
+        CK(ctx->s_feat.ensure(n_used * 256));
+        if (!hdr) CK(ctx->s_planes.ensure(n_used * 16 * all.ch));
+        LAUNCH(launch_gather_blocks(all.planes, all.stride, all.feat, ctx->s_rows.as<uint32_t>(), n_used, all.ch,
+                                    hdr ? nullptr : ctx->s_planes.as<uint4>(), n_used, ctx->s_feat.as<float>(),
+                                    ctx->stream));
+        b.n = n_used;
+        b.planes = hdr ? nullptr : ctx->s_planes.as<uint4>();
+        b.stride = n_used;
+        b.feat = ctx->s_feat.as<float>();
+        n_total = n_used;
+    }
+    if (stats) {
+        stats->n_blocks = (uint32_t)b.n;
+        stats->codebook_size = K;
+    }
+    *t_seed0 = tm.mark();
+    uint32_t rounds = 0;
+    if (run_seeding(ctx, b, K, dr, hdr, stats ? &rounds : nullptr)) return 1;
+    if (stats) stats->seed_rounds = rounds;
+    // seeds -> Oklab centroids: PixelBlockToOklabBlock(pixelCentroids[i]) (:324-326) equals the
+    // feature row of the chosen block (same pixels, same conversion).
+    CK(ctx->cent.ensure((size_t)K * 256));
+    LAUNCH(launch_gather_rows_f32(b.feat, ctx->seed_idx.as<uint32_t>(), K, 64, ctx->cent.as<float>(), ctx->stream));
+    *t_seed1 = tm.mark();
+    const int metric = hdr ? YUPVQ_METRIC_OKLAB : cfg->metric;
+    if (metric != YUPVQ_METRIC_OKLAB) return ctx->fail("SAD metric Lloyd is not built yet");
+    if (run_lloyd(ctx, b, n_total, 0, K, cfg->max_iterations, hdr ? 1u : 0u, cfg->assign_mode, ctx->cent.as<float>(), stats))
+        return 1;
+    *t_lloyd1 = tm.mark();
+    if (hdr) {
+        CK(ctx->cent_px.ensure((size_t)K * 16 * all.ch * 4));
+        LAUNCH(launch_oklab_to_floats(ctx->cent.as<float>(), K, all.ch, ctx->cent_px.as<float>(), ctx->stream));
+    } else {
+        CK(ctx->cent_px.ensure((size_t)K * 16 * all.ch));
+        LAUNCH(launch_oklab_to_pixels(ctx->cent.as<float>(), K, all.ch, ctx->cent_px.as<uint8_t>(), ctx->stream));
+    }
+    *t_fin1 = tm.mark();
+    return 0;
+}
+
+// QuantizeBlocks on device data: centroids (pixel/float, device) -> Oklab -> one assignment pass.
+int quantize_device(yupvq_ctx* ctx, const Blocks& all, const void* cent_px_dev, uint32_t K, bool hdr, int assign_mode) {
+    (void)assign_mode;
+    CK(ctx->cent_feat.ensure((size_t)K * 256));
+    if (hdr) LAUNCH(launch_floats_to_features(reinterpret_cast<const float*>(cent_px_dev), K, all.ch, ctx->cent_feat.as<float>(), ctx->stream));
+    else LAUNCH(launch_pixels_to_features(reinterpret_cast<const uint8_t*>(cent_px_dev), K, all.ch, nullptr, 0, ctx->cent_feat.as<float>(), ctx->stream));
+    CK(ctx->out_idx.ensure(std::max<size_t>(1, all.n) * 4));
+    LAUNCH(launch_assign_exact(all.feat, all.n, ctx->cent_feat.as<float>(), K, ctx->out_idx.as<uint32_t>(), nullptr, nullptr,
+                               ctx->stream));
+    return 0;
+}
+
+int check_cfg(yupvq_ctx* ctx, const yupvq_config* cfg, size_t n, int ch) {
+    if (!cfg) return ctx->fail("config is null");
+    if (ch < 1 || ch > 4) return ctx->fail("channels must be 1..4 (got %d)", ch);
+    if (n == 0) return ctx->fail("no blocks (the reference's LDR BuildCodebook has no N == 0 guard; rejected here)");
+    if (n > 0xffffffffull) return ctx->fail("too many blocks");
+    if (cfg->codebook_size == 0 || cfg->codebook_size > 65536) return ctx->fail("codebook_size out of range");
+    return 0;
+}
+
+struct Scope {  // selects the context's device for the duration of a call
+    int prev = 0;
+    explicit Scope(int dev) {
+        cudaGetDevice(&prev);
+        cudaSetDevice(dev);
+    }
+    ~Scope() { cudaSetDevice(prev); }
+};
+
+}  // namespace
+
+// =====================================================================================================
+// C ABI
+// =====================================================================================================
+extern "C" {
+
+const char* yupvq_version(void) { return "yupvq 0.1 (sm_100a)"; }
+
+uint32_t yupvq_codebook_size(float quality) {
+    // CompressionConfig::SetQuality, src/vq_encoder.cpp:12-18; powers are the struct defaults 4..10
+    // because Compress copies the params' powers only after calling SetQuality.
+    const float q = std::min(std::max(quality, 0.0f), 1.0f);
+    const uint32_t power = 4u + (uint32_t)roundf(q * (float)(10 - 4));
+    return 1u << power;
+}
+
+void yupvq_config_init(yupvq_config* cfg, float quality, uint32_t max_iterations, int metric, float sample_ratio,
+                       uint64_t seed) {
+    std::memset(cfg, 0, sizeof(*cfg));
+    cfg->codebook_size = yupvq_codebook_size(quality);
+    cfg->max_iterations = max_iterations;
+    cfg->metric = metric;
+    cfg->sample_ratio = sample_ratio;
+    cfg->seed = seed;
+    cfg->assign_mode = YUPVQ_ASSIGN_AUTO;
+}
+
+int yupvq_create(int device, yupvq_ctx** out) {
+    if (!out) return 1;
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) {
+        g_create_error = std::string("no CUDA device: ") + cudaGetErrorString(e) + " (yupvq has no CPU fallback)";
+        cudaGetLastError();
+        return 1;
+    }
+    if (device < 0 || device >= count) {
+        g_create_error = "device index out of range";
+        return 1;
+    }
+    cudaDeviceProp prop;
+    cudaGetDeviceProperties(&prop, device);
+    if (prop.major != 10) {
+        g_create_error = std::string("device ") + prop.name + " is not sm_100a (kernels are built for B200 only)";
+        return 1;
+    }
+    Scope scope(device);
+    yupvq_ctx* ctx = new yupvq_ctx();
+    ctx->device = device;
+    bool ok = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) == cudaSuccess;
+    for (auto& ev : ctx->ev) ok = ok && cudaEventCreate(&ev) == cudaSuccess;
+    for (auto& ev : ctx->ev_user) ok = ok && cudaEventCreate(&ev) == cudaSuccess;
+    ok = ok && cudaMallocHost(reinterpret_cast<void**>(&ctx->h_small), 256) == cudaSuccess;
+    ok = ok && ctx->small.ensure(F_WORDS * 4) == cudaSuccess;
+    ok = ok && cudaMemset(ctx->small.p, 0, F_WORDS * 4) == cudaSuccess;
+    ok = ok && colour_tables_init() == cudaSuccess;
+    if (!ok) {
+        g_create_error = std::string("context creation failed: ") + cudaGetErrorString(cudaGetLastError());
+        yupvq_destroy(ctx);
+        return 1;
+    }
+    *out = ctx;
+    return 0;
+}
+
+void yupvq_destroy(yupvq_ctx* ctx) {
+    if (!ctx) return;
+    Scope scope(ctx->device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    if (ctx->comm) ctx->nccl.destroy(ctx->comm);
+    DevBuf* bufs[] = {&ctx->in_bytes, &ctx->planes, &ctx->feat, &ctx->s_planes, &ctx->s_feat, &ctx->s_rows,
+                      &ctx->min_dist, &ctx->partial, &ctx->seed_idx, &ctx->canon, &ctx->small, &ctx->assign,
+                      &ctx->errors, &ctx->cent, &ctx->acc, &ctx->cent_px, &ctx->cent_feat, &ctx->out_idx};
+    for (DevBuf* b : bufs) b->release();
+    if (ctx->h_small) cudaFreeHost(ctx->h_small);
+    for (auto& ev : ctx->ev)
+        if (ev) cudaEventDestroy(ev);
+    for (auto& ev : ctx->ev_user)
+        if (ev) cudaEventDestroy(ev);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+int yupvq_timer_start(yupvq_ctx* ctx) {
+    if (!ctx) return 1;
+    Scope scope(ctx->device);
+    CK(cudaEventRecord(ctx->ev_user[0], ctx->stream));
+    return 0;
+}
+
+int yupvq_timer_stop(yupvq_ctx* ctx, float* out_ms) {
+    if (!ctx) return 1;
+    Scope scope(ctx->device);
+    CK(cudaEventRecord(ctx->ev_user[1], ctx->stream));
+    CK(cudaEventSynchronize(ctx->ev_user[1]));
+    float ms = 0.f;
+    CK(cudaEventElapsedTime(&ms, ctx->ev_user[0], ctx->ev_user[1]));
+    if (out_ms) *out_ms = ms;
+    return 0;
+}
+
+const char* yupvq_last_error(const yupvq_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+// ---- whole path: LDR ---------------------------------------------------------------------------------
+int yupvq_encode_bcn(yupvq_ctx* ctx, const uint8_t* bc_blocks, size_t n_blocks, int bc_format, int channels,
+                     const yupvq_config* cfg, uint8_t* out_pixel_centroids, uint32_t* out_indices, yupvq_stats* stats) {
+    if (!ctx) return 1;
+    Scope scope(ctx->device);
+    init_stats(stats);
+    ctx->launches = 0;
+    if (check_cfg(ctx, cfg, n_blocks, channels)) return 1;
+    if (!bc_supported(bc_format)) return ctx->fail("BC format %d is not supported on the LDR VQ path", bc_format);
+    Timer tm(ctx);
+    const int t0 = tm.mark();
+    const void* bc_dev = nullptr;
+    if (to_device(ctx, bc_blocks, n_blocks * bc_block_bytes(bc_format), ctx->in_bytes, &bc_dev)) return 1;
+    const int t1 = tm.mark();
+    CK(ctx->planes.ensure(n_blocks * 16 * channels));
+    CK(ctx->feat.ensure(n_blocks * 256));
+    LAUNCH(launch_decode_bcn(reinterpret_cast<const uint8_t*>(bc_dev), n_blocks, bc_format, channels,
+                             ctx->planes.as<uint4>(), n_blocks, ctx->feat.as<float>(), nullptr, ctx->stream));
+    const int t2 = tm.mark();
+    Blocks all;
+    all.n = n_blocks;
+    all.ch = channels;
+    all.planes = ctx->planes.as<uint4>();
+    all.stride = n_blocks;
+    all.feat = ctx->feat.as<float>();
+    int ts0, ts1, tl1, tf1;
+    if (build_codebook_device(ctx, all, n_blocks, cfg, false, stats, tm, &ts0, &ts1, &tl1, &tf1)) return 1;
+    if (quantize_device(ctx, all, ctx->cent_px.p, cfg->codebook_size, false, cfg->assign_mode)) return 1;
+    const int t3 = tm.mark();
+    if (from_device(ctx, out_pixel_centroids, ctx->cent_px.p, (size_t)cfg->codebook_size * 16 * channels)) return 1;
+    if (from_device(ctx, out_indices, ctx->out_idx.p, n_blocks * 4)) return 1;
+    const int t4 = tm.mark();
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (stats) {
+        stats->ms_h2d = tm.ms(t0, t1);
+        stats->ms_decode = tm.ms(t1, t2);
+        stats->ms_seed = tm.ms(ts0, ts1);
+        stats->ms_lloyd = tm.ms(ts1, tl1);
+        stats->ms_finalize = tm.ms(tl1, tf1);
+        stats->ms_quantize = tm.ms(tf1, t3);
+        stats->ms_d2h = tm.ms(t3, t4);
+        stats->ms_total = tm.ms(t0, t4);
+        stats->gpu_launches = ctx->launches;
+    }
+    return 0;
+}
+
+// ---- whole path: HDR ---------------------------------------------------------------------------------
+int yupvq_encode_hdr(yupvq_ctx* ctx, const float* image, uint32_t width, uint32_t height, int channels,
+                     const yupvq_config* cfg, float* out_float_centroids, uint32_t* out_indices, yupvq_stats* stats) {
+    if (!ctx) return 1;
+    Scope scope(ctx->device);
+    init_stats(stats);
+    ctx->launches = 0;
+    const size_t n_blocks = (size_t)((width + 3) / 4) * ((height + 3) / 4);
+    if (check_cfg(ctx, cfg, n_blocks, channels)) return 1;
+    Timer tm(ctx);
+    const int t0 = tm.mark();
+    const void* img_dev = nullptr;
+    if (to_device(ctx, image, (size_t)width * height * channels * 4, ctx->in_bytes, &img_dev)) return 1;
+    const int t1 = tm.mark();
+    CK(ctx->feat.ensure(n_blocks * 256));
+    LAUNCH(launch_image_to_features(reinterpret_cast<const float*>(img_dev), width, height, channels,
+                                    ctx->feat.as<float>(), nullptr, ctx->stream));
+    const int t2 = tm.mark();
+    Blocks all;
+    all.n = n_blocks;
+    all.ch = channels;
+    all.feat = ctx->feat.as<float>();
+    int ts0, ts1, tl1, tf1;
+    if (build_codebook_device(ctx, all, n_blocks, cfg, true, stats, tm, &ts0, &ts1, &tl1, &tf1)) return 1;
+    if (quantize_device(ctx, all, ctx->cent_px.p, cfg->codebook_size, true, cfg->assign_mode)) return 1;
+    const int t3 = tm.mark();
+    if (from_device(ctx, out_float_centroids, ctx->cent_px.p, (size_t)cfg->codebook_size * 16 * channels * 4)) return 1;
+    if (from_device(ctx, out_indices, ctx->out_idx.p, n_blocks * 4)) return 1;
+    const int t4 = tm.mark();
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (stats) {
+        stats->ms_h2d = tm.ms(t0, t1);
+        stats->ms_decode = tm.ms(t1, t2);
+        stats->ms_seed = tm.ms(ts0, ts1);
+        stats->ms_lloyd = tm.ms(ts1, tl1);
+        stats->ms_finalize = tm.ms(tl1, tf1);
+        stats->ms_quantize = tm.ms(tf1, t3);
+        stats->ms_d2h = tm.ms(t3, t4);
+        stats->ms_total = tm.ms(t0, t4);
+        stats->gpu_launches = ctx->launches;
+    }
+    return 0;
+}
+
+int yupvq_encode_bcn_batch(yupvq_ctx* ctx, const uint8_t* const* bc_blocks, size_t n_textures, size_t n_blocks,
+                           int bc_format, int channels, const yupvq_config* cfg, uint8_t* const* out_pixel_centroids,
+                           uint32_t* const* out_indices, yupvq_stats* stats) {
+    if (!ctx) return 1;
+    if (!cfg) return ctx->fail("config is null");
+    yupvq_stats total;
+    std::memset(&total, 0, sizeof(total));
+    for (size_t t = 0; t < n_textures; ++t) {
+        yupvq_config c = *cfg;
+        if (c.seed != 0) c.seed = cfg->seed + t;
+        yupvq_stats s;
+        if (yupvq_encode_bcn(ctx, bc_blocks[t], n_blocks, bc_format, channels, &c, out_pixel_centroids[t],
+                             out_indices[t], &s))
+            return 1;
+        total.n_blocks += s.n_blocks;
+        total.codebook_size = s.codebook_size;
+        total.lloyd_passes += s.lloyd_passes;
+        total.seed_rounds += s.seed_rounds;
+        total.reseeds += s.reseeds;
+        total.rerank_blocks += s.rerank_blocks;
+        total.ms_h2d += s.ms_h2d; total.ms_decode += s.ms_decode; total.ms_seed += s.ms_seed;
+        total.ms_lloyd += s.ms_lloyd; total.ms_finalize += s.ms_finalize; total.ms_quantize += s.ms_quantize;
+        total.ms_d2h += s.ms_d2h; total.ms_total += s.ms_total;
+        total.gpu_launches += s.gpu_launches;
+    }
+    if (stats) *stats = total;
+    return 0;
+}
+
+// ---- the four VQEncoder calls -----------------------------------------------------------------------
+int yupvq_build_codebook(yupvq_ctx* ctx, const uint8_t* pixel_blocks, size_t n_blocks, int channels,
+                         const yupvq_config* cfg, uint8_t* out_pixel_centroids, yupvq_stats* stats) {
+    if (!ctx) return 1;
+    Scope scope(ctx->device);
+    init_stats(stats);
+    ctx->launches = 0;
+    if (check_cfg(ctx, cfg, n_blocks, channels)) return 1;
+    Timer tm(ctx);
+    const int t0 = tm.mark();
+    const void* px_dev = nullptr;
+    if (to_device(ctx, pixel_blocks, n_blocks * 16 * channels, ctx->in_bytes, &px_dev)) return 1;
+    CK(ctx->planes.ensure(n_blocks * 16 * channels));
+    CK(ctx->feat.ensure(n_blocks * 256));
+    LAUNCH(launch_pixels_to_features(reinterpret_cast<const uint8_t*>(px_dev), n_blocks, channels,
+                                     ctx->planes.as<uint4>(), n_blocks, ctx->feat.as<float>(), ctx->stream));
+    Blocks all;
+    all.n = n_blocks;
+    all.ch = channels;
+    all.planes = ctx->planes.as<uint4>();
+    all.stride = n_blocks;
+    all.feat = ctx->feat.as<float>();
+    int ts0, ts1, tl1, tf1;
+    if (build_codebook_device(ctx, all, n_blocks, cfg, false, stats, tm, &ts0, &ts1, &tl1, &tf1)) return 1;
+    if (from_device(ctx, out_pixel_centroids, ctx->cent_px.p, (size_t)cfg->codebook_size * 16 * channels)) return 1;
+    const int t4 = tm.mark();
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (stats) {
+        stats->ms_decode = tm.ms(t0, ts0);
+        stats->ms_seed = tm.ms(ts0, ts1);
+        stats->ms_lloyd = tm.ms(ts1, tl1);
+        stats->ms_finalize = tm.ms(tl1, tf1);
+        stats->ms_total = tm.ms(t0, t4);
+        stats->gpu_launches = ctx->launches;
+    }
+    return 0;
+}
+
+int yupvq_quantize_blocks(yupvq_ctx* ctx, const uint8_t* pixel_blocks, size_t n_blocks, int channels,
+                          const uint8_t* pixel_centroids, uint32_t codebook_size, int metric, int assign_mode,
+                          uint32_t* out_indices, yupvq_stats* stats) {
+    if (!ctx) return 1;
+    Scope scope(ctx->device);
+    init_stats(stats);
+    ctx->launches = 0;
+    if (n_blocks == 0) return 0;  // reference returns {} (:449)
+    if (channels < 1 || channels > 4) return ctx->fail("channels must be 1..4");
+    if (metric != YUPVQ_METRIC_OKLAB) return ctx->fail("SAD metric quantise is not built yet");
+    Timer tm(ctx);
+    const int t0 = tm.mark();
+    const void* px_dev = nullptr;
+    if (to_device(ctx, pixel_blocks, n_blocks * 16 * channels, ctx->in_bytes, &px_dev)) return 1;
+    CK(ctx->feat.ensure(n_blocks * 256));
+    LAUNCH(launch_pixels_to_features(reinterpret_cast<const uint8_t*>(px_dev), n_blocks, channels, nullptr, 0,
+                                     ctx->feat.as<float>(), ctx->stream));
+    const void* c_dev = nullptr;
+    if (to_device(ctx, pixel_centroids, (size_t)codebook_size * 16 * channels, ctx->cent_px, &c_dev)) return 1;
+    Blocks all;
+    all.n = n_blocks;
+    all.ch = channels;
+    all.feat = ctx->feat.as<float>();
+    if (quantize_device(ctx, all, c_dev, codebook_size, false, assign_mode)) return 1;
+    if (from_device(ctx, out_indices, ctx->out_idx.p, n_blocks * 4)) return 1;
+    const int t1 = tm.mark();
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (stats) {
+        stats->n_blocks = (uint32_t)n_blocks;
+        stats->codebook_size = codebook_size;
+        stats->ms_quantize = stats->ms_total = tm.ms(t0, t1);
+        stats->gpu_launches = ctx->launches;
+    }
+    return 0;
+}
+
+int yupvq_build_codebook_hdr(yupvq_ctx* ctx, const float* float_blocks, size_t n_blocks, int channels,
+                             const yupvq_config* cfg, float* out_float_centroids, yupvq_stats* stats) {
+    if (!ctx) return 1;
+    Scope scope(ctx->device);
+    init_stats(stats);
+    ctx->launches = 0;
+    if (n_blocks == 0) return 0;  // reference returns {} (:517)
+    if (check_cfg(ctx, cfg, n_blocks, channels)) return 1;
+    Timer tm(ctx);
+    const int t0 = tm.mark();
+    const void* px_dev = nullptr;
+    if (to_device(ctx, float_blocks, n_blocks * 16 * channels * 4, ctx->in_bytes, &px_dev)) return 1;
+    CK(ctx->feat.ensure(n_blocks * 256));
+    LAUNCH(launch_floats_to_features(reinterpret_cast<const float*>(px_dev), n_blocks, channels, ctx->feat.as<float>(),
+                                     ctx->stream));
+    Blocks all;
+    all.n = n_blocks;
+    all.ch = channels;
+    all.feat = ctx->feat.as<float>();
+    int ts0, ts1, tl1, tf1;
+    if (build_codebook_device(ctx, all, n_blocks, cfg, true, stats, tm, &ts0, &ts1, &tl1, &tf1)) return 1;
+    if (from_device(ctx, out_float_centroids, ctx->cent_px.p, (size_t)cfg->codebook_size * 16 * channels * 4)) return 1;
+    const int t4 = tm.mark();
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (stats) {
+        stats->ms_decode = tm.ms(t0, ts0);
+        stats->ms_seed = tm.ms(ts0, ts1);
+        stats->ms_lloyd = tm.ms(ts1, tl1);
+        stats->ms_finalize = tm.ms(tl1, tf1);
+        stats->ms_total = tm.ms(t0, t4);
+        stats->gpu_launches = ctx->launches;
+    }
+    return 0;
+}
+
+int yupvq_quantize_blocks_hdr(yupvq_ctx* ctx, const float* float_blocks, size_t n_blocks, int channels,
+                              const float* float_centroids, uint32_t codebook_size, int assign_mode,
+                              uint32_t* out_indices, yupvq_stats* stats) {
+    if (!ctx) return 1;
+    Scope scope(ctx->device);
+    init_stats(stats);
+    ctx->launches = 0;
+    if (n_blocks == 0) return 0;  // :631
+    if (channels < 1 || channels > 4) return ctx->fail("channels must be 1..4");
+    Timer tm(ctx);
+    const int t0 = tm.mark();
+    const void* px_dev = nullptr;
+    if (to_device(ctx, float_blocks, n_blocks * 16 * channels * 4, ctx->in_bytes, &px_dev)) return 1;
+    CK(ctx->feat.ensure(n_blocks * 256));
+    LAUNCH(launch_floats_to_features(reinterpret_cast<const float*>(px_dev), n_blocks, channels, ctx->feat.as<float>(),
+                                     ctx->stream));
+    const void* c_dev = nullptr;
+    if (to_device(ctx, float_centroids, (size_t)codebook_size * 16 * channels * 4, ctx->cent_px, &c_dev)) return 1;
+    Blocks all;
+    all.n = n_blocks;
+    all.ch = channels;
+    all.feat = ctx->feat.as<float>();
+    if (quantize_device(ctx, all, c_dev, codebook_size, true, assign_mode)) return 1;
+    if (from_device(ctx, out_indices, ctx->out_idx.p, n_blocks * 4)) return 1;
+    const int t1 = tm.mark();
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (stats) {
+        stats->n_blocks = (uint32_t)n_blocks;
+        stats->codebook_size = codebook_size;
+        stats->ms_quantize = stats->ms_total = tm.ms(t0, t1);
+        stats->gpu_launches = ctx->launches;
+    }
+    return 0;
+}
+
+// ---- kernel-level entry points ------------------------------------------------------------------------
+int yupvq_decode_bcn(yupvq_ctx* ctx, const uint8_t* bc_blocks, size_t n_blocks, int bc_format, int channels,
+                     uint8_t* out_pixel_blocks) {
+    if (!ctx) return 1;
+    Scope scope(ctx->device);
+    if (!bc_supported(bc_format)) return ctx->fail("BC format %d is not supported", bc_format);
+    if (channels < 1 || channels > 4) return ctx->fail("channels must be 1..4");
+    if (n_blocks == 0) return 0;
+    const void* bc_dev = nullptr;
+    if (to_device(ctx, bc_blocks, n_blocks * bc_block_bytes(bc_format), ctx->in_bytes, &bc_dev)) return 1;
+    CK(ctx->planes.ensure(n_blocks * 16 * channels));
+    LAUNCH(launch_decode_bcn(reinterpret_cast<const uint8_t*>(bc_dev), n_blocks, bc_format, channels, nullptr, 0,
+                             nullptr, ctx->planes.as<uint8_t>(), ctx->stream));
+    if (from_device(ctx, out_pixel_blocks, ctx->planes.p, n_blocks * 16 * channels)) return 1;
+    CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+int yupvq_pixels_to_oklab(yupvq_ctx* ctx, const uint8_t* pixel_blocks, size_t n_blocks, int channels, float* out_oklab) {
+    if (!ctx) return 1;
+    Scope scope(ctx->device);
+    if (channels < 1 || channels > 4) return ctx->fail("channels must be 1..4");
+    if (n_blocks == 0) return 0;
+    const void* px_dev = nullptr;
+    if (to_device(ctx, pixel_blocks, n_blocks * 16 * channels, ctx->in_bytes, &px_dev)) return 1;
+    CK(ctx->feat.ensure(n_blocks * 256));
+    LAUNCH(launch_pixels_to_features(reinterpret_cast<const uint8_t*>(px_dev), n_blocks, channels, nullptr, 0,
+                                     ctx->feat.as<float>(), ctx->stream));
+    if (from_device(ctx, out_oklab, ctx->feat.p, n_blocks * 256)) return 1;
+    CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+int yupvq_oklab_to_pixels(yupvq_ctx* ctx, const float* oklab, size_t n_blocks, int channels, uint8_t* out_pixel_blocks) {
+    if (!ctx) return 1;
+    Scope scope(ctx->device);
+    if (channels < 1 || channels > 4) return ctx->fail("channels must be 1..4");
+    if (n_blocks == 0) return 0;
+    const void* ok_dev = nullptr;
+    if (to_device(ctx, oklab, n_blocks * 256, ctx->feat, &ok_dev)) return 1;
+    CK(ctx->cent_px.ensure(n_blocks * 16 * channels));
+    LAUNCH(launch_oklab_to_pixels(reinterpret_cast<const float*>(ok_dev), n_blocks, channels, ctx->cent_px.as<uint8_t>(), ctx->stream));
+    if (from_device(ctx, out_pixel_blocks, ctx->cent_px.p, n_blocks * 16 * channels)) return 1;
+    CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+int yupvq_floats_to_oklab(yupvq_ctx* ctx, const float* float_blocks, size_t n_blocks, int channels, float* out_oklab) {
+    if (!ctx) return 1;
+    Scope scope(ctx->device);
+    if (channels < 1 || channels > 4) return ctx->fail("channels must be 1..4");
+    if (n_blocks == 0) return 0;
+    const void* px_dev = nullptr;
+    if (to_device(ctx, float_blocks, n_blocks * 16 * channels * 4, ctx->in_bytes, &px_dev)) return 1;
+    CK(ctx->feat.ensure(n_blocks * 256));
+    LAUNCH(launch_floats_to_features(reinterpret_cast<const float*>(px_dev), n_blocks, channels, ctx->feat.as<float>(), ctx->stream));
+    if (from_device(ctx, out_oklab, ctx->feat.p, n_blocks * 256)) return 1;
+    CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+int yupvq_oklab_to_floats(yupvq_ctx* ctx, const float* oklab, size_t n_blocks, int channels, float* out_float_blocks) {
+    if (!ctx) return 1;
+    Scope scope(ctx->device);
+    if (channels < 1 || channels > 4) return ctx->fail("channels must be 1..4");
+    if (n_blocks == 0) return 0;
+    const void* ok_dev = nullptr;
+    if (to_device(ctx, oklab, n_blocks * 256, ctx->feat, &ok_dev)) return 1;
+    CK(ctx->cent_px.ensure(n_blocks * 16 * channels * 4));
+    LAUNCH(launch_oklab_to_floats(reinterpret_cast<const float*>(ok_dev), n_blocks, channels, ctx->cent_px.as<float>(), ctx->stream));
+    if (from_device(ctx, out_float_blocks, ctx->cent_px.p, n_blocks * 16 * channels * 4)) return 1;
+    CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+int yupvq_gather_tiles(yupvq_ctx* ctx, const float* image, uint32_t width, uint32_t height, int channels,
+                       float* out_float_blocks) {
+    if (!ctx) return 1;
+    Scope scope(ctx->device);
+    if (channels < 1 || channels > 4) return ctx->fail("channels must be 1..4");
+    const size_t n = (size_t)((width + 3) / 4) * ((height + 3) / 4);
+    if (n == 0) return 0;
+    const void* img_dev = nullptr;
+    if (to_device(ctx, image, (size_t)width * height * channels * 4, ctx->in_bytes, &img_dev)) return 1;
+    CK(ctx->cent_px.ensure(n * 16 * channels * 4));
+    LAUNCH(launch_image_to_features(reinterpret_cast<const float*>(img_dev), width, height, channels, nullptr,
+                                    ctx->cent_px.as<float>(), ctx->stream));
+    if (from_device(ctx, out_float_blocks, ctx->cent_px.p, n * 16 * channels * 4)) return 1;
+    CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+int yupvq_assign(yupvq_ctx* ctx, const float* features, size_t n_blocks, const float* centroids, uint32_t codebook_size,
+                 int assign_mode, uint32_t* out_indices, float* out_errors, yupvq_stats* stats) {
+    (void)assign_mode;
+    if (!ctx) return 1;
+    Scope scope(ctx->device);
+    init_stats(stats);
+    ctx->launches = 0;
+    if (n_blocks == 0) return 0;
+    const void* f_dev = nullptr;
+    const void* c_dev = nullptr;
+    if (to_device(ctx, features, n_blocks * 256, ctx->feat, &f_dev)) return 1;
+    if (to_device(ctx, centroids, (size_t)codebook_size * 256, ctx->cent, &c_dev)) return 1;
+    CK(ctx->out_idx.ensure(n_blocks * 4));
+    CK(ctx->errors.ensure(n_blocks * 4));
+    Timer tm(ctx);
+    const int t0 = tm.mark();
+    LAUNCH(launch_assign_exact(reinterpret_cast<const float*>(f_dev), n_blocks, reinterpret_cast<const float*>(c_dev),
+                               codebook_size, ctx->out_idx.as<uint32_t>(), ctx->errors.as<float>(), nullptr, ctx->stream));
+    const int t1 = tm.mark();
+    if (from_device(ctx, out_indices, ctx->out_idx.p, n_blocks * 4)) return 1;
+    if (from_device(ctx, out_errors, ctx->errors.p, n_blocks * 4)) return 1;
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (stats) {
+        stats->n_blocks = (uint32_t)n_blocks;
+        stats->codebook_size = codebook_size;
+        stats->ms_quantize = stats->ms_total = tm.ms(t0, t1);
+        stats->gpu_launches = ctx->launches;
+    }
+    return 0;
+}
+
+int yupvq_seed_ldr(yupvq_ctx* ctx, const uint8_t* pixel_blocks, size_t n_blocks, int channels, uint32_t codebook_size,
+                   uint64_t seed, uint32_t* out_seed_blocks, uint32_t* out_rounds) {
+    if (!ctx) return 1;
+    Scope scope(ctx->device);
+    ctx->launches = 0;
+    if (channels < 1 || channels > 4) return ctx->fail("channels must be 1..4");
+    if (n_blocks == 0 || codebook_size == 0) return ctx->fail("empty input");
+    const void* px_dev = nullptr;
+    if (to_device(ctx, pixel_blocks, n_blocks * 16 * channels, ctx->in_bytes, &px_dev)) return 1;
+    CK(ctx->planes.ensure(n_blocks * 16 * channels));
+    LAUNCH(launch_pixels_to_features(reinterpret_cast<const uint8_t*>(px_dev), n_blocks, channels,
+                                     ctx->planes.as<uint4>(), n_blocks, nullptr, ctx->stream));
+    size_t n_used;
+    Draws dr = make_draws(n_blocks, codebook_size, 1.0f, seed, &n_used);
+    Blocks b;
+    b.n = n_blocks;
+    b.ch = channels;
+    b.planes = ctx->planes.as<uint4>();
+    b.stride = n_blocks;
+    uint32_t rounds = 0;
+    if (run_seeding(ctx, b, codebook_size, dr, false, &rounds)) return 1;
+    if (out_rounds) *out_rounds = rounds;
+    if (from_device(ctx, out_seed_blocks, ctx->seed_idx.p, (size_t)codebook_size * 4)) return 1;
+    CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+int yupvq_seed_hdr(yupvq_ctx* ctx, const float* features, size_t n_blocks, uint32_t codebook_size, uint64_t seed,
+                   uint32_t* out_seed_blocks, uint32_t* out_rounds) {
+    if (!ctx) return 1;
+    Scope scope(ctx->device);
+    ctx->launches = 0;
+    if (n_blocks == 0 || codebook_size == 0) return ctx->fail("empty input");
+    const void* f_dev = nullptr;
+    if (to_device(ctx, features, n_blocks * 256, ctx->feat, &f_dev)) return 1;
+    size_t n_used;
+    Draws dr = make_draws(n_blocks, codebook_size, 1.0f, seed, &n_used);
+    Blocks b;
+    b.n = n_blocks;
+    b.ch = 4;
+    b.feat = reinterpret_cast<const float*>(f_dev);
+    uint32_t rounds = 0;
+    if (run_seeding(ctx, b, codebook_size, dr, true, &rounds)) return 1;
+    if (out_rounds) *out_rounds = rounds;
+    if (from_device(ctx, out_seed_blocks, ctx->seed_idx.p, (size_t)codebook_size * 4)) return 1;
+    CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+int yupvq_update_centroids(yupvq_ctx* ctx, const float* features, size_t n_blocks, const uint32_t* assignments,
+                           const float* errors, uint32_t codebook_size, float* inout_centroids, uint32_t* out_counts) {
+    if (!ctx) return 1;
+    Scope scope(ctx->device);
+    ctx->launches = 0;
+    const uint32_t K = codebook_size;
+    if (n_blocks == 0 || K == 0) return ctx->fail("empty input");
+    const void* f_dev = nullptr;
+    const void* a_dev = nullptr;
+    const void* e_dev = nullptr;
+    if (to_device(ctx, features, n_blocks * 256, ctx->feat, &f_dev)) return 1;
+    if (to_device(ctx, assignments, n_blocks * 4, ctx->assign, &a_dev)) return 1;
+    // errors are modified by the reseed: always work on the context's copy
+    CK(ctx->errors.ensure(n_blocks * 4));
+    CK(cudaMemcpyAsync(ctx->errors.p, errors, n_blocks * 4, cudaMemcpyDefault, ctx->stream));
+    e_dev = ctx->errors.p;
+    CK(ctx->cent.ensure((size_t)K * 256));
+    CK(cudaMemcpyAsync(ctx->cent.p, inout_centroids, (size_t)K * 256, cudaMemcpyDefault, ctx->stream));
+    const size_t acc_words = (size_t)K * 65 + 1;
+    CK(ctx->acc.ensure(acc_words * 8));
+    uint32_t* flags = ctx->small.as<uint32_t>();
+    CK(cudaMemsetAsync(flags, 0, F_WORDS * 4, ctx->stream));
+    LAUNCH(launch_max_abs(reinterpret_cast<const float*>(f_dev), n_blocks * 64, flags + F_MAXABS, ctx->stream));
+    CK(cudaMemcpyAsync(ctx->h_small, flags + F_MAXABS, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    float max_abs;
+    std::memcpy(&max_abs, ctx->h_small, 4);
+    const int shift = fixed_shift(n_blocks, max_abs);
+    CK(cudaMemsetAsync(ctx->acc.p, 0, acc_words * 8, ctx->stream));
+    LAUNCH(launch_accumulate(reinterpret_cast<const float*>(f_dev), n_blocks, reinterpret_cast<const uint32_t*>(a_dev), K,
+                             shift, ctx->acc.as<long long>(), flags, ctx->stream));
+    LAUNCH(launch_finalize_centroids(ctx->acc.as<long long>(), K, shift, ctx->cent.as<float>(), flags, ctx->stream));
+    LAUNCH(launch_reseed_empty(reinterpret_cast<const float*>(f_dev), n_blocks, reinterpret_cast<float*>(const_cast<void*>(e_dev)),
+                               ctx->acc.as<long long>(), K, ctx->cent.as<float>(), flags, ctx->stream));
+    if (from_device(ctx, inout_centroids, ctx->cent.p, (size_t)K * 256)) return 1;
+    if (out_counts) {
+        // counts live as 64-bit words behind the sums
+        std::vector<long long> h(K);
+        CK(cudaMemcpyAsync(h.data(), ctx->acc.as<long long>() + (size_t)K * 64, (size_t)K * 8, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+        if (is_device_ptr(out_counts)) {
+            std::vector<uint32_t> h32(K);
+            for (uint32_t c = 0; c < K; ++c) h32[c] = (uint32_t)h[c];
+            CK(cudaMemcpy(out_counts, h32.data(), (size_t)K * 4, cudaMemcpyHostToDevice));
+        } else {
+            for (uint32_t c = 0; c < K; ++c) out_counts[c] = (uint32_t)h[c];
+        }
+    }
+    CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+int yupvq_gather_codebook(yupvq_ctx* ctx, const uint8_t* codebook, uint32_t n_entries, uint32_t block_size,
+                          const uint32_t* indices, size_t n_blocks, uint8_t* out_bc_blocks) {
+    if (!ctx) return 1;
+    Scope scope(ctx->device);
+    ctx->launches = 0;
+    if (block_size != 8 && block_size != 16) return ctx->fail("block_size must be 8 or 16");
+    if (n_blocks == 0) return 0;
+    const void* cb_dev = nullptr;
+    const void* idx_dev = nullptr;
+    if (to_device(ctx, codebook, (size_t)n_entries * block_size, ctx->cent_px, &cb_dev)) return 1;
+    if (to_device(ctx, indices, n_blocks * 4, ctx->assign, &idx_dev)) return 1;
+    uint8_t* out_dev = out_bc_blocks;
+    const bool out_is_dev = is_device_ptr(out_bc_blocks);
+    if (!out_is_dev) {
+        CK(ctx->in_bytes.ensure(n_blocks * block_size));
+        out_dev = ctx->in_bytes.as<uint8_t>();
+    }
+    LAUNCH(launch_gather_codebook(reinterpret_cast<const uint8_t*>(cb_dev), n_entries, block_size,
+                                  reinterpret_cast<const uint32_t*>(idx_dev), n_blocks, out_dev, ctx->stream));
+    if (!out_is_dev && from_device(ctx, out_bc_blocks, out_dev, n_blocks * block_size)) return 1;
+    CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+// ---- multi-GPU -------------------------------------------------------------------------------------------
+int yupvq_comm_unique_id(yupvq_ctx* ctx, uint8_t out_id[128]) {
+    if (!ctx) return 1;
+    if (ctx->nccl.load()) return ctx->fail("cannot load NCCL: %s", ctx->nccl.error.c_str());
+    if (ctx->nccl.unique_id(out_id)) return ctx->fail("ncclGetUniqueId failed");
+    return 0;
+}
+
+int yupvq_comm_init(yupvq_ctx* ctx, const uint8_t id[128], int n_ranks, int rank) {
+    if (!ctx) return 1;
+    Scope scope(ctx->device);
+    if (ctx->nccl.load()) return ctx->fail("cannot load NCCL: %s", ctx->nccl.error.c_str());
+    if (ctx->comm) {
+        ctx->nccl.destroy(ctx->comm);
+        ctx->comm = nullptr;
+    }
+    if (ctx->nccl.init_rank(&ctx->comm, n_ranks, id, rank)) return ctx->fail("ncclCommInitRank failed");
+    ctx->n_ranks = n_ranks;
+    ctx->rank = rank;
+    return 0;
+}
+
+int yupvq_encode_bcn_sharded(yupvq_ctx* ctx, const uint8_t* bc_blocks, size_t n_total, size_t first_block,
+                             size_t n_local, int bc_format, int channels, const yupvq_config* cfg,
+                             uint8_t* out_pixel_centroids, uint32_t* out_indices, yupvq_stats* stats) {
+    if (!ctx) return 1;
+    Scope scope(ctx->device);
+    init_stats(stats);
+    ctx->launches = 0;
+    if (check_cfg(ctx, cfg, n_total, channels)) return 1;
+    if (!bc_supported(bc_format)) return ctx->fail("BC format %d is not supported on the LDR VQ path", bc_format);
+    if (first_block + n_local > n_total) return ctx->fail("shard [%zu, %zu) exceeds %zu blocks", first_block, first_block + n_local, n_total);
+    if (cfg->sample_ratio < 1.0f && cfg->sample_ratio > 0.0f) return ctx->fail("fast-mode sampling is not supported on the sharded path");
+    if (cfg->metric != YUPVQ_METRIC_OKLAB) return ctx->fail("SAD metric Lloyd is not built yet");
+    const uint32_t K = cfg->codebook_size;
+    Timer tm(ctx);
+    const int t0 = tm.mark();
+    const void* bc_dev = nullptr;
+    if (to_device(ctx, bc_blocks, n_total * bc_block_bytes(bc_format), ctx->in_bytes, &bc_dev)) return 1;
+    const int t1 = tm.mark();
+    // Whole texture decoded on every rank (8-16 MiB in): seeding is replicated and integer-exact, so
+    // all ranks pick the same seeds with no communication.
+    CK(ctx->planes.ensure(n_total * 16 * channels));
+    CK(ctx->feat.ensure(n_total * 256));
+    LAUNCH(launch_decode_bcn(reinterpret_cast<const uint8_t*>(bc_dev), n_total, bc_format, channels,
+                             ctx->planes.as<uint4>(), n_total, ctx->feat.as<float>(), nullptr, ctx->stream));
+    const int t2 = tm.mark();
+    Blocks all;
+    all.n = n_total;
+    all.ch = channels;
+    all.planes = ctx->planes.as<uint4>();
+    all.stride = n_total;
+    all.feat = ctx->feat.as<float>();
+    size_t n_used;
+    Draws dr = make_draws(n_total, K, 1.0f, cfg->seed, &n_used);
+    uint32_t rounds = 0;
+    if (run_seeding(ctx, all, K, dr, false, stats ? &rounds : nullptr)) return 1;
+    CK(ctx->cent.ensure((size_t)K * 256));
+    LAUNCH(launch_gather_rows_f32(all.feat, ctx->seed_idx.as<uint32_t>(), K, 64, ctx->cent.as<float>(), ctx->stream));
+    const int t3 = tm.mark();
+    Blocks mine = all;
+    mine.n = n_local;
+    mine.feat = all.feat + first_block * 64;
+    mine.planes = all.planes + first_block;  // stride unchanged
+    if (run_lloyd(ctx, mine, n_total, first_block, K, cfg->max_iterations, 0u, cfg->assign_mode, ctx->cent.as<float>(), stats)) return 1;
+    const int t4 = tm.mark();
+    CK(ctx->cent_px.ensure((size_t)K * 16 * channels));
+    LAUNCH(launch_oklab_to_pixels(ctx->cent.as<float>(), K, channels, ctx->cent_px.as<uint8_t>(), ctx->stream));
+    const int t5 = tm.mark();
+    if (quantize_device(ctx, mine, ctx->cent_px.p, K, false, cfg->assign_mode)) return 1;
+    const int t6 = tm.mark();
+    if (from_device(ctx, out_pixel_centroids, ctx->cent_px.p, (size_t)K * 16 * channels)) return 1;
+    if (from_device(ctx, out_indices, ctx->out_idx.p, n_local * 4)) return 1;
+    const int t7 = tm.mark();
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (stats) {
+        stats->n_blocks = (uint32_t)n_local;
+        stats->codebook_size = K;
+        stats->seed_rounds = rounds;
+        stats->ms_h2d = tm.ms(t0, t1);
+        stats->ms_decode = tm.ms(t1, t2);
+        stats->ms_seed = tm.ms(t2, t3);
+        stats->ms_lloyd = tm.ms(t3, t4);
+        stats->ms_finalize = tm.ms(t4, t5);
+        stats->ms_quantize = tm.ms(t5, t6);
+        stats->ms_d2h = tm.ms(t6, t7);
+        stats->ms_total = tm.ms(t0, t7);
+        stats->gpu_launches = ctx->launches;
+    }
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,75 @@
+// Internal launch interface between the C-ABI/orchestration (api.cu) and the kernel translation units.
+#pragma once
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdint.h>
+
+namespace yupvq {
+
+// ---- convert.cu : K1 / K1h / K6 -------------------------------------------------
+// Pixel blocks live in HBM as `ch` planes of uint4: plane p holds bytes [16p, 16p+16) of every
+// block's 16*ch-byte pixel block, planes[p * plane_stride + block].  Seeding reads them coalesced.
+cudaError_t colour_tables_init();
+cudaError_t launch_decode_bcn(const uint8_t* bc, size_t n, int fmt, int ch, uint4* planes, size_t plane_stride,
+                              float* feat, uint8_t* px_blocks, cudaStream_t s);
+cudaError_t launch_pixels_to_features(const uint8_t* px_blocks, size_t n, int ch, uint4* planes, size_t plane_stride,
+                                      float* feat, cudaStream_t s);
+cudaError_t launch_floats_to_features(const float* float_blocks, size_t n, int ch, float* feat, cudaStream_t s);
+cudaError_t launch_image_to_features(const float* image, uint32_t w, uint32_t h, int ch, float* feat, float* tiles,
+                                     cudaStream_t s);
+cudaError_t launch_oklab_to_pixels(const float* oklab, size_t n, int ch, uint8_t* out, cudaStream_t s);
+cudaError_t launch_oklab_to_floats(const float* oklab, size_t n, int ch, float* out, cudaStream_t s);
+cudaError_t launch_gather_rows_f32(const float* src, const uint32_t* rows, size_t n_rows, int row_floats, float* dst,
+                                   cudaStream_t s);
+cudaError_t launch_gather_blocks(const uint4* planes, size_t plane_stride, const float* feat, const uint32_t* rows,
+                                 size_t n_rows, int ch, uint4* out_planes, size_t out_stride, float* out_feat,
+                                 cudaStream_t s);
+cudaError_t launch_planes_to_blocks(const uint4* planes, size_t plane_stride, const uint32_t* rows, size_t n_rows,
+                                    int ch, uint8_t* out_px_blocks, cudaStream_t s);
+cudaError_t launch_gather_codebook(const uint8_t* codebook, uint32_t n_entries, uint32_t block_size,
+                                   const uint32_t* indices, size_t n, uint8_t* out, cudaStream_t s);
+
+// ---- seed.cu : K2 / K2h ----------------------------------------------------------------------------
+struct SeedState {
+    float* min_dist;              // n
+    unsigned long long* partial;  // grid partial sums (uint64 for LDR, double bits for HDR)
+    unsigned int* counter;        // last-block-done ticket
+    uint32_t* seed_idx;           // K chosen block indices (device)
+    const double* canon;          // K-1 canonical uniforms in [0,1) (device)
+    uint32_t* status;             // [0] degenerate_from (0 = none), [1] rounds drawn
+    int grid;                     // CTAs per round (fixed for the whole seeding)
+};
+size_t seed_grid_for(size_t n);
+cudaError_t launch_seed_init(const SeedState& st, size_t n, uint32_t first_idx, cudaStream_t s);
+cudaError_t launch_seed_round_ldr(const SeedState& st, const uint4* planes, size_t plane_stride, size_t n, int ch,
+                                  uint32_t round, uint32_t K, cudaStream_t s);
+cudaError_t launch_seed_round_hdr(const SeedState& st, const float* feat, size_t n, uint32_t round, uint32_t K,
+                                  cudaStream_t s);
+
+// ---- assign.cu : K3 --------------------------------------------------------------------------------
+// Exact fp32 assignment in the reference's operation order (also the re-rank kernel).
+// flags[0] |= 1 when any assignment changed.
+cudaError_t launch_assign_exact(const float* feat, size_t n, const float* cent, uint32_t K, uint32_t* assign,
+                                float* errors, uint32_t* flags, cudaStream_t s);
+// errors[i] = exact distance to the assigned centroid (used before an empty-cluster reseed in tensor mode)
+cudaError_t launch_exact_errors(const float* feat, size_t n, const float* cent, const uint32_t* assign, float* errors,
+                                cudaStream_t s);
+
+// ---- update.cu : K4 / K5 -----------------------------------------------------------------------------
+// Accumulator layout (int64 words): [K*64 sums | K counts | 1 changed flag].  Sums are 64-bit fixed
+// point (value * 2^shift): associative, therefore order / CTA / GPU-count independent; the whole
+// buffer is what gets all-reduced when blocks are sharded across GPUs.
+// flags: [0] changed (written by assign), [1] #empty clusters, [2] reseeds (running total).
+cudaError_t launch_accumulate(const float* feat, size_t n, const uint32_t* assign, uint32_t K, int shift,
+                              long long* acc, const uint32_t* flags, cudaStream_t s);
+// centroid = float(sum) * (1.0f / count) (reference src/vq_encoder.cpp:366-368); flags[1] = #empty clusters
+cudaError_t launch_finalize_centroids(const long long* acc, uint32_t K, int shift, float* cent, uint32_t* flags,
+                                      cudaStream_t s);
+// serial-semantics reseed of empty clusters (ascending c, first maximum of errors, then zero it)
+cudaError_t launch_reseed_empty(const float* feat, size_t n, float* errors, const long long* acc, uint32_t K,
+                                float* cent, uint32_t* flags, cudaStream_t s);
+// out[0] = max error (float bits), out[1] = index of its first occurrence
+cudaError_t launch_argmax_error(const float* errors, size_t n, uint32_t* out2, cudaStream_t s);
+cudaError_t launch_max_abs(const float* x, size_t n, uint32_t* out_bits, cudaStream_t s);
+
+}  // namespace yupvq

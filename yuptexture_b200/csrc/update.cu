@@ -1,0 +1,186 @@
+// K4 / K5: centroid sum/count update, normalisation and empty-cluster reseed.
+// Reference: src/vq_encoder.cpp:343-375 (LDR) and :574-605 (HDR).
+//
+// Sums are accumulated in 64-bit fixed point (value * 2^shift, shift chosen from N and max|x| so
+// the total cannot overflow).  Integer addition is associative, so the result does not depend on
+// thread/CTA/GPU order -- 1, 2, 4 and 8 GPUs produce identical centroids -- and it is rounded to
+// fp32 exactly once, which is closer to the true mean than the reference's thread-chunked fp32
+// accumulation (whose own result depends on numThreads).  Normalisation follows the reference's
+// two roundings: c = float(sum) * (1.0f / count).
+// Accumulator layout (int64 words): [K*64 sums | K counts | 1 changed flag].
+// Roofline: HBM-bound, 260 B read per block per pass.
+#include <cfloat>
+
+#include "common.cuh"
+#include "kernels.h"
+
+namespace yupvq {
+
+namespace {
+
+// v1: one warp per block, 64 RED.ADD.64 per block into the accumulator in L2.
+__global__ void __launch_bounds__(256) accumulate_kernel(const float* __restrict__ feat, size_t n,
+                                                         const uint32_t* __restrict__ assign, uint32_t K, float scale,
+                                                         long long* __restrict__ acc, const uint32_t* __restrict__ flags) {
+    const int lane = threadIdx.x & 31;
+    const size_t warp = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const size_t n_warps = ((size_t)gridDim.x * blockDim.x) >> 5;
+    unsigned long long* sums = reinterpret_cast<unsigned long long*>(acc);
+    unsigned long long* counts = sums + (size_t)K * 64;
+    for (size_t i = warp; i < n; i += n_warps) {
+        const uint32_t c = assign[i];
+        const float v0 = feat[i * 64 + lane], v1 = feat[i * 64 + 32 + lane];
+        atomicAdd(sums + (size_t)c * 64 + lane, (unsigned long long)__float2ll_rn(__fmul_rn(v0, scale)));
+        atomicAdd(sums + (size_t)c * 64 + 32 + lane, (unsigned long long)__float2ll_rn(__fmul_rn(v1, scale)));
+        if (lane == 0) atomicAdd(counts + c, 1ull);
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0 && flags) atomicAdd(sums + (size_t)K * 65, (unsigned long long)flags[0]);
+}
+
+__global__ void finalize_kernel(const long long* __restrict__ acc, uint32_t K, double inv_scale,
+                                float* __restrict__ cent, uint32_t* __restrict__ flags) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (size_t)K * 64) return;
+    const uint32_t c = (uint32_t)(i >> 6);
+    const uint32_t cnt = (uint32_t)acc[(size_t)K * 64 + c];
+    if (cnt > 0) {
+        const float inv = __fdiv_rn(1.0f, (float)cnt);          // float inv_count = 1.0f / counts[c]
+        const float s = (float)((double)acc[i] * inv_scale);    // the sum, rounded to fp32 once
+        cent[i] = __fmul_rn(s, inv);                            // newCentroids[c][j] * inv_count
+    } else if ((i & 63) == 0) {
+        atomicAdd(flags + 1, 1u);
+    }
+}
+
+// first index of the maximum of errors[0, n) -- std::max_element semantics -- computed by one CTA.
+__device__ unsigned long long cta_argmax_first(const float* errors, size_t n, float* out_val, float* s_val,
+                                               unsigned long long* s_idx) {
+    float bv = -FLT_MAX;
+    unsigned long long bi = ~0ull;
+    for (size_t j = threadIdx.x; j < n; j += blockDim.x) {
+        const float e = __ldcg(errors + j);
+        if (bi == ~0ull || e > bv) {  // ascending strided scan: strict '>' keeps the first maximum
+            bv = e;
+            bi = j;
+        }
+    }
+    auto merge = [&](float ov, unsigned long long oi) {
+        if (oi != ~0ull && (bi == ~0ull || ov > bv || (ov == bv && oi < bi))) {
+            bv = ov;
+            bi = oi;
+        }
+    };
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+        const unsigned long long oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        merge(ov, oi);
+    }
+    __syncthreads();  // protect s_val/s_idx reuse across calls
+    if ((threadIdx.x & 31) == 0) {
+        s_val[threadIdx.x >> 5] = bv;
+        s_idx[threadIdx.x >> 5] = bi;
+    }
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        const bool has = threadIdx.x < (blockDim.x >> 5);
+        bv = has ? s_val[threadIdx.x] : -FLT_MAX;
+        bi = has ? s_idx[threadIdx.x] : ~0ull;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+            const unsigned long long oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            merge(ov, oi);
+        }
+        if (threadIdx.x == 0) {
+            s_idx[32] = bi;
+            s_val[32] = bv;
+        }
+    }
+    __syncthreads();
+    *out_val = s_val[32];
+    return s_idx[32];
+}
+
+// Serial semantics of the reference's reseed loop: for ascending c with count 0, take
+// the FIRST block with the maximum error, copy its feature vector into the centroid, zero that error.
+__global__ void __launch_bounds__(1024) reseed_kernel(const float* __restrict__ feat, size_t n, float* errors,
+                                                      const long long* __restrict__ acc, uint32_t K, float* cent,
+                                                      uint32_t* flags) {
+    __shared__ float s_val[33];
+    __shared__ unsigned long long s_idx[33];
+    if (flags[1] == 0) return;  // no empty cluster this pass
+    for (uint32_t c = 0; c < K; ++c) {
+        if (acc[(size_t)K * 64 + c] != 0) continue;
+        float v;
+        const unsigned long long worst = cta_argmax_first(errors, n, &v, s_val, s_idx);
+        if (threadIdx.x < 64) cent[(size_t)c * 64 + threadIdx.x] = feat[worst * 64 + threadIdx.x];
+        if (threadIdx.x == 0) {
+            errors[worst] = 0.0f;
+            atomicAdd(flags + 2, 1u);
+        }
+        __threadfence();
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(1024) argmax_kernel(const float* __restrict__ errors, size_t n, uint32_t* out2) {
+    __shared__ float s_val[33];
+    __shared__ unsigned long long s_idx[33];
+    float v;
+    const unsigned long long worst = cta_argmax_first(errors, n, &v, s_val, s_idx);
+    if (threadIdx.x == 0) {
+        out2[0] = __float_as_uint(v);
+        out2[1] = (uint32_t)worst;
+    }
+}
+
+__global__ void max_abs_kernel(const float* __restrict__ x, size_t n, uint32_t* out_bits) {
+    float m = 0.0f;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const float v = fabsf(x[i]);
+        if (v != v) m = INFINITY;
+        else if (v > m) m = v;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0) atomicMax(out_bits, __float_as_uint(m));
+}
+
+}  // namespace
+
+cudaError_t launch_accumulate(const float* feat, size_t n, const uint32_t* assign, uint32_t K, int shift,
+                              long long* acc, const uint32_t* flags, cudaStream_t s) {
+    size_t blocks = (n * 32 + 255) / 256;
+    if (blocks > (size_t)YUPVQ_NUM_SMS * 16) blocks = (size_t)YUPVQ_NUM_SMS * 16;
+    if (blocks < 1) blocks = 1;
+    accumulate_kernel<<<(unsigned)blocks, 256, 0, s>>>(feat, n, assign, K, ldexpf(1.0f, shift), acc, flags);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_finalize_centroids(const long long* acc, uint32_t K, int shift, float* cent, uint32_t* flags,
+                                      cudaStream_t s) {
+    finalize_kernel<<<(K * 64 + 255) / 256, 256, 0, s>>>(acc, K, ldexp(1.0, -shift), cent, flags);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_reseed_empty(const float* feat, size_t n, float* errors, const long long* acc, uint32_t K,
+                                float* cent, uint32_t* flags, cudaStream_t s) {
+    reseed_kernel<<<1, 1024, 0, s>>>(feat, n, errors, acc, K, cent, flags);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_argmax_error(const float* errors, size_t n, uint32_t* out2, cudaStream_t s) {
+    argmax_kernel<<<1, 1024, 0, s>>>(errors, n, out2);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_max_abs(const float* x, size_t n, uint32_t* out_bits, cudaStream_t s) {
+    if (n == 0) return cudaSuccess;
+    size_t blocks = (n + 255) / 256;
+    if (blocks > (size_t)YUPVQ_NUM_SMS * 8) blocks = (size_t)YUPVQ_NUM_SMS * 8;
+    max_abs_kernel<<<(unsigned)blocks, 256, 0, s>>>(x, n, out_bits);
+    return cudaGetLastError();
+}
+
+}  // namespace yupvq
