@@ -65,6 +65,11 @@ struct yupvq_ctx {
     DevBuf min_dist, partial, seed_idx, canon, small;  // seeding
     DevBuf assign, errors, cent, acc;                  // Lloyd
     DevBuf cent_px, cent_feat, out_idx;                // finalize / quantize
+    // tensor engine (assign_tc.cu): per block set A', |x'|, mu; per pass B', folded norms, candidates
+    DevBuf tc_a, tc_xnorm, tc_small, tc_b, tc_bx, tc_cand;
+    const float* tc_feat = nullptr;                    // block set the A' buffer was built from
+    size_t tc_n = 0;
+    uint64_t rerank_pairs = 0;
     uint32_t* h_small = nullptr;                       // pinned: flags + status readback
 
     // multi-GPU
@@ -98,7 +103,10 @@ struct yupvq_ctx {
 namespace {
 
 // small device scratch layout (uint32 words)
-enum { F_CHANGED = 0, F_EMPTY = 1, F_RESEEDS = 2, F_SPARE = 3, F_SEED_STATUS = 4 /*2 words*/, F_COUNTER = 6, F_MAXABS = 7, F_WORDS = 16 };
+enum { F_CHANGED = 0, F_EMPTY = 1, F_RESEEDS = 2, F_SPARE = 3, F_SEED_STATUS = 4 /*2 words*/, F_COUNTER = 6, F_MAXABS = 7,
+       F_PAIRS = 8, F_WORDS = 16 };
+// tc_small layout (bytes): [0,512) column sums fp64 | [512,768) mu fp32 | [768,772) cmax
+enum { TC_SUMS = 0, TC_MU = 512, TC_CMAX = 768, TC_SMALL_BYTES = 1024 };
 
 bool is_device_ptr(const void* p) {
     cudaPointerAttributes a;
@@ -295,13 +303,63 @@ int reseed_sharded(yupvq_ctx* ctx, const Blocks& b, size_t first_block, uint32_t
     return 0;
 }
 
+// ---- K3 dispatch: exact engine or tcgen05 front-end + exact re-rank -----------------------------------
+bool use_tensor(int mode, size_t n, uint32_t K) {
+    if (mode == YUPVQ_ASSIGN_EXACT) return false;
+    if (!tc_supported(K)) return false;
+    if (mode == YUPVQ_ASSIGN_TENSOR) return true;
+    return K >= 64 && n >= 8192;  // below that the exact kernel is already launch-latency sized
+}
+
+// Builds mu / A' / |x'| for a block set (cached per call: the Lloyd passes and the final quantise
+// share them).
+int tc_prepare_blocks(yupvq_ctx* ctx, const float* feat, size_t n) {
+    if (ctx->tc_feat == feat && ctx->tc_n == n) return 0;
+    CK(ctx->tc_small.ensure(TC_SMALL_BYTES));
+    CK(ctx->tc_a.ensure(std::max<size_t>(1, n) * 256));
+    CK(ctx->tc_xnorm.ensure(std::max<size_t>(1, n) * 4));
+    uint8_t* sm = ctx->tc_small.as<uint8_t>();
+    LAUNCH(launch_tc_mean(feat, n, reinterpret_cast<double*>(sm + TC_SUMS), reinterpret_cast<float*>(sm + TC_MU), ctx->stream));
+    ++ctx->launches;  // launch_tc_mean is two kernels
+    LAUNCH(launch_tc_prep_blocks(feat, n, reinterpret_cast<const float*>(sm + TC_MU), ctx->tc_a.as<float>(),
+                                 ctx->tc_xnorm.as<float>(), ctx->stream));
+    ctx->tc_feat = feat;
+    ctx->tc_n = n;
+    return 0;
+}
+
+// One assignment pass.  errors may be null (tensor mode then skips the exact distance of blocks with
+// a single candidate); flags[0] |= 1 when an assignment changed.
+int assign_blocks(yupvq_ctx* ctx, const float* feat, size_t n, const float* cent, uint32_t K, int mode, uint32_t* assign,
+                  float* errors, uint32_t* flags) {
+    if (mode == YUPVQ_ASSIGN_TENSOR && !tc_supported(K))
+        return ctx->fail("tensor assignment needs 1 <= K <= 65535 and a driver with cuTensorMapEncodeTiled (K = %u)", K);
+    if (!use_tensor(mode, n, K)) {
+        LAUNCH(launch_assign_exact(feat, n, cent, K, assign, errors, flags, ctx->stream));
+        return 0;
+    }
+    if (tc_prepare_blocks(ctx, feat, n)) return 1;
+    const uint32_t k_pad = tc_padded_k(K);
+    CK(ctx->tc_b.ensure((size_t)k_pad * 256));
+    CK(ctx->tc_bx.ensure((size_t)k_pad * 32));
+    CK(ctx->tc_cand.ensure(std::max<size_t>(1, n) * 16));
+    uint8_t* sm = ctx->tc_small.as<uint8_t>();
+    LAUNCH(launch_tc_prep_centroids(cent, K, reinterpret_cast<const float*>(sm + TC_MU), ctx->tc_b.as<float>(),
+                                    ctx->tc_bx.as<float>(), reinterpret_cast<float*>(sm + TC_CMAX), ctx->stream));
+    LAUNCH(launch_assign_tc(ctx->tc_a.as<float>(), ctx->tc_xnorm.as<float>(), n, ctx->tc_b.as<float>(), ctx->tc_bx.as<float>(),
+                            K, reinterpret_cast<const float*>(sm + TC_CMAX), ctx->tc_cand.as<uint4>(), ctx->stream));
+    LAUNCH(launch_rerank(feat, n, cent, K, ctx->tc_cand.as<uint4>(), assign, errors, flags,
+                         ctx->small.as<unsigned int>() + F_PAIRS, ctx->stream));
+    return 0;
+}
+
 // ---- K3..K5: Lloyd iterations ----------------------------------------------------------------------
 // break_after: LDR breaks on (!changed && iter > 0), HDR on (!changed && iter > 1)
 // (src/vq_encoder.cpp:341 vs :572).  cent (device, K x 64) holds the seeds on entry.
 int run_lloyd(yupvq_ctx* ctx, const Blocks& b, size_t n_total, size_t first_block, uint32_t K, uint32_t max_iter,
               uint32_t break_after, int assign_mode, float* cent, yupvq_stats* stats) {
-    (void)assign_mode;
     const size_t n = b.n;
+    const bool tensor = use_tensor(assign_mode, n, K);
     CK(ctx->assign.ensure(std::max<size_t>(1, n) * 4));
     CK(ctx->errors.ensure(std::max<size_t>(1, n) * 4));
     const size_t acc_words = (size_t)K * 65 + 1;  // [K*64 sums | K counts | changed]
@@ -312,6 +370,7 @@ int run_lloyd(yupvq_ctx* ctx, const Blocks& b, size_t n_total, size_t first_bloc
     long long* acc = ctx->acc.as<long long>();
     CK(cudaMemsetAsync(assign, 0, n * 4, ctx->stream));  // assignments(numBlocks, 0), :316
     CK(cudaMemsetAsync(flags + F_RESEEDS, 0, 4, ctx->stream));
+    CK(cudaMemsetAsync(flags + F_PAIRS, 0, 4, ctx->stream));
     ctx->reseeds_sharded = 0;
 
     // fixed-point scale from the data range (deterministic function of the data)
@@ -334,7 +393,8 @@ int run_lloyd(yupvq_ctx* ctx, const Blocks& b, size_t n_total, size_t first_bloc
     uint32_t passes = 0;
     for (uint32_t iter = 0; iter < max_iter; ++iter) {
         CK(cudaMemsetAsync(flags, 0, 8, ctx->stream));  // changed, empty
-        LAUNCH(launch_assign_exact(b.feat, n, cent, K, assign, errors, flags, ctx->stream));
+        // tensor mode computes errors[] lazily (they only feed the empty-cluster reseed)
+        if (assign_blocks(ctx, b.feat, n, cent, K, assign_mode, assign, tensor ? nullptr : errors, flags)) return 1;
         ++passes;
         // The reference checks hasChanged between assign and update; the update is launched
         // speculatively so one sync (and, sharded, one all-reduce) per pass carries both.
@@ -343,11 +403,15 @@ int run_lloyd(yupvq_ctx* ctx, const Blocks& b, size_t n_total, size_t first_bloc
         if (ctx->comm) {
             if (ctx->nccl.all_reduce_sum_i64(ctx->comm, acc, acc_words, ctx->stream)) return ctx->fail("ncclAllReduce(sum) failed");
         }
+        LAUNCH(launch_count_empty(acc, K, flags + F_SPARE, ctx->stream));
         CK(cudaMemcpyAsync(ctx->h_small, acc + (size_t)K * 65, 8, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaMemcpyAsync(ctx->h_small + 2, flags + F_SPARE, 4, cudaMemcpyDeviceToHost, ctx->stream));
         CK(cudaStreamSynchronize(ctx->stream));
         long long changed;
         std::memcpy(&changed, ctx->h_small, 8);
         if (!changed && iter > break_after) break;
+        if (tensor && ctx->h_small[2] != 0)  // errors[i] = distance to the assigned centroid, before the update (:336)
+            LAUNCH(launch_exact_errors(b.feat, n, cent, assign, errors, ctx->stream));
         LAUNCH(launch_finalize_centroids(acc, K, shift, cent, flags, ctx->stream));
         if (!ctx->comm) {
             LAUNCH(launch_reseed_empty(b.feat, n, errors, acc, K, cent, flags, ctx->stream));
@@ -356,10 +420,12 @@ int run_lloyd(yupvq_ctx* ctx, const Blocks& b, size_t n_total, size_t first_bloc
         }
     }
     CK(cudaMemcpyAsync(ctx->h_small, flags + F_RESEEDS, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(ctx->h_small + 1, flags + F_PAIRS, 4, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     if (stats) {
         stats->lloyd_passes = passes;
         stats->reseeds = ctx->h_small[0] + ctx->reseeds_sharded;
+        stats->rerank_blocks = ctx->h_small[1];  // exact distance evaluations spent on multi-candidate blocks
     }
     return 0;
 }
@@ -422,14 +488,12 @@ int build_codebook_device(yupvq_ctx* ctx, const Blocks& all, size_t n_total, con
 
 // QuantizeBlocks on device data: centroids (pixel/float, device) -> Oklab -> one assignment pass.
 int quantize_device(yupvq_ctx* ctx, const Blocks& all, const void* cent_px_dev, uint32_t K, bool hdr, int assign_mode) {
-    (void)assign_mode;
     CK(ctx->cent_feat.ensure((size_t)K * 256));
     if (hdr) LAUNCH(launch_floats_to_features(reinterpret_cast<const float*>(cent_px_dev), K, all.ch, ctx->cent_feat.as<float>(), ctx->stream));
     else LAUNCH(launch_pixels_to_features(reinterpret_cast<const uint8_t*>(cent_px_dev), K, all.ch, nullptr, 0, ctx->cent_feat.as<float>(), ctx->stream));
     CK(ctx->out_idx.ensure(std::max<size_t>(1, all.n) * 4));
-    LAUNCH(launch_assign_exact(all.feat, all.n, ctx->cent_feat.as<float>(), K, ctx->out_idx.as<uint32_t>(), nullptr, nullptr,
-                               ctx->stream));
-    return 0;
+    return assign_blocks(ctx, all.feat, all.n, ctx->cent_feat.as<float>(), K, assign_mode, ctx->out_idx.as<uint32_t>(), nullptr,
+                         nullptr);
 }
 
 int check_cfg(yupvq_ctx* ctx, const yupvq_config* cfg, size_t n, int ch) {
@@ -524,7 +588,8 @@ void yupvq_destroy(yupvq_ctx* ctx) {
     if (ctx->comm) ctx->nccl.destroy(ctx->comm);
     DevBuf* bufs[] = {&ctx->in_bytes, &ctx->planes, &ctx->feat, &ctx->s_planes, &ctx->s_feat, &ctx->s_rows,
                       &ctx->min_dist, &ctx->partial, &ctx->seed_idx, &ctx->canon, &ctx->small, &ctx->assign,
-                      &ctx->errors, &ctx->cent, &ctx->acc, &ctx->cent_px, &ctx->cent_feat, &ctx->out_idx};
+                      &ctx->errors, &ctx->cent, &ctx->acc, &ctx->cent_px, &ctx->cent_feat, &ctx->out_idx,
+                      &ctx->tc_a, &ctx->tc_xnorm, &ctx->tc_small, &ctx->tc_b, &ctx->tc_bx, &ctx->tc_cand};
     for (DevBuf* b : bufs) b->release();
     if (ctx->h_small) cudaFreeHost(ctx->h_small);
     for (auto& ev : ctx->ev)
@@ -562,6 +627,7 @@ int yupvq_encode_bcn(yupvq_ctx* ctx, const uint8_t* bc_blocks, size_t n_blocks, 
     Scope scope(ctx->device);
     init_stats(stats);
     ctx->launches = 0;
+    ctx->tc_feat = nullptr;
     if (check_cfg(ctx, cfg, n_blocks, channels)) return 1;
     if (!bc_supported(bc_format)) return ctx->fail("BC format %d is not supported on the LDR VQ path", bc_format);
     Timer tm(ctx);
@@ -609,6 +675,7 @@ int yupvq_encode_hdr(yupvq_ctx* ctx, const float* image, uint32_t width, uint32_
     Scope scope(ctx->device);
     init_stats(stats);
     ctx->launches = 0;
+    ctx->tc_feat = nullptr;
     const size_t n_blocks = (size_t)((width + 3) / 4) * ((height + 3) / 4);
     if (check_cfg(ctx, cfg, n_blocks, channels)) return 1;
     Timer tm(ctx);
@@ -682,6 +749,7 @@ int yupvq_build_codebook(yupvq_ctx* ctx, const uint8_t* pixel_blocks, size_t n_b
     Scope scope(ctx->device);
     init_stats(stats);
     ctx->launches = 0;
+    ctx->tc_feat = nullptr;
     if (check_cfg(ctx, cfg, n_blocks, channels)) return 1;
     Timer tm(ctx);
     const int t0 = tm.mark();
@@ -720,6 +788,7 @@ int yupvq_quantize_blocks(yupvq_ctx* ctx, const uint8_t* pixel_blocks, size_t n_
     Scope scope(ctx->device);
     init_stats(stats);
     ctx->launches = 0;
+    ctx->tc_feat = nullptr;
     if (n_blocks == 0) return 0;  // reference returns {} (:449)
     if (channels < 1 || channels > 4) return ctx->fail("channels must be 1..4");
     if (metric != YUPVQ_METRIC_OKLAB) return ctx->fail("SAD metric quantise is not built yet");
@@ -755,6 +824,7 @@ int yupvq_build_codebook_hdr(yupvq_ctx* ctx, const float* float_blocks, size_t n
     Scope scope(ctx->device);
     init_stats(stats);
     ctx->launches = 0;
+    ctx->tc_feat = nullptr;
     if (n_blocks == 0) return 0;  // reference returns {} (:517)
     if (check_cfg(ctx, cfg, n_blocks, channels)) return 1;
     Timer tm(ctx);
@@ -791,6 +861,7 @@ int yupvq_quantize_blocks_hdr(yupvq_ctx* ctx, const float* float_blocks, size_t 
     Scope scope(ctx->device);
     init_stats(stats);
     ctx->launches = 0;
+    ctx->tc_feat = nullptr;
     if (n_blocks == 0) return 0;  // :631
     if (channels < 1 || channels > 4) return ctx->fail("channels must be 1..4");
     Timer tm(ctx);
@@ -913,11 +984,11 @@ int yupvq_gather_tiles(yupvq_ctx* ctx, const float* image, uint32_t width, uint3
 
 int yupvq_assign(yupvq_ctx* ctx, const float* features, size_t n_blocks, const float* centroids, uint32_t codebook_size,
                  int assign_mode, uint32_t* out_indices, float* out_errors, yupvq_stats* stats) {
-    (void)assign_mode;
     if (!ctx) return 1;
     Scope scope(ctx->device);
     init_stats(stats);
     ctx->launches = 0;
+    ctx->tc_feat = nullptr;
     if (n_blocks == 0) return 0;
     const void* f_dev = nullptr;
     const void* c_dev = nullptr;
@@ -927,8 +998,9 @@ int yupvq_assign(yupvq_ctx* ctx, const float* features, size_t n_blocks, const f
     CK(ctx->errors.ensure(n_blocks * 4));
     Timer tm(ctx);
     const int t0 = tm.mark();
-    LAUNCH(launch_assign_exact(reinterpret_cast<const float*>(f_dev), n_blocks, reinterpret_cast<const float*>(c_dev),
-                               codebook_size, ctx->out_idx.as<uint32_t>(), ctx->errors.as<float>(), nullptr, ctx->stream));
+    if (assign_blocks(ctx, reinterpret_cast<const float*>(f_dev), n_blocks, reinterpret_cast<const float*>(c_dev), codebook_size,
+                      assign_mode, ctx->out_idx.as<uint32_t>(), out_errors ? ctx->errors.as<float>() : nullptr, nullptr))
+        return 1;
     const int t1 = tm.mark();
     if (from_device(ctx, out_indices, ctx->out_idx.p, n_blocks * 4)) return 1;
     if (from_device(ctx, out_errors, ctx->errors.p, n_blocks * 4)) return 1;
@@ -947,6 +1019,7 @@ int yupvq_seed_ldr(yupvq_ctx* ctx, const uint8_t* pixel_blocks, size_t n_blocks,
     if (!ctx) return 1;
     Scope scope(ctx->device);
     ctx->launches = 0;
+    ctx->tc_feat = nullptr;
     if (channels < 1 || channels > 4) return ctx->fail("channels must be 1..4");
     if (n_blocks == 0 || codebook_size == 0) return ctx->fail("empty input");
     const void* px_dev = nullptr;
@@ -974,6 +1047,7 @@ int yupvq_seed_hdr(yupvq_ctx* ctx, const float* features, size_t n_blocks, uint3
     if (!ctx) return 1;
     Scope scope(ctx->device);
     ctx->launches = 0;
+    ctx->tc_feat = nullptr;
     if (n_blocks == 0 || codebook_size == 0) return ctx->fail("empty input");
     const void* f_dev = nullptr;
     if (to_device(ctx, features, n_blocks * 256, ctx->feat, &f_dev)) return 1;
@@ -996,6 +1070,7 @@ int yupvq_update_centroids(yupvq_ctx* ctx, const float* features, size_t n_block
     if (!ctx) return 1;
     Scope scope(ctx->device);
     ctx->launches = 0;
+    ctx->tc_feat = nullptr;
     const uint32_t K = codebook_size;
     if (n_blocks == 0 || K == 0) return ctx->fail("empty input");
     const void* f_dev = nullptr;
@@ -1048,6 +1123,7 @@ int yupvq_gather_codebook(yupvq_ctx* ctx, const uint8_t* codebook, uint32_t n_en
     if (!ctx) return 1;
     Scope scope(ctx->device);
     ctx->launches = 0;
+    ctx->tc_feat = nullptr;
     if (block_size != 8 && block_size != 16) return ctx->fail("block_size must be 8 or 16");
     if (n_blocks == 0) return 0;
     const void* cb_dev = nullptr;
@@ -1096,6 +1172,7 @@ int yupvq_encode_bcn_sharded(yupvq_ctx* ctx, const uint8_t* bc_blocks, size_t n_
     Scope scope(ctx->device);
     init_stats(stats);
     ctx->launches = 0;
+    ctx->tc_feat = nullptr;
     if (check_cfg(ctx, cfg, n_total, channels)) return 1;
     if (!bc_supported(bc_format)) return ctx->fail("BC format %d is not supported on the LDR VQ path", bc_format);
     if (first_block + n_local > n_total) return ctx->fail("shard [%zu, %zu) exceeds %zu blocks", first_block, first_block + n_local, n_total);

@@ -1,0 +1,633 @@
+// K3 (tensor engine): nearest-centroid assignment as a dense N x K x 64 contraction on the tcgen05
+// tensor cores, followed by an exact fp32 re-rank so the argmin is the reference's argmin.
+// Reference: the loops of src/vq_encoder.cpp:330-340, :462-471, :561-571, :643-656 over
+// OklabBlockDistanceSq_SIMD (:212-237).
+//
+//   d(x, c) = sum_i (w_i (x_i - c_i))^2 = |x'|^2 - 2 x'.c' + |c'|^2,   x' = w (x - mu), c' = w (c - mu)
+//
+// (w = [2,1,1,1] per pixel, mu = the texture's mean feature vector: distances are translation
+// invariant and centring removes ~1.5 decimal digits of cancellation).  For a
+// fixed block only  s(c) = x'.c' - |c'|^2 / 2  matters (argmin d == argmax s).  The front-end
+// computes s for all K centroids with kind::tf32 MMAs:
+//   A  = rna_tf32(x')             128 blocks  x 64 (+8)   TMA, 128B swizzle, 2-stage ring
+//   B  = rna_tf32(c')             256 centroids x 64 (+8) TMA, resident in smem when K <= 512
+//   the 9th K-step multiplies a column of ones in A by a three-term tf32 split of -|c'|^2/2 in B,
+//   so the norm is folded into the accumulator exactly (to 2^-33) and the epilogue has no FFMA.
+//   D  = 128 lanes x 256 columns fp32 in TMEM, two accumulator stages (512 columns).
+// The epilogue (8 warps, one TMEM lane == one block per thread) makes two passes over each
+// accumulator stage: max3 reduction, then a sign-bit sweep that collects every centroid whose score
+// is within a proven error margin of the running maximum.  Blocks end up with a short candidate list
+// (uint16 x 7 + count in one uint4); rerank_kernel evaluates those candidates with the reference's
+// exact operation order (common.cuh DistAcc) and resolves ties to the lowest index.
+//
+// Error margin: inputs are rounded to nearest tf32 (u = 2^-11), so
+//   |x'.c' - mma| <= (2u + u^2) |x'||c'| + accumulation  <=  kDotErr * |x'| * Cmax
+// with Cmax = max_c |c'|.  A centroid can only be the reference argmin if
+//   s(c) >= s_max - (2 * E + reference-rounding slack).
+// The list is therefore a superset of the possible winners; an empty or overflowing list falls back
+// to a full exact scan of that block inside rerank_kernel (flat textures, NaNs).
+//
+// Roofline: tensor pipe (2 * N * K * 72 FLOP per pass at the tf32 rate) against an epilogue that is
+// ALU-issue bound (about 4 issue slots per block-centroid pair); HBM traffic is 256 B per block.
+#include <cfloat>
+#include <cuda.h>
+
+#include "common.cuh"
+#include "kernels.h"
+
+namespace yupvq {
+
+namespace {
+
+constexpr int BM = 128;            // blocks per tile (MMA M, TMEM lanes)
+constexpr int BN = 256;            // centroids per chunk (MMA N, TMEM columns per accumulator stage)
+constexpr int kEpiWarps = 8;       // epilogue warps: 4 TMEM lane quadrants x 2 column halves
+constexpr int kThreadsTc = (2 + kEpiWarps) * 32;
+constexpr int kMaxCand = 7;
+
+constexpr uint32_t A_HALF_BYTES = BM * 128;        // 128 rows x 32 floats
+constexpr uint32_t A_STAGE_BYTES = 2 * A_HALF_BYTES;
+constexpr uint32_t B_HALF_BYTES = BN * 128;
+constexpr uint32_t BX_BYTES = BN * 32;             // 256 rows x 8 floats (32B swizzle)
+constexpr uint32_t B_STAGE_BYTES = 2 * B_HALF_BYTES + BX_BYTES;
+constexpr uint32_t ONES_BYTES = BM * 32;
+
+// dynamic shared memory map (offsets from a 1024-byte aligned base)
+constexpr uint32_t OFF_A = 0;
+constexpr uint32_t OFF_B = OFF_A + 2 * A_STAGE_BYTES;
+constexpr uint32_t OFF_ONES = OFF_B + 2 * B_STAGE_BYTES;
+constexpr uint32_t OFF_LIST = OFF_ONES + ONES_BYTES;                 // u16 [256][8]
+constexpr uint32_t OFF_MAX = OFF_LIST + 256 * 8 * 2;                 // float [2 parity][2 half][128]
+constexpr uint32_t OFF_CNT = OFF_MAX + 2 * 2 * 128 * 4;              // u32 [128] (column-half 1 counts)
+constexpr uint32_t OFF_BAR = OFF_CNT + 128 * 4;                      // 12 mbarriers + tmem ptr
+constexpr uint32_t SMEM_TC = OFF_BAR + 16 * 8 + 1024 /* alignment slack */;
+
+enum { BAR_FULL_A = 0, BAR_EMPTY_A = 2, BAR_FULL_B = 4, BAR_EMPTY_B = 6, BAR_TFULL = 8, BAR_TEMPTY = 10, BAR_COUNT = 12 };
+
+// error model constants (see header comment)
+constexpr float kDotErr = 0.0009765625f * 1.0625f + 0.0000152587890625f * 2.0f;  // 2^-10 * 1.0625 + 2^-15
+constexpr float kRefRel = 0.000030517578125f;                                     // 2^-15
+
+// ---- PTX wrappers ----------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done;
+    do {
+        asm volatile(
+            "{\n\t"
+            ".reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t"
+            "}\n"
+            : "=r"(done)
+            : "r"(bar), "r"(parity)
+            : "memory");
+    } while (!done);
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
+        "l"(map), "r"(bar), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_mma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+        "}\n" ::"r"(tmem_d),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void tc_ld64(uint32_t taddr, uint32_t (&v)[64]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x64.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, "
+        "%32, %33, %34, %35, %36, %37, %38, %39, %40, %41, %42, %43, %44, %45, %46, %47, "
+        "%48, %49, %50, %51, %52, %53, %54, %55, %56, %57, %58, %59, %60, %61, %62, %63}, [%64];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+          "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+          "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31]), "=r"(v[32]),
+          "=r"(v[33]), "=r"(v[34]), "=r"(v[35]), "=r"(v[36]), "=r"(v[37]), "=r"(v[38]), "=r"(v[39]), "=r"(v[40]),
+          "=r"(v[41]), "=r"(v[42]), "=r"(v[43]), "=r"(v[44]), "=r"(v[45]), "=r"(v[46]), "=r"(v[47]), "=r"(v[48]),
+          "=r"(v[49]), "=r"(v[50]), "=r"(v[51]), "=r"(v[52]), "=r"(v[53]), "=r"(v[54]), "=r"(v[55]), "=r"(v[56]),
+          "=r"(v[57]), "=r"(v[58]), "=r"(v[59]), "=r"(v[60]), "=r"(v[61]), "=r"(v[62]), "=r"(v[63])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ float fmax3(float a, float b, float c) {
+    float d;
+    asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+    return d;
+}
+__device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, %0;" ::"n"(kEpiWarps * 32) : "memory"); }
+
+// K-major shared-memory matrix descriptor (cute::UMMA::SmemDescriptor, version 1 == Blackwell).
+// layout: 2 = 128B swizzle (rows of 128 B, 8-row atoms 1024 B apart), 6 = 32B swizzle (rows of 32 B,
+// 8-row atoms 256 B apart).  LBO is unused for swizzled K-major operands.
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t sbo_bytes, uint32_t layout) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr & 0x3ffffu) >> 4);
+    d |= (uint64_t)1 << 16;                          // leading byte offset (ignored)
+    d |= (uint64_t)((sbo_bytes >> 4) & 0x3fffu) << 32;
+    d |= (uint64_t)1 << 46;                          // descriptor version
+    d |= (uint64_t)layout << 61;
+    return d;
+}
+
+// kind::tf32, D = f32, A/B = tf32, both K-major, M = 128, N = 256 (cute::UMMA::InstrDescriptor)
+constexpr uint32_t kIdesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+
+// ---- the front-end kernel -----------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreadsTc, 1)
+assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
+                 const __grid_constant__ CUtensorMap tm_bx, const float* __restrict__ xnorm,
+                 const float* __restrict__ cmax_ptr, uint32_t n, uint32_t num_tiles, uint32_t num_chunks,
+                 uint32_t resident_b, uint4* __restrict__ cand) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    uint8_t* base_ptr = smem_raw + (base - smem_u32(smem_raw));
+    const uint32_t bar0 = base + OFF_BAR;
+    auto bar = [&](int i) { return bar0 + 8u * (uint32_t)i; };
+    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(base_ptr + OFF_BAR + BAR_COUNT * 8);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (warp == 0 && lane == 0) {
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(bar(BAR_FULL_A + i), 1);
+            mbar_init(bar(BAR_EMPTY_A + i), 1);
+            mbar_init(bar(BAR_FULL_B + i), 1);
+            mbar_init(bar(BAR_EMPTY_B + i), 1);
+            mbar_init(bar(BAR_TFULL + i), 1);
+            mbar_init(bar(BAR_TEMPTY + i), kEpiWarps);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {  // TMEM: all 512 columns (two 256-column accumulator stages)
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32((const void*)tmem_slot)),
+                     "r"(512u)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    // the column of ones that multiplies the folded norm terms (layout-invariant: every element is 1)
+    for (uint32_t i = threadIdx.x; i < ONES_BYTES / 4; i += kThreadsTc) reinterpret_cast<float*>(base_ptr + OFF_ONES)[i] = 1.0f;
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== TMA producer ==============================================================================
+        if (lane == 0) {
+            if (resident_b) {
+                for (uint32_t j = 0; j < num_chunks; ++j) {
+                    const uint32_t dst = base + OFF_B + j * B_STAGE_BYTES;
+                    mbar_expect_tx(bar(BAR_FULL_B + j), B_STAGE_BYTES);
+                    tma_load_2d(dst, &tm_b, 0, (int)(j * BN), bar(BAR_FULL_B + j));
+                    tma_load_2d(dst + B_HALF_BYTES, &tm_b, 32, (int)(j * BN), bar(BAR_FULL_B + j));
+                    tma_load_2d(dst + 2 * B_HALF_BYTES, &tm_bx, 0, (int)(j * BN), bar(BAR_FULL_B + j));
+                }
+            }
+            uint32_t it = 0, u = 0;
+            for (uint32_t t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
+                const uint32_t sa = it & 1, pa = (it >> 1) & 1;
+                mbar_wait(bar(BAR_EMPTY_A + sa), pa ^ 1);
+                const uint32_t dst = base + OFF_A + sa * A_STAGE_BYTES;
+                mbar_expect_tx(bar(BAR_FULL_A + sa), A_STAGE_BYTES);
+                tma_load_2d(dst, &tm_a, 0, (int)(t * BM), bar(BAR_FULL_A + sa));
+                tma_load_2d(dst + A_HALF_BYTES, &tm_a, 32, (int)(t * BM), bar(BAR_FULL_A + sa));
+                if (!resident_b) {
+                    for (uint32_t j = 0; j < num_chunks; ++j, ++u) {
+                        const uint32_t sb = u & 1, pb = (u >> 1) & 1;
+                        mbar_wait(bar(BAR_EMPTY_B + sb), pb ^ 1);
+                        const uint32_t dstb = base + OFF_B + sb * B_STAGE_BYTES;
+                        mbar_expect_tx(bar(BAR_FULL_B + sb), B_STAGE_BYTES);
+                        tma_load_2d(dstb, &tm_b, 0, (int)(j * BN), bar(BAR_FULL_B + sb));
+                        tma_load_2d(dstb + B_HALF_BYTES, &tm_b, 32, (int)(j * BN), bar(BAR_FULL_B + sb));
+                        tma_load_2d(dstb + 2 * B_HALF_BYTES, &tm_bx, 0, (int)(j * BN), bar(BAR_FULL_B + sb));
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer (one thread) ===================================================================
+        if (lane == 0) {
+            uint32_t it = 0, u = 0;
+            const uint64_t ones_desc = make_desc(base + OFF_ONES, 256, 6);
+            for (uint32_t t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
+                const uint32_t sa = it & 1, pa = (it >> 1) & 1;
+                mbar_wait(bar(BAR_FULL_A + sa), pa);
+                const uint32_t a_addr = base + OFF_A + sa * A_STAGE_BYTES;
+                for (uint32_t j = 0; j < num_chunks; ++j, ++u) {
+                    const uint32_t acc = u & 1, pacc = (u >> 1) & 1;
+                    mbar_wait(bar(BAR_TEMPTY + acc), pacc ^ 1);
+                    uint32_t sb;
+                    if (resident_b) {
+                        sb = j;
+                        if (it == 0) mbar_wait(bar(BAR_FULL_B + sb), 0);
+                    } else {
+                        sb = u & 1;
+                        mbar_wait(bar(BAR_FULL_B + sb), (u >> 1) & 1);
+                    }
+                    tc_fence_after();
+                    const uint32_t b_addr = base + OFF_B + sb * B_STAGE_BYTES;
+                    const uint32_t d_tmem = tmem_base + acc * BN;
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) {
+                        const uint32_t koff = (uint32_t)(k >> 2) * A_HALF_BYTES + (uint32_t)(k & 3) * 32u;
+                        const uint32_t boff = (uint32_t)(k >> 2) * B_HALF_BYTES + (uint32_t)(k & 3) * 32u;
+                        tc_mma_tf32(d_tmem, make_desc(a_addr + koff, 1024, 2), make_desc(b_addr + boff, 1024, 2), kIdesc,
+                                    k > 0 ? 1u : 0u);
+                    }
+                    tc_mma_tf32(d_tmem, ones_desc, make_desc(b_addr + 2 * B_HALF_BYTES, 256, 6), kIdesc, 1u);
+                    tc_commit(bar(BAR_TFULL + acc));
+                    if (!resident_b) tc_commit(bar(BAR_EMPTY_B + sb));
+                }
+                tc_commit(bar(BAR_EMPTY_A + sa));
+            }
+        }
+    } else {
+        // ===== epilogue: 8 warps, thread == (TMEM lane, column half) ====================================
+        const int ew = warp - 2;
+        const int quad = warp & 3;          // TMEM lane quadrant this warp may access
+        const int half = ew >> 2;           // which 128 of the stage's 256 columns
+        const int r = quad * 32 + lane;     // row inside the tile
+        const int etid = half * 128 + r;
+        uint16_t* my_list = reinterpret_cast<uint16_t*>(base_ptr + OFF_LIST) + etid * 8;
+        const uint16_t* other_list = reinterpret_cast<const uint16_t*>(base_ptr + OFF_LIST) + (128 + r) * 8;
+        float* s_max = reinterpret_cast<float*>(base_ptr + OFF_MAX);
+        uint32_t* s_cnt = reinterpret_cast<uint32_t*>(base_ptr + OFF_CNT);
+        const float cmax = __ldg(cmax_ptr);
+        const uint32_t lane_taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)half * 128u;
+        uint32_t u = 0;
+        for (uint32_t t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+            const size_t row = (size_t)t * BM + r;
+            const float xn = row < n ? __ldg(xnorm + row) : 0.0f;
+            const float e_dot = kDotErr * xn * cmax;
+            float m_run = -INFINITY;
+            uint32_t cnt = 0;
+            bool bad = false;
+            for (uint32_t j = 0; j < num_chunks; ++j, ++u) {
+                const uint32_t acc = u & 1, pacc = (u >> 1) & 1;
+                mbar_wait(bar(BAR_TFULL + acc), pacc);
+                tc_fence_after();
+                const uint32_t taddr = lane_taddr + acc * BN;
+                uint32_t v[64];
+                // ---- pass 1: maximum score over this thread's 128 columns
+                float m0 = -INFINITY, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
+#pragma unroll
+                for (int q = 0; q < 2; ++q) {
+                    tc_ld64(taddr + q * 64, v);
+                    tc_wait_ld();
+#pragma unroll
+                    for (int i = 0; i < 64; i += 8) {
+                        m0 = fmax3(m0, __uint_as_float(v[i]), __uint_as_float(v[i + 1]));
+                        m1 = fmax3(m1, __uint_as_float(v[i + 2]), __uint_as_float(v[i + 3]));
+                        m2 = fmax3(m2, __uint_as_float(v[i + 4]), __uint_as_float(v[i + 5]));
+                        m3 = fmax3(m3, __uint_as_float(v[i + 6]), __uint_as_float(v[i + 7]));
+                    }
+                }
+                float* sm = s_max + (u & 1) * 256;
+                sm[half * 128 + r] = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
+                epi_bar();
+                m_run = fmax3(m_run, sm[r], sm[128 + r]);
+                // every centroid that could still be the reference argmin has score >= thr
+                const float d_up = fmaxf(xn * xn - 2.0f * m_run + 2.0f * e_dot, 0.0f);
+                const float margin = 2.0f * e_dot + kRefRel * d_up;
+                // NaN / Inf anywhere (or only padding columns): no proof possible, take the exact scan
+                if (!(m_run > -1.0e29f) || !(margin < 1.0e30f)) bad = true;
+                float thr = m_run - margin;
+                thr = __uint_as_float(__float_as_uint(thr) + (thr > 0.0f ? -1 : (thr < 0.0f ? 1 : 0)));  // one ulp down
+                if (thr == 0.0f) thr = -FLT_MIN;
+                // ---- pass 2: sign-bit sweep, candidates are the columns with (thr - s) < 0
+#pragma unroll
+                for (int q = 0; q < 2; ++q) {
+                    tc_ld64(taddr + q * 64, v);
+                    tc_wait_ld();
+#pragma unroll
+                    for (int g = 0; g < 2; ++g) {
+                        uint32_t mask = 0;
+#pragma unroll
+                        for (int i = 0; i < 32; ++i)
+                            mask = __funnelshift_l(__float_as_uint(thr - __uint_as_float(v[g * 32 + i])), mask, 1);
+                        while (mask) {
+                            const int b = __clz(mask);
+                            mask &= ~(0x80000000u >> b);
+                            if (cnt < 8) my_list[cnt] = (uint16_t)(j * BN + half * 128 + q * 64 + g * 32 + b);
+                            ++cnt;
+                        }
+                    }
+                }
+                // release the accumulator stage to the MMA warp
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar(BAR_TEMPTY + acc));
+            }
+            // ---- merge the two column halves and publish the candidate list
+            if (bad) cnt = 100;
+            if (half == 1) s_cnt[r] = cnt;
+            epi_bar();
+            if (half == 0 && row < n) {
+                const uint32_t c1 = s_cnt[r];
+                uint32_t w[4] = {0, 0, 0, 0};
+                const uint32_t total = cnt + c1;
+                if (total >= 1 && total <= (uint32_t)kMaxCand) {
+                    for (uint32_t i = 0; i < total; ++i) {
+                        const uint32_t c = i < cnt ? my_list[i] : other_list[i - cnt];
+                        w[i >> 1] |= c << (16 * (i & 1));
+                    }
+                    w[3] |= total << 16;
+                } else {
+                    w[3] = 0xffffu << 16;  // empty (NaN) or overflow: full exact scan in the re-rank
+                }
+                cand[row] = make_uint4(w[0], w[1], w[2], w[3]);
+            }
+            epi_bar();  // lists / counts are reused by the next tile
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+    }
+}
+
+// ---- operand preparation ------------------------------------------------------------------------------
+__device__ __forceinline__ float to_tf32(float x) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+    return __uint_as_float(r);
+}
+
+// column sums of the N x 64 feature matrix (fp64, atomics: mu only steers the error margin, it never
+// changes a result, so its last bits need not be reproducible)
+__global__ void __launch_bounds__(256) col_sums_kernel(const float* __restrict__ feat, size_t n, double* __restrict__ sums) {
+    __shared__ double red[4][64];
+    const int col = threadIdx.x & 63, sub = threadIdx.x >> 6;
+    double acc = 0.0;
+    for (size_t i = (size_t)blockIdx.x * 4 + sub; i < n; i += (size_t)gridDim.x * 4) acc += (double)feat[i * 64 + col];
+    red[sub][col] = acc;
+    __syncthreads();
+    if (sub == 0) atomicAdd(sums + col, red[0][col] + red[1][col] + red[2][col] + red[3][col]);
+}
+
+__global__ void mean_kernel(const double* __restrict__ sums, double inv_n, float* __restrict__ mu) {
+    const float m = (float)(sums[threadIdx.x] * inv_n);
+    mu[threadIdx.x] = isfinite(m) ? m : 0.0f;
+}
+
+// A' = rna_tf32(w (x - mu)),  xnorm = |w (x - mu)| (rounded up a little)
+__global__ void __launch_bounds__(256) prep_blocks_kernel(const float* __restrict__ feat, size_t n, const float* __restrict__ mu,
+                                                          float* __restrict__ a_prime, float* __restrict__ xnorm) {
+    const size_t row = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 4;   // 16 threads per row
+    const int q = threadIdx.x & 15;                                            // pixel == float4 index
+    float ss = 0.0f;
+    if (row < n) {
+        const float4 x = ldg_nc_f4(reinterpret_cast<const float4*>(feat) + row * 16 + q);
+        const float4 m = reinterpret_cast<const float4*>(mu)[q];
+        float4 o;
+        o.x = 2.0f * (x.x - m.x);
+        o.y = x.y - m.y;
+        o.z = x.z - m.z;
+        o.w = x.w - m.w;
+        ss = o.x * o.x + o.y * o.y + o.z * o.z + o.w * o.w;
+        o.x = to_tf32(o.x);
+        o.y = to_tf32(o.y);
+        o.z = to_tf32(o.z);
+        o.w = to_tf32(o.w);
+        reinterpret_cast<float4*>(a_prime)[row * 16 + q] = o;
+    }
+#pragma unroll
+    for (int o = 8; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+    if (row < n && q == 0) xnorm[row] = sqrtf(ss) * 1.0001f;
+}
+
+// B' = rna_tf32(w (c - mu)); the ext columns hold a three-term tf32 split of -|c'|^2 / 2;
+// rows K..K_pad-1 are padding that can never win (score -1e30).  cmax = max_c |c'| (rounded up).
+__global__ void __launch_bounds__(64) prep_centroids_kernel(const float* __restrict__ cent, uint32_t K, const float* __restrict__ mu,
+                                                            float* __restrict__ b_main, float* __restrict__ b_ext,
+                                                            unsigned int* __restrict__ cmax_bits) {
+    const uint32_t c = blockIdx.x;
+    const int i = threadIdx.x;
+    float v = 0.0f;
+    if (c < K) {
+        const float w = (i & 3) == 0 ? 2.0f : 1.0f;
+        v = w * (cent[(size_t)c * 64 + i] - mu[i]);
+        if (!isfinite(v)) v = 0.0f;  // a non-finite centroid is handled by the exact scan (its blocks overflow)
+    }
+    b_main[(size_t)c * 64 + i] = to_tf32(v);
+    __shared__ double red[2];
+    double ss = (double)v * (double)v;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+    if ((i & 31) == 0) red[i >> 5] = ss;
+    __syncthreads();
+    if (i < 8) {
+        float e = 0.0f;
+        if (c < K) {
+            const double nh = -0.5 * (red[0] + red[1]);
+            const float hi = to_tf32((float)nh);
+            const float mid = to_tf32((float)(nh - (double)hi));
+            const float lo = to_tf32((float)(nh - (double)hi - (double)mid));
+            e = i == 0 ? hi : (i == 1 ? mid : (i == 2 ? lo : 0.0f));
+        } else if (i == 0) {
+            e = -1.0e30f;
+        }
+        b_ext[(size_t)c * 8 + i] = e;
+    }
+    if (i == 0 && c < K) {
+        const float nrm = (float)sqrt(red[0] + red[1]) * 1.0001f;
+        atomicMax(cmax_bits, __float_as_uint(nrm));  // non-negative floats order like their bit patterns
+    }
+}
+
+// ---- exact re-rank ---------------------------------------------------------------------------------------
+constexpr int kTile = 128;
+constexpr int kPitch4 = 17;
+
+__global__ void __launch_bounds__(kTile) rerank_kernel(const float* __restrict__ feat, size_t n, const float* __restrict__ cent,
+                                                       uint32_t K, const uint4* __restrict__ cand, uint32_t* __restrict__ assign,
+                                                       float* __restrict__ errors, uint32_t* __restrict__ flags,
+                                                       unsigned int* __restrict__ stat_pairs) {
+    __shared__ float4 xs[kTile * kPitch4];
+    const size_t tile_first = (size_t)blockIdx.x * kTile;
+    const size_t rows = (n - tile_first) < (size_t)kTile ? (n - tile_first) : (size_t)kTile;
+    const bool valid = threadIdx.x < rows;
+    const size_t blk = tile_first + threadIdx.x;
+    uint4 cw = make_uint4(0, 0, 0, 1u << 16);
+    if (valid) cw = cand[blk];
+    const uint32_t cnt = cw.w >> 16;
+    const bool need_x = valid && (cnt != 1 || errors != nullptr);
+    if (__syncthreads_or(need_x)) {
+        const float4* src = reinterpret_cast<const float4*>(feat) + tile_first * 16;
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+            const int idx = threadIdx.x + kTile * k;
+            const int row = idx >> 4, col = idx & 15;
+            if ((size_t)row < rows) xs[row * kPitch4 + col] = ldg_nc_f4(src + idx);
+        }
+        __syncthreads();
+    }
+    uint32_t pairs = 0;
+    if (valid) {
+        uint32_t best_c = cw.x & 0xffffu;
+        float best = 0.0f;
+        if (need_x) {
+            float4 x[16];
+#pragma unroll
+            for (int k = 0; k < 16; ++k) x[k] = xs[threadIdx.x * kPitch4 + k];
+            best = FLT_MAX;
+            best_c = 0;
+            if (cnt == 0xffffu) {  // full exact scan (reference order: strict '<', ascending c)
+                for (uint32_t c = 0; c < K; ++c) {
+                    const float d = oklab_dist_reg(x, reinterpret_cast<const float4*>(cent) + (size_t)c * 16);
+                    if (d < best) {
+                        best = d;
+                        best_c = c;
+                    }
+                }
+                pairs = K;
+            } else {
+                const uint32_t words[4] = {cw.x, cw.y, cw.z, cw.w};
+                bool first = true;
+                for (uint32_t i = 0; i < cnt; ++i) {
+                    const uint32_t c = (words[i >> 1] >> (16 * (i & 1))) & 0xffffu;
+                    const float d = oklab_dist_reg(x, reinterpret_cast<const float4*>(cent) + (size_t)c * 16);
+                    // the reference scans c ascending with strict '<' from FLT_MAX: smallest distance, lowest index
+                    if (d < FLT_MAX && (first || d < best || (d == best && c < best_c))) {
+                        best = d;
+                        best_c = c;
+                        first = false;
+                    }
+                }
+                pairs = cnt > 1 ? cnt : 0;
+            }
+        }
+        if (flags && assign[blk] != best_c) flags[0] = 1u;
+        assign[blk] = best_c;
+        if (errors) errors[blk] = best;
+    }
+    if (stat_pairs) {
+        pairs = __reduce_add_sync(0xffffffffu, pairs);
+        if ((threadIdx.x & 31) == 0 && pairs) atomicAdd(stat_pairs, pairs);
+    }
+}
+
+// ---- host side -------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    return fn;
+}
+
+bool make_map(CUtensorMap* m, const float* ptr, uint64_t cols, uint64_t rows, uint32_t box_cols, uint32_t box_rows,
+              CUtensorMapSwizzle sw) {
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) return false;
+    const cuuint64_t dims[2] = {cols, rows};
+    const cuuint64_t strides[1] = {cols * sizeof(float)};
+    const cuuint32_t box[2] = {box_cols, box_rows};
+    const cuuint32_t estr[2] = {1, 1};
+    return fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(ptr), dims, strides, box, estr,
+              CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+}  // namespace
+
+uint32_t tc_padded_k(uint32_t K) { return (K + BN - 1) / BN * BN; }
+
+bool tc_supported(uint32_t K) { return K >= 1 && K <= 65535 && encode_fn() != nullptr; }
+
+cudaError_t launch_tc_mean(const float* feat, size_t n, double* sums64, float* mu, cudaStream_t s) {
+    cudaError_t e = cudaMemsetAsync(sums64, 0, 64 * sizeof(double), s);
+    if (e != cudaSuccess) return e;
+    if (n > 0) {
+        size_t blocks = (n + 3) / 4;
+        if (blocks > (size_t)YUPVQ_NUM_SMS * 8) blocks = (size_t)YUPVQ_NUM_SMS * 8;
+        col_sums_kernel<<<(unsigned)blocks, 256, 0, s>>>(feat, n, sums64);
+    }
+    mean_kernel<<<1, 64, 0, s>>>(sums64, n ? 1.0 / (double)n : 0.0, mu);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_tc_prep_blocks(const float* feat, size_t n, const float* mu, float* a_prime, float* xnorm, cudaStream_t s) {
+    if (n == 0) return cudaSuccess;
+    prep_blocks_kernel<<<(unsigned)((n * 16 + 255) / 256), 256, 0, s>>>(feat, n, mu, a_prime, xnorm);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_tc_prep_centroids(const float* cent, uint32_t K, const float* mu, float* b_main, float* b_ext,
+                                     float* cmax, cudaStream_t s) {
+    cudaError_t e = cudaMemsetAsync(cmax, 0, 4, s);
+    if (e != cudaSuccess) return e;
+    prep_centroids_kernel<<<tc_padded_k(K), 64, 0, s>>>(cent, K, mu, b_main, b_ext, reinterpret_cast<unsigned int*>(cmax));
+    return cudaGetLastError();
+}
+
+cudaError_t launch_assign_tc(const float* a_prime, const float* xnorm, size_t n, const float* b_main, const float* b_ext,
+                             uint32_t K, const float* cmax, uint4* cand, cudaStream_t s) {
+    if (n == 0) return cudaSuccess;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(assign_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_TC);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    const uint32_t k_pad = tc_padded_k(K);
+    CUtensorMap tm_a, tm_b, tm_bx;
+    if (!make_map(&tm_a, a_prime, 64, n, 32, BM, CU_TENSOR_MAP_SWIZZLE_128B) ||
+        !make_map(&tm_b, b_main, 64, k_pad, 32, BN, CU_TENSOR_MAP_SWIZZLE_128B) ||
+        !make_map(&tm_bx, b_ext, 8, k_pad, 8, BN, CU_TENSOR_MAP_SWIZZLE_32B))
+        return cudaErrorInvalidValue;
+    const uint32_t num_tiles = (uint32_t)((n + BM - 1) / BM);
+    const uint32_t num_chunks = k_pad / BN;
+    const uint32_t grid = num_tiles < (uint32_t)YUPVQ_NUM_SMS ? num_tiles : (uint32_t)YUPVQ_NUM_SMS;
+    assign_tc_kernel<<<grid, kThreadsTc, SMEM_TC, s>>>(tm_a, tm_b, tm_bx, xnorm, cmax, (uint32_t)n, num_tiles, num_chunks,
+                                                      num_chunks <= 2 ? 1u : 0u, cand);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_rerank(const float* feat, size_t n, const float* cent, uint32_t K, const uint4* cand, uint32_t* assign,
+                          float* errors, uint32_t* flags, unsigned int* stat_pairs, cudaStream_t s) {
+    if (n == 0) return cudaSuccess;
+    rerank_kernel<<<(unsigned)((n + kTile - 1) / kTile), kTile, 0, s>>>(feat, n, cent, K, cand, assign, errors, flags,
+                                                                        stat_pairs);
+    return cudaGetLastError();
+}
+
+}  // namespace yupvq

@@ -55,6 +55,23 @@ cudaError_t launch_assign_exact(const float* feat, size_t n, const float* cent, 
 cudaError_t launch_exact_errors(const float* feat, size_t n, const float* cent, const uint32_t* assign, float* errors,
                                 cudaStream_t s);
 
+// ---- assign_tc.cu : K3, tensor engine (tcgen05 front-end + exact re-rank) ------------------------------
+// Per block set (once):  mu = column means, A' = rna_tf32(w (x - mu)), xnorm = |w (x - mu)|.
+// Per pass: B' / folded norms / cmax from the current centroids, the MMA front-end writes one uint4
+// candidate list per block (7 x uint16 + count; count 0xffff = full exact scan), the re-rank turns
+// the lists into assignments with the reference's exact arithmetic.
+bool tc_supported(uint32_t K);
+uint32_t tc_padded_k(uint32_t K);  // rows of b_main / b_ext
+cudaError_t launch_tc_mean(const float* feat, size_t n, double* sums64, float* mu, cudaStream_t s);
+cudaError_t launch_tc_prep_blocks(const float* feat, size_t n, const float* mu, float* a_prime, float* xnorm,
+                                  cudaStream_t s);
+cudaError_t launch_tc_prep_centroids(const float* cent, uint32_t K, const float* mu, float* b_main, float* b_ext,
+                                     float* cmax, cudaStream_t s);
+cudaError_t launch_assign_tc(const float* a_prime, const float* xnorm, size_t n, const float* b_main,
+                             const float* b_ext, uint32_t K, const float* cmax, uint4* cand, cudaStream_t s);
+cudaError_t launch_rerank(const float* feat, size_t n, const float* cent, uint32_t K, const uint4* cand,
+                          uint32_t* assign, float* errors, uint32_t* flags, unsigned int* stat_pairs, cudaStream_t s);
+
 // ---- update.cu : K4 / K5 -----------------------------------------------------------------------------
 // Accumulator layout (int64 words): [K*64 sums | K counts | 1 changed flag].  Sums are 64-bit fixed
 // point (value * 2^shift): associative, therefore order / CTA / GPU-count independent; the whole
@@ -65,6 +82,7 @@ cudaError_t launch_accumulate(const float* feat, size_t n, const uint32_t* assig
 // centroid = float(sum) * (1.0f / count) (reference src/vq_encoder.cpp:366-368); flags[1] = #empty clusters
 cudaError_t launch_finalize_centroids(const long long* acc, uint32_t K, int shift, float* cent, uint32_t* flags,
                                       cudaStream_t s);
+cudaError_t launch_count_empty(const long long* acc, uint32_t K, uint32_t* out, cudaStream_t s);
 // serial-semantics reseed of empty clusters (ascending c, first maximum of errors, then zero it)
 cudaError_t launch_reseed_empty(const float* feat, size_t n, float* errors, const long long* acc, uint32_t K,
                                 float* cent, uint32_t* flags, cudaStream_t s);

@@ -52,6 +52,20 @@ __global__ void finalize_kernel(const long long* __restrict__ acc, uint32_t K, d
     }
 }
 
+// out[0] = number of clusters with count 0 (known before the centroids are overwritten, so the tensor
+// engine can compute errors[] only when a reseed will need them)
+__global__ void count_empty_kernel(const long long* __restrict__ acc, uint32_t K, uint32_t* __restrict__ out) {
+    __shared__ unsigned int total;
+    if (threadIdx.x == 0) total = 0;
+    __syncthreads();
+    unsigned int local = 0;
+    for (uint32_t c = threadIdx.x; c < K; c += blockDim.x) local += acc[(size_t)K * 64 + c] == 0 ? 1u : 0u;
+    local = warp_sum(local);
+    if ((threadIdx.x & 31) == 0 && local) atomicAdd(&total, local);
+    __syncthreads();
+    if (threadIdx.x == 0) *out = total;
+}
+
 // first index of the maximum of errors[0, n) -- std::max_element semantics -- computed by one CTA.
 __device__ unsigned long long cta_argmax_first(const float* errors, size_t n, float* out_val, float* s_val,
                                                unsigned long long* s_idx) {
@@ -161,6 +175,11 @@ cudaError_t launch_accumulate(const float* feat, size_t n, const uint32_t* assig
 cudaError_t launch_finalize_centroids(const long long* acc, uint32_t K, int shift, float* cent, uint32_t* flags,
                                       cudaStream_t s) {
     finalize_kernel<<<(K * 64 + 255) / 256, 256, 0, s>>>(acc, K, ldexp(1.0, -shift), cent, flags);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_count_empty(const long long* acc, uint32_t K, uint32_t* out, cudaStream_t s) {
+    count_empty_kernel<<<1, 256, 0, s>>>(acc, K, out);
     return cudaGetLastError();
 }
 
