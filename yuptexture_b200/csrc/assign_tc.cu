@@ -464,66 +464,148 @@ __global__ void __launch_bounds__(64) prep_centroids_kernel(const float* __restr
 }
 
 // ---- exact re-rank ---------------------------------------------------------------------------------------
-constexpr int kTile = 128;
-constexpr int kPitch4 = 17;
+// Work is re-distributed from "one thread per block" (divergent candidate counts, uncoalesced centroid
+// rows) to "eight lanes per (block, candidate) pair": lane l owns the reference's lane accumulator l
+// (src/vq_encoder.cpp:220-229), so a pair costs eight dependent FMAs per lane, every load is a full
+// 32-byte sector, and the horizontal add tree (:231-236) is three shuffles.  Blocks with a single
+// candidate need no arithmetic at all unless errors[] is requested.
+constexpr int kRrThreads = 256;                       // blocks per CTA == threads per CTA
+constexpr int kRrMaxPairs = kRrThreads * kMaxCand;
 
-__global__ void __launch_bounds__(kTile) rerank_kernel(const float* __restrict__ feat, size_t n, const float* __restrict__ cent,
-                                                       uint32_t K, const uint4* __restrict__ cand, uint32_t* __restrict__ assign,
-                                                       float* __restrict__ errors, uint32_t* __restrict__ flags,
-                                                       unsigned int* __restrict__ stat_pairs) {
-    __shared__ float4 xs[kTile * kPitch4];
-    const size_t tile_first = (size_t)blockIdx.x * kTile;
-    const size_t rows = (n - tile_first) < (size_t)kTile ? (n - tile_first) : (size_t)kTile;
-    const bool valid = threadIdx.x < rows;
-    const size_t blk = tile_first + threadIdx.x;
-    uint4 cw = make_uint4(0, 0, 0, 1u << 16);
-    if (valid) cw = cand[blk];
-    const uint32_t cnt = cw.w >> 16;
-    const bool need_x = valid && (cnt != 1 || errors != nullptr);
-    if (__syncthreads_or(need_x)) {
-        const float4* src = reinterpret_cast<const float4*>(feat) + tile_first * 16;
+// distance of one block to one centroid, computed by the 8 lanes of a group (all 8 get the result)
+__device__ __forceinline__ float pair_distance(const float* __restrict__ x, const float* __restrict__ c, int l) {
+    float xv[8], cv[8];
 #pragma unroll
-        for (int k = 0; k < 16; ++k) {
-            const int idx = threadIdx.x + kTile * k;
-            const int row = idx >> 4, col = idx & 15;
-            if ((size_t)row < rows) xs[row * kPitch4 + col] = ldg_nc_f4(src + idx);
-        }
-        __syncthreads();
+    for (int i = 0; i < 8; ++i) {
+        xv[i] = __ldg(x + 8 * i + l);
+        cv[i] = __ldg(c + 8 * i + l);
     }
+    const float w = (l & 3) == 0 ? 2.0f : 1.0f;
+    float acc = 0.0f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const float d = __fmul_rn(__fsub_rn(xv[i], cv[i]), w);
+        acc = __fmaf_rn(d, d, acc);
+    }
+    const float s = __fadd_rn(acc, __shfl_xor_sync(0xffffffffu, acc, 4));   // s_j = acc_j + acc_{j+4}
+    const float t = __fadd_rn(s, __shfl_xor_sync(0xffffffffu, s, 1));       // s0 + s1 | s2 + s3
+    return __fadd_rn(t, __shfl_xor_sync(0xffffffffu, t, 2));                // (s0 + s1) + (s2 + s3)
+}
+
+__global__ void __launch_bounds__(kRrThreads) rerank_kernel(const float* __restrict__ feat, size_t n, const float* __restrict__ cent,
+                                                            uint32_t K, const uint4* __restrict__ cand, uint32_t* __restrict__ assign,
+                                                            float* __restrict__ errors, uint32_t* __restrict__ flags,
+                                                            unsigned int* __restrict__ stat_pairs) {
+    __shared__ uint16_t p_blk[kRrMaxPairs];
+    __shared__ uint16_t p_c[kRrMaxPairs];
+    __shared__ float p_d[kRrMaxPairs];
+    __shared__ uint32_t warp_tot[kRrThreads / 32 + 1];
+    __shared__ uint32_t ovf_best_c[kRrThreads];
+    __shared__ float ovf_best_d[kRrThreads];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const size_t tile_first = (size_t)blockIdx.x * kRrThreads;
+    const size_t blk = tile_first + tid;
+    const bool valid = blk < n;
+    uint4 cw = make_uint4(0, 0, 0, 0);
+    if (valid) cw = cand[blk];
+    const uint32_t cnt_raw = valid ? (cw.w >> 16) : 0u;
+    const bool overflow = cnt_raw == 0xffffu;
+    const uint32_t words[4] = {cw.x, cw.y, cw.z, cw.w};
+    // pairs this block contributes: none when the list has one entry and no error is wanted
+    uint32_t my_pairs = 0;
+    if (valid && !overflow && (cnt_raw > 1 || errors != nullptr)) my_pairs = cnt_raw;
+    // ---- exclusive scan of my_pairs over the CTA
+    uint32_t incl = my_pairs;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+    }
+    if (lane == 31) warp_tot[wid] = incl;
+    __syncthreads();
+    if (wid == 0) {
+        uint32_t w = lane < kRrThreads / 32 ? warp_tot[lane] : 0u, wi = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, wi, o);
+            if (lane >= o) wi += t;
+        }
+        if (lane < kRrThreads / 32) warp_tot[lane] = wi - w;
+        if (lane == kRrThreads / 32 - 1) warp_tot[kRrThreads / 32] = wi;
+    }
+    __syncthreads();
+    const uint32_t first = warp_tot[wid] + incl - my_pairs;
+    const uint32_t total = warp_tot[kRrThreads / 32];
+    for (uint32_t i = 0; i < my_pairs; ++i) {
+        p_blk[first + i] = (uint16_t)tid;
+        p_c[first + i] = (uint16_t)((words[i >> 1] >> (16 * (i & 1))) & 0xffffu);
+    }
+    __syncthreads();
+    // ---- pairs: 4 per warp iteration
+    const int g = lane >> 3, l = lane & 7;
+    for (uint32_t p0 = (uint32_t)wid * 4; p0 < total; p0 += (kRrThreads / 32) * 4) {
+        const uint32_t p = p0 + g;
+        const bool act = p < total;
+        const uint32_t pb = act ? p_blk[p] : 0u, pc = act ? p_c[p] : 0u;
+        const float d = pair_distance(feat + (tile_first + pb) * 64, cent + (size_t)pc * 64, l);
+        if (act && l == 0) p_d[p] = d;
+    }
+    // ---- overflow blocks: full scan, one block per warp at a time, 4 centroids per iteration
+    unsigned ovf_mask = __ballot_sync(0xffffffffu, overflow);
+    while (ovf_mask) {
+        const int src = __ffs(ovf_mask) - 1;
+        ovf_mask &= ovf_mask - 1;
+        const float* x = feat + (tile_first + (size_t)(wid * 32 + src)) * 64;
+        float best = FLT_MAX;
+        uint32_t best_c = 0;
+        for (uint32_t c0 = 0; c0 < K; c0 += 4) {
+            const uint32_t c = c0 + g;
+            const float d = pair_distance(x, cent + (size_t)(c < K ? c : 0) * 64, l);
+            if (c < K && d < best) {  // ascending c inside the group: strict '<' keeps the first minimum
+                best = d;
+                best_c = c;
+            }
+        }
+        // combine the four groups: smallest distance, lowest index on ties (what a serial scan returns)
+#pragma unroll
+        for (int o = 8; o <= 16; o <<= 1) {
+            const float od = __shfl_xor_sync(0xffffffffu, best, o);
+            const uint32_t oc = __shfl_xor_sync(0xffffffffu, best_c, o);
+            if (od < best || (od == best && od < FLT_MAX && oc < best_c)) {
+                best = od;
+                best_c = oc;
+            }
+        }
+        if (lane == 0) {
+            ovf_best_c[wid * 32 + src] = best_c;
+            ovf_best_d[wid * 32 + src] = best;
+        }
+    }
+    __syncthreads();
+    // ---- selection
     uint32_t pairs = 0;
     if (valid) {
         uint32_t best_c = cw.x & 0xffffu;
         float best = 0.0f;
-        if (need_x) {
-            float4 x[16];
-#pragma unroll
-            for (int k = 0; k < 16; ++k) x[k] = xs[threadIdx.x * kPitch4 + k];
+        if (overflow) {
+            best_c = ovf_best_c[tid];
+            best = ovf_best_d[tid];
+            pairs = K;
+        } else if (my_pairs) {
+            // the reference scans c ascending with strict '<' from FLT_MAX: smallest distance, lowest index
             best = FLT_MAX;
             best_c = 0;
-            if (cnt == 0xffffu) {  // full exact scan (reference order: strict '<', ascending c)
-                for (uint32_t c = 0; c < K; ++c) {
-                    const float d = oklab_dist_reg(x, reinterpret_cast<const float4*>(cent) + (size_t)c * 16);
-                    if (d < best) {
-                        best = d;
-                        best_c = c;
-                    }
+            bool have = false;
+            for (uint32_t i = 0; i < my_pairs; ++i) {
+                const float d = p_d[first + i];
+                const uint32_t c = p_c[first + i];
+                if (d < FLT_MAX && (!have || d < best || (d == best && c < best_c))) {
+                    best = d;
+                    best_c = c;
+                    have = true;
                 }
-                pairs = K;
-            } else {
-                const uint32_t words[4] = {cw.x, cw.y, cw.z, cw.w};
-                bool first = true;
-                for (uint32_t i = 0; i < cnt; ++i) {
-                    const uint32_t c = (words[i >> 1] >> (16 * (i & 1))) & 0xffffu;
-                    const float d = oklab_dist_reg(x, reinterpret_cast<const float4*>(cent) + (size_t)c * 16);
-                    // the reference scans c ascending with strict '<' from FLT_MAX: smallest distance, lowest index
-                    if (d < FLT_MAX && (first || d < best || (d == best && c < best_c))) {
-                        best = d;
-                        best_c = c;
-                        first = false;
-                    }
-                }
-                pairs = cnt > 1 ? cnt : 0;
             }
+            pairs = my_pairs > 1 ? my_pairs : 0;
         }
         if (flags && assign[blk] != best_c) flags[0] = 1u;
         assign[blk] = best_c;
@@ -531,7 +613,7 @@ __global__ void __launch_bounds__(kTile) rerank_kernel(const float* __restrict__
     }
     if (stat_pairs) {
         pairs = __reduce_add_sync(0xffffffffu, pairs);
-        if ((threadIdx.x & 31) == 0 && pairs) atomicAdd(stat_pairs, pairs);
+        if (lane == 0 && pairs) atomicAdd(stat_pairs, pairs);
     }
 }
 
@@ -625,8 +707,8 @@ cudaError_t launch_assign_tc(const float* a_prime, const float* xnorm, size_t n,
 cudaError_t launch_rerank(const float* feat, size_t n, const float* cent, uint32_t K, const uint4* cand, uint32_t* assign,
                           float* errors, uint32_t* flags, unsigned int* stat_pairs, cudaStream_t s) {
     if (n == 0) return cudaSuccess;
-    rerank_kernel<<<(unsigned)((n + kTile - 1) / kTile), kTile, 0, s>>>(feat, n, cent, K, cand, assign, errors, flags,
-                                                                        stat_pairs);
+    rerank_kernel<<<(unsigned)((n + kRrThreads - 1) / kRrThreads), kRrThreads, 0, s>>>(feat, n, cent, K, cand, assign, errors,
+                                                                                      flags, stat_pairs);
     return cudaGetLastError();
 }
 
