@@ -115,25 +115,26 @@ __device__ __forceinline__ void tc_mma_tf32(uint32_t tmem_d, uint64_t adesc, uin
         "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
-__device__ __forceinline__ void tc_ld64(uint32_t taddr, uint32_t (&v)[64]) {
+__device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t (&v)[32]) {
     asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x64.b32 "
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
         "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, "
-        "%32, %33, %34, %35, %36, %37, %38, %39, %40, %41, %42, %43, %44, %45, %46, %47, "
-        "%48, %49, %50, %51, %52, %53, %54, %55, %56, %57, %58, %59, %60, %61, %62, %63}, [%64];"
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
         : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
           "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
           "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
-          "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31]), "=r"(v[32]),
-          "=r"(v[33]), "=r"(v[34]), "=r"(v[35]), "=r"(v[36]), "=r"(v[37]), "=r"(v[38]), "=r"(v[39]), "=r"(v[40]),
-          "=r"(v[41]), "=r"(v[42]), "=r"(v[43]), "=r"(v[44]), "=r"(v[45]), "=r"(v[46]), "=r"(v[47]), "=r"(v[48]),
-          "=r"(v[49]), "=r"(v[50]), "=r"(v[51]), "=r"(v[52]), "=r"(v[53]), "=r"(v[54]), "=r"(v[55]), "=r"(v[56]),
-          "=r"(v[57]), "=r"(v[58]), "=r"(v[59]), "=r"(v[60]), "=r"(v[61]), "=r"(v[62]), "=r"(v[63])
+          "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
         : "r"(taddr)
         : "memory");
 }
-__device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+// tcgen05.wait::ld with the destination registers as read-write operands, so the compiler cannot move a
+// use of the tile above the wait
+__device__ __forceinline__ void tc_wait_ld(uint32_t (&v)[32]) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]), "+r"(v[8]), "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15]), "+r"(v[16]), "+r"(v[17]), "+r"(v[18]), "+r"(v[19]), "+r"(v[20]), "+r"(v[21]), "+r"(v[22]), "+r"(v[23]), "+r"(v[24]), "+r"(v[25]), "+r"(v[26]), "+r"(v[27]), "+r"(v[28]), "+r"(v[29]), "+r"(v[30]), "+r"(v[31])
+                 :
+                 : "memory");
+}
 __device__ __forceinline__ float fmax3(float a, float b, float c) {
     float d;
     asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
@@ -293,21 +294,33 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                 mbar_wait(bar(BAR_TFULL + acc), pacc);
                 tc_fence_after();
                 const uint32_t taddr = lane_taddr + acc * BN;
-                uint32_t v[64];
-                // ---- pass 1: maximum score over this thread's 128 columns
+                // TMEM reads are double-buffered (two 32-column register tiles): the load of the next tile is
+                // in flight while the current one is reduced, across the pass-1 / pass-2 boundary as well.
+                uint32_t va[32], vb[32];
                 float m0 = -INFINITY, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
+                auto reduce_max = [&](const uint32_t (&v)[32]) {
 #pragma unroll
-                for (int q = 0; q < 2; ++q) {
-                    tc_ld64(taddr + q * 64, v);
-                    tc_wait_ld();
-#pragma unroll
-                    for (int i = 0; i < 64; i += 8) {
+                    for (int i = 0; i < 32; i += 8) {
                         m0 = fmax3(m0, __uint_as_float(v[i]), __uint_as_float(v[i + 1]));
                         m1 = fmax3(m1, __uint_as_float(v[i + 2]), __uint_as_float(v[i + 3]));
                         m2 = fmax3(m2, __uint_as_float(v[i + 4]), __uint_as_float(v[i + 5]));
                         m3 = fmax3(m3, __uint_as_float(v[i + 6]), __uint_as_float(v[i + 7]));
                     }
-                }
+                };
+                // ---- pass 1: maximum score over this thread's 128 columns
+                tc_ld32(taddr, va);
+                tc_wait_ld(va);
+                tc_ld32(taddr + 32, vb);
+                reduce_max(va);
+                tc_wait_ld(vb);
+                tc_ld32(taddr + 64, va);
+                reduce_max(vb);
+                tc_wait_ld(va);
+                tc_ld32(taddr + 96, vb);
+                reduce_max(va);
+                tc_wait_ld(vb);
+                tc_ld32(taddr, va);  // first tile of pass 2
+                reduce_max(vb);
                 float* sm = s_max + (u & 1) * 256;
                 sm[half * 128 + r] = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
                 epi_bar();
@@ -320,25 +333,37 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                 float thr = m_run - margin;
                 thr = __uint_as_float(__float_as_uint(thr) + (thr > 0.0f ? -1 : (thr < 0.0f ? 1 : 0)));  // one ulp down
                 if (thr == 0.0f) thr = -FLT_MIN;
-                // ---- pass 2: sign-bit sweep, candidates are the columns with (thr - s) < 0
+                // ---- pass 2: sign-bit sweep, candidates are the columns with (thr - s) < 0.  Four
+                // independent 8-bit funnel-shift chains per tile keep the ALU pipe busy.
+                auto sweep = [&](const uint32_t (&v)[32], uint32_t col0) {
+                    uint32_t k0 = 0, k1 = 0, k2 = 0, k3 = 0;
 #pragma unroll
-                for (int q = 0; q < 2; ++q) {
-                    tc_ld64(taddr + q * 64, v);
-                    tc_wait_ld();
-#pragma unroll
-                    for (int g = 0; g < 2; ++g) {
-                        uint32_t mask = 0;
-#pragma unroll
-                        for (int i = 0; i < 32; ++i)
-                            mask = __funnelshift_l(__float_as_uint(thr - __uint_as_float(v[g * 32 + i])), mask, 1);
-                        while (mask) {
-                            const int b = __clz(mask);
-                            mask &= ~(0x80000000u >> b);
-                            if (cnt < 8) my_list[cnt] = (uint16_t)(j * BN + half * 128 + q * 64 + g * 32 + b);
-                            ++cnt;
-                        }
+                    for (int i = 0; i < 8; ++i) {
+                        k0 = __funnelshift_l(__float_as_uint(thr - __uint_as_float(v[i])), k0, 1);
+                        k1 = __funnelshift_l(__float_as_uint(thr - __uint_as_float(v[8 + i])), k1, 1);
+                        k2 = __funnelshift_l(__float_as_uint(thr - __uint_as_float(v[16 + i])), k2, 1);
+                        k3 = __funnelshift_l(__float_as_uint(thr - __uint_as_float(v[24 + i])), k3, 1);
                     }
-                }
+                    uint32_t mask = (k0 << 24) | (k1 << 16) | (k2 << 8) | k3;  // bit 31 - i <-> column col0 + i
+                    while (mask) {
+                        const int b = __clz(mask);
+                        mask &= ~(0x80000000u >> b);
+                        if (cnt < 8) my_list[cnt] = (uint16_t)(col0 + b);
+                        ++cnt;
+                    }
+                };
+                const uint32_t cbase = j * BN + half * 128;
+                tc_wait_ld(va);
+                tc_ld32(taddr + 32, vb);
+                sweep(va, cbase);
+                tc_wait_ld(vb);
+                tc_ld32(taddr + 64, va);
+                sweep(vb, cbase + 32);
+                tc_wait_ld(va);
+                tc_ld32(taddr + 96, vb);
+                sweep(va, cbase + 64);
+                tc_wait_ld(vb);
+                sweep(vb, cbase + 96);
                 // release the accumulator stage to the MMA warp
                 tc_fence_before();
                 __syncwarp();
@@ -465,31 +490,38 @@ __global__ void __launch_bounds__(64) prep_centroids_kernel(const float* __restr
 
 // ---- exact re-rank ---------------------------------------------------------------------------------------
 // Work is re-distributed from "one thread per block" (divergent candidate counts, uncoalesced centroid
-// rows) to "eight lanes per (block, candidate) pair": lane l owns the reference's lane accumulator l
-// (src/vq_encoder.cpp:220-229), so a pair costs eight dependent FMAs per lane, every load is a full
-// 32-byte sector, and the horizontal add tree (:231-236) is three shuffles.  Blocks with a single
+// rows) to "two lanes per (block, candidate) pair" over a compacted pair list: each lane owns four of
+// the reference's eight lane accumulators (src/vq_encoder.cpp:220-229), loads are 16-byte vectors, and
+// the horizontal add tree (:231-236) is four shuffles.  Blocks with a single
 // candidate need no arithmetic at all unless errors[] is requested.
 constexpr int kRrThreads = 256;                       // blocks per CTA == threads per CTA
 constexpr int kRrMaxPairs = kRrThreads * kMaxCand;
 
-// distance of one block to one centroid, computed by the 8 lanes of a group (all 8 get the result)
-__device__ __forceinline__ float pair_distance(const float* __restrict__ x, const float* __restrict__ c, int l) {
-    float xv[8], cv[8];
+// distance of one block to one centroid, computed by a pair of lanes: lane h (0/1) owns the reference's
+// lane accumulators 4h..4h+3 (src/vq_encoder.cpp:220-229) and reads float4s, so a warp covers 16
+// (block, candidate) pairs per step with 16 independent 16-byte loads in flight per lane.
+__device__ __forceinline__ float pair_distance(const float* __restrict__ x, const float* __restrict__ c, int h) {
+    float4 xv[8], cv[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-        xv[i] = __ldg(x + 8 * i + l);
-        cv[i] = __ldg(c + 8 * i + l);
+        xv[i] = __ldg(reinterpret_cast<const float4*>(x) + 2 * i + h);
+        cv[i] = __ldg(reinterpret_cast<const float4*>(c) + 2 * i + h);
     }
-    const float w = (l & 3) == 0 ? 2.0f : 1.0f;
-    float acc = 0.0f;
+    float a0 = 0.0f, a1 = 0.0f, a2 = 0.0f, a3 = 0.0f;
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-        const float d = __fmul_rn(__fsub_rn(xv[i], cv[i]), w);
-        acc = __fmaf_rn(d, d, acc);
+        float d;
+        d = __fmul_rn(__fsub_rn(xv[i].x, cv[i].x), 2.0f); a0 = __fmaf_rn(d, d, a0);
+        d = __fsub_rn(xv[i].y, cv[i].y);                  a1 = __fmaf_rn(d, d, a1);
+        d = __fsub_rn(xv[i].z, cv[i].z);                  a2 = __fmaf_rn(d, d, a2);
+        d = __fsub_rn(xv[i].w, cv[i].w);                  a3 = __fmaf_rn(d, d, a3);
     }
-    const float s = __fadd_rn(acc, __shfl_xor_sync(0xffffffffu, acc, 4));   // s_j = acc_j + acc_{j+4}
-    const float t = __fadd_rn(s, __shfl_xor_sync(0xffffffffu, s, 1));       // s0 + s1 | s2 + s3
-    return __fadd_rn(t, __shfl_xor_sync(0xffffffffu, t, 2));                // (s0 + s1) + (s2 + s3)
+    // s_j = acc_j + acc_{j+4}: the partner lane holds the other half (fp add is commutative)
+    const float s0 = __fadd_rn(a0, __shfl_xor_sync(0xffffffffu, a0, 1));
+    const float s1 = __fadd_rn(a1, __shfl_xor_sync(0xffffffffu, a1, 1));
+    const float s2 = __fadd_rn(a2, __shfl_xor_sync(0xffffffffu, a2, 1));
+    const float s3 = __fadd_rn(a3, __shfl_xor_sync(0xffffffffu, a3, 1));
+    return __fadd_rn(__fadd_rn(s0, s1), __fadd_rn(s2, s3));
 }
 
 __global__ void __launch_bounds__(kRrThreads) rerank_kernel(const float* __restrict__ feat, size_t n, const float* __restrict__ cent,
@@ -541,16 +573,16 @@ __global__ void __launch_bounds__(kRrThreads) rerank_kernel(const float* __restr
         p_c[first + i] = (uint16_t)((words[i >> 1] >> (16 * (i & 1))) & 0xffffu);
     }
     __syncthreads();
-    // ---- pairs: 4 per warp iteration
-    const int g = lane >> 3, l = lane & 7;
-    for (uint32_t p0 = (uint32_t)wid * 4; p0 < total; p0 += (kRrThreads / 32) * 4) {
+    // ---- pairs: 16 per warp iteration
+    const int g = lane >> 1, l = lane & 1;
+    for (uint32_t p0 = (uint32_t)wid * 16; p0 < total; p0 += (kRrThreads / 32) * 16) {
         const uint32_t p = p0 + g;
         const bool act = p < total;
         const uint32_t pb = act ? p_blk[p] : 0u, pc = act ? p_c[p] : 0u;
         const float d = pair_distance(feat + (tile_first + pb) * 64, cent + (size_t)pc * 64, l);
         if (act && l == 0) p_d[p] = d;
     }
-    // ---- overflow blocks: full scan, one block per warp at a time, 4 centroids per iteration
+    // ---- overflow blocks: full scan, one block per warp at a time, 16 centroids per iteration
     unsigned ovf_mask = __ballot_sync(0xffffffffu, overflow);
     while (ovf_mask) {
         const int src = __ffs(ovf_mask) - 1;
@@ -558,7 +590,7 @@ __global__ void __launch_bounds__(kRrThreads) rerank_kernel(const float* __restr
         const float* x = feat + (tile_first + (size_t)(wid * 32 + src)) * 64;
         float best = FLT_MAX;
         uint32_t best_c = 0;
-        for (uint32_t c0 = 0; c0 < K; c0 += 4) {
+        for (uint32_t c0 = 0; c0 < K; c0 += 16) {
             const uint32_t c = c0 + g;
             const float d = pair_distance(x, cent + (size_t)(c < K ? c : 0) * 64, l);
             if (c < K && d < best) {  // ascending c inside the group: strict '<' keeps the first minimum
@@ -566,9 +598,9 @@ __global__ void __launch_bounds__(kRrThreads) rerank_kernel(const float* __restr
                 best_c = c;
             }
         }
-        // combine the four groups: smallest distance, lowest index on ties (what a serial scan returns)
+        // combine the 16 groups: smallest distance, lowest index on ties (what a serial scan returns)
 #pragma unroll
-        for (int o = 8; o <= 16; o <<= 1) {
+        for (int o = 2; o <= 16; o <<= 1) {
             const float od = __shfl_xor_sync(0xffffffffu, best, o);
             const uint32_t oc = __shfl_xor_sync(0xffffffffu, best_c, o);
             if (od < best || (od == best && od < FLT_MAX && oc < best_c)) {

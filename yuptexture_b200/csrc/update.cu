@@ -37,14 +37,14 @@ __global__ void __launch_bounds__(256) accumulate_kernel(const float* __restrict
     if (blockIdx.x == 0 && threadIdx.x == 0 && flags) atomicAdd(sums + (size_t)K * 65, (unsigned long long)flags[0]);
 }
 
-// v2: sort-and-own.  A CTA takes chunks of kAccChunk consecutive blocks, counting-sorts the chunk's
+// v2: sort-and-own.  A CTA (two per SM) takes chunks of kAccChunk consecutive blocks, counting-sorts the chunk's
 // assignments in shared memory (histogram, scan, scatter of 16-bit local ids), then its warps claim
 // centroids and sum each centroid's member rows in registers: a row is one coalesced 256-byte read
-// (float2 per lane), the fixed-point conversion happens once per element, and only one 64-bit RED
-// per (chunk, centroid, column) reaches L2 -- 16x fewer than one per (block, column).  No shared
+// (float4 per lane of a half-warp), the fixed-point conversion happens once per element, and only one 64-bit RED
+// per (chunk, centroid, column) reaches L2 -- 8x fewer than one per (block, column) at K = 512.  No shared
 // memory atomics on the data path; integer sums keep the result order-independent.
 constexpr int kAccThreads = 512;
-constexpr int kAccChunk = 8192;
+constexpr int kAccChunk = 4096;
 constexpr int kAccMaxK = 4096;
 
 __global__ void __launch_bounds__(kAccThreads, 2)
@@ -110,8 +110,10 @@ accumulate_sorted_kernel(const float* __restrict__ feat, size_t n, const uint32_
         for (int k = 0; k < kPer; ++k)
             if (a[k] < K) sorted[offs[a[k]] + rank[k]] = (uint16_t)((uint32_t)k * kAccThreads + tid);
         __syncthreads();
-        // warps claim centroids; each sums its member rows in two 64-bit registers per lane
-        const float2* rows = reinterpret_cast<const float2*>(feat) + first * 32 + lane;
+        // warps claim centroids; a half-warp reads one member row (float4 per lane, 256 B coalesced), so a
+        // step of 8 loads per lane covers 16 rows; sums live in four 64-bit registers per lane
+        const float4* rows = reinterpret_cast<const float4*>(feat) + first * 16 + (lane & 15);
+        const uint32_t hw = (uint32_t)lane >> 4;
         for (;;) {
             uint32_t c = 0;
             if (lane == 0) c = atomicAdd(&next_c, 1u);
@@ -120,25 +122,35 @@ accumulate_sorted_kernel(const float* __restrict__ feat, size_t n, const uint32_
             const uint32_t m = hist[c];
             if (m == 0) continue;
             const uint16_t* ids = sorted + offs[c];
-            long long s0 = 0, s1 = 0;
-            uint32_t j = 0;
-            for (; j + 4 <= m; j += 4) {
-                float2 v[4];
+            long long s0 = 0, s1 = 0, s2 = 0, s3 = 0;
+            for (uint32_t j = 0; j < m; j += 16) {
+                float4 v[8];
 #pragma unroll
-                for (int q = 0; q < 4; ++q) v[q] = __ldg(rows + (size_t)ids[j + q] * 32);
+                for (int q = 0; q < 8; ++q) {
+                    const uint32_t r = j + 2 * q + hw;
+                    v[q] = r < m ? __ldg(rows + (size_t)ids[r] * 16) : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    s0 += __float2ll_rn(__fmul_rn(v[q].x, scale));
-                    s1 += __float2ll_rn(__fmul_rn(v[q].y, scale));
+                for (int q = 0; q < 8; ++q) {
+                    if (j + 2 * q + hw < m) {
+                        s0 += __float2ll_rn(__fmul_rn(v[q].x, scale));
+                        s1 += __float2ll_rn(__fmul_rn(v[q].y, scale));
+                        s2 += __float2ll_rn(__fmul_rn(v[q].z, scale));
+                        s3 += __float2ll_rn(__fmul_rn(v[q].w, scale));
+                    }
                 }
             }
-            for (; j < m; ++j) {
-                const float2 v = __ldg(rows + (size_t)ids[j] * 32);
-                s0 += __float2ll_rn(__fmul_rn(v.x, scale));
-                s1 += __float2ll_rn(__fmul_rn(v.y, scale));
+            s0 += __shfl_xor_sync(0xffffffffu, s0, 16);
+            s1 += __shfl_xor_sync(0xffffffffu, s1, 16);
+            s2 += __shfl_xor_sync(0xffffffffu, s2, 16);
+            s3 += __shfl_xor_sync(0xffffffffu, s3, 16);
+            if (lane < 16) {
+                unsigned long long* dst = sums + (size_t)c * 64 + 4 * lane;
+                atomicAdd(dst + 0, (unsigned long long)s0);
+                atomicAdd(dst + 1, (unsigned long long)s1);
+                atomicAdd(dst + 2, (unsigned long long)s2);
+                atomicAdd(dst + 3, (unsigned long long)s3);
             }
-            atomicAdd(sums + (size_t)c * 64 + 2 * lane, (unsigned long long)s0);
-            atomicAdd(sums + (size_t)c * 64 + 2 * lane + 1, (unsigned long long)s1);
             if (lane == 0) atomicAdd(counts + c, (unsigned long long)m);
         }
         __syncthreads();
