@@ -1,0 +1,4 @@
+// Source-compatibility forwarder: the reference header of this name (include/bcn_compressor.h) is provided by
+// include/yuptexture.h in this build.
+#pragma once
+#include "yuptexture.h"

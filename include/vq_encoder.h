@@ -1,0 +1,4 @@
+// Source-compatibility forwarder: the reference header of this name (include/vq_encoder.h) is provided by
+// include/yuptexture.h in this build.
+#pragma once
+#include "yuptexture.h"

@@ -14,7 +14,7 @@
 //   the 9th K-step multiplies a column of ones in A by a three-term tf32 split of -|c'|^2/2 in B,
 //   so the norm is folded into the accumulator exactly (to 2^-33) and the epilogue has no FFMA.
 //   D  = 128 lanes x 256 columns fp32 in TMEM, two accumulator stages (512 columns).
-// The epilogue (8 warps, one TMEM lane == one block per thread) makes two passes over each
+// The epilogue (16 warps, one TMEM lane == one block per thread, four column slices) makes two passes over each
 // accumulator stage: max3 reduction, then a sign-bit sweep that collects every centroid whose score
 // is within a proven error margin of the running maximum.  Blocks end up with a short candidate list
 // (uint16 x 7 + count in one uint4); rerank_kernel evaluates those candidates with the reference's
@@ -30,6 +30,7 @@
 // Roofline: tensor pipe (2 * N * K * 72 FLOP per pass at the tf32 rate) against an epilogue that is
 // ALU-issue bound (about 4 issue slots per block-centroid pair); HBM traffic is 256 B per block.
 #include <cfloat>
+#include <cstdlib>
 #include <cuda.h>
 
 #include "common.cuh"
@@ -41,7 +42,8 @@ namespace {
 
 constexpr int BM = 128;            // blocks per tile (MMA M, TMEM lanes)
 constexpr int BN = 256;            // centroids per chunk (MMA N, TMEM columns per accumulator stage)
-constexpr int kEpiWarps = 8;       // epilogue warps: 4 TMEM lane quadrants x 2 column halves
+constexpr int kEpiWarps = 16;      // epilogue warps: 4 TMEM lane quadrants x 4 column slices
+constexpr int kListCap = 4;        // candidates one (row, column slice) thread can record per tile
 constexpr int kThreadsTc = (2 + kEpiWarps) * 32;
 constexpr int kMaxCand = 7;
 
@@ -56,10 +58,10 @@ constexpr uint32_t ONES_BYTES = BM * 32;
 constexpr uint32_t OFF_A = 0;
 constexpr uint32_t OFF_B = OFF_A + 2 * A_STAGE_BYTES;
 constexpr uint32_t OFF_ONES = OFF_B + 2 * B_STAGE_BYTES;
-constexpr uint32_t OFF_LIST = OFF_ONES + ONES_BYTES;                 // u16 [256][8]
-constexpr uint32_t OFF_MAX = OFF_LIST + 256 * 8 * 2;                 // float [2 parity][2 half][128]
-constexpr uint32_t OFF_CNT = OFF_MAX + 2 * 2 * 128 * 4;              // u32 [128] (column-half 1 counts)
-constexpr uint32_t OFF_BAR = OFF_CNT + 128 * 4;                      // 12 mbarriers + tmem ptr
+constexpr uint32_t OFF_LIST = OFF_ONES + ONES_BYTES;                 // u16 [2 parity][4 slices][128][kListCap]
+constexpr uint32_t OFF_MAX = OFF_LIST + 2 * 4 * 128 * kListCap * 2;  // float [2 parity][4 slices][128]
+constexpr uint32_t OFF_CNT = OFF_MAX + 2 * 4 * 128 * 4;              // u8 [2 parity][4 slices][128]
+constexpr uint32_t OFF_BAR = OFF_CNT + 2 * 4 * 128;                  // 12 mbarriers + tmem ptr
 constexpr uint32_t SMEM_TC = OFF_BAR + 16 * 8 + 1024 /* alignment slack */;
 
 enum { BAR_FULL_A = 0, BAR_EMPTY_A = 2, BAR_FULL_B = 4, BAR_EMPTY_B = 6, BAR_TFULL = 8, BAR_TEMPTY = 10, BAR_COUNT = 12 };
@@ -163,7 +165,7 @@ __global__ void __launch_bounds__(kThreadsTc, 1)
 assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
                  const __grid_constant__ CUtensorMap tm_bx, const float* __restrict__ xnorm,
                  const float* __restrict__ cmax_ptr, uint32_t n, uint32_t num_tiles, uint32_t num_chunks,
-                 uint32_t resident_b, uint4* __restrict__ cand) {
+                 uint32_t resident_b, uint4* __restrict__ cand, uint32_t dbg) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     uint8_t* base_ptr = smem_raw + (base - smem_u32(smem_raw));
@@ -269,26 +271,35 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
             }
         }
     } else {
-        // ===== epilogue: 8 warps, thread == (TMEM lane, column half) ====================================
+        // ===== epilogue: 16 warps, thread == (TMEM lane, column quarter) =================================
+        constexpr int kSplit = kEpiWarps / 4;        // column slices per accumulator stage
+        constexpr int kCols = BN / kSplit;           // columns per thread per stage
+        constexpr int kTiles = kCols / 32;           // 32-column register tiles per pass
+        static_assert(kTiles == 2, "the unrolled load schedule below is written for two tiles per pass");
         const int ew = warp - 2;
         const int quad = warp & 3;          // TMEM lane quadrant this warp may access
-        const int half = ew >> 2;           // which 128 of the stage's 256 columns
+        const int slice = ew >> 2;          // which kCols of the stage's 256 columns
         const int r = quad * 32 + lane;     // row inside the tile
-        const int etid = half * 128 + r;
-        uint16_t* my_list = reinterpret_cast<uint16_t*>(base_ptr + OFF_LIST) + etid * 8;
-        const uint16_t* other_list = reinterpret_cast<const uint16_t*>(base_ptr + OFF_LIST) + (128 + r) * 8;
-        float* s_max = reinterpret_cast<float*>(base_ptr + OFF_MAX);
-        uint32_t* s_cnt = reinterpret_cast<uint32_t*>(base_ptr + OFF_CNT);
+        uint16_t* lists = reinterpret_cast<uint16_t*>(base_ptr + OFF_LIST);   // [2 parity][kSplit][128][kListCap]
+        float* s_max = reinterpret_cast<float*>(base_ptr + OFF_MAX);          // [2 parity][kSplit][128]
+        uint8_t* s_cnt = reinterpret_cast<uint8_t*>(base_ptr + OFF_CNT);      // [2 parity][kSplit][128]
         const float cmax = __ldg(cmax_ptr);
-        const uint32_t lane_taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)half * 128u;
-        uint32_t u = 0;
-        for (uint32_t t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+        const uint32_t lane_taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(slice * kCols);
+        uint32_t u = 0, tpar = 0;
+        float xn_next = 0.0f;
+        if ((size_t)blockIdx.x * BM + r < n) xn_next = __ldg(xnorm + (size_t)blockIdx.x * BM + r);
+        for (uint32_t t = blockIdx.x; t < num_tiles; t += gridDim.x, tpar ^= 1) {
             const size_t row = (size_t)t * BM + r;
-            const float xn = row < n ? __ldg(xnorm + row) : 0.0f;
+            const float xn = xn_next;
+            {   // prefetch the next tile's |x'| so its DRAM latency hides behind this tile
+                const size_t nrow = row + (size_t)gridDim.x * BM;
+                xn_next = (t + gridDim.x < num_tiles && nrow < n) ? __ldg(xnorm + nrow) : 0.0f;
+            }
             const float e_dot = kDotErr * xn * cmax;
             float m_run = -INFINITY;
             uint32_t cnt = 0;
             bool bad = false;
+            uint16_t* my_list = lists + ((tpar * kSplit + slice) * 128 + r) * kListCap;
             for (uint32_t j = 0; j < num_chunks; ++j, ++u) {
                 const uint32_t acc = u & 1, pacc = (u >> 1) & 1;
                 mbar_wait(bar(BAR_TFULL + acc), pacc);
@@ -307,24 +318,18 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                         m3 = fmax3(m3, __uint_as_float(v[i + 6]), __uint_as_float(v[i + 7]));
                     }
                 };
-                // ---- pass 1: maximum score over this thread's 128 columns
+                // ---- pass 1: maximum score over this thread's columns
                 tc_ld32(taddr, va);
                 tc_wait_ld(va);
                 tc_ld32(taddr + 32, vb);
-                reduce_max(va);
-                tc_wait_ld(vb);
-                tc_ld32(taddr + 64, va);
-                reduce_max(vb);
-                tc_wait_ld(va);
-                tc_ld32(taddr + 96, vb);
-                reduce_max(va);
+                if (!(dbg & 1)) reduce_max(va);
                 tc_wait_ld(vb);
                 tc_ld32(taddr, va);  // first tile of pass 2
-                reduce_max(vb);
-                float* sm = s_max + (u & 1) * 256;
-                sm[half * 128 + r] = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
+                if (!(dbg & 1)) reduce_max(vb);
+                float* sm = s_max + (u & 1) * (kSplit * 128);
+                sm[slice * 128 + r] = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
                 epi_bar();
-                m_run = fmax3(m_run, sm[r], sm[128 + r]);
+                m_run = fmaxf(fmax3(m_run, sm[r], sm[128 + r]), fmaxf(sm[256 + r], sm[384 + r]));
                 // every centroid that could still be the reference argmin has score >= thr
                 const float d_up = fmaxf(xn * xn - 2.0f * m_run + 2.0f * e_dot, 0.0f);
                 const float margin = 2.0f * e_dot + kRefRel * d_up;
@@ -348,47 +353,48 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                     while (mask) {
                         const int b = __clz(mask);
                         mask &= ~(0x80000000u >> b);
-                        if (cnt < 8) my_list[cnt] = (uint16_t)(col0 + b);
+                        if (cnt < (uint32_t)kListCap) my_list[cnt] = (uint16_t)(col0 + b);
                         ++cnt;
                     }
                 };
-                const uint32_t cbase = j * BN + half * 128;
+                const uint32_t cbase = j * BN + slice * kCols;
                 tc_wait_ld(va);
                 tc_ld32(taddr + 32, vb);
-                sweep(va, cbase);
+                if (!(dbg & 2)) sweep(va, cbase);
                 tc_wait_ld(vb);
-                tc_ld32(taddr + 64, va);
-                sweep(vb, cbase + 32);
-                tc_wait_ld(va);
-                tc_ld32(taddr + 96, vb);
-                sweep(va, cbase + 64);
-                tc_wait_ld(vb);
-                sweep(vb, cbase + 96);
+                if (!(dbg & 2)) sweep(vb, cbase + 32);
                 // release the accumulator stage to the MMA warp
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(bar(BAR_TEMPTY + acc));
             }
-            // ---- merge the two column halves and publish the candidate list
-            if (bad) cnt = 100;
-            if (half == 1) s_cnt[r] = cnt;
+            // ---- merge the column slices and publish the candidate list.  Lists and counts are double
+            // buffered by tile parity, so one barrier per tile is enough.
+            if (bad || cnt > (uint32_t)kListCap) cnt = 100;
+            s_cnt[(tpar * kSplit + slice) * 128 + r] = (uint8_t)cnt;
             epi_bar();
-            if (half == 0 && row < n) {
-                const uint32_t c1 = s_cnt[r];
+            if (slice == 0 && row < n) {
                 uint32_t w[4] = {0, 0, 0, 0};
-                const uint32_t total = cnt + c1;
-                if (total >= 1 && total <= (uint32_t)kMaxCand) {
-                    for (uint32_t i = 0; i < total; ++i) {
-                        const uint32_t c = i < cnt ? my_list[i] : other_list[i - cnt];
-                        w[i >> 1] |= c << (16 * (i & 1));
+                uint32_t total = 0;
+                bool ovf = false;
+#pragma unroll
+                for (int q = 0; q < kSplit; ++q) {
+                    const uint32_t cq = s_cnt[(tpar * kSplit + q) * 128 + r];
+                    ovf |= cq > (uint32_t)kListCap;
+                    const uint16_t* lq = lists + ((tpar * kSplit + q) * 128 + r) * kListCap;
+                    for (uint32_t i = 0; i < cq && !ovf && total < 8; ++i, ++total) {
+                        const uint32_t c = lq[i];
+                        w[total >> 1] |= c << (16 * (total & 1));
                     }
-                    w[3] |= total << 16;
+                }
+                if (!ovf && total >= 1 && total <= (uint32_t)kMaxCand) {
+                    w[3] = (w[3] & 0xffffu) | (total << 16);
                 } else {
+                    w[0] = w[1] = w[2] = 0;
                     w[3] = 0xffffu << 16;  // empty (NaN) or overflow: full exact scan in the re-rank
                 }
                 cand[row] = make_uint4(w[0], w[1], w[2], w[3]);
             }
-            epi_bar();  // lists / counts are reused by the next tile
         }
     }
 
@@ -730,9 +736,10 @@ cudaError_t launch_assign_tc(const float* a_prime, const float* xnorm, size_t n,
         return cudaErrorInvalidValue;
     const uint32_t num_tiles = (uint32_t)((n + BM - 1) / BM);
     const uint32_t num_chunks = k_pad / BN;
+    static const uint32_t dbg = getenv("YUPVQ_TC_DEBUG") ? (uint32_t)atoi(getenv("YUPVQ_TC_DEBUG")) : 0u;  // timing experiments only
     const uint32_t grid = num_tiles < (uint32_t)YUPVQ_NUM_SMS ? num_tiles : (uint32_t)YUPVQ_NUM_SMS;
     assign_tc_kernel<<<grid, kThreadsTc, SMEM_TC, s>>>(tm_a, tm_b, tm_bx, xnorm, cmax, (uint32_t)n, num_tiles, num_chunks,
-                                                      num_chunks <= 2 ? 1u : 0u, cand);
+                                                      num_chunks <= 2 ? 1u : 0u, cand, dbg);
     return cudaGetLastError();
 }
 
