@@ -62,10 +62,10 @@ typedef struct yupvq_stats {
     uint32_t lloyd_passes;    /* assignment passes run inside BuildCodebook                         */
     uint32_t seed_rounds;     /* K-Means++ rounds that drew a sample                                */
     uint32_t reseeds;         /* empty clusters re-seeded over all passes                           */
-    uint32_t rerank_blocks;   /* blocks sent to the exact re-rank over all passes (tensor mode)     */
+    uint32_t rerank_blocks;   /* exact distance evaluations of the re-rank over all passes (tensor)  */
     float ms_h2d, ms_decode, ms_seed, ms_lloyd, ms_finalize, ms_quantize, ms_d2h, ms_total;
     uint32_t gpu_launches;    /* kernels launched by this call                                      */
-    uint32_t reserved;
+    uint32_t rerank_overflow; /* blocks that needed a full exact scan (empty/overfull candidate list) */
 } yupvq_stats;
 
 /* ---- lifetime ------------------------------------------------------------------------------ */

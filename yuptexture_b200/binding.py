@@ -27,7 +27,7 @@ class Stats(C.Structure):
                 ("seed_rounds", C.c_uint32), ("reseeds", C.c_uint32), ("rerank_blocks", C.c_uint32),
                 ("ms_h2d", C.c_float), ("ms_decode", C.c_float), ("ms_seed", C.c_float), ("ms_lloyd", C.c_float),
                 ("ms_finalize", C.c_float), ("ms_quantize", C.c_float), ("ms_d2h", C.c_float),
-                ("ms_total", C.c_float), ("gpu_launches", C.c_uint32), ("reserved", C.c_uint32)]
+                ("ms_total", C.c_float), ("gpu_launches", C.c_uint32), ("rerank_overflow", C.c_uint32)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_ if k != "reserved"}

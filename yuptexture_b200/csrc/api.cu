@@ -370,7 +370,7 @@ int run_lloyd(yupvq_ctx* ctx, const Blocks& b, size_t n_total, size_t first_bloc
     long long* acc = ctx->acc.as<long long>();
     CK(cudaMemsetAsync(assign, 0, n * 4, ctx->stream));  // assignments(numBlocks, 0), :316
     CK(cudaMemsetAsync(flags + F_RESEEDS, 0, 4, ctx->stream));
-    CK(cudaMemsetAsync(flags + F_PAIRS, 0, 4, ctx->stream));
+    CK(cudaMemsetAsync(flags + F_PAIRS, 0, 8, ctx->stream));
     ctx->reseeds_sharded = 0;
 
     // fixed-point scale from the data range (deterministic function of the data)
@@ -420,12 +420,13 @@ int run_lloyd(yupvq_ctx* ctx, const Blocks& b, size_t n_total, size_t first_bloc
         }
     }
     CK(cudaMemcpyAsync(ctx->h_small, flags + F_RESEEDS, 4, cudaMemcpyDeviceToHost, ctx->stream));
-    CK(cudaMemcpyAsync(ctx->h_small + 1, flags + F_PAIRS, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(ctx->h_small + 1, flags + F_PAIRS, 8, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     if (stats) {
         stats->lloyd_passes = passes;
         stats->reseeds = ctx->h_small[0] + ctx->reseeds_sharded;
-        stats->rerank_blocks = ctx->h_small[1];  // exact distance evaluations spent on multi-candidate blocks
+        stats->rerank_blocks = ctx->h_small[1];    // exact distance evaluations spent on multi-candidate blocks
+        stats->rerank_overflow = ctx->h_small[2];  // blocks whose candidate list was empty/overfull (full scan)
     }
     return 0;
 }
@@ -733,6 +734,7 @@ int yupvq_encode_bcn_batch(yupvq_ctx* ctx, const uint8_t* const* bc_blocks, size
         total.seed_rounds += s.seed_rounds;
         total.reseeds += s.reseeds;
         total.rerank_blocks += s.rerank_blocks;
+        total.rerank_overflow += s.rerank_overflow;
         total.ms_h2d += s.ms_h2d; total.ms_decode += s.ms_decode; total.ms_seed += s.ms_seed;
         total.ms_lloyd += s.ms_lloyd; total.ms_finalize += s.ms_finalize; total.ms_quantize += s.ms_quantize;
         total.ms_d2h += s.ms_d2h; total.ms_total += s.ms_total;
@@ -996,6 +998,7 @@ int yupvq_assign(yupvq_ctx* ctx, const float* features, size_t n_blocks, const f
     if (to_device(ctx, centroids, (size_t)codebook_size * 256, ctx->cent, &c_dev)) return 1;
     CK(ctx->out_idx.ensure(n_blocks * 4));
     CK(ctx->errors.ensure(n_blocks * 4));
+    CK(cudaMemsetAsync(ctx->small.as<uint32_t>() + F_PAIRS, 0, 8, ctx->stream));
     Timer tm(ctx);
     const int t0 = tm.mark();
     if (assign_blocks(ctx, reinterpret_cast<const float*>(f_dev), n_blocks, reinterpret_cast<const float*>(c_dev), codebook_size,
@@ -1004,10 +1007,13 @@ int yupvq_assign(yupvq_ctx* ctx, const float* features, size_t n_blocks, const f
     const int t1 = tm.mark();
     if (from_device(ctx, out_indices, ctx->out_idx.p, n_blocks * 4)) return 1;
     if (from_device(ctx, out_errors, ctx->errors.p, n_blocks * 4)) return 1;
+    CK(cudaMemcpyAsync(ctx->h_small, ctx->small.as<uint32_t>() + F_PAIRS, 8, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     if (stats) {
         stats->n_blocks = (uint32_t)n_blocks;
         stats->codebook_size = codebook_size;
+        stats->rerank_blocks = ctx->h_small[0];
+        stats->rerank_overflow = ctx->h_small[1];
         stats->ms_quantize = stats->ms_total = tm.ms(t0, t1);
         stats->gpu_launches = ctx->launches;
     }

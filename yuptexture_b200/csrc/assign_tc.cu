@@ -8,11 +8,17 @@
 // (w = [2,1,1,1] per pixel, mu = the texture's mean feature vector: distances are translation
 // invariant and centring removes ~1.5 decimal digits of cancellation).  For a
 // fixed block only  s(c) = x'.c' - |c'|^2 / 2  matters (argmin d == argmax s).  The front-end
-// computes s for all K centroids with kind::tf32 MMAs:
-//   A  = rna_tf32(x')             128 blocks  x 64 (+8)   TMA, 128B swizzle, 2-stage ring
-//   B  = rna_tf32(c')             256 centroids x 64 (+8) TMA, resident in smem when K <= 512
-//   the 9th K-step multiplies a column of ones in A by a three-term tf32 split of -|c'|^2/2 in B,
-//   so the norm is folded into the accumulator exactly (to 2^-33) and the epilogue has no FFMA.
+// computes s for all K centroids with kind::f16 (bf16) MMAs on two-term bf16 splits of both operands,
+//   x' = xh + xl (+ 2^-18 |x'|),  c' = ch + cl (+ 2^-18 |c'|),     s ~ xh.ch + xh.cl + xl.ch - |c'|^2/2
+// which costs 13 K=16 MMAs per 128 x 256 tile instead of the 9 K=8 MMAs of a single-pass tf32 product but
+// is 2^6 times more accurate (error 2^-16 |x'||c'| instead of 2^-10): the candidate lists shrink from
+// 2.2 to ~1.0 entries per block and the exact re-rank has almost nothing to do.  Operand rows keep the
+// tf32 design's 256 bytes:
+//   A  = [xh | xl]  128 blocks    x (64 + 64) bf16   TMA, 128B swizzle, 2-stage ring
+//   B  = [ch | cl]  256 centroids x (64 + 64) bf16   TMA, resident in smem when K <= 512
+//   the three partial products re-use the same shared-memory tiles through their descriptors; a 13th
+//   K-step multiplies a column of ones in A by a three-term bf16 split of -|c'|^2/2 in B, so the norm
+//   is folded into the accumulator (24 bits) and the epilogue has no FFMA.
 //   D  = 128 lanes x 256 columns fp32 in TMEM, two accumulator stages (512 columns).
 // The epilogue (16 warps, one TMEM lane == one block per thread, four column slices) makes two passes over each
 // accumulator stage: max3 reduction, then a sign-bit sweep that collects every centroid whose score
@@ -20,18 +26,20 @@
 // (uint16 x 7 + count in one uint4); rerank_kernel evaluates those candidates with the reference's
 // exact operation order (common.cuh DistAcc) and resolves ties to the lowest index.
 //
-// Error margin: inputs are rounded to nearest tf32 (u = 2^-11), so
-//   |x'.c' - mma| <= (2u + u^2) |x'||c'| + accumulation  <=  kDotErr * |x'| * Cmax
+// Error margin: each operand is represented to 2^-18 relative, the dropped xl.cl term is
+// 2^-18 |x_i c_i|, so
+//   |x'.c' - mma| <= 3 * 2^-18 |x'||c'| + fp32 accumulation  <=  kDotErr * |x'| * Cmax,  kDotErr = 1.5 * 2^-16
 // with Cmax = max_c |c'|.  A centroid can only be the reference argmin if
 //   s(c) >= s_max - (2 * E + reference-rounding slack).
 // The list is therefore a superset of the possible winners; an empty or overflowing list falls back
 // to a full exact scan of that block inside rerank_kernel (flat textures, NaNs).
 //
-// Roofline: tensor pipe (2 * N * K * 72 FLOP per pass at the tf32 rate) against an epilogue that is
+// Roofline: tensor pipe (2 * N * K * 208 FLOP per pass at the bf16 rate) against an epilogue that is
 // ALU-issue bound (about 4 issue slots per block-centroid pair); HBM traffic is 256 B per block.
 #include <cfloat>
 #include <cstdlib>
 #include <cuda.h>
+#include <cuda_bf16.h>
 
 #include "common.cuh"
 #include "kernels.h"
@@ -47,10 +55,10 @@ constexpr int kListCap = 4;        // candidates one (row, column slice) thread 
 constexpr int kThreadsTc = (2 + kEpiWarps) * 32;
 constexpr int kMaxCand = 7;
 
-constexpr uint32_t A_HALF_BYTES = BM * 128;        // 128 rows x 32 floats
+constexpr uint32_t A_HALF_BYTES = BM * 128;        // 128 rows x 64 bf16 (xh, then xl)
 constexpr uint32_t A_STAGE_BYTES = 2 * A_HALF_BYTES;
 constexpr uint32_t B_HALF_BYTES = BN * 128;
-constexpr uint32_t BX_BYTES = BN * 32;             // 256 rows x 8 floats (32B swizzle)
+constexpr uint32_t BX_BYTES = BN * 32;             // 256 rows x 16 bf16 (32B swizzle)
 constexpr uint32_t B_STAGE_BYTES = 2 * B_HALF_BYTES + BX_BYTES;
 constexpr uint32_t ONES_BYTES = BM * 32;
 
@@ -67,7 +75,7 @@ constexpr uint32_t SMEM_TC = OFF_BAR + 16 * 8 + 1024 /* alignment slack */;
 enum { BAR_FULL_A = 0, BAR_EMPTY_A = 2, BAR_FULL_B = 4, BAR_EMPTY_B = 6, BAR_TFULL = 8, BAR_TEMPTY = 10, BAR_COUNT = 12 };
 
 // error model constants (see header comment)
-constexpr float kDotErr = 0.0009765625f * 1.0625f + 0.0000152587890625f * 2.0f;  // 2^-10 * 1.0625 + 2^-15
+constexpr float kDotErr = 0.0000152587890625f * 1.5f;                             // 1.5 * 2^-16
 constexpr float kRefRel = 0.000030517578125f;                                     // 2^-15
 
 // ---- PTX wrappers ----------------------------------------------------------------------------------
@@ -107,12 +115,12 @@ __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::
 __device__ __forceinline__ void tc_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
-__device__ __forceinline__ void tc_mma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+__device__ __forceinline__ void tc_mma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
     asm volatile(
         "{\n\t"
         ".reg .pred p;\n\t"
         "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
         "}\n" ::"r"(tmem_d),
         "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
         : "memory");
@@ -157,8 +165,8 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t sbo_bytes
     return d;
 }
 
-// kind::tf32, D = f32, A/B = tf32, both K-major, M = 128, N = 256 (cute::UMMA::InstrDescriptor)
-constexpr uint32_t kIdesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+// kind::f16, D = f32, A/B = bf16, both K-major, M = 128, N = 256 (cute::UMMA::InstrDescriptor)
+constexpr uint32_t kIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
 
 // ---- the front-end kernel -----------------------------------------------------------------------------
 __global__ void __launch_bounds__(kThreadsTc, 1)
@@ -193,7 +201,7 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     // the column of ones that multiplies the folded norm terms (layout-invariant: every element is 1)
-    for (uint32_t i = threadIdx.x; i < ONES_BYTES / 4; i += kThreadsTc) reinterpret_cast<float*>(base_ptr + OFF_ONES)[i] = 1.0f;
+    for (uint32_t i = threadIdx.x; i < ONES_BYTES / 4; i += kThreadsTc) reinterpret_cast<uint32_t*>(base_ptr + OFF_ONES)[i] = 0x3f803f80u;  // bf16 1.0 x 2
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     tc_fence_before();
     __syncthreads();
@@ -208,7 +216,7 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                     const uint32_t dst = base + OFF_B + j * B_STAGE_BYTES;
                     mbar_expect_tx(bar(BAR_FULL_B + j), B_STAGE_BYTES);
                     tma_load_2d(dst, &tm_b, 0, (int)(j * BN), bar(BAR_FULL_B + j));
-                    tma_load_2d(dst + B_HALF_BYTES, &tm_b, 32, (int)(j * BN), bar(BAR_FULL_B + j));
+                    tma_load_2d(dst + B_HALF_BYTES, &tm_b, 64, (int)(j * BN), bar(BAR_FULL_B + j));
                     tma_load_2d(dst + 2 * B_HALF_BYTES, &tm_bx, 0, (int)(j * BN), bar(BAR_FULL_B + j));
                 }
             }
@@ -219,7 +227,7 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                 const uint32_t dst = base + OFF_A + sa * A_STAGE_BYTES;
                 mbar_expect_tx(bar(BAR_FULL_A + sa), A_STAGE_BYTES);
                 tma_load_2d(dst, &tm_a, 0, (int)(t * BM), bar(BAR_FULL_A + sa));
-                tma_load_2d(dst + A_HALF_BYTES, &tm_a, 32, (int)(t * BM), bar(BAR_FULL_A + sa));
+                tma_load_2d(dst + A_HALF_BYTES, &tm_a, 64, (int)(t * BM), bar(BAR_FULL_A + sa));
                 if (!resident_b) {
                     for (uint32_t j = 0; j < num_chunks; ++j, ++u) {
                         const uint32_t sb = u & 1, pb = (u >> 1) & 1;
@@ -227,7 +235,7 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                         const uint32_t dstb = base + OFF_B + sb * B_STAGE_BYTES;
                         mbar_expect_tx(bar(BAR_FULL_B + sb), B_STAGE_BYTES);
                         tma_load_2d(dstb, &tm_b, 0, (int)(j * BN), bar(BAR_FULL_B + sb));
-                        tma_load_2d(dstb + B_HALF_BYTES, &tm_b, 32, (int)(j * BN), bar(BAR_FULL_B + sb));
+                        tma_load_2d(dstb + B_HALF_BYTES, &tm_b, 64, (int)(j * BN), bar(BAR_FULL_B + sb));
                         tma_load_2d(dstb + 2 * B_HALF_BYTES, &tm_bx, 0, (int)(j * BN), bar(BAR_FULL_B + sb));
                     }
                 }
@@ -256,14 +264,17 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                     tc_fence_after();
                     const uint32_t b_addr = base + OFF_B + sb * B_STAGE_BYTES;
                     const uint32_t d_tmem = tmem_base + acc * BN;
+                    // xl.ch + xh.cl + xh.ch: twelve K = 16 steps over the two 128-byte halves of each operand row
+                    // (small terms first), then the folded norm
 #pragma unroll
-                    for (int k = 0; k < 8; ++k) {
-                        const uint32_t koff = (uint32_t)(k >> 2) * A_HALF_BYTES + (uint32_t)(k & 3) * 32u;
-                        const uint32_t boff = (uint32_t)(k >> 2) * B_HALF_BYTES + (uint32_t)(k & 3) * 32u;
-                        tc_mma_tf32(d_tmem, make_desc(a_addr + koff, 1024, 2), make_desc(b_addr + boff, 1024, 2), kIdesc,
+                    for (int k = 0; k < 12; ++k) {
+                        const int seg = k >> 2;
+                        const uint32_t koff = (seg == 0 ? A_HALF_BYTES : 0u) + (uint32_t)(k & 3) * 32u;
+                        const uint32_t boff = (seg == 1 ? B_HALF_BYTES : 0u) + (uint32_t)(k & 3) * 32u;
+                        tc_mma_bf16(d_tmem, make_desc(a_addr + koff, 1024, 2), make_desc(b_addr + boff, 1024, 2), kIdesc,
                                     k > 0 ? 1u : 0u);
                     }
-                    tc_mma_tf32(d_tmem, ones_desc, make_desc(b_addr + 2 * B_HALF_BYTES, 256, 6), kIdesc, 1u);
+                    tc_mma_bf16(d_tmem, ones_desc, make_desc(b_addr + 2 * B_HALF_BYTES, 256, 6), kIdesc, 1u);
                     tc_commit(bar(BAR_TFULL + acc));
                     if (!resident_b) tc_commit(bar(BAR_EMPTY_B + sb));
                 }
@@ -329,6 +340,7 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                 float* sm = s_max + (u & 1) * (kSplit * 128);
                 sm[slice * 128 + r] = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
                 epi_bar();
+                const float m_prev = m_run;
                 m_run = fmaxf(fmax3(m_run, sm[r], sm[128 + r]), fmaxf(sm[256 + r], sm[384 + r]));
                 // every centroid that could still be the reference argmin has score >= thr
                 const float d_up = fmaxf(xn * xn - 2.0f * m_run + 2.0f * e_dot, 0.0f);
@@ -338,6 +350,9 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                 float thr = m_run - margin;
                 thr = __uint_as_float(__float_as_uint(thr) + (thr > 0.0f ? -1 : (thr < 0.0f ? 1 : 0)));  // one ulp down
                 if (thr == 0.0f) thr = -FLT_MIN;
+                // every candidate recorded in earlier chunks has score <= m_prev: once the threshold has moved
+                // past that, none of them can win any more
+                if (m_prev < thr) cnt = 0;
                 // ---- pass 2: sign-bit sweep, candidates are the columns with (thr - s) < 0.  Four
                 // independent 8-bit funnel-shift chains per tile keep the ALU pipe busy.
                 auto sweep = [&](const uint32_t (&v)[32], uint32_t col0) {
@@ -406,10 +421,12 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
 }
 
 // ---- operand preparation ------------------------------------------------------------------------------
-__device__ __forceinline__ float to_tf32(float x) {
-    uint32_t r;
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
-    return __uint_as_float(r);
+// two-term bf16 split: v = hi + lo + r, |r| <= 2^-18 |v| (v - hi is exact in fp32)
+__device__ __forceinline__ void split_bf16(float v, uint16_t& hi, uint16_t& lo) {
+    const __nv_bfloat16 h = __float2bfloat16_rn(v);
+    const __nv_bfloat16 l = __float2bfloat16_rn(__fsub_rn(v, __bfloat162float(h)));
+    hi = __bfloat16_as_ushort(h);
+    lo = __bfloat16_as_ushort(l);
 }
 
 // column sums of the N x 64 feature matrix (fp64, atomics: mu only steers the error margin, it never
@@ -429,7 +446,7 @@ __global__ void mean_kernel(const double* __restrict__ sums, double inv_n, float
     mu[threadIdx.x] = isfinite(m) ? m : 0.0f;
 }
 
-// A' = rna_tf32(w (x - mu)),  xnorm = |w (x - mu)| (rounded up a little)
+// A' row (256 B) = [bf16 hi of w (x - mu) x 64 | bf16 lo x 64],  xnorm = |w (x - mu)| (rounded up a little)
 __global__ void __launch_bounds__(256) prep_blocks_kernel(const float* __restrict__ feat, size_t n, const float* __restrict__ mu,
                                                           float* __restrict__ a_prime, float* __restrict__ xnorm) {
     const size_t row = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 4;   // 16 threads per row
@@ -444,19 +461,23 @@ __global__ void __launch_bounds__(256) prep_blocks_kernel(const float* __restric
         o.z = x.z - m.z;
         o.w = x.w - m.w;
         ss = o.x * o.x + o.y * o.y + o.z * o.z + o.w * o.w;
-        o.x = to_tf32(o.x);
-        o.y = to_tf32(o.y);
-        o.z = to_tf32(o.z);
-        o.w = to_tf32(o.w);
-        reinterpret_cast<float4*>(a_prime)[row * 16 + q] = o;
+        uint16_t h0, h1, h2, h3, l0, l1, l2, l3;
+        split_bf16(o.x, h0, l0);
+        split_bf16(o.y, h1, l1);
+        split_bf16(o.z, h2, l2);
+        split_bf16(o.w, h3, l3);
+        uint2* dst = reinterpret_cast<uint2*>(a_prime) + row * 32 + q;          // 32 x 8 B per row
+        dst[0] = make_uint2((uint32_t)h0 | ((uint32_t)h1 << 16), (uint32_t)h2 | ((uint32_t)h3 << 16));
+        dst[16] = make_uint2((uint32_t)l0 | ((uint32_t)l1 << 16), (uint32_t)l2 | ((uint32_t)l3 << 16));
     }
 #pragma unroll
     for (int o = 8; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
     if (row < n && q == 0) xnorm[row] = sqrtf(ss) * 1.0001f;
 }
 
-// B' = rna_tf32(w (c - mu)); the ext columns hold a three-term tf32 split of -|c'|^2 / 2;
-// rows K..K_pad-1 are padding that can never win (score -1e30).  cmax = max_c |c'| (rounded up).
+// B' row (256 B) = [bf16 hi of w (c - mu) x 64 | bf16 lo x 64]; the ext row (32 B = 16 bf16) holds a three-term
+// bf16 split of -|c'|^2 / 2 (24 bits); rows K..K_pad-1 are padding that can never win (score -1e30).
+// cmax = max_c |c'| (rounded up).
 __global__ void __launch_bounds__(64) prep_centroids_kernel(const float* __restrict__ cent, uint32_t K, const float* __restrict__ mu,
                                                             float* __restrict__ b_main, float* __restrict__ b_ext,
                                                             unsigned int* __restrict__ cmax_bits) {
@@ -468,25 +489,29 @@ __global__ void __launch_bounds__(64) prep_centroids_kernel(const float* __restr
         v = w * (cent[(size_t)c * 64 + i] - mu[i]);
         if (!isfinite(v)) v = 0.0f;  // a non-finite centroid is handled by the exact scan (its blocks overflow)
     }
-    b_main[(size_t)c * 64 + i] = to_tf32(v);
+    uint16_t hi16, lo16;
+    split_bf16(v, hi16, lo16);
+    uint16_t* brow = reinterpret_cast<uint16_t*>(b_main) + (size_t)c * 128;
+    brow[i] = hi16;
+    brow[64 + i] = lo16;
     __shared__ double red[2];
     double ss = (double)v * (double)v;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
     if ((i & 31) == 0) red[i >> 5] = ss;
     __syncthreads();
-    if (i < 8) {
+    if (i < 16) {
         float e = 0.0f;
         if (c < K) {
             const double nh = -0.5 * (red[0] + red[1]);
-            const float hi = to_tf32((float)nh);
-            const float mid = to_tf32((float)(nh - (double)hi));
-            const float lo = to_tf32((float)(nh - (double)hi - (double)mid));
+            const float hi = __bfloat162float(__float2bfloat16_rn((float)nh));
+            const float mid = __bfloat162float(__float2bfloat16_rn((float)(nh - (double)hi)));
+            const float lo = __bfloat162float(__float2bfloat16_rn((float)(nh - (double)hi - (double)mid)));
             e = i == 0 ? hi : (i == 1 ? mid : (i == 2 ? lo : 0.0f));
         } else if (i == 0) {
             e = -1.0e30f;
         }
-        b_ext[(size_t)c * 8 + i] = e;
+        reinterpret_cast<uint16_t*>(b_ext)[(size_t)c * 16 + i] = __bfloat16_as_ushort(__float2bfloat16_rn(e));
     }
     if (i == 0 && c < K) {
         const float nrm = (float)sqrt(red[0] + red[1]) * 1.0001f;
@@ -495,32 +520,38 @@ __global__ void __launch_bounds__(64) prep_centroids_kernel(const float* __restr
 }
 
 // ---- exact re-rank ---------------------------------------------------------------------------------------
-// Work is re-distributed from "one thread per block" (divergent candidate counts, uncoalesced centroid
-// rows) to "two lanes per (block, candidate) pair" over a compacted pair list: each lane owns four of
-// the reference's eight lane accumulators (src/vq_encoder.cpp:220-229), loads are 16-byte vectors, and
-// the horizontal add tree (:231-236) is four shuffles.  Blocks with a single
-// candidate need no arithmetic at all unless errors[] is requested.
-constexpr int kRrThreads = 256;                       // blocks per CTA == threads per CTA
-constexpr int kRrMaxPairs = kRrThreads * kMaxCand;
+// Streaming, warp-granular: a warp owns 32 consecutive blocks.  It reads their candidate words with one
+// coalesced 512-byte load, votes which blocks need arithmetic at all (more than one candidate, or
+// errors[] requested), compacts those and evaluates them 16 at a time with two lanes per block: lane h
+// (0/1) owns the reference's lane accumulators 4h..4h+3 (src/vq_encoder.cpp:220-229), keeps its half of
+// the feature row in registers (8 x 16-byte no-allocate loads, so L1 is left to the K centroid rows) and
+// walks the block's candidates.  The horizontal add tree (:231-236) is four shuffles.  No shared-memory
+// staging and no CTA-wide barrier: the only cross-lane traffic is warp shuffles, and the final
+// assign/errors stores are coalesced.
+constexpr int kRrThreads = 256;
 
-// distance of one block to one centroid, computed by a pair of lanes: lane h (0/1) owns the reference's
-// lane accumulators 4h..4h+3 (src/vq_encoder.cpp:220-229) and reads float4s, so a warp covers 16
-// (block, candidate) pairs per step with 16 independent 16-byte loads in flight per lane.
-__device__ __forceinline__ float pair_distance(const float* __restrict__ x, const float* __restrict__ c, int h) {
-    float4 xv[8], cv[8];
+// the feature-row half of lane h: float4 #(2i + h), i = 0..7
+struct RowHalf {
+    float4 v[8];
+    __device__ __forceinline__ void load_stream(const float* __restrict__ row, int h) {
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-        xv[i] = __ldg(reinterpret_cast<const float4*>(x) + 2 * i + h);
-        cv[i] = __ldg(reinterpret_cast<const float4*>(c) + 2 * i + h);
+        for (int i = 0; i < 8; ++i) v[i] = ldg_nc_f4(reinterpret_cast<const float4*>(row) + 2 * i + h);
     }
+};
+
+// distance of the block held by a lane pair to centroid row c (L1/L2-resident); both lanes return it
+__device__ __forceinline__ float pair_distance(const RowHalf& x, const float* __restrict__ c, int h) {
+    float4 cv[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) cv[i] = __ldg(reinterpret_cast<const float4*>(c) + 2 * i + h);
     float a0 = 0.0f, a1 = 0.0f, a2 = 0.0f, a3 = 0.0f;
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
         float d;
-        d = __fmul_rn(__fsub_rn(xv[i].x, cv[i].x), 2.0f); a0 = __fmaf_rn(d, d, a0);
-        d = __fsub_rn(xv[i].y, cv[i].y);                  a1 = __fmaf_rn(d, d, a1);
-        d = __fsub_rn(xv[i].z, cv[i].z);                  a2 = __fmaf_rn(d, d, a2);
-        d = __fsub_rn(xv[i].w, cv[i].w);                  a3 = __fmaf_rn(d, d, a3);
+        d = __fmul_rn(__fsub_rn(x.v[i].x, cv[i].x), 2.0f); a0 = __fmaf_rn(d, d, a0);
+        d = __fsub_rn(x.v[i].y, cv[i].y);                  a1 = __fmaf_rn(d, d, a1);
+        d = __fsub_rn(x.v[i].z, cv[i].z);                  a2 = __fmaf_rn(d, d, a2);
+        d = __fsub_rn(x.v[i].w, cv[i].w);                  a3 = __fmaf_rn(d, d, a3);
     }
     // s_j = acc_j + acc_{j+4}: the partner lane holds the other half (fp add is commutative)
     const float s0 = __fadd_rn(a0, __shfl_xor_sync(0xffffffffu, a0, 1));
@@ -530,128 +561,109 @@ __device__ __forceinline__ float pair_distance(const float* __restrict__ x, cons
     return __fadd_rn(__fadd_rn(s0, s1), __fadd_rn(s2, s3));
 }
 
-__global__ void __launch_bounds__(kRrThreads) rerank_kernel(const float* __restrict__ feat, size_t n, const float* __restrict__ cent,
-                                                            uint32_t K, const uint4* __restrict__ cand, uint32_t* __restrict__ assign,
-                                                            float* __restrict__ errors, uint32_t* __restrict__ flags,
-                                                            unsigned int* __restrict__ stat_pairs) {
-    __shared__ uint16_t p_blk[kRrMaxPairs];
-    __shared__ uint16_t p_c[kRrMaxPairs];
-    __shared__ float p_d[kRrMaxPairs];
-    __shared__ uint32_t warp_tot[kRrThreads / 32 + 1];
-    __shared__ uint32_t ovf_best_c[kRrThreads];
-    __shared__ float ovf_best_d[kRrThreads];
-    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const size_t tile_first = (size_t)blockIdx.x * kRrThreads;
-    const size_t blk = tile_first + tid;
+// stat[0] += exact distance evaluations on multi-candidate / overflow blocks, stat[1] += overflow blocks
+__global__ void __launch_bounds__(kRrThreads, 2) rerank_kernel(const float* __restrict__ feat, size_t n, const float* __restrict__ cent,
+                                                               uint32_t K, const uint4* __restrict__ cand, uint32_t* __restrict__ assign,
+                                                               float* __restrict__ errors, uint32_t* __restrict__ flags,
+                                                               unsigned int* __restrict__ stat) {
+    __shared__ uint8_t s_src[kRrThreads / 32][32];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int g = lane >> 1, h = lane & 1;
+    const size_t blk0 = ((size_t)blockIdx.x * (kRrThreads / 32) + wid) * 32;
+    if (blk0 >= n) return;
+    const size_t blk = blk0 + lane;
     const bool valid = blk < n;
     uint4 cw = make_uint4(0, 0, 0, 0);
-    if (valid) cw = cand[blk];
+    if (valid) cw = ldg_nc_v4(cand + blk);
     const uint32_t cnt_raw = valid ? (cw.w >> 16) : 0u;
     const bool overflow = cnt_raw == 0xffffu;
-    const uint32_t words[4] = {cw.x, cw.y, cw.z, cw.w};
-    // pairs this block contributes: none when the list has one entry and no error is wanted
-    uint32_t my_pairs = 0;
-    if (valid && !overflow && (cnt_raw > 1 || errors != nullptr)) my_pairs = cnt_raw;
-    // ---- exclusive scan of my_pairs over the CTA
-    uint32_t incl = my_pairs;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
-        if (lane >= o) incl += t;
-    }
-    if (lane == 31) warp_tot[wid] = incl;
-    __syncthreads();
-    if (wid == 0) {
-        uint32_t w = lane < kRrThreads / 32 ? warp_tot[lane] : 0u, wi = w;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const uint32_t t = __shfl_up_sync(0xffffffffu, wi, o);
-            if (lane >= o) wi += t;
+    // blocks that need arithmetic: none when the list has one entry and no error is wanted
+    const bool need = valid && !overflow && (cnt_raw > 1 || (errors != nullptr && cnt_raw == 1));
+    uint32_t best_c = cw.x & 0xffffu;
+    float best = 0.0f;
+    uint32_t pairs = (need && cnt_raw > 1) ? cnt_raw : 0u;
+
+    const unsigned need_mask = __ballot_sync(0xffffffffu, need);
+    const int n_need = __popc(need_mask);
+    const int my_rank = __popc(need_mask & ((1u << lane) - 1u));
+    if (need) s_src[wid][my_rank] = (uint8_t)lane;
+    __syncwarp();
+    for (int base = 0; base < n_need; base += 16) {
+        const int r = base + g;
+        const bool act = r < n_need;
+        const int src = act ? (int)s_src[wid][r] : 0;
+        const uint32_t w0 = __shfl_sync(0xffffffffu, cw.x, src), w1 = __shfl_sync(0xffffffffu, cw.y, src);
+        const uint32_t w2 = __shfl_sync(0xffffffffu, cw.z, src), w3 = __shfl_sync(0xffffffffu, cw.w, src);
+        const uint32_t m = act ? (w3 >> 16) : 0u;
+        RowHalf x;
+        x.load_stream(feat + (blk0 + (size_t)src) * 64, h);
+        const uint32_t m_max = __reduce_max_sync(0xffffffffu, m);
+        // the reference scans c ascending with strict '<' from FLT_MAX: smallest distance, lowest index
+        float bd = FLT_MAX;
+        uint32_t bc = 0;
+        bool have = false;
+        for (uint32_t i = 0; i < m_max; ++i) {
+            const uint32_t wsel = i < 2 ? w0 : (i < 4 ? w1 : (i < 6 ? w2 : w3));
+            const uint32_t c = i < m ? ((wsel >> (16 * (i & 1))) & 0xffffu) : 0u;
+            const float d = pair_distance(x, cent + (size_t)c * 64, h);
+            if (i < m && d < FLT_MAX && (!have || d < bd || (d == bd && c < bc))) {
+                bd = d;
+                bc = c;
+                have = true;
+            }
         }
-        if (lane < kRrThreads / 32) warp_tot[lane] = wi - w;
-        if (lane == kRrThreads / 32 - 1) warp_tot[kRrThreads / 32] = wi;
+        // hand the result back to the lane that owns the block
+        const int back = (2 * (my_rank - base)) & 31;
+        const uint32_t rc = __shfl_sync(0xffffffffu, bc, back);
+        const float rd = __shfl_sync(0xffffffffu, bd, back);
+        if (need && my_rank >= base && my_rank < base + 16) {
+            best_c = rc;
+            best = rd;
+        }
     }
-    __syncthreads();
-    const uint32_t first = warp_tot[wid] + incl - my_pairs;
-    const uint32_t total = warp_tot[kRrThreads / 32];
-    for (uint32_t i = 0; i < my_pairs; ++i) {
-        p_blk[first + i] = (uint16_t)tid;
-        p_c[first + i] = (uint16_t)((words[i >> 1] >> (16 * (i & 1))) & 0xffffu);
-    }
-    __syncthreads();
-    // ---- pairs: 16 per warp iteration
-    const int g = lane >> 1, l = lane & 1;
-    for (uint32_t p0 = (uint32_t)wid * 16; p0 < total; p0 += (kRrThreads / 32) * 16) {
-        const uint32_t p = p0 + g;
-        const bool act = p < total;
-        const uint32_t pb = act ? p_blk[p] : 0u, pc = act ? p_c[p] : 0u;
-        const float d = pair_distance(feat + (tile_first + pb) * 64, cent + (size_t)pc * 64, l);
-        if (act && l == 0) p_d[p] = d;
-    }
-    // ---- overflow blocks: full scan, one block per warp at a time, 16 centroids per iteration
+    // ---- overflow blocks (empty or overfull list: flat textures, NaN): full scan, 16 centroids per step
     unsigned ovf_mask = __ballot_sync(0xffffffffu, overflow);
+    const uint32_t n_ovf = (uint32_t)__popc(ovf_mask);
     while (ovf_mask) {
         const int src = __ffs(ovf_mask) - 1;
         ovf_mask &= ovf_mask - 1;
-        const float* x = feat + (tile_first + (size_t)(wid * 32 + src)) * 64;
-        float best = FLT_MAX;
-        uint32_t best_c = 0;
+        RowHalf x;
+        x.load_stream(feat + (blk0 + (size_t)src) * 64, h);
+        float bd = FLT_MAX;
+        uint32_t bc = 0;
         for (uint32_t c0 = 0; c0 < K; c0 += 16) {
             const uint32_t c = c0 + g;
-            const float d = pair_distance(x, cent + (size_t)(c < K ? c : 0) * 64, l);
-            if (c < K && d < best) {  // ascending c inside the group: strict '<' keeps the first minimum
-                best = d;
-                best_c = c;
+            const float d = pair_distance(x, cent + (size_t)(c < K ? c : 0) * 64, h);
+            if (c < K && d < bd) {  // ascending c inside the group: strict '<' keeps the first minimum
+                bd = d;
+                bc = c;
             }
         }
         // combine the 16 groups: smallest distance, lowest index on ties (what a serial scan returns)
 #pragma unroll
         for (int o = 2; o <= 16; o <<= 1) {
-            const float od = __shfl_xor_sync(0xffffffffu, best, o);
-            const uint32_t oc = __shfl_xor_sync(0xffffffffu, best_c, o);
-            if (od < best || (od == best && od < FLT_MAX && oc < best_c)) {
-                best = od;
-                best_c = oc;
+            const float od = __shfl_xor_sync(0xffffffffu, bd, o);
+            const uint32_t oc = __shfl_xor_sync(0xffffffffu, bc, o);
+            if (od < bd || (od == bd && od < FLT_MAX && oc < bc)) {
+                bd = od;
+                bc = oc;
             }
         }
-        if (lane == 0) {
-            ovf_best_c[wid * 32 + src] = best_c;
-            ovf_best_d[wid * 32 + src] = best;
+        if (lane == src) {
+            best_c = bc;
+            best = bd;
+            pairs = K;
         }
     }
-    __syncthreads();
-    // ---- selection
-    uint32_t pairs = 0;
     if (valid) {
-        uint32_t best_c = cw.x & 0xffffu;
-        float best = 0.0f;
-        if (overflow) {
-            best_c = ovf_best_c[tid];
-            best = ovf_best_d[tid];
-            pairs = K;
-        } else if (my_pairs) {
-            // the reference scans c ascending with strict '<' from FLT_MAX: smallest distance, lowest index
-            best = FLT_MAX;
-            best_c = 0;
-            bool have = false;
-            for (uint32_t i = 0; i < my_pairs; ++i) {
-                const float d = p_d[first + i];
-                const uint32_t c = p_c[first + i];
-                if (d < FLT_MAX && (!have || d < best || (d == best && c < best_c))) {
-                    best = d;
-                    best_c = c;
-                    have = true;
-                }
-            }
-            pairs = my_pairs > 1 ? my_pairs : 0;
-        }
         if (flags && assign[blk] != best_c) flags[0] = 1u;
         assign[blk] = best_c;
         if (errors) errors[blk] = best;
     }
-    if (stat_pairs) {
+    if (stat) {
         pairs = __reduce_add_sync(0xffffffffu, pairs);
-        if (lane == 0 && pairs) atomicAdd(stat_pairs, pairs);
+        if (lane == 0 && pairs) atomicAdd(stat, pairs);
+        if (lane == 0 && n_ovf) atomicAdd(stat + 1, n_ovf);
     }
 }
 
@@ -674,15 +686,16 @@ EncodeTiledFn encode_fn() {
     return fn;
 }
 
+// 2-D map over rows of `cols` bf16 elements
 bool make_map(CUtensorMap* m, const float* ptr, uint64_t cols, uint64_t rows, uint32_t box_cols, uint32_t box_rows,
               CUtensorMapSwizzle sw) {
     EncodeTiledFn fn = encode_fn();
     if (!fn) return false;
     const cuuint64_t dims[2] = {cols, rows};
-    const cuuint64_t strides[1] = {cols * sizeof(float)};
+    const cuuint64_t strides[1] = {cols * 2};
     const cuuint32_t box[2] = {box_cols, box_rows};
     const cuuint32_t estr[2] = {1, 1};
-    return fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(ptr), dims, strides, box, estr,
+    return fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<float*>(ptr), dims, strides, box, estr,
               CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
@@ -730,9 +743,9 @@ cudaError_t launch_assign_tc(const float* a_prime, const float* xnorm, size_t n,
     }
     const uint32_t k_pad = tc_padded_k(K);
     CUtensorMap tm_a, tm_b, tm_bx;
-    if (!make_map(&tm_a, a_prime, 64, n, 32, BM, CU_TENSOR_MAP_SWIZZLE_128B) ||
-        !make_map(&tm_b, b_main, 64, k_pad, 32, BN, CU_TENSOR_MAP_SWIZZLE_128B) ||
-        !make_map(&tm_bx, b_ext, 8, k_pad, 8, BN, CU_TENSOR_MAP_SWIZZLE_32B))
+    if (!make_map(&tm_a, a_prime, 128, n, 64, BM, CU_TENSOR_MAP_SWIZZLE_128B) ||
+        !make_map(&tm_b, b_main, 128, k_pad, 64, BN, CU_TENSOR_MAP_SWIZZLE_128B) ||
+        !make_map(&tm_bx, b_ext, 16, k_pad, 16, BN, CU_TENSOR_MAP_SWIZZLE_32B))
         return cudaErrorInvalidValue;
     const uint32_t num_tiles = (uint32_t)((n + BM - 1) / BM);
     const uint32_t num_chunks = k_pad / BN;
