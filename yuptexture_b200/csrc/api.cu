@@ -7,6 +7,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <numeric>
 #include <random>
@@ -219,7 +220,7 @@ int run_seeding(yupvq_ctx* ctx, const Blocks& b, uint32_t K, const Draws& dr, bo
     const size_t n = b.n;
     const int grid = (int)seed_grid_for(n);
     CK(ctx->min_dist.ensure(n * sizeof(float)));
-    CK(ctx->partial.ensure((size_t)grid * 8));
+    CK(ctx->partial.ensure(seed_partial_bytes(grid)));
     CK(ctx->seed_idx.ensure((size_t)K * 4));
     CK(ctx->canon.ensure(std::max<size_t>(1, dr.canon.size()) * 8));
     if (!dr.canon.empty())
@@ -233,9 +234,20 @@ int run_seeding(yupvq_ctx* ctx, const Blocks& b, uint32_t K, const Draws& dr, bo
     st.status = ctx->small.as<uint32_t>() + F_SEED_STATUS;
     st.grid = grid;
     LAUNCH(launch_seed_init(st, n, dr.first, ctx->stream));
-    for (uint32_t i = 1; i < K; ++i) {
-        if (hdr) LAUNCH(launch_seed_round_hdr(st, b.feat, n, i, K, ctx->stream));
-        else LAUNCH(launch_seed_round_ldr(st, b.planes, b.stride, n, b.ch, i, K, ctx->stream));
+    // one persistent cooperative kernel for all K-1 rounds; per-round launches only where that is not possible
+    static const bool per_round = getenv("YUPVQ_SEED_PER_ROUND") != nullptr;  // A/B timing and tests
+    cudaError_t pe = per_round ? cudaErrorNotSupported
+                               : launch_seed_persistent(st, b.planes, b.stride, b.feat, n, b.ch, hdr, K, ctx->stream);
+    if (pe == cudaSuccess) {
+        if (K > 1) ++ctx->launches;
+    } else if (pe == cudaErrorNotSupported || pe == cudaErrorCooperativeLaunchTooLarge) {
+        cudaGetLastError();  // not all CTAs can be co-resident (shared GPU, MPS limits): one launch per round instead
+        for (uint32_t i = 1; i < K; ++i) {
+            if (hdr) LAUNCH(launch_seed_round_hdr(st, b.feat, n, i, K, ctx->stream));
+            else LAUNCH(launch_seed_round_ldr(st, b.planes, b.stride, n, b.ch, i, K, ctx->stream));
+        }
+    } else {
+        CK(pe);
     }
     if (out_rounds) {
         CK(cudaMemcpyAsync(ctx->h_small, st.status, 8, cudaMemcpyDeviceToHost, ctx->stream));

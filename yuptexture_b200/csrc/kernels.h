@@ -40,9 +40,13 @@ struct SeedState {
     int grid;                     // CTAs per round (fixed for the whole seeding)
 };
 size_t seed_grid_for(size_t n);
+size_t seed_partial_bytes(int grid);
 cudaError_t launch_seed_init(const SeedState& st, size_t n, uint32_t first_idx, cudaStream_t s);
 cudaError_t launch_seed_round_ldr(const SeedState& st, const uint4* planes, size_t plane_stride, size_t n, int ch,
                                   uint32_t round, uint32_t K, cudaStream_t s);
+// all K-1 rounds in one cooperative launch; cudaErrorNotSupported -> use the per-round launches
+cudaError_t launch_seed_persistent(const SeedState& st, const uint4* planes, size_t plane_stride, const float* feat, size_t n,
+                                   int ch, bool hdr, uint32_t K, cudaStream_t s);
 cudaError_t launch_seed_round_hdr(const SeedState& st, const float* feat, size_t n, uint32_t round, uint32_t K,
                                   cudaStream_t s);
 

@@ -11,6 +11,9 @@
 // Roofline: HBM/L2-bound, (16*ch + 8) B per block per round; additionally latency-bound by K-1
 // dependent launches.
 #include <cfloat>
+#include <cstdio>
+#include <cstdlib>
+#include <type_traits>
 
 #include "common.cuh"
 #include "kernels.h"
@@ -253,12 +256,399 @@ __global__ void __launch_bounds__(kThreads) seed_round_hdr_kernel(SeedState st, 
     if (threadIdx.x == 0) *st.counter = 0;
 }
 
+// ================================================================================================
+// Persistent variant: ALL K-1 rounds in one cooperative launch (one CTA of 1024 threads per SM).
+// A round is latency-, not bandwidth-bound (its working set lives in L2 and partly in shared memory),
+// so what matters is the dependency chain  min-update -> global sum -> weighted pick -> next seed:
+//   (1) every WARP publishes its partial sum as one tagged 64-bit word [round:16 | sum:48] with a
+//       release store (HDR: a {double, tag} pair) -- no CTA barrier on the way;
+//   (2) the leader CTA polls all W warp words (five per thread, requested together), scans them, draws
+//       p = u * S, finds the owning warp, reads that warp's <= bpw minimum distances from L2 (acquire /
+//       release makes them visible) and finds the block;
+//   (3) the pick is published as a tagged word that one thread per CTA polls.
+// Three L2 round trips per round and no all-to-all polling (148 x 148 pollers on ten cache lines cost
+// 8 us per round when tried).  Block ownership is hierarchical and contiguous (warp > 32-block segment
+// > lane), so prefix order == block index order, which "first j with prefix >= p" (reference :306-312)
+// needs.  LDR sums are uint64 (exact, F12): the search runs on integers, first j with prefix_j >= ceil(p).
+// The first `cseg` segments of every warp keep their pixel planes in shared memory for the whole kernel
+// (up to ~200 KB per SM), which takes that share of the per-round traffic off the L2.
+// ================================================================================================
+constexpr int kPThreads = 1024;
+constexpr int kPWarps = kPThreads / 32;
+constexpr int kPMaxGrid = 160;                    // >= SM count
+constexpr int kPPer = kPMaxGrid * kPWarps / kPThreads;   // warp words per leader thread (5)
+constexpr unsigned long long kTagShift = 48;
+constexpr unsigned long long kPayloadMask = (1ull << kTagShift) - 1ull;
+constexpr unsigned long long kStopBit = 1ull << 47;
+
+__device__ __forceinline__ void st_relaxed_u64(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_u64(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+template <typename T>
+__device__ __forceinline__ T warp_incl_scan(T v, int lane) {
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const T t = __shfl_up_sync(0xffffffffu, v, o);
+        if (lane >= o) v += t;
+    }
+    return v;
+}
+
+#ifdef YUPVQ_SEED_TIMING
+#define TICK(acc) do { t1 = clock64(); acc += t1 - t0; t0 = t1; } while (0)
+#else
+#define TICK(acc) do { } while (0)
+#endif
+
+// HDR == false: CH uint4 planes per block, SAD^2, uint64 sums.  HDR == true: 64-float rows, weighted L2, double sums.
+// Exchange words in st.partial: [0, 2W) warp words (LDR uses the first W), then the pick word.
+template <bool HDR, int CH, bool MDREG>
+__global__ void __launch_bounds__(kPThreads, 1)
+seed_persistent_kernel(SeedState st, const uint4* __restrict__ planes, size_t stride, const float* __restrict__ feat, size_t n,
+                       size_t bpw, int cseg, uint32_t K) {
+    using ACC = typename std::conditional<HDR, double, unsigned long long>::type;
+    extern __shared__ uint4 s_cache[];            // LDR: [warp][cseg][CH][32] pixel planes
+    __shared__ ACC s_scan[kPWarps + 1];
+    __shared__ ACC s_target;
+    __shared__ unsigned int s_hit;
+    __shared__ unsigned long long s_pick;
+    __shared__ float4 s_seedf[16];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int W = gridDim.x * kPWarps;
+    const size_t gw = (size_t)blockIdx.x * kPWarps + wid;
+    const size_t wbase = gw * bpw;
+    const size_t wend = wbase + bpw < n ? wbase + bpw : n;  // may be <= wbase: empty warp
+    const int nseg = (int)(bpw / 32);
+    unsigned long long* wwords = st.partial;
+    unsigned long long* pick = st.partial + 2 * kPMaxGrid * kPWarps;
+    const bool leader = blockIdx.x == 0;
+
+    if (!HDR) {  // resident pixel planes
+        for (int i = 0; i < cseg; ++i) {
+            const size_t j = wbase + (size_t)i * 32 + lane;
+#pragma unroll
+            for (int q = 0; q < CH; ++q)
+                s_cache[((wid * cseg + i) * CH + q) * 32 + lane] = j < wend ? ldg_nc_v4(planes + q * stride + j) : make_uint4(0, 0, 0, 0);
+        }
+        __syncwarp();
+    }
+
+    float md[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) md[i] = FLT_MAX;  // seed_init_kernel wrote the same value to min_dist
+    // per-lane constants of the update loop
+    unsigned int vmask = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+        if (i < nseg && wbase + (size_t)i * 32 + lane < wend) vmask |= 1u << i;
+    float* const mdp = st.min_dist + wbase + lane;
+    const uint4* gp[HDR ? 1 : CH];
+#pragma unroll
+    for (int q = 0; q < (HDR ? 1 : CH); ++q) gp[q] = planes + q * stride + wbase + lane;
+    const uint4* const sc = s_cache + (size_t)wid * cseg * CH * 32 + lane;
+    uint32_t seed = st.seed_idx[0];
+#ifdef YUPVQ_SEED_TIMING
+    long long t_upd = 0, t_poll = 0, t_l2 = 0, t_pick = 0, t_p1 = 0, t_p2 = 0, t0 = 0, t1;
+#endif
+    for (uint32_t round = 1; round < K; ++round) {
+#ifdef YUPVQ_SEED_TIMING
+        t0 = clock64();
+#endif
+        const double canon_u = (leader && tid == 31) ? st.canon[round - 1] : 0.0;  // fetched early: off the critical path
+        // ---- the new seed's data
+        uint4 sp[HDR ? 1 : CH];
+        if (HDR) {
+            if (tid < 16) s_seedf[tid] = reinterpret_cast<const float4*>(feat)[(size_t)seed * 16 + tid];
+            __syncthreads();
+        } else {
+#pragma unroll
+            for (int q = 0; q < CH; ++q) sp[q] = __ldg(planes + q * stride + seed);
+        }
+        // ---- min-distance update over this lane's blocks
+        ACC local = (ACC)0;
+        auto block_dist = [&](int i, size_t j) -> float {
+            if (HDR) {
+                const float4* x = reinterpret_cast<const float4*>(feat) + j * 16;
+                DistAcc acc;
+                acc.reset();
+#pragma unroll
+                for (int k = 0; k < 8; ++k) acc.step(x[2 * k], x[2 * k + 1], s_seedf[2 * k], s_seedf[2 * k + 1]);
+                return acc.finish();                                           // HDR seeds on d, not d*d (:536-537)
+            } else {
+                unsigned int sad = 0;
+#pragma unroll
+                for (int q = 0; q < CH; ++q) {
+                    const uint4 v = i < cseg ? s_cache[((wid * cseg + i) * CH + q) * 32 + lane] : ldg_nc_v4(planes + q * stride + j);
+                    sad = __vsadu4(v.x, sp[q].x) + sad;
+                    sad = __vsadu4(v.y, sp[q].y) + sad;
+                    sad = __vsadu4(v.z, sp[q].z) + sad;
+                    sad = __vsadu4(v.w, sp[q].w) + sad;
+                }
+                const float d = (float)sad;                                    // BlockDistanceSAD returns float(sad)
+                return __fmul_rn(d, d);
+            }
+        };
+        if (MDREG && !HDR) {
+            // minimum distances live in registers (nseg <= 8): no loads that could alias the stores, so the
+            // pixel loads of all segments are free to be issued early; a value is stored (for the leader's
+            // level-2 search) only when it changed.  Addresses and validity are precomputed: about 25
+            // instructions per block.  Values are integers < 2^29 and there are at most 8: a 32-bit sum is exact.
+            unsigned int loc32 = 0;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                if ((vmask >> i) & 1u) {
+                    unsigned int sad = 0;
+                    if (i < cseg) {
+#pragma unroll
+                        for (int q = 0; q < CH; ++q) {
+                            const uint4 v = sc[(i * CH + q) * 32];
+                            sad = __vsadu4(v.x, sp[q].x) + sad;
+                            sad = __vsadu4(v.y, sp[q].y) + sad;
+                            sad = __vsadu4(v.z, sp[q].z) + sad;
+                            sad = __vsadu4(v.w, sp[q].w) + sad;
+                        }
+                    } else {
+#pragma unroll
+                        for (int q = 0; q < CH; ++q) {
+                            const uint4 v = ldg_nc_v4(gp[q] + i * 32);
+                            sad = __vsadu4(v.x, sp[q].x) + sad;
+                            sad = __vsadu4(v.y, sp[q].y) + sad;
+                            sad = __vsadu4(v.z, sp[q].z) + sad;
+                            sad = __vsadu4(v.w, sp[q].w) + sad;
+                        }
+                    }
+                    const float d = (float)sad;                                // BlockDistanceSAD returns float(sad)
+                    const float m = fminf(__fmul_rn(d, d), md[i]);             // std::min(d * d, minDistSq[j])
+                    if (m != md[i]) {
+                        md[i] = m;
+                        __stcg(mdp + i * 32, m);
+                    }
+                    loc32 += __float2uint_rn(m);
+                }
+            }
+            local = (ACC)loc32;
+        } else if (MDREG) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const size_t j = wbase + (size_t)i * 32 + lane;
+                if ((vmask >> i) & 1u) {
+                    const float m = fminf(block_dist(i, j), md[i]);               // std::min(d, minDistSq[j])
+                    if (m != md[i]) {
+                        md[i] = m;
+                        __stcg(mdp + i * 32, m);
+                    }
+                    local += (ACC)m;
+                }
+            }
+        } else {
+#pragma unroll 2
+            for (int i = 0; i < nseg; ++i) {
+                const size_t j = wbase + (size_t)i * 32 + lane;
+                if (j < wend) {
+                    const float m = fminf(block_dist(i, j), __ldcg(st.min_dist + j));
+                    __stcg(st.min_dist + j, m);
+                    local += (ACC)m;
+                }
+            }
+        }
+        local = warp_sum(local);
+        __syncwarp();  // orders every lane's min_dist stores before lane 0's release
+        if (lane == 0) {
+            if (HDR) {
+                st_relaxed_u64(wwords + 2 * gw, (unsigned long long)__double_as_longlong((double)local));
+                st_release_u64(wwords + 2 * gw + 1, (unsigned long long)round);
+            } else {
+                st_release_u64(wwords + gw, ((unsigned long long)round << kTagShift) | (unsigned long long)local);
+            }
+        }
+        TICK(t_upd);
+        if (leader) {
+            // ---- (2) all warp partials -> S, p, owning warp
+            ACC v[kPPer];
+            for (;;) {  // this thread's words are requested together and re-requested until every tag matches
+                unsigned long long w[kPPer], tg[kPPer];
+#pragma unroll
+                for (int k = 0; k < kPPer; ++k) {
+                    const int idx = tid * kPPer + k;
+                    w[k] = 0;
+                    tg[k] = (unsigned long long)round;
+                    if (idx < W) {
+                        if (HDR) {
+                            tg[k] = ld_relaxed_u64(wwords + 2 * idx + 1);
+                        } else {
+                            w[k] = ld_relaxed_u64(wwords + idx);
+                            tg[k] = w[k] >> kTagShift;
+                            w[k] &= kPayloadMask;
+                        }
+                    }
+                }
+                bool ok = true;
+#pragma unroll
+                for (int k = 0; k < kPPer; ++k) ok = ok && tg[k] == (unsigned long long)round;
+                if (ok) {
+                    // relaxed polls (independent, one round trip for all five) + one acquire fence: pairs with the
+                    // warps' release stores, so their min_dist (and HDR value) stores are visible from here on
+                    __threadfence();
+#pragma unroll
+                    for (int k = 0; k < kPPer; ++k) {
+                        const int idx = tid * kPPer + k;
+                        if (HDR) v[k] = idx < W ? (ACC)__longlong_as_double((long long)ld_relaxed_u64(wwords + 2 * idx)) : (ACC)0;
+                        else v[k] = (ACC)w[k];
+                    }
+                    break;
+                }
+            }
+            TICK(t_p1);
+            ACC thread_tot = (ACC)0;
+#pragma unroll
+            for (int k = 0; k < kPPer; ++k) thread_tot += v[k];
+            const ACC incl = warp_incl_scan<ACC>(thread_tot, lane);
+            if (lane == 31) s_scan[wid] = incl;
+            if (tid == 0) s_hit = 0xffffffffu;
+            __syncthreads();
+            TICK(t_p2);
+            if (wid == 0) {
+                const ACC wt = s_scan[lane];
+                const ACC wi = warp_incl_scan<ACC>(wt, lane);
+                s_scan[lane] = wi - wt;                                        // exclusive prefix of the warps
+                if (lane == 31) {
+                    s_scan[kPWarps] = wi;                                      // S
+                    ACC target = (ACC)0;
+                    if ((double)wi > 0.0) {
+                        const double p = __dadd_rn(__dmul_rn(canon_u, (double)wi), 0.0);
+                        // LDR: first j with prefix_j >= p  <=>  prefix_j >= ceil(p) on exact integers
+                        target = HDR ? (ACC)p : (ACC)(p <= 0.0 ? 0.0 : ceil(p));
+                    }
+                    s_target = target;
+                }
+            }
+            __syncthreads();
+            const ACC total = s_scan[kPWarps];
+            if (!((double)total > 0.0)) {  // reference :299-302: fill the rest with seed 0 and stop
+                for (uint32_t rr = round + tid; rr < K; rr += kPThreads) st.seed_idx[rr] = st.seed_idx[0];
+                if (tid == 0) {
+                    st.status[0] = round;
+                    st_relaxed_u64(pick, ((unsigned long long)round << kTagShift) | kStopBit);
+                }
+                return;
+            }
+            const ACC target = s_target;
+            ACC cum = s_scan[wid] + (incl - thread_tot);
+            const ACC my_before = cum;
+            int my_hit = -1;
+#pragma unroll
+            for (int k = 0; k < kPPer; ++k) {
+                const int idx = tid * kPPer + k;
+                if (idx < W && my_hit < 0) {
+                    if (cum + v[k] >= target) my_hit = k;
+                    else cum += v[k];
+                }
+            }
+            if (my_hit >= 0) atomicMin(&s_hit, (unsigned int)(tid * kPPer + my_hit));
+            __syncthreads();
+            unsigned int hw = s_hit;                                           // owning warp (global index)
+            const bool take_last = hw == 0xffffffffu;                          // HDR only: rounding of the tree sum
+            if (take_last) hw = (unsigned int)(W - 1);
+            if ((int)hw / kPPer == tid) s_target = target - cum;               // residual inside that warp (cum stopped there)
+            (void)my_before;
+            __syncthreads();
+            TICK(t_poll);
+            if (wid == 0) {
+                // ---- level 2: which block of warp hw's range
+                const ACC resid = s_target;
+                const size_t obase = (size_t)hw * bpw;
+                const size_t oend = obase + bpw < n ? obase + bpw : n;
+                ACC run = (ACC)0;
+                size_t chosen = n - 1;                                         // take_last / rounding fallback
+                bool found = false;
+                // the warp's blocks are contiguous in memory: lane l takes eight consecutive values of each
+                // 256-block chunk, so prefix order is lane order and one warp scan per chunk locates the block
+                for (size_t k0 = 0; k0 < bpw && !found; k0 += 256) {
+                    const size_t j0 = obase + k0 + (size_t)lane * 8;
+                    float vals[8];
+                    if (j0 + 8 <= oend) {  // obase, bpw multiples of 32 -> 16-byte aligned
+                        const float4 a = __ldcg(reinterpret_cast<const float4*>(st.min_dist + j0));
+                        const float4 b = __ldcg(reinterpret_cast<const float4*>(st.min_dist + j0) + 1);
+                        vals[0] = a.x; vals[1] = a.y; vals[2] = a.z; vals[3] = a.w;
+                        vals[4] = b.x; vals[5] = b.y; vals[6] = b.z; vals[7] = b.w;
+                    } else {
+#pragma unroll
+                        for (int u = 0; u < 8; ++u) vals[u] = (j0 + u < oend && k0 + (size_t)lane * 8 + u < bpw) ? __ldcg(st.min_dist + j0 + u) : 0.0f;
+                    }
+                    if (k0 + (size_t)lane * 8 >= bpw) {
+#pragma unroll
+                        for (int u = 0; u < 8; ++u) vals[u] = 0.0f;
+                    }
+                    ACC mine = (ACC)0;
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) mine += (ACC)vals[u];
+                    const ACC sincl = warp_incl_scan<ACC>(mine, lane);
+                    const ACC chunk = __shfl_sync(0xffffffffu, sincl, 31);
+                    if (!take_last && run + chunk >= resid) {
+                        ACC cum2 = run + (sincl - mine);
+                        int u_hit = -1;
+#pragma unroll
+                        for (int u = 0; u < 8; ++u) {
+                            cum2 += (ACC)vals[u];
+                            if (u_hit < 0 && j0 + u < oend && cum2 >= resid) u_hit = u;
+                        }
+                        const unsigned hit = __ballot_sync(0xffffffffu, u_hit >= 0);
+                        if (hit) {
+                            const int f = __ffs(hit) - 1;
+                            chosen = obase + k0 + (size_t)f * 8 + (size_t)__shfl_sync(0xffffffffu, u_hit, f);
+                            found = true;
+                        }
+                    }
+                    run += chunk;
+                }
+                if (lane == 0) {
+                    st.seed_idx[round] = (uint32_t)chosen;
+                    st.status[1] = round;                                      // rounds that drew a sample
+                    st_relaxed_u64(pick, ((unsigned long long)round << kTagShift) | (unsigned long long)chosen);
+                }
+            }
+            TICK(t_l2);
+        }
+        // ---- (3) everyone: wait for the pick
+        if (tid == 0) {
+            unsigned long long w;
+            do { w = ld_relaxed_u64(pick); } while ((w >> kTagShift) != (unsigned long long)round);
+            s_pick = w;
+        }
+        __syncthreads();
+        if (s_pick & kStopBit) return;
+        seed = (uint32_t)(s_pick & 0xffffffffull);
+        TICK(t_pick);
+    }
+#ifdef YUPVQ_SEED_TIMING
+    if (tid == 0 && (blockIdx.x == 0 || blockIdx.x == 77))
+        printf("cta %d: cycles/round update %lld, poll %lld, sync1 %lld, scan %lld, level2 %lld, pick %lld\n", blockIdx.x, t_upd / (K - 1),
+               t_p1 / (K - 1), t_p2 / (K - 1), t_poll / (K - 1), t_l2 / (K - 1), t_pick / (K - 1));
+#endif
+}
+
 inline size_t chunk_for(size_t n, int grid) {
     size_t c = (n + grid - 1) / grid;
     return (c + kThreads - 1) / kThreads * kThreads;
 }
 
 }  // namespace
+
+// bytes of SeedState::partial: per-round partial sums of the launch-per-round kernels, or the tagged
+// exchange words of the persistent kernel ([2 * kPMaxGrid] slots + the pick word)
+size_t seed_partial_bytes(int grid) {
+    const size_t a = (size_t)(grid > 0 ? grid : 0) * 8, b = (size_t)(2 * kPMaxGrid * kPWarps + 8) * 8;
+    return a > b ? a : b;
+}
 
 size_t seed_grid_for(size_t n) {
     size_t g = (n + kThreads - 1) / kThreads;
@@ -271,6 +661,8 @@ size_t seed_grid_for(size_t n) {
 }
 
 cudaError_t launch_seed_init(const SeedState& st, size_t n, uint32_t first_idx, cudaStream_t s) {
+    cudaError_t e = cudaMemsetAsync(st.partial, 0, seed_partial_bytes(0), s);  // tagged words of the persistent kernel
+    if (e != cudaSuccess) return e;
     seed_init_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(st.min_dist, n, st.counter, st.status, st.seed_idx,
                                                                  first_idx);
     return cudaGetLastError();
@@ -288,6 +680,55 @@ cudaError_t launch_seed_round_ldr(const SeedState& st, const uint4* planes, size
         default: return cudaErrorInvalidValue;
     }
     return cudaGetLastError();
+}
+
+cudaError_t launch_seed_persistent(const SeedState& st, const uint4* planes, size_t plane_stride, const float* feat, size_t n,
+                                   int ch, bool hdr, uint32_t K, cudaStream_t s) {
+    if (K <= 1) return cudaSuccess;
+    static int sms = 0, coop = -1;
+    if (coop < 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+    }
+    if (!coop || sms <= 0) return cudaErrorNotSupported;
+    size_t g = (n + kPThreads - 1) / kPThreads;
+    if (g > (size_t)sms) g = sms;
+    if (g > (size_t)kPMaxGrid) g = kPMaxGrid;
+    if (g < 1) g = 1;
+    size_t bpw = (n + g * kPWarps - 1) / (g * kPWarps);
+    bpw = (bpw + 31) / 32 * 32;
+    if (!hdr && bpw * kPWarps >= ((size_t)1 << 19)) return cudaErrorNotSupported;  // CTA partial must fit 48 bits
+    const bool mdreg = bpw / 32 <= 8;
+    const void* fn = nullptr;
+    if (hdr) fn = mdreg ? (const void*)seed_persistent_kernel<true, 1, true> : (const void*)seed_persistent_kernel<true, 1, false>;
+    else if (ch == 1) fn = mdreg ? (const void*)seed_persistent_kernel<false, 1, true> : (const void*)seed_persistent_kernel<false, 1, false>;
+    else if (ch == 2) fn = mdreg ? (const void*)seed_persistent_kernel<false, 2, true> : (const void*)seed_persistent_kernel<false, 2, false>;
+    else if (ch == 3) fn = mdreg ? (const void*)seed_persistent_kernel<false, 3, true> : (const void*)seed_persistent_kernel<false, 3, false>;
+    else if (ch == 4) fn = mdreg ? (const void*)seed_persistent_kernel<false, 4, true> : (const void*)seed_persistent_kernel<false, 4, false>;
+    else return cudaErrorInvalidValue;
+    // shared-memory resident segments per warp: as many as fit in ~200 KB
+    int cseg = 0;
+    size_t smem = 0;
+    if (!hdr) {
+        const size_t seg_bytes = (size_t)kPWarps * 32 * ch * 16;
+        cseg = (int)((200u * 1024u) / seg_bytes);
+        if ((size_t)cseg > bpw / 32) cseg = (int)(bpw / 32);
+        static const char* no_cache = getenv("YUPVQ_SEED_NO_SMEM");
+        if (no_cache) cseg = 0;
+        smem = (size_t)cseg * seg_bytes;
+        static bool attr[12] = {};  // dynamic + static shared memory may exceed the 48 KB default: always opt in
+        const int ai = ch * 2 + (mdreg ? 1 : 0);
+        if (smem > 0 && !attr[ai]) {
+            cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(200u * 1024u));
+            if (e != cudaSuccess) return e;
+            attr[ai] = true;
+        }
+    }
+    SeedState st_copy = st;
+    void* args[] = {&st_copy, (void*)&planes, &plane_stride, (void*)&feat, &n, &bpw, &cseg, &K};
+    return cudaLaunchCooperativeKernel(fn, dim3((unsigned)g), dim3(kPThreads), args, smem, s);
 }
 
 cudaError_t launch_seed_round_hdr(const SeedState& st, const float* feat, size_t n, uint32_t round, uint32_t K,
