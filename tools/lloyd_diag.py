@@ -8,7 +8,7 @@ img = synth.ldr_rgb(4096, 4096, seed=1000)
 bc = synth.bc1_encode(img)
 n = len(bc)
 prev = None
-for iters in (1, 2, 4, 8, 16, 32):
+for iters in [int(x) for x in os.environ.get('LLOYD_ITERS', '1,2,4,8,16,32').split(',')]:
     cfg = binding.make_config(quality=0.8, max_iterations=iters, seed=42)
     for _ in range(2):
         cent, idx, st = enc.encode_bcn(bc, n, 1, 3, cfg)

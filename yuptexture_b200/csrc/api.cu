@@ -67,7 +67,7 @@ struct yupvq_ctx {
     DevBuf assign, errors, cent, acc;                  // Lloyd
     DevBuf cent_px, cent_feat, out_idx;                // finalize / quantize
     // tensor engine (assign_tc.cu): per block set A', |x'|, mu; per pass B', folded norms, candidates
-    DevBuf tc_a, tc_xnorm, tc_small, tc_b, tc_bx, tc_cand;
+    DevBuf tc_a, tc_xnorm, tc_small, tc_b, tc_bx, tc_cand, tc_amb;
     const float* tc_feat = nullptr;                    // block set the A' buffer was built from
     size_t tc_n = 0;
     uint64_t rerank_pairs = 0;
@@ -105,7 +105,8 @@ namespace {
 
 // small device scratch layout (uint32 words)
 enum { F_CHANGED = 0, F_EMPTY = 1, F_RESEEDS = 2, F_SPARE = 3, F_SEED_STATUS = 4 /*2 words*/, F_COUNTER = 6, F_MAXABS = 7,
-       F_PAIRS = 8, F_WORDS = 16 };
+       F_PAIRS = 8 /*2 words*/, F_CTL = 10 /*stop, passes, empty clusters*/, F_AMB = 13 /*count, ticket*/,
+       F_WORDS = 16 };
 // tc_small layout (bytes): [0,512) column sums fp64 | [512,768) mu fp32 | [768,772) cmax
 enum { TC_SUMS = 0, TC_MU = 512, TC_CMAX = 768, TC_SMALL_BYTES = 1024 };
 
@@ -343,11 +344,11 @@ int tc_prepare_blocks(yupvq_ctx* ctx, const float* feat, size_t n) {
 // One assignment pass.  errors may be null (tensor mode then skips the exact distance of blocks with
 // a single candidate); flags[0] |= 1 when an assignment changed.
 int assign_blocks(yupvq_ctx* ctx, const float* feat, size_t n, const float* cent, uint32_t K, int mode, uint32_t* assign,
-                  float* errors, uint32_t* flags) {
+                  float* errors, uint32_t* flags, const uint32_t* stop = nullptr) {
     if (mode == YUPVQ_ASSIGN_TENSOR && !tc_supported(K))
         return ctx->fail("tensor assignment needs 1 <= K <= 65535 and a driver with cuTensorMapEncodeTiled (K = %u)", K);
     if (!use_tensor(mode, n, K)) {
-        LAUNCH(launch_assign_exact(feat, n, cent, K, assign, errors, flags, ctx->stream));
+        LAUNCH(launch_assign_exact(feat, n, cent, K, assign, errors, flags, stop, ctx->stream));
         return 0;
     }
     if (tc_prepare_blocks(ctx, feat, n)) return 1;
@@ -358,10 +359,23 @@ int assign_blocks(yupvq_ctx* ctx, const float* feat, size_t n, const float* cent
     uint8_t* sm = ctx->tc_small.as<uint8_t>();
     LAUNCH(launch_tc_prep_centroids(cent, K, reinterpret_cast<const float*>(sm + TC_MU), ctx->tc_b.as<float>(),
                                     ctx->tc_bx.as<float>(), reinterpret_cast<float*>(sm + TC_CMAX), ctx->stream));
-    LAUNCH(launch_assign_tc(ctx->tc_a.as<float>(), ctx->tc_xnorm.as<float>(), n, ctx->tc_b.as<float>(), ctx->tc_bx.as<float>(),
-                            K, reinterpret_cast<const float*>(sm + TC_CMAX), ctx->tc_cand.as<uint4>(), ctx->stream));
-    LAUNCH(launch_rerank(feat, n, cent, K, ctx->tc_cand.as<uint4>(), assign, errors, flags,
-                         ctx->small.as<unsigned int>() + F_PAIRS, ctx->stream));
+    uint32_t* small = ctx->small.as<uint32_t>();
+    if (errors) {
+        // errors[] wanted for every block: dense candidate lists + dense re-rank
+        LAUNCH(launch_assign_tc(ctx->tc_a.as<float>(), ctx->tc_xnorm.as<float>(), n, ctx->tc_b.as<float>(), ctx->tc_bx.as<float>(),
+                                K, reinterpret_cast<const float*>(sm + TC_CMAX), ctx->tc_cand.as<uint4>(), nullptr, nullptr, nullptr,
+                                nullptr, stop, ctx->stream));
+        LAUNCH(launch_rerank(feat, n, cent, K, ctx->tc_cand.as<uint4>(), assign, errors, flags, small + F_PAIRS, stop, ctx->stream));
+    } else {
+        // the front-end finishes single-candidate blocks itself; the exact re-rank sees only the ambiguous ones
+        CK(ctx->tc_amb.ensure(std::max<size_t>(1, n) * 4));
+        if (!stop) CK(cudaMemsetAsync(small + F_AMB, 0, 8, ctx->stream));  // inside the Lloyd loop the re-rank leaves it cleared
+        LAUNCH(launch_assign_tc(ctx->tc_a.as<float>(), ctx->tc_xnorm.as<float>(), n, ctx->tc_b.as<float>(), ctx->tc_bx.as<float>(),
+                                K, reinterpret_cast<const float*>(sm + TC_CMAX), ctx->tc_cand.as<uint4>(), assign, flags,
+                                ctx->tc_amb.as<uint32_t>(), small + F_AMB, stop, ctx->stream));
+        LAUNCH(launch_rerank_sparse(feat, cent, K, ctx->tc_cand.as<uint4>(), ctx->tc_amb.as<uint32_t>(), small + F_AMB,
+                                    small + F_AMB + 1, assign, flags, small + F_PAIRS, ctx->stream));
+    }
     return 0;
 }
 
@@ -403,37 +417,69 @@ int run_lloyd(yupvq_ctx* ctx, const Blocks& b, size_t n_total, size_t first_bloc
     const int shift = fixed_shift(n_total, max_abs);
 
     uint32_t passes = 0;
-    for (uint32_t iter = 0; iter < max_iter; ++iter) {
+    static const bool force_sync = getenv("YUPVQ_LLOYD_SYNC") != nullptr;  // A/B timing only
+    const bool async_loop = !ctx->comm && !force_sync;
+    if (async_loop) {
+        // Single GPU: every pass is enqueued without a host round trip.  The reference's convergence test
+        // (between assign and update) runs on the device (launch_lloyd_control); once it fires, the kernels
+        // of that pass' update and of all later passes return immediately.  The host looks at the stop word
+        // only a few times, to avoid enqueueing dozens of no-op passes for textures that converge at once.
+        uint32_t* ctl = flags + F_CTL;
+        static const int dbg_async0 = getenv("YUPVQ_ASYNC_DBG") ? atoi(getenv("YUPVQ_ASYNC_DBG")) : 0;
+        const uint32_t* stopk = (dbg_async0 & 4) ? nullptr : ctl;
+        CK(cudaMemsetAsync(ctl, 0, 12 + 8, ctx->stream));  // stop, passes, empty | ambiguous-row count, ticket
         CK(cudaMemsetAsync(flags, 0, 8, ctx->stream));  // changed, empty
-        // tensor mode computes errors[] lazily (they only feed the empty-cluster reseed)
-        if (assign_blocks(ctx, b.feat, n, cent, K, assign_mode, assign, tensor ? nullptr : errors, flags)) return 1;
-        ++passes;
-        // The reference checks hasChanged between assign and update; the update is launched
-        // speculatively so one sync (and, sharded, one all-reduce) per pass carries both.
-        CK(cudaMemsetAsync(acc, 0, acc_words * 8, ctx->stream));
-        LAUNCH(launch_accumulate(b.feat, n, assign, K, shift, acc, flags, ctx->stream));
-        if (ctx->comm) {
-            if (ctx->nccl.all_reduce_sum_i64(ctx->comm, acc, acc_words, ctx->stream)) return ctx->fail("ncclAllReduce(sum) failed");
+        for (uint32_t iter = 0; iter < max_iter; ++iter) {
+            // tensor mode computes errors[] lazily (they only feed the empty-cluster reseed)
+            if (assign_blocks(ctx, b.feat, n, cent, K, assign_mode, assign, tensor ? nullptr : errors, flags, stopk)) return 1;
+            CK(cudaMemsetAsync(acc, 0, acc_words * 8, ctx->stream));
+            LAUNCH(launch_accumulate(b.feat, n, assign, K, shift, acc, flags, stopk, ctx->stream));
+            LAUNCH(launch_lloyd_control(acc, K, iter, break_after, flags, ctl, ctx->stream));
+            static const int dbg_async2 = getenv("YUPVQ_ASYNC_DBG") ? atoi(getenv("YUPVQ_ASYNC_DBG")) : 0;
+            if (tensor && !(dbg_async2 & 2))  // errors[i] = distance to the assigned centroid, before the update (:336); only if a reseed needs them
+                LAUNCH(launch_exact_errors(b.feat, n, cent, assign, errors, stopk, ctl + 2, ctx->stream));
+            LAUNCH(launch_finalize_centroids(acc, K, shift, cent, flags, stopk, ctx->stream));
+            LAUNCH(launch_reseed_empty(b.feat, n, errors, acc, K, cent, flags, stopk, ctx->stream));
+            static const int dbg_async = getenv("YUPVQ_ASYNC_DBG") ? atoi(getenv("YUPVQ_ASYNC_DBG")) : 0;
+            if (dbg_async & 1) CK(cudaStreamSynchronize(ctx->stream));
+            if ((iter == 3 || iter == 7 || iter == 15) && iter + 1 < max_iter) {
+                CK(cudaMemcpyAsync(ctx->h_small, ctl, 4, cudaMemcpyDeviceToHost, ctx->stream));
+                CK(cudaStreamSynchronize(ctx->stream));
+                if (ctx->h_small[0]) break;
+            }
         }
-        LAUNCH(launch_count_empty(acc, K, flags + F_SPARE, ctx->stream));
-        CK(cudaMemcpyAsync(ctx->h_small, acc + (size_t)K * 65, 8, cudaMemcpyDeviceToHost, ctx->stream));
-        CK(cudaMemcpyAsync(ctx->h_small + 2, flags + F_SPARE, 4, cudaMemcpyDeviceToHost, ctx->stream));
-        CK(cudaStreamSynchronize(ctx->stream));
-        long long changed;
-        std::memcpy(&changed, ctx->h_small, 8);
-        if (!changed && iter > break_after) break;
-        if (tensor && ctx->h_small[2] != 0)  // errors[i] = distance to the assigned centroid, before the update (:336)
-            LAUNCH(launch_exact_errors(b.feat, n, cent, assign, errors, ctx->stream));
-        LAUNCH(launch_finalize_centroids(acc, K, shift, cent, flags, ctx->stream));
-        if (!ctx->comm) {
-            LAUNCH(launch_reseed_empty(b.feat, n, errors, acc, K, cent, flags, ctx->stream));
-        } else if (reseed_sharded(ctx, b, first_block, K, cent, errors, acc, flags)) {
-            return 1;
+        CK(cudaMemcpyAsync(ctx->h_small + 4, ctl + 1, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    } else {
+        for (uint32_t iter = 0; iter < max_iter; ++iter) {
+            CK(cudaMemsetAsync(flags, 0, 8, ctx->stream));  // changed, empty
+            if (assign_blocks(ctx, b.feat, n, cent, K, assign_mode, assign, tensor ? nullptr : errors, flags)) return 1;
+            ++passes;
+            // The reference checks hasChanged between assign and update; the update is launched
+            // speculatively so one sync and one all-reduce per pass carry both.
+            CK(cudaMemsetAsync(acc, 0, acc_words * 8, ctx->stream));
+            LAUNCH(launch_accumulate(b.feat, n, assign, K, shift, acc, flags, nullptr, ctx->stream));
+            if (ctx->comm && ctx->nccl.all_reduce_sum_i64(ctx->comm, acc, acc_words, ctx->stream)) return ctx->fail("ncclAllReduce(sum) failed");
+            LAUNCH(launch_count_empty(acc, K, flags + F_SPARE, ctx->stream));
+            CK(cudaMemcpyAsync(ctx->h_small, acc + (size_t)K * 65, 8, cudaMemcpyDeviceToHost, ctx->stream));
+            CK(cudaMemcpyAsync(ctx->h_small + 2, flags + F_SPARE, 4, cudaMemcpyDeviceToHost, ctx->stream));
+            CK(cudaStreamSynchronize(ctx->stream));
+            long long changed;
+            std::memcpy(&changed, ctx->h_small, 8);
+            if (!changed && iter > break_after) break;
+            if (tensor && ctx->h_small[2] != 0)  // errors[i] = distance to the assigned centroid, before the update (:336)
+                LAUNCH(launch_exact_errors(b.feat, n, cent, assign, errors, nullptr, nullptr, ctx->stream));
+            LAUNCH(launch_finalize_centroids(acc, K, shift, cent, flags, nullptr, ctx->stream));
+            if (!ctx->comm) {
+                LAUNCH(launch_reseed_empty(b.feat, n, errors, acc, K, cent, flags, nullptr, ctx->stream));
+            } else if (reseed_sharded(ctx, b, first_block, K, cent, errors, acc, flags)) {
+                return 1;
+            }
         }
     }
     CK(cudaMemcpyAsync(ctx->h_small, flags + F_RESEEDS, 4, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaMemcpyAsync(ctx->h_small + 1, flags + F_PAIRS, 8, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
+    if (async_loop) passes = ctx->h_small[4];
     if (stats) {
         stats->lloyd_passes = passes;
         stats->reseeds = ctx->h_small[0] + ctx->reseeds_sharded;
@@ -602,7 +648,7 @@ void yupvq_destroy(yupvq_ctx* ctx) {
     DevBuf* bufs[] = {&ctx->in_bytes, &ctx->planes, &ctx->feat, &ctx->s_planes, &ctx->s_feat, &ctx->s_rows,
                       &ctx->min_dist, &ctx->partial, &ctx->seed_idx, &ctx->canon, &ctx->small, &ctx->assign,
                       &ctx->errors, &ctx->cent, &ctx->acc, &ctx->cent_px, &ctx->cent_feat, &ctx->out_idx,
-                      &ctx->tc_a, &ctx->tc_xnorm, &ctx->tc_small, &ctx->tc_b, &ctx->tc_bx, &ctx->tc_cand};
+                      &ctx->tc_a, &ctx->tc_xnorm, &ctx->tc_small, &ctx->tc_b, &ctx->tc_bx, &ctx->tc_cand, &ctx->tc_amb};
     for (DevBuf* b : bufs) b->release();
     if (ctx->h_small) cudaFreeHost(ctx->h_small);
     for (auto& ev : ctx->ev)
@@ -1114,10 +1160,10 @@ int yupvq_update_centroids(yupvq_ctx* ctx, const float* features, size_t n_block
     const int shift = fixed_shift(n_blocks, max_abs);
     CK(cudaMemsetAsync(ctx->acc.p, 0, acc_words * 8, ctx->stream));
     LAUNCH(launch_accumulate(reinterpret_cast<const float*>(f_dev), n_blocks, reinterpret_cast<const uint32_t*>(a_dev), K,
-                             shift, ctx->acc.as<long long>(), flags, ctx->stream));
-    LAUNCH(launch_finalize_centroids(ctx->acc.as<long long>(), K, shift, ctx->cent.as<float>(), flags, ctx->stream));
+                             shift, ctx->acc.as<long long>(), flags, nullptr, ctx->stream));
+    LAUNCH(launch_finalize_centroids(ctx->acc.as<long long>(), K, shift, ctx->cent.as<float>(), flags, nullptr, ctx->stream));
     LAUNCH(launch_reseed_empty(reinterpret_cast<const float*>(f_dev), n_blocks, reinterpret_cast<float*>(const_cast<void*>(e_dev)),
-                               ctx->acc.as<long long>(), K, ctx->cent.as<float>(), flags, ctx->stream));
+                               ctx->acc.as<long long>(), K, ctx->cent.as<float>(), flags, nullptr, ctx->stream));
     if (from_device(ctx, inout_centroids, ctx->cent.p, (size_t)K * 256)) return 1;
     if (out_counts) {
         // counts live as 64-bit words behind the sums

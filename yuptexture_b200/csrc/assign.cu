@@ -21,8 +21,9 @@ constexpr int kCTile = 32;   // centroids staged per step
 __global__ void __launch_bounds__(kTile) assign_exact_kernel(const float* __restrict__ feat, size_t n,
                                                              const float* __restrict__ cent, uint32_t K,
                                                              uint32_t* __restrict__ assign, float* __restrict__ errors,
-                                                             uint32_t* __restrict__ flags) {
+                                                             uint32_t* __restrict__ flags, const uint32_t* __restrict__ stop) {
     __shared__ float4 xs[kTile * kPitch4];
+    if (stop && __ldg(stop)) return;
     __shared__ float4 cs[kCTile * 16];
     const size_t tile_first = (size_t)blockIdx.x * kTile;
     const size_t rows = (n - tile_first) < (size_t)kTile ? (n - tile_first) : (size_t)kTile;
@@ -64,7 +65,9 @@ __global__ void __launch_bounds__(kTile) assign_exact_kernel(const float* __rest
 }
 
 __global__ void exact_errors_kernel(const float* __restrict__ feat, size_t n, const float* __restrict__ cent,
-                                    const uint32_t* __restrict__ assign, float* __restrict__ errors) {
+                                    const uint32_t* __restrict__ assign, float* __restrict__ errors,
+                                    const uint32_t* __restrict__ stop, const uint32_t* __restrict__ n_empty) {
+    if ((stop && __ldg(stop)) || (n_empty && __ldg(n_empty) == 0)) return;
     const size_t blk = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (blk >= n) return;
     const float4* x = reinterpret_cast<const float4*>(feat) + blk * 16;
@@ -79,16 +82,16 @@ __global__ void exact_errors_kernel(const float* __restrict__ feat, size_t n, co
 }  // namespace
 
 cudaError_t launch_assign_exact(const float* feat, size_t n, const float* cent, uint32_t K, uint32_t* assign,
-                                float* errors, uint32_t* flags, cudaStream_t s) {
+                                float* errors, uint32_t* flags, const uint32_t* stop, cudaStream_t s) {
     if (n == 0) return cudaSuccess;
-    assign_exact_kernel<<<(unsigned)((n + kTile - 1) / kTile), kTile, 0, s>>>(feat, n, cent, K, assign, errors, flags);
+    assign_exact_kernel<<<(unsigned)((n + kTile - 1) / kTile), kTile, 0, s>>>(feat, n, cent, K, assign, errors, flags, stop);
     return cudaGetLastError();
 }
 
 cudaError_t launch_exact_errors(const float* feat, size_t n, const float* cent, const uint32_t* assign, float* errors,
-                                cudaStream_t s) {
+                                const uint32_t* stop, const uint32_t* n_empty, cudaStream_t s) {
     if (n == 0) return cudaSuccess;
-    exact_errors_kernel<<<(unsigned)((n + 127) / 128), 128, 0, s>>>(feat, n, cent, assign, errors);
+    exact_errors_kernel<<<(unsigned)((n + 127) / 128), 128, 0, s>>>(feat, n, cent, assign, errors, stop, n_empty);
     return cudaGetLastError();
 }
 

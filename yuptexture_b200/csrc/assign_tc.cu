@@ -173,7 +173,9 @@ __global__ void __launch_bounds__(kThreadsTc, 1)
 assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
                  const __grid_constant__ CUtensorMap tm_bx, const float* __restrict__ xnorm,
                  const float* __restrict__ cmax_ptr, uint32_t n, uint32_t num_tiles, uint32_t num_chunks,
-                 uint32_t resident_b, uint4* __restrict__ cand, uint32_t dbg) {
+                 uint32_t resident_b, uint4* __restrict__ cand, uint32_t* __restrict__ assign, uint32_t* __restrict__ flags,
+                 uint32_t* __restrict__ amb_list, unsigned int* __restrict__ amb_count, const uint32_t* __restrict__ stop) {
+    if (stop && __ldg(stop)) return;  // the Lloyd loop has converged: passes enqueued ahead of time do nothing
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     uint8_t* base_ptr = smem_raw + (base - smem_u32(smem_raw));
@@ -283,6 +285,14 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
         }
     } else {
         // ===== epilogue: 16 warps, thread == (TMEM lane, column quarter) =================================
+        // Every (row, column slice) thread works on its own: running maximum, threshold and candidate list
+        // are slice-local, so there is no barrier between the two passes over an accumulator stage and the
+        // 16 warps drift apart (one warp's TMEM latency hides behind another's ALU work).  The four slices
+        // of a row meet once per tile: a slice whose maximum is below the row's final threshold cannot hold
+        // the winner and is dropped whole; the others are concatenated.  (A slice-local threshold is never
+        // above the final one, so the true winner is always recorded in its slice -- see the margin proof in
+        // the header.)  Rows with exactly one candidate are final: their assignment is written here; the
+        // rest go to the exact re-rank through a compact list.
         constexpr int kSplit = kEpiWarps / 4;        // column slices per accumulator stage
         constexpr int kCols = BN / kSplit;           // columns per thread per stage
         constexpr int kTiles = kCols / 32;           // 32-column register tiles per pass
@@ -298,18 +308,36 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
         const uint32_t lane_taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(slice * kCols);
         uint32_t u = 0, tpar = 0;
         float xn_next = 0.0f;
-        if ((size_t)blockIdx.x * BM + r < n) xn_next = __ldg(xnorm + (size_t)blockIdx.x * BM + r);
+        uint32_t old_next = 0;
+        if ((size_t)blockIdx.x * BM + r < n) {
+            xn_next = __ldg(xnorm + (size_t)blockIdx.x * BM + r);
+            if (slice == 0 && assign) old_next = assign[(size_t)blockIdx.x * BM + r];
+        }
+        // threshold below which a score cannot belong to the reference argmin, given the best score m
+        auto threshold = [&](float m, float xn, float e_dot, bool& bad) -> float {
+            const float d_up = fmaxf(xn * xn - 2.0f * m + 2.0f * e_dot, 0.0f);
+            const float margin = 2.0f * e_dot + kRefRel * d_up;
+            // NaN / Inf anywhere (or only padding columns): no proof possible, take the exact scan
+            if (!(m > -1.0e29f) || !(margin < 1.0e30f)) bad = true;
+            float thr = m - margin;
+            thr = __uint_as_float(__float_as_uint(thr) + (thr > 0.0f ? -1 : (thr < 0.0f ? 1 : 0)));  // one ulp down
+            if (thr == 0.0f) thr = -FLT_MIN;
+            return thr;
+        };
         for (uint32_t t = blockIdx.x; t < num_tiles; t += gridDim.x, tpar ^= 1) {
             const size_t row = (size_t)t * BM + r;
             const float xn = xn_next;
-            {   // prefetch the next tile's |x'| so its DRAM latency hides behind this tile
+            const uint32_t old_c = old_next;
+            {   // prefetch the next tile's |x'| (and previous assignment) so its DRAM latency hides behind this tile
                 const size_t nrow = row + (size_t)gridDim.x * BM;
-                xn_next = (t + gridDim.x < num_tiles && nrow < n) ? __ldg(xnorm + nrow) : 0.0f;
+                const bool has = t + gridDim.x < num_tiles && nrow < n;
+                xn_next = has ? __ldg(xnorm + nrow) : 0.0f;
+                if (slice == 0 && assign) old_next = has ? assign[nrow] : 0u;
             }
             const float e_dot = kDotErr * xn * cmax;
             float m_run = -INFINITY;
             uint32_t cnt = 0;
-            bool bad = false;
+            bool local_bad = false;  // ignored: a slice of padding columns is not an error; the merge decides
             uint16_t* my_list = lists + ((tpar * kSplit + slice) * 128 + r) * kListCap;
             for (uint32_t j = 0; j < num_chunks; ++j, ++u) {
                 const uint32_t acc = u & 1, pacc = (u >> 1) & 1;
@@ -333,23 +361,13 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                 tc_ld32(taddr, va);
                 tc_wait_ld(va);
                 tc_ld32(taddr + 32, vb);
-                if (!(dbg & 1)) reduce_max(va);
+                reduce_max(va);
                 tc_wait_ld(vb);
                 tc_ld32(taddr, va);  // first tile of pass 2
-                if (!(dbg & 1)) reduce_max(vb);
-                float* sm = s_max + (u & 1) * (kSplit * 128);
-                sm[slice * 128 + r] = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
-                epi_bar();
+                reduce_max(vb);
                 const float m_prev = m_run;
-                m_run = fmaxf(fmax3(m_run, sm[r], sm[128 + r]), fmaxf(sm[256 + r], sm[384 + r]));
-                // every centroid that could still be the reference argmin has score >= thr
-                const float d_up = fmaxf(xn * xn - 2.0f * m_run + 2.0f * e_dot, 0.0f);
-                const float margin = 2.0f * e_dot + kRefRel * d_up;
-                // NaN / Inf anywhere (or only padding columns): no proof possible, take the exact scan
-                if (!(m_run > -1.0e29f) || !(margin < 1.0e30f)) bad = true;
-                float thr = m_run - margin;
-                thr = __uint_as_float(__float_as_uint(thr) + (thr > 0.0f ? -1 : (thr < 0.0f ? 1 : 0)));  // one ulp down
-                if (thr == 0.0f) thr = -FLT_MIN;
+                m_run = fmaxf(fmax3(m_run, m0, m1), fmaxf(m2, m3));
+                const float thr = threshold(m_run, xn, e_dot, local_bad);
                 // every candidate recorded in earlier chunks has score <= m_prev: once the threshold has moved
                 // past that, none of them can win any more
                 if (m_prev < thr) cnt = 0;
@@ -375,26 +393,33 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                 const uint32_t cbase = j * BN + slice * kCols;
                 tc_wait_ld(va);
                 tc_ld32(taddr + 32, vb);
-                if (!(dbg & 2)) sweep(va, cbase);
+                sweep(va, cbase);
                 tc_wait_ld(vb);
-                if (!(dbg & 2)) sweep(vb, cbase + 32);
+                sweep(vb, cbase + 32);
                 // release the accumulator stage to the MMA warp
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(bar(BAR_TEMPTY + acc));
             }
-            // ---- merge the column slices and publish the candidate list.  Lists and counts are double
-            // buffered by tile parity, so one barrier per tile is enough.
-            if (bad || cnt > (uint32_t)kListCap) cnt = 100;
-            s_cnt[(tpar * kSplit + slice) * 128 + r] = (uint8_t)cnt;
+            // ---- the four slices of a row meet.  Lists, maxima and counts are double buffered by tile parity,
+            // so one barrier per tile is enough.  count 100 = list overflow.
+            s_cnt[(tpar * kSplit + slice) * 128 + r] = (uint8_t)(cnt > (uint32_t)kListCap ? 100u : cnt);
+            s_max[(tpar * kSplit + slice) * 128 + r] = m_run;
             epi_bar();
             if (slice == 0 && row < n) {
+                float mq[kSplit];
+#pragma unroll
+                for (int q = 0; q < kSplit; ++q) mq[q] = s_max[(tpar * kSplit + q) * 128 + r];
+                bool any_bad = false;
+                const float m_all = fmaxf(fmaxf(mq[0], mq[1]), fmaxf(mq[2], mq[3]));
+                const float thr_all = threshold(m_all, xn, e_dot, any_bad);
                 uint32_t w[4] = {0, 0, 0, 0};
                 uint32_t total = 0;
-                bool ovf = false;
+                bool ovf = any_bad;
 #pragma unroll
                 for (int q = 0; q < kSplit; ++q) {
                     const uint32_t cq = s_cnt[(tpar * kSplit + q) * 128 + r];
+                    if (!(mq[q] > thr_all)) continue;      // this slice's best score cannot be the winner's
                     ovf |= cq > (uint32_t)kListCap;
                     const uint16_t* lq = lists + ((tpar * kSplit + q) * 128 + r) * kListCap;
                     for (uint32_t i = 0; i < cq && !ovf && total < 8; ++i, ++total) {
@@ -402,13 +427,21 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                         w[total >> 1] |= c << (16 * (total & 1));
                     }
                 }
-                if (!ovf && total >= 1 && total <= (uint32_t)kMaxCand) {
-                    w[3] = (w[3] & 0xffffu) | (total << 16);
+                if (!ovf && total == 1 && assign) {
+                    // a single candidate is the exact argmin: final
+                    const uint32_t c = w[0] & 0xffffu;
+                    if (flags && old_c != c) flags[0] = 1u;
+                    assign[row] = c;
                 } else {
-                    w[0] = w[1] = w[2] = 0;
-                    w[3] = 0xffffu << 16;  // empty (NaN) or overflow: full exact scan in the re-rank
+                    if (!ovf && total >= 1 && total <= (uint32_t)kMaxCand) {
+                        w[3] = (w[3] & 0xffffu) | (total << 16);
+                    } else {
+                        w[0] = w[1] = w[2] = 0;
+                        w[3] = 0xffffu << 16;  // empty (NaN) or overflow: full exact scan in the re-rank
+                    }
+                    cand[row] = make_uint4(w[0], w[1], w[2], w[3]);
+                    if (amb_list) amb_list[atomicAdd(amb_count, 1u)] = (uint32_t)row;
                 }
-                cand[row] = make_uint4(w[0], w[1], w[2], w[3]);
             }
         }
     }
@@ -565,8 +598,9 @@ __device__ __forceinline__ float pair_distance(const RowHalf& x, const float* __
 __global__ void __launch_bounds__(kRrThreads, 2) rerank_kernel(const float* __restrict__ feat, size_t n, const float* __restrict__ cent,
                                                                uint32_t K, const uint4* __restrict__ cand, uint32_t* __restrict__ assign,
                                                                float* __restrict__ errors, uint32_t* __restrict__ flags,
-                                                               unsigned int* __restrict__ stat) {
+                                                               unsigned int* __restrict__ stat, const uint32_t* __restrict__ stop) {
     __shared__ uint8_t s_src[kRrThreads / 32][32];
+    const uint32_t stopped = stop ? __ldg(stop) : 0u;  // tested after the candidate load has been issued
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int g = lane >> 1, h = lane & 1;
     const size_t blk0 = ((size_t)blockIdx.x * (kRrThreads / 32) + wid) * 32;
@@ -575,6 +609,7 @@ __global__ void __launch_bounds__(kRrThreads, 2) rerank_kernel(const float* __re
     const bool valid = blk < n;
     uint4 cw = make_uint4(0, 0, 0, 0);
     if (valid) cw = ldg_nc_v4(cand + blk);
+    if (stopped) return;
     const uint32_t cnt_raw = valid ? (cw.w >> 16) : 0u;
     const bool overflow = cnt_raw == 0xffffu;
     // blocks that need arithmetic: none when the list has one entry and no error is wanted
@@ -667,6 +702,95 @@ __global__ void __launch_bounds__(kRrThreads, 2) rerank_kernel(const float* __re
     }
 }
 
+// List-driven variant for the Lloyd passes: the front-end has already written the assignment of every block
+// with a single candidate; `amb_list[0, *amb_count)` holds the rows that still need exact arithmetic (about
+// 1 % of a texture).  Two lanes per row as above.  The last CTA to finish clears the counter for the next pass.
+__global__ void __launch_bounds__(kRrThreads, 2) rerank_sparse_kernel(const float* __restrict__ feat, const float* __restrict__ cent,
+                                                                      uint32_t K, const uint4* __restrict__ cand,
+                                                                      const uint32_t* __restrict__ amb_list, unsigned int* amb_count,
+                                                                      unsigned int* ticket, uint32_t* __restrict__ assign,
+                                                                      uint32_t* __restrict__ flags, unsigned int* __restrict__ stat) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int g = lane >> 1, h = lane & 1;
+    const uint32_t total = __ldcg(amb_count);
+    const uint32_t n_warps = gridDim.x * (kRrThreads / 32);
+    uint32_t pairs = 0, n_ovf = 0;
+    for (uint32_t base = (blockIdx.x * (kRrThreads / 32) + wid) * 16; base < total; base += n_warps * 16) {
+        const uint32_t idx = base + g;
+        const bool act = idx < total;
+        const size_t row = __ldcg(amb_list + (act ? idx : base));
+        const uint4 cw = ldg_nc_v4(cand + row);
+        const uint32_t m_raw = cw.w >> 16;
+        const bool overflow = act && m_raw == 0xffffu;
+        const uint32_t m = (act && !overflow) ? m_raw : 0u;
+        RowHalf x;
+        x.load_stream(feat + row * 64, h);
+        const uint32_t m_max = __reduce_max_sync(0xffffffffu, m);
+        float bd = FLT_MAX;
+        uint32_t bc = 0;
+        bool have = false;
+        for (uint32_t i = 0; i < m_max; ++i) {
+            const uint32_t wsel = i < 2 ? cw.x : (i < 4 ? cw.y : (i < 6 ? cw.z : cw.w));
+            const uint32_t c = i < m ? ((wsel >> (16 * (i & 1))) & 0xffffu) : 0u;
+            const float d = pair_distance(x, cent + (size_t)c * 64, h);
+            if (i < m && d < FLT_MAX && (!have || d < bd || (d == bd && c < bc))) {
+                bd = d;
+                bc = c;
+                have = true;
+            }
+        }
+        if (h == 0) pairs += m;
+        // rows without a usable list (flat textures, NaN): full scan, the whole warp on one row at a time
+        unsigned ovf_mask = __ballot_sync(0xffffffffu, overflow && h == 0);
+        while (ovf_mask) {
+            const int src = __ffs(ovf_mask) - 1;
+            ovf_mask &= ovf_mask - 1;
+            const size_t orow = __shfl_sync(0xffffffffu, (unsigned long long)row, src);
+            RowHalf ox;
+            ox.load_stream(feat + orow * 64, h);
+            float od = FLT_MAX;
+            uint32_t oc = 0;
+            for (uint32_t c0 = 0; c0 < K; c0 += 16) {
+                const uint32_t c = c0 + g;
+                const float d = pair_distance(ox, cent + (size_t)(c < K ? c : 0) * 64, h);
+                if (c < K && d < od) {  // ascending c inside the group: strict '<' keeps the first minimum
+                    od = d;
+                    oc = c;
+                }
+            }
+#pragma unroll
+            for (int o = 2; o <= 16; o <<= 1) {
+                const float pd = __shfl_xor_sync(0xffffffffu, od, o);
+                const uint32_t pc = __shfl_xor_sync(0xffffffffu, oc, o);
+                if (pd < od || (pd == od && pd < FLT_MAX && pc < oc)) {
+                    od = pd;
+                    oc = pc;
+                }
+            }
+            if (lane == src) {
+                bc = oc;
+                pairs += K;
+                ++n_ovf;
+            }
+        }
+        if (act && h == 0) {
+            if (flags && assign[row] != bc) flags[0] = 1u;
+            assign[row] = bc;
+        }
+    }
+    if (stat) {
+        pairs = __reduce_add_sync(0xffffffffu, pairs);
+        n_ovf = __reduce_add_sync(0xffffffffu, n_ovf);
+        if (lane == 0 && pairs) atomicAdd(stat, pairs);
+        if (lane == 0 && n_ovf) atomicAdd(stat + 1, n_ovf);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0 && atomicAdd(ticket, 1u) == gridDim.x - 1) {  // every CTA has read the count by now
+        *amb_count = 0;
+        *ticket = 0;
+    }
+}
+
 // ---- host side -------------------------------------------------------------------------------------------
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -733,7 +857,8 @@ cudaError_t launch_tc_prep_centroids(const float* cent, uint32_t K, const float*
 }
 
 cudaError_t launch_assign_tc(const float* a_prime, const float* xnorm, size_t n, const float* b_main, const float* b_ext,
-                             uint32_t K, const float* cmax, uint4* cand, cudaStream_t s) {
+                             uint32_t K, const float* cmax, uint4* cand, uint32_t* assign, uint32_t* flags, uint32_t* amb_list,
+                             unsigned int* amb_count, const uint32_t* stop, cudaStream_t s) {
     if (n == 0) return cudaSuccess;
     static bool attr_set = false;
     if (!attr_set) {
@@ -749,18 +874,25 @@ cudaError_t launch_assign_tc(const float* a_prime, const float* xnorm, size_t n,
         return cudaErrorInvalidValue;
     const uint32_t num_tiles = (uint32_t)((n + BM - 1) / BM);
     const uint32_t num_chunks = k_pad / BN;
-    static const uint32_t dbg = getenv("YUPVQ_TC_DEBUG") ? (uint32_t)atoi(getenv("YUPVQ_TC_DEBUG")) : 0u;  // timing experiments only
     const uint32_t grid = num_tiles < (uint32_t)YUPVQ_NUM_SMS ? num_tiles : (uint32_t)YUPVQ_NUM_SMS;
     assign_tc_kernel<<<grid, kThreadsTc, SMEM_TC, s>>>(tm_a, tm_b, tm_bx, xnorm, cmax, (uint32_t)n, num_tiles, num_chunks,
-                                                      num_chunks <= 2 ? 1u : 0u, cand, dbg);
+                                                      num_chunks <= 2 ? 1u : 0u, cand, assign, flags, amb_list, amb_count, stop);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_rerank_sparse(const float* feat, const float* cent, uint32_t K, const uint4* cand, const uint32_t* amb_list,
+                                 unsigned int* amb_count, unsigned int* ticket, uint32_t* assign, uint32_t* flags,
+                                 unsigned int* stat_pairs, cudaStream_t s) {
+    rerank_sparse_kernel<<<YUPVQ_NUM_SMS * 2, kRrThreads, 0, s>>>(feat, cent, K, cand, amb_list, amb_count, ticket, assign, flags,
+                                                                 stat_pairs);
     return cudaGetLastError();
 }
 
 cudaError_t launch_rerank(const float* feat, size_t n, const float* cent, uint32_t K, const uint4* cand, uint32_t* assign,
-                          float* errors, uint32_t* flags, unsigned int* stat_pairs, cudaStream_t s) {
+                          float* errors, uint32_t* flags, unsigned int* stat_pairs, const uint32_t* stop, cudaStream_t s) {
     if (n == 0) return cudaSuccess;
     rerank_kernel<<<(unsigned)((n + kRrThreads - 1) / kRrThreads), kRrThreads, 0, s>>>(feat, n, cent, K, cand, assign, errors,
-                                                                                      flags, stat_pairs);
+                                                                                      flags, stat_pairs, stop);
     return cudaGetLastError();
 }
 

@@ -54,10 +54,11 @@ cudaError_t launch_seed_round_hdr(const SeedState& st, const float* feat, size_t
 // Exact fp32 assignment in the reference's operation order (also the re-rank kernel).
 // flags[0] |= 1 when any assignment changed.
 cudaError_t launch_assign_exact(const float* feat, size_t n, const float* cent, uint32_t K, uint32_t* assign,
-                                float* errors, uint32_t* flags, cudaStream_t s);
+                                float* errors, uint32_t* flags, const uint32_t* stop, cudaStream_t s);
 // errors[i] = exact distance to the assigned centroid (used before an empty-cluster reseed in tensor mode)
+// runs only when *stop == 0 and *n_empty != 0 (either pointer may be null = unconditional)
 cudaError_t launch_exact_errors(const float* feat, size_t n, const float* cent, const uint32_t* assign, float* errors,
-                                cudaStream_t s);
+                                const uint32_t* stop, const uint32_t* n_empty, cudaStream_t s);
 
 // ---- assign_tc.cu : K3, tensor engine (tcgen05 front-end + exact re-rank) ------------------------------
 // Per block set (once):  mu = column means, A' = rna_tf32(w (x - mu)), xnorm = |w (x - mu)|.
@@ -71,10 +72,21 @@ cudaError_t launch_tc_prep_blocks(const float* feat, size_t n, const float* mu, 
                                   cudaStream_t s);
 cudaError_t launch_tc_prep_centroids(const float* cent, uint32_t K, const float* mu, float* b_main, float* b_ext,
                                      float* cmax, cudaStream_t s);
+// `stop` (may be null): device word; when non-zero the kernel returns at once (Lloyd passes are enqueued
+// ahead of the convergence test, see launch_lloyd_control).
+// assign != null: rows with exactly one candidate get their assignment (and the changed flag) written by the
+// front-end, the other rows are appended to amb_list (counter amb_count) for launch_rerank_sparse.
+// assign == null: every row's candidate list goes to `cand` for the dense launch_rerank (errors[] wanted).
 cudaError_t launch_assign_tc(const float* a_prime, const float* xnorm, size_t n, const float* b_main,
-                             const float* b_ext, uint32_t K, const float* cmax, uint4* cand, cudaStream_t s);
+                             const float* b_ext, uint32_t K, const float* cmax, uint4* cand, uint32_t* assign,
+                             uint32_t* flags, uint32_t* amb_list, unsigned int* amb_count, const uint32_t* stop,
+                             cudaStream_t s);
+cudaError_t launch_rerank_sparse(const float* feat, const float* cent, uint32_t K, const uint4* cand,
+                                 const uint32_t* amb_list, unsigned int* amb_count, unsigned int* ticket,
+                                 uint32_t* assign, uint32_t* flags, unsigned int* stat_pairs, cudaStream_t s);
 cudaError_t launch_rerank(const float* feat, size_t n, const float* cent, uint32_t K, const uint4* cand,
-                          uint32_t* assign, float* errors, uint32_t* flags, unsigned int* stat_pairs, cudaStream_t s);
+                          uint32_t* assign, float* errors, uint32_t* flags, unsigned int* stat_pairs,
+                          const uint32_t* stop, cudaStream_t s);
 
 // ---- update.cu : K4 / K5 -----------------------------------------------------------------------------
 // Accumulator layout (int64 words): [K*64 sums | K counts | 1 changed flag].  Sums are 64-bit fixed
@@ -82,14 +94,20 @@ cudaError_t launch_rerank(const float* feat, size_t n, const float* cent, uint32
 // buffer is what gets all-reduced when blocks are sharded across GPUs.
 // flags: [0] changed (written by assign), [1] #empty clusters, [2] reseeds (running total).
 cudaError_t launch_accumulate(const float* feat, size_t n, const uint32_t* assign, uint32_t K, int shift,
-                              long long* acc, const uint32_t* flags, cudaStream_t s);
+                              long long* acc, const uint32_t* flags, const uint32_t* stop, cudaStream_t s);
 // centroid = float(sum) * (1.0f / count) (reference src/vq_encoder.cpp:366-368); flags[1] = #empty clusters
 cudaError_t launch_finalize_centroids(const long long* acc, uint32_t K, int shift, float* cent, uint32_t* flags,
-                                      cudaStream_t s);
+                                      const uint32_t* stop, cudaStream_t s);
 cudaError_t launch_count_empty(const long long* acc, uint32_t K, uint32_t* out, cudaStream_t s);
+// The between-assign-and-update test of the reference's Lloyd loop (src/vq_encoder.cpp:341 / :572), on the
+// device so that passes can be enqueued without a host round trip: reads the (all-reduced) changed word
+// acc[K*65]; if nothing changed and iter > break_after sets ctl[0] (stop) else ++ctl[1] (passes run);
+// writes the number of empty clusters to ctl[2] and clears flags[0] (changed) and flags[1] (#empty).
+cudaError_t launch_lloyd_control(const long long* acc, uint32_t K, uint32_t iter, uint32_t break_after, uint32_t* flags,
+                                 uint32_t* ctl, cudaStream_t s);
 // serial-semantics reseed of empty clusters (ascending c, first maximum of errors, then zero it)
 cudaError_t launch_reseed_empty(const float* feat, size_t n, float* errors, const long long* acc, uint32_t K,
-                                float* cent, uint32_t* flags, cudaStream_t s);
+                                float* cent, uint32_t* flags, const uint32_t* stop, cudaStream_t s);
 // out[0] = max error (float bits), out[1] = index of its first occurrence
 cudaError_t launch_argmax_error(const float* errors, size_t n, uint32_t* out2, cudaStream_t s);
 cudaError_t launch_max_abs(const float* x, size_t n, uint32_t* out_bits, cudaStream_t s);

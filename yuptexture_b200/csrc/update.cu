@@ -21,7 +21,9 @@ namespace {
 // v1: one warp per block, 64 RED.ADD.64 per block into the accumulator in L2.
 __global__ void __launch_bounds__(256) accumulate_kernel(const float* __restrict__ feat, size_t n,
                                                          const uint32_t* __restrict__ assign, uint32_t K, float scale,
-                                                         long long* __restrict__ acc, const uint32_t* __restrict__ flags) {
+                                                         long long* __restrict__ acc, const uint32_t* __restrict__ flags,
+                                                         const uint32_t* __restrict__ stop) {
+    if (stop && __ldg(stop)) return;
     const int lane = threadIdx.x & 31;
     const size_t warp = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const size_t n_warps = ((size_t)gridDim.x * blockDim.x) >> 5;
@@ -49,8 +51,9 @@ constexpr int kAccMaxK = 4096;
 
 __global__ void __launch_bounds__(kAccThreads, 2)
 accumulate_sorted_kernel(const float* __restrict__ feat, size_t n, const uint32_t* __restrict__ assign, uint32_t K, float scale,
-                         long long* __restrict__ acc, const uint32_t* __restrict__ flags) {
+                         long long* __restrict__ acc, const uint32_t* __restrict__ flags, const uint32_t* __restrict__ stop) {
     extern __shared__ uint32_t sm_acc[];
+    if (stop && __ldg(stop)) return;
     uint32_t* hist = sm_acc;                                      // K
     uint32_t* offs = sm_acc + K;                                  // K
     uint16_t* sorted = reinterpret_cast<uint16_t*>(sm_acc + 2 * K);  // kAccChunk
@@ -159,7 +162,8 @@ accumulate_sorted_kernel(const float* __restrict__ feat, size_t n, const uint32_
 }
 
 __global__ void finalize_kernel(const long long* __restrict__ acc, uint32_t K, double inv_scale,
-                                float* __restrict__ cent, uint32_t* __restrict__ flags) {
+                                float* __restrict__ cent, uint32_t* __restrict__ flags, const uint32_t* __restrict__ stop) {
+    if (stop && __ldg(stop)) return;
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= (size_t)K * 64) return;
     const uint32_t c = (uint32_t)(i >> 6);
@@ -175,6 +179,28 @@ __global__ void finalize_kernel(const long long* __restrict__ acc, uint32_t K, d
 
 // out[0] = number of clusters with count 0 (known before the centroids are overwritten, so the tensor
 // engine can compute errors[] only when a reseed will need them)
+// see kernels.h: the reference's `if (!hasChanged && iter > N) break;` evaluated on the device
+__global__ void lloyd_control_kernel(const long long* __restrict__ acc, uint32_t K, uint32_t iter, uint32_t break_after,
+                                     uint32_t* __restrict__ flags, uint32_t* __restrict__ ctl) {
+    __shared__ unsigned int total;
+    if (ctl[0]) return;
+    if (threadIdx.x == 0) total = 0;
+    __syncthreads();
+    unsigned int local = 0;
+    for (uint32_t c = threadIdx.x; c < K; c += blockDim.x) local += acc[(size_t)K * 64 + c] == 0 ? 1u : 0u;
+    local = warp_sum(local);
+    if ((threadIdx.x & 31) == 0 && local) atomicAdd(&total, local);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const bool changed = acc[(size_t)K * 65] != 0;
+        ctl[1] += 1u;     // assignment passes run
+        ctl[2] = total;   // empty clusters of this pass
+        if (!changed && iter > break_after) ctl[0] = 1u;  // stop: this pass' update and every later pass are skipped
+        flags[0] = 0u;
+        flags[1] = 0u;
+    }
+}
+
 __global__ void count_empty_kernel(const long long* __restrict__ acc, uint32_t K, uint32_t* __restrict__ out) {
     __shared__ unsigned int total;
     if (threadIdx.x == 0) total = 0;
@@ -241,9 +267,10 @@ __device__ unsigned long long cta_argmax_first(const float* errors, size_t n, fl
 // the FIRST block with the maximum error, copy its feature vector into the centroid, zero that error.
 __global__ void __launch_bounds__(1024) reseed_kernel(const float* __restrict__ feat, size_t n, float* errors,
                                                       const long long* __restrict__ acc, uint32_t K, float* cent,
-                                                      uint32_t* flags) {
+                                                      uint32_t* flags, const uint32_t* __restrict__ stop) {
     __shared__ float s_val[33];
     __shared__ unsigned long long s_idx[33];
+    if (stop && __ldg(stop)) return;
     if (flags[1] == 0) return;  // no empty cluster this pass
     for (uint32_t c = 0; c < K; ++c) {
         if (acc[(size_t)K * 64 + c] != 0) continue;
@@ -285,7 +312,7 @@ __global__ void max_abs_kernel(const float* __restrict__ x, size_t n, uint32_t* 
 }  // namespace
 
 cudaError_t launch_accumulate(const float* feat, size_t n, const uint32_t* assign, uint32_t K, int shift,
-                              long long* acc, const uint32_t* flags, cudaStream_t s) {
+                              long long* acc, const uint32_t* flags, const uint32_t* stop, cudaStream_t s) {
     if (K <= (uint32_t)kAccMaxK && n >= (size_t)kAccChunk) {
         const size_t smem = (size_t)K * 8 + (size_t)kAccChunk * 2;
         static size_t attr_smem = 0;
@@ -296,19 +323,19 @@ cudaError_t launch_accumulate(const float* feat, size_t n, const uint32_t* assig
         }
         size_t chunks = (n + kAccChunk - 1) / kAccChunk;
         size_t grid = chunks < (size_t)YUPVQ_NUM_SMS * 2 ? chunks : (size_t)YUPVQ_NUM_SMS * 2;
-        accumulate_sorted_kernel<<<(unsigned)grid, kAccThreads, smem, s>>>(feat, n, assign, K, ldexpf(1.0f, shift), acc, flags);
+        accumulate_sorted_kernel<<<(unsigned)grid, kAccThreads, smem, s>>>(feat, n, assign, K, ldexpf(1.0f, shift), acc, flags, stop);
         return cudaGetLastError();
     }
     size_t blocks = (n * 32 + 255) / 256;
     if (blocks > (size_t)YUPVQ_NUM_SMS * 16) blocks = (size_t)YUPVQ_NUM_SMS * 16;
     if (blocks < 1) blocks = 1;
-    accumulate_kernel<<<(unsigned)blocks, 256, 0, s>>>(feat, n, assign, K, ldexpf(1.0f, shift), acc, flags);
+    accumulate_kernel<<<(unsigned)blocks, 256, 0, s>>>(feat, n, assign, K, ldexpf(1.0f, shift), acc, flags, stop);
     return cudaGetLastError();
 }
 
 cudaError_t launch_finalize_centroids(const long long* acc, uint32_t K, int shift, float* cent, uint32_t* flags,
-                                      cudaStream_t s) {
-    finalize_kernel<<<(K * 64 + 255) / 256, 256, 0, s>>>(acc, K, ldexp(1.0, -shift), cent, flags);
+                                      const uint32_t* stop, cudaStream_t s) {
+    finalize_kernel<<<(K * 64 + 255) / 256, 256, 0, s>>>(acc, K, ldexp(1.0, -shift), cent, flags, stop);
     return cudaGetLastError();
 }
 
@@ -317,9 +344,15 @@ cudaError_t launch_count_empty(const long long* acc, uint32_t K, uint32_t* out, 
     return cudaGetLastError();
 }
 
+cudaError_t launch_lloyd_control(const long long* acc, uint32_t K, uint32_t iter, uint32_t break_after, uint32_t* flags,
+                                 uint32_t* ctl, cudaStream_t s) {
+    lloyd_control_kernel<<<1, 256, 0, s>>>(acc, K, iter, break_after, flags, ctl);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_reseed_empty(const float* feat, size_t n, float* errors, const long long* acc, uint32_t K,
-                                float* cent, uint32_t* flags, cudaStream_t s) {
-    reseed_kernel<<<1, 1024, 0, s>>>(feat, n, errors, acc, K, cent, flags);
+                                float* cent, uint32_t* flags, const uint32_t* stop, cudaStream_t s) {
+    reseed_kernel<<<1, 1024, 0, s>>>(feat, n, errors, acc, K, cent, flags, stop);
     return cudaGetLastError();
 }
 
