@@ -6,8 +6,9 @@
 One "step" = one pass of the whole VQ hot path over one synthetic 4096^2 BC1 texture (1,048,576
 blocks, K = 512, 32 Lloyd iterations max, Oklab metric): BCn decode -> Oklab features, K-Means++
 seeding, Lloyd iterations, centroid conversion, final assignment.  N > 1 (torchrun, one rank per
-GPU): weak scaling -- N textures, every texture's blocks sharded over the N GPUs, with the per-pass
-K x 65 fixed-point sums/counts NCCL-all-reduced (the exchange step north_star names).
+GPU): weak scaling -- N textures per step in lock step (BASELINE config 5's shape), every texture's blocks
+sharded over the N GPUs, seeding texture-parallel (texture t on rank t % N), and ONE NCCL all-reduce per
+Lloyd pass carrying the K x 65 fixed-point sums/counts of all N textures (the exchange step north_star names).
 
 `value`  : blocks/s with the BCn bytes already resident in HBM and outputs left in HBM.
 `e2e`    : the same through the C ABI with HOST (pinned) buffers: H2D of the BCn bytes and D2H of the
@@ -166,26 +167,26 @@ def run_ours(args, rank, world, local_rank):
     textures = [make_texture(1000 + t) for t in range(n_tex)]
     pinned_in = [torch.from_numpy(t.reshape(-1).copy()).pin_memory() for t in textures]
     dev_in = [p.to(dev) for p in pinned_in]
-    per = (n + world - 1) // world
-    first = min(rank * per, n)
-    n_local = min(per, n - first)
-    dev_cent = torch.empty(k * 48, dtype=torch.uint8, device=dev)
-    dev_idx = torch.empty(max(1, n_local), dtype=torch.int32, device=dev)
-    host_cent = torch.empty(k * 48, dtype=torch.uint8).pin_memory()
-    host_idx = torch.empty(max(1, n_local), dtype=torch.int32).pin_memory()
+    from yuptexture_b200 import sharding
+    first, n_local = sharding.shard_range(n, world, rank)
+    dev_cent = [torch.empty(k * 48, dtype=torch.uint8, device=dev) for _ in range(n_tex)]
+    dev_idx = [torch.empty(max(1, n_local), dtype=torch.int32, device=dev) for _ in range(n_tex)]
+    host_cent = [torch.empty(k * 48, dtype=torch.uint8).pin_memory() for _ in range(n_tex)]
+    host_idx = [torch.empty(max(1, n_local), dtype=torch.int32).pin_memory() for _ in range(n_tex)]
 
     def step(resident):
-        stats = []
-        for t in range(n_tex):
-            src = dev_in[t].data_ptr() if resident else pinned_in[t].numpy()
-            oc = dev_cent.data_ptr() if resident else host_cent.numpy()
-            oi = dev_idx.data_ptr() if resident else host_idx.numpy().view(np.uint32)
-            if world == 1:
-                _, _, st = enc.encode_bcn(src, n, 1, 3, cfg, oc, oi)
-            else:
-                _, _, st = enc.encode_bcn_sharded(src, n, first, n_local, 1, 3, cfg, oc, oi)
-            stats.append(st)
-        return stats
+        if world == 1:
+            src = dev_in[0].data_ptr() if resident else pinned_in[0].numpy()
+            oc = dev_cent[0].data_ptr() if resident else host_cent[0].numpy()
+            oi = dev_idx[0].data_ptr() if resident else host_idx[0].numpy().view(np.uint32)
+            _, _, st = enc.encode_bcn(src, n, 1, 3, cfg, oc, oi)
+            return [st]
+        # N GPUs: N textures in lock step, every texture's blocks sharded over the N GPUs; one all-reduce per pass
+        srcs = [d.data_ptr() for d in dev_in] if resident else [p.numpy() for p in pinned_in]
+        ocs = [d.data_ptr() for d in dev_cent] if resident else [h.numpy() for h in host_cent]
+        ois = [d.data_ptr() for d in dev_idx] if resident else [h.numpy().view(np.uint32) for h in host_idx]
+        _, _, st = enc.encode_bcn_batch_sharded(srcs, n, first, n_local, 1, 3, cfg, ocs, ois)
+        return [st]
 
     def barrier():
         torch.cuda.synchronize()
@@ -224,29 +225,29 @@ def run_ours(args, rank, world, local_rank):
     value = total_blocks * args.steps / (ms_dev * 1e-3)
     e2e = total_blocks * args.steps / (ms_e2e * 1e-3)
 
+    # one more real step (all ranks: it contains collectives) with the front-end launches bracketed by events
+    enc.profile(True)
+    step(True)
+    ms_fe, n_fe = enc.profile_read()
+    enc.profile(False)
+
     out = None
     if rank == 0:
         pk = peaks()
-        # dominant kernel: the assignment pass, timed alone with CUDA events on the library's stream
-        feat = torch.empty(n * 64, dtype=torch.float32, device=dev).uniform_(0, 1)
-        cent = torch.empty(k * 64, dtype=torch.float32, device=dev).uniform_(0, 1)
-        idx_d = torch.empty(n, dtype=torch.int32, device=dev)
-        torch.cuda.synchronize()
-        ms_assign = []
-        for i in range(6):
-            st = binding.Stats()
-            rc = enc._L.yupvq_assign(enc._ctx, feat.data_ptr(), n, cent.data_ptr(), k, cfg.assign_mode,
-                                     idx_d.data_ptr(), None, binding.C.byref(st))
-            assert rc == 0
-            if i:
-                ms_assign.append(st.ms_total)
-        ms_a = float(np.mean(ms_assign))
-        flop = 2.0 * n * k * 64
-        achieved = flop / (ms_a * 1e-3) / 1e12
-        roofline = {"bound": "tensor", "kernel": "assign (N x K x 64 contraction + argmin)", "achieved": achieved,
-                    "peak": pk["bf16_tflops"], "unit": "TFLOP/s", "frac": achieved / pk["bf16_tflops"],
-                    "traffic": None, "peak_source": pk["src"] + " bf16 burst (kernel timed alone)",
-                    "ms_per_launch": ms_a, "flop_per_launch": flop}
+        # dominant kernel: the tcgen05 assignment front-end (assign_tc_kernel), every launch of it inside one
+        # more real step bracketed by CUDA events on the library's stream (yupvq_profile)
+        ms_a = ms_fe / max(1, n_fe)
+        blocks_per_launch = n_local if world > 1 else n
+        flop_alg = 2.0 * blocks_per_launch * k * 64          # 2 K D per block per pass
+        split = 3                                            # xh.ch + xh.cl + xl.ch bf16 partial products
+        achieved = split * flop_alg / (ms_a * 1e-3) / 1e12 if ms_a > 0 else 0.0
+        roofline = {"bound": "tensor", "kernel": "assign_tc_kernel (N x K x 64 contraction as 3 bf16 partial products + argmax epilogue)",
+                    "achieved": achieved, "peak": pk["bf16_tflops_sustained"], "unit": "TFLOP/s",
+                    "frac": achieved / pk["bf16_tflops_sustained"], "traffic": None,
+                    "peak_source": pk["src"] + " bf16 sustained (kernel timed inside a step)",
+                    "ms_per_launch": ms_a, "launches_timed": n_fe, "flop_per_launch_algorithmic": flop_alg, "bf16_split": split,
+                    "achieved_unsplit": flop_alg / (ms_a * 1e-3) / 1e12 if ms_a > 0 else 0.0,
+                    "share_of_step": ms_fe / (ms_dev / args.steps) if ms_dev > 0 else None}
         # bounded CPU sample of the same workload on this box's host cores
         px = cpu_sample_pixels(textures[0])
         threads = os.cpu_count() or 1
@@ -256,6 +257,7 @@ def run_ours(args, rank, world, local_rank):
                          f"BuildCodebook+QuantizeBlocks {dt:.2f} s"}
         bytes_in = n * 8 * n_tex
         bytes_out = (k * 48 + n_local * 4) * n_tex
+        phases = ("h2d", "decode", "seed", "lloyd", "finalize", "quantize", "d2h")
         out = {
             "metric": "vq_blocks_per_sec", "value": value, "unit": "blocks/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(3, args.warmup), "ms_per_step": ms_dev / args.steps, "higher_is_better": True,
@@ -263,10 +265,11 @@ def run_ours(args, rank, world, local_rank):
             "config": {"workload": f"BC1 VQ compress of {n_tex} synthetic 4096x4096 texture(s) (config 2 per GPU): "
                                    "seeding+Lloyd+assign, K=512, maxIterations=32, Oklab metric",
                        "blocks_per_texture": n, "textures": n_tex, "codebook": k,
-                       "parallelism": "1 GPU" if world == 1 else f"blocks sharded over {world} GPUs, NCCL all-reduce of K x 65 int64 per pass",
+                       "parallelism": "1 GPU" if world == 1 else f"{n_tex} textures in lock step, blocks sharded over {world} GPUs, seeding texture-parallel, "
+                                      f"one NCCL all-reduce of {n_tex} x K x 65 int64 per pass",
                        "l2": "no explicit flush: each step streams a 330 MB working set (features + pixel planes) > 126 MB L2",
                        "lloyd_passes": last.lloyd_passes, "ms_per_texture": ms_dev / args.steps / n_tex,
-                       "phases_ms": {p: getattr(last, "ms_" + p) for p in ("h2d", "decode", "seed", "lloyd", "finalize", "quantize", "d2h")},
+                       "phases_ms": {p: getattr(last, "ms_" + p) for p in phases},
                        "wall_ms_per_step": wall_dev / args.steps},
             "e2e": {"value": e2e, "unit": "blocks/s", "h2d_bytes_per_step": bytes_in, "d2h_bytes_per_step": bytes_out,
                     "ms_per_step": ms_e2e / args.steps, "wall_ms_per_step": wall_e2e / args.steps},

@@ -80,6 +80,14 @@ YUPVQ_API const char* yupvq_version(void);
 YUPVQ_API int yupvq_timer_start(yupvq_ctx* ctx);
 YUPVQ_API int yupvq_timer_stop(yupvq_ctx* ctx, float* out_ms);
 
+/* Per-launch timing of the dominant kernel (the tcgen05 assignment front-end) inside real calls:
+ * while enabled, every launch of it in the Lloyd / quantise passes is bracketed by a CUDA event pair
+ * on the context's stream (up to 128 launches); yupvq_profile_read synchronises, returns the summed
+ * time and the number of launches, and rearms.  Used by bench.py for the roofline line only (the
+ * timed region of the bench runs with profiling off). */
+YUPVQ_API int yupvq_profile(yupvq_ctx* ctx, int enable);
+YUPVQ_API int yupvq_profile_read(yupvq_ctx* ctx, float* out_ms_front_end, uint32_t* out_launches);
+
 /* CompressionConfig::SetQuality, src/vq_encoder.cpp:12-18 (powers hard-wired 4..10). */
 YUPVQ_API uint32_t yupvq_codebook_size(float quality);
 /* Fill cfg the way VQBCnCompressor::Compress does from CompressionParams,
@@ -189,6 +197,20 @@ YUPVQ_API int yupvq_comm_init(yupvq_ctx* ctx, const uint8_t id[128], int n_ranks
 YUPVQ_API int yupvq_encode_bcn_sharded(yupvq_ctx* ctx, const uint8_t* bc_blocks, size_t n_total, size_t first_block,
                                        size_t n_local, int bc_format, int channels, const yupvq_config* cfg,
                                        uint8_t* out_pixel_centroids, uint32_t* out_indices, yupvq_stats* stats);
+
+/* Lock-step batch over block shards (BASELINE config 5): n_textures textures of n_total
+ * blocks each (every rank passes all of them), this rank owns blocks [first_block, first_block +
+ * n_local) of EVERY texture.  Texture t is seeded on rank t % n_ranks (the K seed rows are combined
+ * by one all-reduce), all textures run their Lloyd passes together and ONE all-reduce per pass carries
+ * the K x 65 fixed-point sums/counts of the whole batch.  Texture t uses seed cfg->seed + t, as
+ * yupvq_encode_bcn_batch does; results are identical to the single-GPU call.  Without a
+ * communicator (yupvq_comm_init not called) it is the single-GPU lock-step batch (n_local = n_total).
+ * out_pixel_centroids[t]: K x 16*channels bytes; out_indices[t]: n_local indices. */
+YUPVQ_API int yupvq_encode_bcn_batch_sharded(yupvq_ctx* ctx, const uint8_t* const* bc_blocks, size_t n_textures,
+                                             size_t n_total, size_t first_block, size_t n_local, int bc_format,
+                                             int channels, const yupvq_config* cfg,
+                                             uint8_t* const* out_pixel_centroids, uint32_t* const* out_indices,
+                                             yupvq_stats* stats);
 
 #ifdef __cplusplus
 }

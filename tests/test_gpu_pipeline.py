@@ -133,3 +133,40 @@ def test_errors_are_reported(enc):
         enc.encode_bcn(np.zeros(16, np.uint8), 1, 2, 4, cfg)
     with pytest.raises(RuntimeError, match="channels"):
         enc.encode_bcn(np.zeros(8, np.uint8), 1, 1, 5, cfg)
+
+
+def test_lockstep_batch_equals_per_texture_calls(enc):
+    """yupvq_encode_bcn_batch_sharded on one GPU (no communicator, the whole texture as the shard): every
+    texture's centroids and indices are bit-identical to yupvq_encode_bcn with seed + t -- the lock-step
+    schedule, the per-texture operand views and the host-side convergence test change nothing."""
+    from yuptexture_b200 import binding
+    texs = [synth.bc1_encode(synth.ldr_rgb(256, 512, seed=31 + t)) for t in range(3)]
+    texs.append(synth.bc1_encode(np.full((256, 512, 3), 77, np.uint8)))   # flat: converges at once, leaves the set early
+    n, k = len(texs[0]), 128
+    cfg = binding.make_config(codebook=k, max_iterations=12, seed=5, assign_mode=binding.ASSIGN_TENSOR)
+    cents, idxs, st = enc.encode_bcn_batch_sharded(texs, n, 0, n, 1, 3, cfg)
+    total_passes = 0
+    for t, bc in enumerate(texs):
+        c1 = binding.make_config(codebook=k, max_iterations=12, seed=5 + t, assign_mode=binding.ASSIGN_TENSOR)
+        cent, idx, s1 = enc.encode_bcn(bc, n, 1, 3, c1)
+        assert bits_equal(cents[t], cent), t
+        assert bits_equal(idxs[t], idx), t
+        total_passes += s1.lloyd_passes
+    assert st.lloyd_passes == total_passes and st.gpu_launches > 0
+
+
+def test_multi_gpu_sharded_matches_single_gpu():
+    """Blocks sharded over 2 GPUs (NCCL all-reduce of the fixed-point sums): identical codebooks and
+    indices to the single-GPU run, for both the per-texture and the lock-step batch entry points."""
+    import os
+    import subprocess
+    import sys
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    root = os.path.normpath(os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
+                        "127.0.0.1", "--master-port", "29533", os.path.join(root, "tools", "multi_gpu_check.py")],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "multi_gpu_check ok" in r.stdout

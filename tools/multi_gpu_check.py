@@ -1,0 +1,73 @@
+#!/usr/bin/env python
+"""Multi-GPU parity check, one rank per GPU (torchrun): blocks sharded over the ranks must give the same
+codebooks and indices as one GPU, for yupvq_encode_bcn_sharded and yupvq_encode_bcn_batch_sharded.
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 tools/multi_gpu_check.py
+"""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.normpath(os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    import torch
+    import torch.distributed as dist
+    from yuptexture_b200 import binding, sharding, synth
+
+    rank, world, local = (int(os.environ.get(k, d)) for k, d in (("RANK", 0), ("WORLD_SIZE", 1), ("LOCAL_RANK", 0)))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    enc = binding.Encoder(local)
+    uid = torch.zeros(128, dtype=torch.uint8)
+    if rank == 0:
+        uid = torch.from_numpy(enc.comm_unique_id().copy())
+    uid = uid.to(dev)
+    dist.broadcast(uid, 0)
+    enc.comm_init(uid.cpu().numpy(), world, rank)
+
+    size, k, iters = 1024, 256, 10
+    texs = [synth.bc1_encode(synth.ldr_rgb(size, size, seed=200 + t)) for t in range(world + 1)]
+    texs.append(synth.bc1_encode(synth.checker_rgb(size, size)))  # few distinct blocks: empty clusters, sharded reseed
+    n = len(texs[0])
+    first, n_local = sharding.shard_range(n, world, rank)
+    cfg = binding.make_config(codebook=k, max_iterations=iters, seed=9)
+
+    # single-GPU answers (every rank computes them on its own GPU with a second, communicator-less context)
+    solo = binding.Encoder(local)
+    want = []
+    for t, bc in enumerate(texs):
+        c = binding.make_config(codebook=k, max_iterations=iters, seed=9 + t)
+        cent, idx, st = solo.encode_bcn(bc, n, 1, 3, c)
+        want.append((cent, idx, st.lloyd_passes))
+    solo.close()
+
+    ok = True
+    # (1) per-texture sharded call
+    for t, bc in enumerate(texs):
+        c = binding.make_config(codebook=k, max_iterations=iters, seed=9 + t)
+        cent, idx, st = enc.encode_bcn_sharded(bc, n, first, n_local, 1, 3, c)
+        ok &= np.array_equal(cent, want[t][0]) and np.array_equal(idx, want[t][1][first:first + n_local])
+        ok &= st.lloyd_passes == want[t][2]
+    # (2) lock-step batch
+    cents, idxs, st = enc.encode_bcn_batch_sharded(texs, n, first, n_local, 1, 3, cfg)
+    for t in range(len(texs)):
+        ok &= np.array_equal(cents[t], want[t][0]) and np.array_equal(idxs[t], want[t][1][first:first + n_local])
+    ok &= st.lloyd_passes == sum(w[2] for w in want)
+
+    flag = torch.tensor([1 if ok else 0], device=dev)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    enc.close()
+    dist.barrier()
+    dist.destroy_process_group()
+    if rank == 0:
+        print("multi_gpu_check ok" if int(flag) else "multi_gpu_check FAILED", f"world={world} textures={len(texs)}")
+    sys.exit(0 if int(flag) else 1)
+
+
+if __name__ == "__main__":
+    main()

@@ -74,10 +74,14 @@ def lib():
         L.yupvq_seed_hdr.argtypes = [_vp, _vp, C.c_size_t, C.c_uint32, C.c_uint64, _vp, C.POINTER(C.c_uint32)]
         L.yupvq_update_centroids.argtypes = [_vp, _vp, C.c_size_t, _vp, _vp, C.c_uint32, _vp, _vp]
         L.yupvq_gather_codebook.argtypes = [_vp, _vp, C.c_uint32, C.c_uint32, _vp, C.c_size_t, _vp]
+        L.yupvq_profile.argtypes = [_vp, C.c_int]
+        L.yupvq_profile_read.argtypes = [_vp, C.POINTER(C.c_float), C.POINTER(C.c_uint32)]
         L.yupvq_comm_unique_id.argtypes = [_vp, _vp]
         L.yupvq_comm_init.argtypes = [_vp, _vp, C.c_int, C.c_int]
         L.yupvq_encode_bcn_sharded.argtypes = [_vp, _vp, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int, C.c_int, cfgp,
                                                _vp, _vp, stp]
+        L.yupvq_encode_bcn_batch_sharded.argtypes = [_vp, C.POINTER(_vp), C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t,
+                                                     C.c_int, C.c_int, cfgp, C.POINTER(_vp), C.POINTER(_vp), stp]
         _lib = L
     return _lib
 
@@ -181,6 +185,31 @@ class Encoder:
         self._ck(self._L.yupvq_encode_bcn_sharded(self._ctx, _ptr(bc), n_total, first, n_local, fmt, ch, C.byref(cfg),
                                                   _ptr(out_centroids), _ptr(out_indices), C.byref(st)),
                  "yupvq_encode_bcn_sharded")
+        return out_centroids, out_indices, st
+
+    def profile(self, enable):
+        self._ck(self._L.yupvq_profile(self._ctx, 1 if enable else 0), "yupvq_profile")
+
+    def profile_read(self):
+        """(summed ms of the tensor front-end launches since the last read, number of launches)"""
+        ms, n = C.c_float(0), C.c_uint32(0)
+        self._ck(self._L.yupvq_profile_read(self._ctx, C.byref(ms), C.byref(n)), "yupvq_profile_read")
+        return ms.value, n.value
+
+    def encode_bcn_batch_sharded(self, textures, n_total, first, n_local, fmt, ch, cfg, out_centroids=None, out_indices=None):
+        """Lock-step batch (config 5): `textures` = list of whole-texture BCn arrays or raw device pointers;
+        outputs are lists (numpy arrays or raw device pointers), one per texture."""
+        t_n = len(textures)
+        textures = [x if isinstance(x, int) else _c(x, np.uint8) for x in textures]
+        if out_centroids is None:
+            out_centroids = [np.empty((cfg.codebook_size, 16 * ch), np.uint8) for _ in range(t_n)]
+        if out_indices is None:
+            out_indices = [np.empty(n_local, np.uint32) for _ in range(t_n)]
+        arr = lambda xs: (_vp * t_n)(*[None if x is None else _ptr(x).value for x in xs])
+        st = Stats()
+        self._ck(self._L.yupvq_encode_bcn_batch_sharded(self._ctx, arr(textures), t_n, n_total, first, n_local, fmt, ch,
+                                                        C.byref(cfg), arr(out_centroids), arr(out_indices), C.byref(st)),
+                 "yupvq_encode_bcn_batch_sharded")
         return out_centroids, out_indices, st
 
     # ---- the four VQEncoder calls

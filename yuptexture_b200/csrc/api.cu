@@ -68,10 +68,16 @@ struct yupvq_ctx {
     DevBuf cent_px, cent_feat, out_idx;                // finalize / quantize
     // tensor engine (assign_tc.cu): per block set A', |x'|, mu; per pass B', folded norms, candidates
     DevBuf tc_a, tc_xnorm, tc_small, tc_b, tc_bx, tc_cand, tc_amb;
+    // lock-step batch (yupvq_encode_bcn_batch_sharded): per-texture slices of one buffer each
+    DevBuf bt_feat, bt_tca, bt_xnorm, bt_tcsmall, bt_assign, bt_errors, bt_cent, bt_acc, bt_misc, bt_centpx;
     const float* tc_feat = nullptr;                    // block set the A' buffer was built from
     size_t tc_n = 0;
     uint64_t rerank_pairs = 0;
     uint32_t* h_small = nullptr;                       // pinned: flags + status readback
+    // optional per-launch timing of the tensor front-end (yupvq_profile): event pairs around each launch
+    bool profile = false;
+    std::vector<cudaEvent_t> pev;
+    size_t pev_used = 0;
 
     // multi-GPU
     NcclApi nccl;
@@ -343,26 +349,43 @@ int tc_prepare_blocks(yupvq_ctx* ctx, const float* feat, size_t n) {
 
 // One assignment pass.  errors may be null (tensor mode then skips the exact distance of blocks with
 // a single candidate); flags[0] |= 1 when an assignment changed.
+// `view` (lock-step batch): the per-texture A' / |x'| / mu buffers built by tc_prepare_view; null = the
+// context's own, built on demand for `feat`.
+struct TcView {
+    float* a = nullptr;
+    float* xnorm = nullptr;
+    uint8_t* small = nullptr;  // TC_SMALL_BYTES
+};
+
+int tc_prepare_view(yupvq_ctx* ctx, const float* feat, size_t n, const TcView& v) {
+    LAUNCH(launch_tc_mean(feat, n, reinterpret_cast<double*>(v.small + TC_SUMS), reinterpret_cast<float*>(v.small + TC_MU), ctx->stream));
+    ++ctx->launches;
+    LAUNCH(launch_tc_prep_blocks(feat, n, reinterpret_cast<const float*>(v.small + TC_MU), v.a, v.xnorm, ctx->stream));
+    return 0;
+}
+
 int assign_blocks(yupvq_ctx* ctx, const float* feat, size_t n, const float* cent, uint32_t K, int mode, uint32_t* assign,
-                  float* errors, uint32_t* flags, const uint32_t* stop = nullptr) {
+                  float* errors, uint32_t* flags, const uint32_t* stop = nullptr, const TcView* view = nullptr) {
     if (mode == YUPVQ_ASSIGN_TENSOR && !tc_supported(K))
         return ctx->fail("tensor assignment needs 1 <= K <= 65535 and a driver with cuTensorMapEncodeTiled (K = %u)", K);
     if (!use_tensor(mode, n, K)) {
         LAUNCH(launch_assign_exact(feat, n, cent, K, assign, errors, flags, stop, ctx->stream));
         return 0;
     }
-    if (tc_prepare_blocks(ctx, feat, n)) return 1;
+    if (!view && tc_prepare_blocks(ctx, feat, n)) return 1;
     const uint32_t k_pad = tc_padded_k(K);
     CK(ctx->tc_b.ensure((size_t)k_pad * 256));
     CK(ctx->tc_bx.ensure((size_t)k_pad * 32));
     CK(ctx->tc_cand.ensure(std::max<size_t>(1, n) * 16));
-    uint8_t* sm = ctx->tc_small.as<uint8_t>();
+    uint8_t* sm = view ? view->small : ctx->tc_small.as<uint8_t>();
+    float* tc_a = view ? view->a : ctx->tc_a.as<float>();
+    float* tc_xnorm = view ? view->xnorm : ctx->tc_xnorm.as<float>();
     LAUNCH(launch_tc_prep_centroids(cent, K, reinterpret_cast<const float*>(sm + TC_MU), ctx->tc_b.as<float>(),
                                     ctx->tc_bx.as<float>(), reinterpret_cast<float*>(sm + TC_CMAX), ctx->stream));
     uint32_t* small = ctx->small.as<uint32_t>();
     if (errors) {
         // errors[] wanted for every block: dense candidate lists + dense re-rank
-        LAUNCH(launch_assign_tc(ctx->tc_a.as<float>(), ctx->tc_xnorm.as<float>(), n, ctx->tc_b.as<float>(), ctx->tc_bx.as<float>(),
+        LAUNCH(launch_assign_tc(tc_a, tc_xnorm, n, ctx->tc_b.as<float>(), ctx->tc_bx.as<float>(),
                                 K, reinterpret_cast<const float*>(sm + TC_CMAX), ctx->tc_cand.as<uint4>(), nullptr, nullptr, nullptr,
                                 nullptr, stop, ctx->stream));
         LAUNCH(launch_rerank(feat, n, cent, K, ctx->tc_cand.as<uint4>(), assign, errors, flags, small + F_PAIRS, stop, ctx->stream));
@@ -370,9 +393,12 @@ int assign_blocks(yupvq_ctx* ctx, const float* feat, size_t n, const float* cent
         // the front-end finishes single-candidate blocks itself; the exact re-rank sees only the ambiguous ones
         CK(ctx->tc_amb.ensure(std::max<size_t>(1, n) * 4));
         if (!stop) CK(cudaMemsetAsync(small + F_AMB, 0, 8, ctx->stream));  // inside the Lloyd loop the re-rank leaves it cleared
-        LAUNCH(launch_assign_tc(ctx->tc_a.as<float>(), ctx->tc_xnorm.as<float>(), n, ctx->tc_b.as<float>(), ctx->tc_bx.as<float>(),
+        const bool prof = ctx->profile && ctx->pev_used + 2 <= ctx->pev.size();
+        if (prof) cudaEventRecord(ctx->pev[ctx->pev_used++], ctx->stream);
+        LAUNCH(launch_assign_tc(tc_a, tc_xnorm, n, ctx->tc_b.as<float>(), ctx->tc_bx.as<float>(),
                                 K, reinterpret_cast<const float*>(sm + TC_CMAX), ctx->tc_cand.as<uint4>(), assign, flags,
                                 ctx->tc_amb.as<uint32_t>(), small + F_AMB, stop, ctx->stream));
+        if (prof) cudaEventRecord(ctx->pev[ctx->pev_used++], ctx->stream);
         LAUNCH(launch_rerank_sparse(feat, cent, K, ctx->tc_cand.as<uint4>(), ctx->tc_amb.as<uint32_t>(), small + F_AMB,
                                     small + F_AMB + 1, assign, flags, small + F_PAIRS, ctx->stream));
     }
@@ -627,7 +653,7 @@ int yupvq_create(int device, yupvq_ctx** out) {
     bool ok = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) == cudaSuccess;
     for (auto& ev : ctx->ev) ok = ok && cudaEventCreate(&ev) == cudaSuccess;
     for (auto& ev : ctx->ev_user) ok = ok && cudaEventCreate(&ev) == cudaSuccess;
-    ok = ok && cudaMallocHost(reinterpret_cast<void**>(&ctx->h_small), 256) == cudaSuccess;
+    ok = ok && cudaMallocHost(reinterpret_cast<void**>(&ctx->h_small), 65536) == cudaSuccess;
     ok = ok && ctx->small.ensure(F_WORDS * 4) == cudaSuccess;
     ok = ok && cudaMemset(ctx->small.p, 0, F_WORDS * 4) == cudaSuccess;
     ok = ok && colour_tables_init() == cudaSuccess;
@@ -648,15 +674,49 @@ void yupvq_destroy(yupvq_ctx* ctx) {
     DevBuf* bufs[] = {&ctx->in_bytes, &ctx->planes, &ctx->feat, &ctx->s_planes, &ctx->s_feat, &ctx->s_rows,
                       &ctx->min_dist, &ctx->partial, &ctx->seed_idx, &ctx->canon, &ctx->small, &ctx->assign,
                       &ctx->errors, &ctx->cent, &ctx->acc, &ctx->cent_px, &ctx->cent_feat, &ctx->out_idx,
-                      &ctx->tc_a, &ctx->tc_xnorm, &ctx->tc_small, &ctx->tc_b, &ctx->tc_bx, &ctx->tc_cand, &ctx->tc_amb};
+                      &ctx->tc_a, &ctx->tc_xnorm, &ctx->tc_small, &ctx->tc_b, &ctx->tc_bx, &ctx->tc_cand, &ctx->tc_amb,
+                      &ctx->bt_feat, &ctx->bt_tca, &ctx->bt_xnorm, &ctx->bt_tcsmall, &ctx->bt_assign, &ctx->bt_errors,
+                      &ctx->bt_cent, &ctx->bt_acc, &ctx->bt_misc, &ctx->bt_centpx};
     for (DevBuf* b : bufs) b->release();
     if (ctx->h_small) cudaFreeHost(ctx->h_small);
     for (auto& ev : ctx->ev)
         if (ev) cudaEventDestroy(ev);
     for (auto& ev : ctx->ev_user)
         if (ev) cudaEventDestroy(ev);
+    for (auto& ev : ctx->pev)
+        if (ev) cudaEventDestroy(ev);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
+}
+
+int yupvq_profile(yupvq_ctx* ctx, int enable) {
+    if (!ctx) return 1;
+    Scope scope(ctx->device);
+    if (enable && ctx->pev.empty()) {
+        ctx->pev.resize(256);
+        for (auto& e : ctx->pev) CK(cudaEventCreate(&e));
+    }
+    ctx->profile = enable != 0;
+    ctx->pev_used = 0;
+    return 0;
+}
+
+int yupvq_profile_read(yupvq_ctx* ctx, float* out_ms_front_end, uint32_t* out_launches) {
+    if (!ctx) return 1;
+    Scope scope(ctx->device);
+    CK(cudaStreamSynchronize(ctx->stream));
+    float total = 0.f;
+    uint32_t n = 0;
+    for (size_t i = 0; i + 1 < ctx->pev_used; i += 2) {
+        float ms = 0.f;
+        CK(cudaEventElapsedTime(&ms, ctx->pev[i], ctx->pev[i + 1]));
+        total += ms;
+        ++n;
+    }
+    ctx->pev_used = 0;
+    if (out_ms_front_end) *out_ms_front_end = total;
+    if (out_launches) *out_launches = n;
+    return 0;
 }
 
 int yupvq_timer_start(yupvq_ctx* ctx) {
@@ -1297,6 +1357,227 @@ int yupvq_encode_bcn_sharded(yupvq_ctx* ctx, const uint8_t* bc_blocks, size_t n_
         stats->ms_total = tm.ms(t0, t7);
         stats->gpu_launches = ctx->launches;
     }
+    return 0;
+}
+
+
+// Lock-step batch over block shards: T textures of n_total blocks each, this rank
+// holds blocks [first_block, first_block + n_local) of EVERY texture.
+//   phase A  texture-parallel seeding: texture t is decoded whole and seeded on rank t % R only (K-Means++
+//            is K-1 dependent rounds: latency, not bandwidth, so it is spread over textures rather than
+//            replicated); the K seed rows of all textures are then combined with one all-reduce (every
+//            row is non-zero on exactly one rank: an integer sum with zeros is exact).
+//   phase B  every rank decodes its shard of every texture.
+//   Lloyd    all textures advance one pass at a time; ONE all-reduce per pass carries the fixed-point
+//            [K x 64 sums | K counts | changed] of all T textures, and one host readback carries the T
+//            convergence / empty-cluster words.  A texture leaves the active set when the reference's
+//            break rule fires for it (src/vq_encoder.cpp:341).
+// Results per texture are identical to yupvq_encode_bcn with seed + t (fixed-point sums).
+int yupvq_encode_bcn_batch_sharded(yupvq_ctx* ctx, const uint8_t* const* bc_blocks, size_t n_textures, size_t n_total,
+                                   size_t first_block, size_t n_local, int bc_format, int channels,
+                                   const yupvq_config* cfg, uint8_t* const* out_pixel_centroids,
+                                   uint32_t* const* out_indices, yupvq_stats* stats) {
+    if (!ctx) return 1;
+    Scope scope(ctx->device);
+    init_stats(stats);
+    ctx->launches = 0;
+    ctx->tc_feat = nullptr;
+    if (check_cfg(ctx, cfg, n_total, channels)) return 1;
+    if (!bc_blocks || n_textures == 0) return ctx->fail("no textures");
+    if (n_textures > 4096) return ctx->fail("too many textures in one batch (%zu > 4096)", n_textures);
+    if (!bc_supported(bc_format)) return ctx->fail("BC format %d is not supported on the LDR VQ path", bc_format);
+    if (first_block + n_local > n_total) return ctx->fail("shard [%zu, %zu) exceeds %zu blocks", first_block, first_block + n_local, n_total);
+    if (cfg->sample_ratio < 1.0f && cfg->sample_ratio > 0.0f) return ctx->fail("fast-mode sampling is not supported on the sharded path");
+    if (cfg->metric != YUPVQ_METRIC_OKLAB) return ctx->fail("the SAD metric is not supported on the sharded path");
+    const uint32_t K = cfg->codebook_size;
+    const size_t T = n_textures;
+    const int R = ctx->comm ? ctx->n_ranks : 1, rank = ctx->comm ? ctx->rank : 0;
+    const size_t bb = bc_block_bytes(bc_format);
+    const size_t nl = std::max<size_t>(1, n_local);
+    const size_t acc_words = (size_t)K * 65 + 1;
+    const bool tensor = use_tensor(cfg->assign_mode, n_local, K);
+    Timer tm(ctx);
+    const int t0 = tm.mark();
+
+    CK(ctx->bt_feat.ensure(T * nl * 256));
+    CK(ctx->bt_assign.ensure(T * nl * 4));
+    CK(ctx->bt_errors.ensure(T * nl * 4));
+    CK(ctx->bt_cent.ensure(T * (size_t)K * 256));
+    CK(ctx->bt_acc.ensure(T * acc_words * 8));
+    CK(ctx->bt_misc.ensure(T * 8 + 64));
+    CK(ctx->bt_centpx.ensure(T * (size_t)K * 16 * channels));
+    if (tensor) {
+        CK(ctx->bt_tca.ensure(T * nl * 256));
+        CK(ctx->bt_xnorm.ensure(T * nl * 4));
+        CK(ctx->bt_tcsmall.ensure(T * TC_SMALL_BYTES));
+    }
+    auto feat_t = [&](size_t t) { return ctx->bt_feat.as<float>() + t * nl * 64; };
+    auto assign_t = [&](size_t t) { return ctx->bt_assign.as<uint32_t>() + t * nl; };
+    auto errors_t = [&](size_t t) { return ctx->bt_errors.as<float>() + t * nl; };
+    auto cent_t = [&](size_t t) { return ctx->bt_cent.as<float>() + t * (size_t)K * 64; };
+    auto acc_t = [&](size_t t) { return ctx->bt_acc.as<long long>() + t * acc_words; };
+    auto centpx_t = [&](size_t t) { return ctx->bt_centpx.as<uint8_t>() + t * (size_t)K * 16 * channels; };
+    uint32_t* maxabs_d = ctx->bt_misc.as<uint32_t>();
+    uint32_t* empty_d = maxabs_d + T;
+    std::vector<TcView> views(T);
+    for (size_t t = 0; t < T && tensor; ++t) {
+        views[t].a = ctx->bt_tca.as<float>() + t * nl * 64;
+        views[t].xnorm = ctx->bt_xnorm.as<float>() + t * nl;
+        views[t].small = ctx->bt_tcsmall.as<uint8_t>() + t * TC_SMALL_BYTES;
+    }
+
+    // ---- phase A: seeding, texture-parallel --------------------------------------------------------------
+    uint32_t seed_rounds = 0;
+    CK(cudaMemsetAsync(ctx->bt_cent.p, 0, T * (size_t)K * 256, ctx->stream));
+    for (size_t t = 0; t < T; ++t) {
+        if ((int)(t % (size_t)R) != rank) continue;
+        const void* bc_dev = nullptr;
+        if (to_device(ctx, bc_blocks[t], n_total * bb, ctx->in_bytes, &bc_dev)) return 1;
+        CK(ctx->planes.ensure(n_total * 16 * channels));
+        CK(ctx->feat.ensure(n_total * 256));
+        LAUNCH(launch_decode_bcn(reinterpret_cast<const uint8_t*>(bc_dev), n_total, bc_format, channels,
+                                 ctx->planes.as<uint4>(), n_total, ctx->feat.as<float>(), nullptr, ctx->stream));
+        Blocks all;
+        all.n = n_total;
+        all.ch = channels;
+        all.planes = ctx->planes.as<uint4>();
+        all.stride = n_total;
+        all.feat = ctx->feat.as<float>();
+        size_t n_used;
+        Draws dr = make_draws(n_total, K, 1.0f, cfg->seed ? cfg->seed + t : 0, &n_used);
+        uint32_t rounds = 0;
+        if (run_seeding(ctx, all, K, dr, false, stats ? &rounds : nullptr)) return 1;
+        seed_rounds += rounds;
+        LAUNCH(launch_gather_rows_f32(all.feat, ctx->seed_idx.as<uint32_t>(), K, 64, cent_t(t), ctx->stream));
+    }
+    if (ctx->comm && ctx->nccl.all_reduce_sum_i64(ctx->comm, ctx->bt_cent.as<long long>(), T * (size_t)K * 32, ctx->stream))
+        return ctx->fail("ncclAllReduce(seed rows) failed");
+    const int t1 = tm.mark();
+
+    // ---- phase B: this rank's shard of every texture -> features, fixed-point scale, tensor operands --------
+    CK(cudaMemsetAsync(maxabs_d, 0, T * 8, ctx->stream));
+    for (size_t t = 0; t < T; ++t) {
+        const uint8_t* shard_dev = nullptr;
+        if (is_device_ptr(bc_blocks[t])) {
+            shard_dev = bc_blocks[t] + first_block * bb;
+        } else {
+            const void* p = nullptr;
+            if (to_device(ctx, bc_blocks[t] + first_block * bb, nl * bb, ctx->in_bytes, &p)) return 1;
+            shard_dev = reinterpret_cast<const uint8_t*>(p);
+        }
+        if (n_local) {
+            LAUNCH(launch_decode_bcn(shard_dev, n_local, bc_format, channels, nullptr, 0, feat_t(t), nullptr, ctx->stream));
+            LAUNCH(launch_max_abs(feat_t(t), n_local * 64, maxabs_d + t, ctx->stream));
+        }
+    }
+    if (ctx->comm && ctx->nccl.all_reduce_max_u32(ctx->comm, maxabs_d, T, ctx->stream)) return ctx->fail("ncclAllReduce(max) failed");
+    uint32_t* h_words = ctx->h_small + 64;
+    CK(cudaMemcpyAsync(h_words, maxabs_d, T * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    std::vector<int> shift(T);
+    for (size_t t = 0; t < T; ++t) {
+        float m;
+        std::memcpy(&m, h_words + t, 4);
+        shift[t] = fixed_shift(n_total, m);
+    }
+    for (size_t t = 0; t < T && tensor; ++t)
+        if (tc_prepare_view(ctx, feat_t(t), n_local, views[t])) return 1;
+    const int t2 = tm.mark();
+
+    // ---- Lloyd, all textures in lock step ------------------------------------------------------------------------
+    uint32_t* flags = ctx->small.as<uint32_t>();
+    CK(cudaMemsetAsync(ctx->bt_assign.p, 0, T * nl * 4, ctx->stream));  // assignments(numBlocks, 0), :316
+    CK(cudaMemsetAsync(flags + F_RESEEDS, 0, 4, ctx->stream));
+    CK(cudaMemsetAsync(flags + F_PAIRS, 0, 8, ctx->stream));
+    CK(cudaMemsetAsync(ctx->bt_acc.p, 0, T * acc_words * 8, ctx->stream));
+    ctx->reseeds_sharded = 0;
+    std::vector<char> active(T, 1);
+    std::vector<uint32_t> passes(T, 0);
+    size_t n_active = T;
+    uint32_t collectives = 0;
+    for (uint32_t iter = 0; iter < cfg->max_iterations && n_active; ++iter) {
+        for (size_t t = 0; t < T; ++t) {
+            if (!active[t]) continue;
+            CK(cudaMemsetAsync(flags, 0, 8, ctx->stream));  // changed, empty
+            if (assign_blocks(ctx, feat_t(t), n_local, cent_t(t), K, cfg->assign_mode, assign_t(t), tensor ? nullptr : errors_t(t),
+                              flags, nullptr, tensor ? &views[t] : nullptr))
+                return 1;
+            ++passes[t];
+            CK(cudaMemsetAsync(acc_t(t), 0, acc_words * 8, ctx->stream));
+            LAUNCH(launch_accumulate(feat_t(t), n_local, assign_t(t), K, shift[t], acc_t(t), flags, nullptr, ctx->stream));
+        }
+        // one exchange step per pass for the whole batch (converged textures ride along: their slices are stale, unused)
+        if (ctx->comm) {
+            if (ctx->nccl.all_reduce_sum_i64(ctx->comm, ctx->bt_acc.as<long long>(), T * acc_words, ctx->stream))
+                return ctx->fail("ncclAllReduce(sum) failed");
+            ++collectives;
+        }
+        for (size_t t = 0; t < T; ++t)
+            if (active[t]) LAUNCH(launch_count_empty(acc_t(t), K, empty_d + t, ctx->stream));
+        CK(cudaMemcpy2DAsync(h_words, 8, ctx->bt_acc.as<long long>() + (size_t)K * 65, acc_words * 8, 8, T, cudaMemcpyDeviceToHost,
+                             ctx->stream));
+        CK(cudaMemcpyAsync(h_words + 2 * T, empty_d, T * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+        for (size_t t = 0; t < T; ++t) {
+            if (!active[t]) continue;
+            long long changed;
+            std::memcpy(&changed, h_words + 2 * t, 8);
+            const uint32_t n_empty = h_words[2 * T + t];
+            if (!changed && iter > 0) {  // src/vq_encoder.cpp:341
+                active[t] = 0;
+                --n_active;
+                continue;
+            }
+            if (tensor && n_empty)  // errors[i] = distance to the assigned centroid, before the update (:336)
+                LAUNCH(launch_exact_errors(feat_t(t), n_local, cent_t(t), assign_t(t), errors_t(t), nullptr, nullptr, ctx->stream));
+            CK(cudaMemsetAsync(flags + F_EMPTY, 0, 4, ctx->stream));
+            LAUNCH(launch_finalize_centroids(acc_t(t), K, shift[t], cent_t(t), flags, nullptr, ctx->stream));
+            if (!n_empty) continue;
+            if (!ctx->comm) {
+                LAUNCH(launch_reseed_empty(feat_t(t), n_local, errors_t(t), acc_t(t), K, cent_t(t), flags, nullptr, ctx->stream));
+            } else {
+                Blocks mine;
+                mine.n = n_local;
+                mine.ch = channels;
+                mine.feat = feat_t(t);
+                if (reseed_sharded(ctx, mine, first_block, K, cent_t(t), errors_t(t), acc_t(t), flags)) return 1;
+            }
+        }
+    }
+    const int t3 = tm.mark();
+
+    // ---- centroids -> pixels, final index map of this rank's shard (QuantizeBlocks, :447-471) -------------
+    CK(ctx->cent_feat.ensure((size_t)K * 256));
+    CK(ctx->out_idx.ensure(nl * 4));
+    for (size_t t = 0; t < T; ++t) {
+        LAUNCH(launch_oklab_to_pixels(cent_t(t), K, channels, centpx_t(t), ctx->stream));
+        LAUNCH(launch_pixels_to_features(centpx_t(t), K, channels, nullptr, 0, ctx->cent_feat.as<float>(), ctx->stream));
+        if (assign_blocks(ctx, feat_t(t), n_local, ctx->cent_feat.as<float>(), K, cfg->assign_mode, ctx->out_idx.as<uint32_t>(),
+                          nullptr, nullptr, nullptr, tensor ? &views[t] : nullptr))
+            return 1;
+        if (out_pixel_centroids && from_device(ctx, out_pixel_centroids[t], centpx_t(t), (size_t)K * 16 * channels)) return 1;
+        if (out_indices && from_device(ctx, out_indices[t], ctx->out_idx.p, n_local * 4)) return 1;
+    }
+    const int t4 = tm.mark();
+    CK(cudaMemcpyAsync(ctx->h_small, flags + F_RESEEDS, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(ctx->h_small + 1, flags + F_PAIRS, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (stats) {
+        stats->n_blocks = (uint32_t)(n_local * T);
+        stats->codebook_size = K;
+        stats->seed_rounds = seed_rounds;
+        for (size_t t = 0; t < T; ++t) stats->lloyd_passes += passes[t];
+        stats->reseeds = ctx->h_small[0] + ctx->reseeds_sharded;
+        stats->rerank_blocks = ctx->h_small[1];
+        stats->rerank_overflow = ctx->h_small[2];
+        stats->ms_seed = tm.ms(t0, t1);      // phase A (whole-texture decode + seeding of the owned textures)
+        stats->ms_decode = tm.ms(t1, t2);    // phase B (shard decode, scale, tensor operands)
+        stats->ms_lloyd = tm.ms(t2, t3);
+        stats->ms_quantize = tm.ms(t3, t4);  // incl. centroid conversion and the D2H of the results
+        stats->ms_total = tm.ms(t0, t4);
+        stats->gpu_launches = ctx->launches;
+    }
+    (void)collectives;
     return 0;
 }
 
