@@ -69,7 +69,7 @@ struct yupvq_ctx {
     // tensor engine (assign_tc.cu): per block set A', |x'|, mu; per pass B', folded norms, candidates
     DevBuf tc_a, tc_xnorm, tc_small, tc_b, tc_bx, tc_cand, tc_amb;
     // lock-step batch (yupvq_encode_bcn_batch_sharded): per-texture slices of one buffer each
-    DevBuf bt_feat, bt_tca, bt_xnorm, bt_tcsmall, bt_assign, bt_errors, bt_cent, bt_acc, bt_misc, bt_centpx;
+    DevBuf bt_feat, bt_tca, bt_xnorm, bt_tcsmall, bt_assign, bt_errors, bt_cent, bt_acc, bt_misc, bt_centpx, bt_cent0;
     const float* tc_feat = nullptr;                    // block set the A' buffer was built from
     size_t tc_n = 0;
     uint64_t rerank_pairs = 0;
@@ -676,7 +676,7 @@ void yupvq_destroy(yupvq_ctx* ctx) {
                       &ctx->errors, &ctx->cent, &ctx->acc, &ctx->cent_px, &ctx->cent_feat, &ctx->out_idx,
                       &ctx->tc_a, &ctx->tc_xnorm, &ctx->tc_small, &ctx->tc_b, &ctx->tc_bx, &ctx->tc_cand, &ctx->tc_amb,
                       &ctx->bt_feat, &ctx->bt_tca, &ctx->bt_xnorm, &ctx->bt_tcsmall, &ctx->bt_assign, &ctx->bt_errors,
-                      &ctx->bt_cent, &ctx->bt_acc, &ctx->bt_misc, &ctx->bt_centpx};
+                      &ctx->bt_cent, &ctx->bt_acc, &ctx->bt_misc, &ctx->bt_centpx, &ctx->bt_cent0};
     for (DevBuf* b : bufs) b->release();
     if (ctx->h_small) cudaFreeHost(ctx->h_small);
     for (auto& ev : ctx->ev)
@@ -1404,7 +1404,7 @@ int yupvq_encode_bcn_batch_sharded(yupvq_ctx* ctx, const uint8_t* const* bc_bloc
     CK(ctx->bt_errors.ensure(T * nl * 4));
     CK(ctx->bt_cent.ensure(T * (size_t)K * 256));
     CK(ctx->bt_acc.ensure(T * acc_words * 8));
-    CK(ctx->bt_misc.ensure(T * 8 + 64));
+    CK(ctx->bt_misc.ensure(T * 56 + 512));  // maxabs | empty | (pad) ctl[3] | flags[4] | sticky | scales f32 | inv_scales f64
     CK(ctx->bt_centpx.ensure(T * (size_t)K * 16 * channels));
     if (tensor) {
         CK(ctx->bt_tca.ensure(T * nl * 256));
@@ -1486,70 +1486,247 @@ int yupvq_encode_bcn_batch_sharded(yupvq_ctx* ctx, const uint8_t* const* bc_bloc
 
     // ---- Lloyd, all textures in lock step ------------------------------------------------------------------------
     uint32_t* flags = ctx->small.as<uint32_t>();
-    CK(cudaMemsetAsync(ctx->bt_assign.p, 0, T * nl * 4, ctx->stream));  // assignments(numBlocks, 0), :316
-    CK(cudaMemsetAsync(flags + F_RESEEDS, 0, 4, ctx->stream));
-    CK(cudaMemsetAsync(flags + F_PAIRS, 0, 8, ctx->stream));
-    CK(cudaMemsetAsync(ctx->bt_acc.p, 0, T * acc_words * 8, ctx->stream));
-    ctx->reseeds_sharded = 0;
-    std::vector<char> active(T, 1);
+    // control words | per-texture flags | sticky: one contiguous run (cleared and read back together); the flags are
+    // written by the kernels while the stop words are polled, so the run starts on its own 128-byte line
+    uint32_t* ctl_d = maxabs_d + ((2 * T + 31) & ~(size_t)31);   // [T][3]: stop, passes, empty clusters
+    uint32_t* tflags_d = ctl_d + 3 * T;   // [T][4]: changed, empty, reseeds, spare
+    uint32_t* sticky_d = tflags_d + 4 * T;
     std::vector<uint32_t> passes(T, 0);
-    size_t n_active = T;
-    uint32_t collectives = 0;
-    for (uint32_t iter = 0; iter < cfg->max_iterations && n_active; ++iter) {
-        for (size_t t = 0; t < T; ++t) {
-            if (!active[t]) continue;
-            CK(cudaMemsetAsync(flags, 0, 8, ctx->stream));  // changed, empty
-            if (assign_blocks(ctx, feat_t(t), n_local, cent_t(t), K, cfg->assign_mode, assign_t(t), tensor ? nullptr : errors_t(t),
-                              flags, nullptr, tensor ? &views[t] : nullptr))
-                return 1;
-            ++passes[t];
-            CK(cudaMemsetAsync(acc_t(t), 0, acc_words * 8, ctx->stream));
-            LAUNCH(launch_accumulate(feat_t(t), n_local, assign_t(t), K, shift[t], acc_t(t), flags, nullptr, ctx->stream));
-        }
-        // one exchange step per pass for the whole batch (converged textures ride along: their slices are stale, unused)
-        if (ctx->comm) {
-            if (ctx->nccl.all_reduce_sum_i64(ctx->comm, ctx->bt_acc.as<long long>(), T * acc_words, ctx->stream))
-                return ctx->fail("ncclAllReduce(sum) failed");
-            ++collectives;
-        }
-        for (size_t t = 0; t < T; ++t)
-            if (active[t]) LAUNCH(launch_count_empty(acc_t(t), K, empty_d + t, ctx->stream));
-        CK(cudaMemcpy2DAsync(h_words, 8, ctx->bt_acc.as<long long>() + (size_t)K * 65, acc_words * 8, 8, T, cudaMemcpyDeviceToHost,
-                             ctx->stream));
-        CK(cudaMemcpyAsync(h_words + 2 * T, empty_d, T * 4, cudaMemcpyDeviceToHost, ctx->stream));
-        CK(cudaStreamSynchronize(ctx->stream));
-        for (size_t t = 0; t < T; ++t) {
-            if (!active[t]) continue;
-            long long changed;
-            std::memcpy(&changed, h_words + 2 * t, 8);
-            const uint32_t n_empty = h_words[2 * T + t];
-            if (!changed && iter > 0) {  // src/vq_encoder.cpp:341
-                active[t] = 0;
-                --n_active;
-                continue;
-            }
-            if (tensor && n_empty)  // errors[i] = distance to the assigned centroid, before the update (:336)
-                LAUNCH(launch_exact_errors(feat_t(t), n_local, cent_t(t), assign_t(t), errors_t(t), nullptr, nullptr, ctx->stream));
-            CK(cudaMemsetAsync(flags + F_EMPTY, 0, 4, ctx->stream));
-            LAUNCH(launch_finalize_centroids(acc_t(t), K, shift[t], cent_t(t), flags, nullptr, ctx->stream));
-            if (!n_empty) continue;
-            if (!ctx->comm) {
-                LAUNCH(launch_reseed_empty(feat_t(t), n_local, errors_t(t), acc_t(t), K, cent_t(t), flags, nullptr, ctx->stream));
-            } else {
-                Blocks mine;
-                mine.n = n_local;
-                mine.ch = channels;
-                mine.feat = feat_t(t);
-                if (reseed_sharded(ctx, mine, first_block, K, cent_t(t), errors_t(t), acc_t(t), flags)) return 1;
-            }
-        }
+    uint32_t reseeds_async = 0;
+    static const bool force_sync = getenv("YUPVQ_LLOYD_SYNC") != nullptr;  // A/B timing and tests
+    if (ctx->comm) {  // the seeds, should the pass loop have to be redone synchronously
+        CK(ctx->bt_cent0.ensure(T * (size_t)K * 256));
+        CK(cudaMemcpyAsync(ctx->bt_cent0.p, ctx->bt_cent.p, T * (size_t)K * 256, cudaMemcpyDeviceToDevice, ctx->stream));
     }
+    auto reset_state = [&]() -> int {
+        CK(cudaMemsetAsync(ctx->bt_assign.p, 0, T * nl * 4, ctx->stream));  // assignments(numBlocks, 0), :316
+        CK(cudaMemsetAsync(flags + F_RESEEDS, 0, 4, ctx->stream));
+        CK(cudaMemsetAsync(flags + F_PAIRS, 0, 8, ctx->stream));
+        CK(cudaMemsetAsync(ctl_d, 0, (7 * T + 1) * 4, ctx->stream));
+        CK(cudaMemsetAsync(flags + F_AMB, 0, 8, ctx->stream));  // ambiguous-row count, ticket (the re-rank leaves them cleared)
+        ctx->reseeds_sharded = 0;
+        return 0;
+    };
+    // Asynchronous loop: no host round trip per pass.  The reference's convergence test runs on the device for
+    // every texture (launch_lloyd_control_batch); kernels of a stopped texture return at once.  Block-sharded
+    // runs cannot reseed an empty cluster on the device: the first one raises `sticky` and the host redoes the
+    // batch with the synchronous loop below (rare: flat or few-colour textures).
+    auto run_async = [&](bool* redo) -> int {
+        *redo = false;
+        if (reset_state()) return 1;
+        for (uint32_t iter = 0; iter < cfg->max_iterations; ++iter) {
+            CK(cudaMemsetAsync(ctx->bt_acc.p, 0, T * acc_words * 8, ctx->stream));
+            for (size_t t = 0; t < T; ++t) {
+                const uint32_t* stop = ctl_d + 3 * t;
+                if (assign_blocks(ctx, feat_t(t), n_local, cent_t(t), K, cfg->assign_mode, assign_t(t), tensor ? nullptr : errors_t(t),
+                                  tflags_d + 4 * t, stop, tensor ? &views[t] : nullptr))
+                    return 1;
+                LAUNCH(launch_accumulate(feat_t(t), n_local, assign_t(t), K, shift[t], acc_t(t), tflags_d + 4 * t, stop, ctx->stream));
+            }
+            if (ctx->comm && ctx->nccl.all_reduce_sum_i64(ctx->comm, ctx->bt_acc.as<long long>(), T * acc_words, ctx->stream))
+                return ctx->fail("ncclAllReduce(sum) failed");
+            LAUNCH(launch_lloyd_control_batch(ctx->bt_acc.as<long long>(), acc_words, (uint32_t)T, K, iter, 0u, tflags_d, 4u, ctl_d,
+                                              ctx->comm ? sticky_d : nullptr, ctx->stream));
+            for (size_t t = 0; t < T; ++t) {
+                const uint32_t* stop = ctl_d + 3 * t;
+                if (tensor && !ctx->comm)
+                    LAUNCH(launch_exact_errors(feat_t(t), n_local, cent_t(t), assign_t(t), errors_t(t), stop, ctl_d + 3 * t + 2, ctx->stream));
+                LAUNCH(launch_finalize_centroids(acc_t(t), K, shift[t], cent_t(t), tflags_d + 4 * t, stop, ctx->stream));
+                if (!ctx->comm)
+                    LAUNCH(launch_reseed_empty(feat_t(t), n_local, errors_t(t), acc_t(t), K, cent_t(t), tflags_d + 4 * t, stop, ctx->stream));
+            }
+            if ((iter == 3 || iter == 7 || iter == 15) && iter + 1 < cfg->max_iterations) {  // all converged / redo needed?
+                CK(cudaMemcpyAsync(h_words, ctl_d, (7 * T + 1) * 4, cudaMemcpyDeviceToHost, ctx->stream));
+                CK(cudaStreamSynchronize(ctx->stream));
+                bool all_stopped = true;
+                for (size_t t = 0; t < T; ++t) all_stopped = all_stopped && h_words[3 * t] != 0;
+                if (all_stopped || h_words[7 * T]) break;
+            }
+        }
+        CK(cudaMemcpyAsync(h_words, ctl_d, (7 * T + 1) * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+        if (h_words[7 * T]) {
+            *redo = true;
+            return 0;
+        }
+        for (size_t t = 0; t < T; ++t) {
+            passes[t] = h_words[3 * t + 1];
+            reseeds_async += h_words[3 * T + 4 * t + 2];
+        }
+        return 0;
+    };
+    auto run_sync = [&]() -> int {
+        if (reset_state()) return 1;
+        if (ctx->comm) CK(cudaMemcpyAsync(ctx->bt_cent.p, ctx->bt_cent0.p, T * (size_t)K * 256, cudaMemcpyDeviceToDevice, ctx->stream));
+        CK(cudaMemsetAsync(ctx->bt_acc.p, 0, T * acc_words * 8, ctx->stream));
+        std::vector<char> active(T, 1);
+        std::fill(passes.begin(), passes.end(), 0u);
+        size_t n_active = T;
+        for (uint32_t iter = 0; iter < cfg->max_iterations && n_active; ++iter) {
+            for (size_t t = 0; t < T; ++t) {
+                if (!active[t]) continue;
+                CK(cudaMemsetAsync(flags, 0, 8, ctx->stream));  // changed, empty
+                if (assign_blocks(ctx, feat_t(t), n_local, cent_t(t), K, cfg->assign_mode, assign_t(t), tensor ? nullptr : errors_t(t),
+                                  flags, nullptr, tensor ? &views[t] : nullptr))
+                    return 1;
+                ++passes[t];
+                CK(cudaMemsetAsync(acc_t(t), 0, acc_words * 8, ctx->stream));
+                LAUNCH(launch_accumulate(feat_t(t), n_local, assign_t(t), K, shift[t], acc_t(t), flags, nullptr, ctx->stream));
+            }
+            // one exchange step per pass for the whole batch (converged textures ride along: their slices are stale, unused)
+            if (ctx->comm && ctx->nccl.all_reduce_sum_i64(ctx->comm, ctx->bt_acc.as<long long>(), T * acc_words, ctx->stream))
+                return ctx->fail("ncclAllReduce(sum) failed");
+            for (size_t t = 0; t < T; ++t)
+                if (active[t]) LAUNCH(launch_count_empty(acc_t(t), K, empty_d + t, ctx->stream));
+            CK(cudaMemcpy2DAsync(h_words, 8, ctx->bt_acc.as<long long>() + (size_t)K * 65, acc_words * 8, 8, T, cudaMemcpyDeviceToHost,
+                                 ctx->stream));
+            CK(cudaMemcpyAsync(h_words + 2 * T, empty_d, T * 4, cudaMemcpyDeviceToHost, ctx->stream));
+            CK(cudaStreamSynchronize(ctx->stream));
+            for (size_t t = 0; t < T; ++t) {
+                if (!active[t]) continue;
+                long long changed;
+                std::memcpy(&changed, h_words + 2 * t, 8);
+                const uint32_t n_empty = h_words[2 * T + t];
+                if (!changed && iter > 0) {  // src/vq_encoder.cpp:341
+                    active[t] = 0;
+                    --n_active;
+                    continue;
+                }
+                if (tensor && n_empty)  // errors[i] = distance to the assigned centroid, before the update (:336)
+                    LAUNCH(launch_exact_errors(feat_t(t), n_local, cent_t(t), assign_t(t), errors_t(t), nullptr, nullptr, ctx->stream));
+                CK(cudaMemsetAsync(flags + F_EMPTY, 0, 4, ctx->stream));
+                LAUNCH(launch_finalize_centroids(acc_t(t), K, shift[t], cent_t(t), flags, nullptr, ctx->stream));
+                if (!n_empty) continue;
+                if (!ctx->comm) {
+                    LAUNCH(launch_reseed_empty(feat_t(t), n_local, errors_t(t), acc_t(t), K, cent_t(t), flags, nullptr, ctx->stream));
+                } else {
+                    Blocks mine;
+                    mine.n = n_local;
+                    mine.ch = channels;
+                    mine.feat = feat_t(t);
+                    if (reseed_sharded(ctx, mine, first_block, K, cent_t(t), errors_t(t), acc_t(t), flags)) return 1;
+                }
+            }
+        }
+        return 0;
+    };
+    // Whole-batch launches: when the shards are tile-aligned the rows of all textures are one matrix, so every kernel
+    // of a pass is launched ONCE for the batch (the front-end reloads its resident centroid operand when a CTA crosses
+    // into the next texture) -- a pass costs the same handful of launches whatever the number of textures.
+    static const bool no_fuse = getenv("YUPVQ_BATCH_PER_TEXTURE") != nullptr;  // A/B timing and tests
+    const uint32_t k_pad = tc_padded_k(K);
+    const bool fused = !no_fuse && tensor && n_local > 0 && n_local % 128 == 0 && k_pad <= 512 && accumulate_batch_supported(n_local, K) &&
+                       T * n_local < 0xffffffffull;
+    TcBatch tb{};
+    AccBatch ab{};
+    float* scales_d = reinterpret_cast<float*>(sticky_d + 1);
+    double* inv_scales_d = reinterpret_cast<double*>(ctx->bt_misc.as<uint8_t>() + ((T * 48 + 256 + 7) & ~(size_t)7));
+    if (fused) {
+        CK(ctx->tc_b.ensure(T * (size_t)k_pad * 256));
+        CK(ctx->tc_bx.ensure(T * (size_t)k_pad * 32));
+        CK(ctx->tc_cand.ensure(T * nl * 16));
+        CK(ctx->tc_amb.ensure(T * nl * 4));
+        std::vector<float> sc(T);
+        std::vector<double> isc(T);
+        for (size_t t = 0; t < T; ++t) {
+            sc[t] = std::ldexp(1.0f, shift[t]);
+            isc[t] = std::ldexp(1.0, -shift[t]);
+        }
+        CK(cudaMemcpyAsync(scales_d, sc.data(), T * 4, cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaMemcpyAsync(inv_scales_d, isc.data(), T * 8, cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));  // sc / isc are stack-owned
+        tb.tiles_per_tex = (uint32_t)(n_local / 128);
+        tb.k_pad = k_pad;
+        tb.cmax_stride = TC_SMALL_BYTES / 4;
+        tb.flags_stride = 4;
+        tb.stop_stride = 3;
+        tb.rows_per_tex = (uint32_t)n_local;
+        tb.n_textures = (uint32_t)T;
+        ab.n_textures = (uint32_t)T;
+        ab.acc_stride = acc_words;
+        ab.scales = scales_d;
+        ab.flags_stride = 4;
+        ab.stop_stride = 3;
+    }
+    // one assignment pass over the whole batch; out == bt_assign inside the Lloyd loop, the index map for the quantise
+    auto assign_fused = [&](const float* cent_all, uint32_t* out, uint32_t* fl, const uint32_t* stop) -> int {
+        uint8_t* sm = ctx->bt_tcsmall.as<uint8_t>();
+        TcBatch b = tb;
+        if (!fl) b.flags_stride = 0;
+        if (!stop) b.stop_stride = 0;
+        LAUNCH(launch_tc_prep_centroids_batch(cent_all, K, (uint32_t)T, sm, TC_SMALL_BYTES, TC_MU, TC_CMAX, ctx->tc_b.as<float>(),
+                                              ctx->tc_bx.as<float>(), ctx->stream));
+        const bool prof = ctx->profile && ctx->pev_used + 2 <= ctx->pev.size();
+        if (prof) cudaEventRecord(ctx->pev[ctx->pev_used++], ctx->stream);
+        LAUNCH(launch_assign_tc(ctx->bt_tca.as<float>(), ctx->bt_xnorm.as<float>(), T * n_local, ctx->tc_b.as<float>(), ctx->tc_bx.as<float>(),
+                                K, reinterpret_cast<const float*>(sm + TC_CMAX), ctx->tc_cand.as<uint4>(), out, fl,
+                                ctx->tc_amb.as<uint32_t>(), flags + F_AMB, stop, ctx->stream, &b));
+        if (prof) cudaEventRecord(ctx->pev[ctx->pev_used++], ctx->stream);
+        LAUNCH(launch_rerank_sparse(ctx->bt_feat.as<float>(), cent_all, K, ctx->tc_cand.as<uint4>(), ctx->tc_amb.as<uint32_t>(), flags + F_AMB,
+                                    flags + F_AMB + 1, out, fl, flags + F_PAIRS, ctx->stream, &b));
+        return 0;
+    };
+    auto run_async_fused = [&](bool* redo) -> int {
+        *redo = false;
+        if (reset_state()) return 1;
+        for (uint32_t iter = 0; iter < cfg->max_iterations; ++iter) {
+            CK(cudaMemsetAsync(ctx->bt_acc.p, 0, T * acc_words * 8, ctx->stream));
+            if (assign_fused(ctx->bt_cent.as<float>(), ctx->bt_assign.as<uint32_t>(), tflags_d, ctl_d)) return 1;
+            LAUNCH(launch_accumulate_batch(ctx->bt_feat.as<float>(), n_local, ctx->bt_assign.as<uint32_t>(), K, ctx->bt_acc.as<long long>(),
+                                           tflags_d, ctl_d, ab, ctx->stream));
+            if (ctx->comm && ctx->nccl.all_reduce_sum_i64(ctx->comm, ctx->bt_acc.as<long long>(), T * acc_words, ctx->stream))
+                return ctx->fail("ncclAllReduce(sum) failed");
+            LAUNCH(launch_lloyd_control_batch(ctx->bt_acc.as<long long>(), acc_words, (uint32_t)T, K, iter, 0u, tflags_d, 4u, ctl_d,
+                                              ctx->comm ? sticky_d : nullptr, ctx->stream));
+            if (!ctx->comm)
+                for (size_t t = 0; t < T; ++t)
+                    LAUNCH(launch_exact_errors(feat_t(t), n_local, cent_t(t), assign_t(t), errors_t(t), ctl_d + 3 * t, ctl_d + 3 * t + 2, ctx->stream));
+            LAUNCH(launch_finalize_centroids_batch(ctx->bt_acc.as<long long>(), acc_words, (uint32_t)T, K, inv_scales_d, ctx->bt_cent.as<float>(),
+                                                   tflags_d, 4u, ctl_d, 3u, ctx->stream));
+            if (!ctx->comm)
+                for (size_t t = 0; t < T; ++t)
+                    LAUNCH(launch_reseed_empty(feat_t(t), n_local, errors_t(t), acc_t(t), K, cent_t(t), tflags_d + 4 * t, ctl_d + 3 * t, ctx->stream));
+            if ((iter == 3 || iter == 7 || iter == 15) && iter + 1 < cfg->max_iterations) {  // all converged / redo needed?
+                CK(cudaMemcpyAsync(h_words, ctl_d, (7 * T + 1) * 4, cudaMemcpyDeviceToHost, ctx->stream));
+                CK(cudaStreamSynchronize(ctx->stream));
+                bool all_stopped = true;
+                for (size_t t = 0; t < T; ++t) all_stopped = all_stopped && h_words[3 * t] != 0;
+                if (all_stopped || h_words[7 * T]) break;
+            }
+        }
+        CK(cudaMemcpyAsync(h_words, ctl_d, (7 * T + 1) * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+        if (h_words[7 * T]) {
+            *redo = true;
+            return 0;
+        }
+        for (size_t t = 0; t < T; ++t) {
+            passes[t] = h_words[3 * t + 1];
+            reseeds_async += h_words[3 * T + 4 * t + 2];
+        }
+        return 0;
+    };
+    bool redo = force_sync;
+    if (!force_sync && (fused ? run_async_fused(&redo) : run_async(&redo))) return 1;
+    if (redo && run_sync()) return 1;
     const int t3 = tm.mark();
 
     // ---- centroids -> pixels, final index map of this rank's shard (QuantizeBlocks, :447-471) -------------
+    if (fused) {
+        CK(ctx->cent_feat.ensure(T * (size_t)K * 256));
+        CK(ctx->out_idx.ensure(T * nl * 4));
+        LAUNCH(launch_oklab_to_pixels(ctx->bt_cent.as<float>(), T * (size_t)K, channels, ctx->bt_centpx.as<uint8_t>(), ctx->stream));
+        LAUNCH(launch_pixels_to_features(ctx->bt_centpx.as<uint8_t>(), T * (size_t)K, channels, nullptr, 0, ctx->cent_feat.as<float>(), ctx->stream));
+        CK(cudaMemsetAsync(flags + F_AMB, 0, 8, ctx->stream));
+        if (assign_fused(ctx->cent_feat.as<float>(), ctx->out_idx.as<uint32_t>(), nullptr, nullptr)) return 1;
+        for (size_t t = 0; t < T; ++t) {
+            if (out_pixel_centroids && from_device(ctx, out_pixel_centroids[t], centpx_t(t), (size_t)K * 16 * channels)) return 1;
+            if (out_indices && from_device(ctx, out_indices[t], ctx->out_idx.as<uint32_t>() + t * nl, n_local * 4)) return 1;
+        }
+    }
     CK(ctx->cent_feat.ensure((size_t)K * 256));
     CK(ctx->out_idx.ensure(nl * 4));
-    for (size_t t = 0; t < T; ++t) {
+    for (size_t t = 0; t < T && !fused; ++t) {
         LAUNCH(launch_oklab_to_pixels(cent_t(t), K, channels, centpx_t(t), ctx->stream));
         LAUNCH(launch_pixels_to_features(centpx_t(t), K, channels, nullptr, 0, ctx->cent_feat.as<float>(), ctx->stream));
         if (assign_blocks(ctx, feat_t(t), n_local, ctx->cent_feat.as<float>(), K, cfg->assign_mode, ctx->out_idx.as<uint32_t>(),
@@ -1567,7 +1744,7 @@ int yupvq_encode_bcn_batch_sharded(yupvq_ctx* ctx, const uint8_t* const* bc_bloc
         stats->codebook_size = K;
         stats->seed_rounds = seed_rounds;
         for (size_t t = 0; t < T; ++t) stats->lloyd_passes += passes[t];
-        stats->reseeds = ctx->h_small[0] + ctx->reseeds_sharded;
+        stats->reseeds = ctx->h_small[0] + ctx->reseeds_sharded + reseeds_async;
         stats->rerank_blocks = ctx->h_small[1];
         stats->rerank_overflow = ctx->h_small[2];
         stats->ms_seed = tm.ms(t0, t1);      // phase A (whole-texture decode + seeding of the owned textures)
@@ -1577,7 +1754,6 @@ int yupvq_encode_bcn_batch_sharded(yupvq_ctx* ctx, const uint8_t* const* bc_bloc
         stats->ms_total = tm.ms(t0, t4);
         stats->gpu_launches = ctx->launches;
     }
-    (void)collectives;
     return 0;
 }
 

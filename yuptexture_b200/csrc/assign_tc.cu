@@ -169,13 +169,34 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t sbo_bytes
 constexpr uint32_t kIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
 
 // ---- the front-end kernel -----------------------------------------------------------------------------
+template <bool BATCH>
 __global__ void __launch_bounds__(kThreadsTc, 1)
 assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
                  const __grid_constant__ CUtensorMap tm_bx, const float* __restrict__ xnorm,
                  const float* __restrict__ cmax_ptr, uint32_t n, uint32_t num_tiles, uint32_t num_chunks,
                  uint32_t resident_b, uint4* __restrict__ cand, uint32_t* __restrict__ assign, uint32_t* __restrict__ flags,
-                 uint32_t* __restrict__ amb_list, unsigned int* __restrict__ amb_count, const uint32_t* __restrict__ stop) {
-    if (stop && __ldg(stop)) return;  // the Lloyd loop has converged: passes enqueued ahead of time do nothing
+                 uint32_t* __restrict__ amb_list, unsigned int* __restrict__ amb_count, const uint32_t* __restrict__ stop,
+                 TcBatch bt) {
+    // Lock-step batch (bt.tiles_per_tex < num_tiles): the rows of all textures are one contiguous matrix, tile t belongs
+    // to texture t / tiles_per_tex; that texture's centroid operand is rows [tex * k_pad, (tex + 1) * k_pad) of the B maps
+    // and its cmax / flags / stop words sit at the given strides.  A CTA reloads its resident B when it crosses
+    // into the next texture (about once per 1/T of its tiles).  Single texture: tiles_per_tex == num_tiles.
+    // The single-texture instantiation (BATCH = false) has none of the per-tile texture bookkeeping.
+    if (!BATCH && stop && __ldg(stop)) return;  // converged: passes enqueued ahead of time do nothing
+    // batch: a texture's stop word is read once per texture a role walks into, not per tile (the words share cache lines
+    // with flags the epilogue writes)
+    uint32_t chk_tex = 0xffffffffu;
+    bool chk_live = true;
+    auto tex_of = [&](uint32_t tt) -> uint32_t { return BATCH ? tt / bt.tiles_per_tex : 0u; };
+    auto live = [&](uint32_t tt) {
+        if (!BATCH || !stop) return true;
+        const uint32_t x = tt / bt.tiles_per_tex;
+        if (x != chk_tex) {
+            chk_tex = x;
+            chk_live = __ldg(stop + (size_t)x * bt.stop_stride) == 0u;
+        }
+        return chk_live;
+    };
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     uint8_t* base_ptr = smem_raw + (base - smem_u32(smem_raw));
@@ -213,32 +234,53 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
     if (warp == 0) {
         // ===== TMA producer ==============================================================================
         if (lane == 0) {
-            if (resident_b) {
+            uint32_t it = 0, u = 0, cur_tex = 0xffffffffu, bgen = 0;
+            if (!BATCH && resident_b) {
                 for (uint32_t j = 0; j < num_chunks; ++j) {
-                    const uint32_t dst = base + OFF_B + j * B_STAGE_BYTES;
+                    const uint32_t dstb = base + OFF_B + j * B_STAGE_BYTES;
                     mbar_expect_tx(bar(BAR_FULL_B + j), B_STAGE_BYTES);
-                    tma_load_2d(dst, &tm_b, 0, (int)(j * BN), bar(BAR_FULL_B + j));
-                    tma_load_2d(dst + B_HALF_BYTES, &tm_b, 64, (int)(j * BN), bar(BAR_FULL_B + j));
-                    tma_load_2d(dst + 2 * B_HALF_BYTES, &tm_bx, 0, (int)(j * BN), bar(BAR_FULL_B + j));
+                    tma_load_2d(dstb, &tm_b, 0, (int)(j * BN), bar(BAR_FULL_B + j));
+                    tma_load_2d(dstb + B_HALF_BYTES, &tm_b, 64, (int)(j * BN), bar(BAR_FULL_B + j));
+                    tma_load_2d(dstb + 2 * B_HALF_BYTES, &tm_bx, 0, (int)(j * BN), bar(BAR_FULL_B + j));
                 }
+                cur_tex = 0;
+                bgen = 1;
             }
-            uint32_t it = 0, u = 0;
-            for (uint32_t t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
+            for (uint32_t t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+                const uint32_t tex = tex_of(t);
+                if (!live(t)) continue;
                 const uint32_t sa = it & 1, pa = (it >> 1) & 1;
+                ++it;
                 mbar_wait(bar(BAR_EMPTY_A + sa), pa ^ 1);
                 const uint32_t dst = base + OFF_A + sa * A_STAGE_BYTES;
                 mbar_expect_tx(bar(BAR_FULL_A + sa), A_STAGE_BYTES);
                 tma_load_2d(dst, &tm_a, 0, (int)(t * BM), bar(BAR_FULL_A + sa));
                 tma_load_2d(dst + A_HALF_BYTES, &tm_a, 64, (int)(t * BM), bar(BAR_FULL_A + sa));
+                if (BATCH && resident_b && tex != cur_tex) {
+                    // (re)load the resident centroid operand (after this tile's A load is in flight); a reload waits until the
+                    // MMAs of the previous texture are done
+                    for (uint32_t j = 0; j < num_chunks; ++j) {
+                        if (bgen) mbar_wait(bar(BAR_EMPTY_B + j), (bgen - 1) & 1);
+                        const uint32_t dstb = base + OFF_B + j * B_STAGE_BYTES;
+                        const int brow = (int)(tex * bt.k_pad + j * BN);
+                        mbar_expect_tx(bar(BAR_FULL_B + j), B_STAGE_BYTES);
+                        tma_load_2d(dstb, &tm_b, 0, brow, bar(BAR_FULL_B + j));
+                        tma_load_2d(dstb + B_HALF_BYTES, &tm_b, 64, brow, bar(BAR_FULL_B + j));
+                        tma_load_2d(dstb + 2 * B_HALF_BYTES, &tm_bx, 0, brow, bar(BAR_FULL_B + j));
+                    }
+                    ++bgen;
+                    cur_tex = tex;
+                }
                 if (!resident_b) {
                     for (uint32_t j = 0; j < num_chunks; ++j, ++u) {
                         const uint32_t sb = u & 1, pb = (u >> 1) & 1;
                         mbar_wait(bar(BAR_EMPTY_B + sb), pb ^ 1);
                         const uint32_t dstb = base + OFF_B + sb * B_STAGE_BYTES;
+                        const int brow = (int)(tex * bt.k_pad + j * BN);
                         mbar_expect_tx(bar(BAR_FULL_B + sb), B_STAGE_BYTES);
-                        tma_load_2d(dstb, &tm_b, 0, (int)(j * BN), bar(BAR_FULL_B + sb));
-                        tma_load_2d(dstb + B_HALF_BYTES, &tm_b, 64, (int)(j * BN), bar(BAR_FULL_B + sb));
-                        tma_load_2d(dstb + 2 * B_HALF_BYTES, &tm_bx, 0, (int)(j * BN), bar(BAR_FULL_B + sb));
+                        tma_load_2d(dstb, &tm_b, 0, brow, bar(BAR_FULL_B + sb));
+                        tma_load_2d(dstb + B_HALF_BYTES, &tm_b, 64, brow, bar(BAR_FULL_B + sb));
+                        tma_load_2d(dstb + 2 * B_HALF_BYTES, &tm_bx, 0, brow, bar(BAR_FULL_B + sb));
                     }
                 }
             }
@@ -246,10 +288,21 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
     } else if (warp == 1) {
         // ===== MMA issuer (one thread) ===================================================================
         if (lane == 0) {
-            uint32_t it = 0, u = 0;
+            uint32_t it = 0, u = 0, cur_tex = 0xffffffffu, bgen = 0;
             const uint64_t ones_desc = make_desc(base + OFF_ONES, 256, 6);
-            for (uint32_t t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
+            for (uint32_t t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+                const uint32_t tex = tex_of(t);
+                if (!live(t)) continue;
+                const bool first_of_tex = tex != cur_tex;   // wait for this texture's resident B
+                if (first_of_tex) {
+                    cur_tex = tex;
+                    ++bgen;
+                }
+                // last tile this CTA runs on this texture: hand the resident B back to the producer afterwards
+                // (a texture is live or stopped as a whole, so the next tile of the same texture is live too)
+                const bool last_of_tex = BATCH && !(t + gridDim.x < num_tiles && (t + gridDim.x) / bt.tiles_per_tex == tex);
                 const uint32_t sa = it & 1, pa = (it >> 1) & 1;
+                ++it;
                 mbar_wait(bar(BAR_FULL_A + sa), pa);
                 const uint32_t a_addr = base + OFF_A + sa * A_STAGE_BYTES;
                 for (uint32_t j = 0; j < num_chunks; ++j, ++u) {
@@ -258,7 +311,7 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                     uint32_t sb;
                     if (resident_b) {
                         sb = j;
-                        if (it == 0) mbar_wait(bar(BAR_FULL_B + sb), 0);
+                        if (first_of_tex) mbar_wait(bar(BAR_FULL_B + sb), (bgen - 1) & 1);
                     } else {
                         sb = u & 1;
                         mbar_wait(bar(BAR_FULL_B + sb), (u >> 1) & 1);
@@ -278,7 +331,7 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                     }
                     tc_mma_bf16(d_tmem, ones_desc, make_desc(b_addr + 2 * B_HALF_BYTES, 256, 6), kIdesc, 1u);
                     tc_commit(bar(BAR_TFULL + acc));
-                    if (!resident_b) tc_commit(bar(BAR_EMPTY_B + sb));
+                    if (!resident_b || last_of_tex) tc_commit(bar(BAR_EMPTY_B + sb));
                 }
                 tc_commit(bar(BAR_EMPTY_A + sa));
             }
@@ -304,14 +357,21 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
         uint16_t* lists = reinterpret_cast<uint16_t*>(base_ptr + OFF_LIST);   // [2 parity][kSplit][128][kListCap]
         float* s_max = reinterpret_cast<float*>(base_ptr + OFF_MAX);          // [2 parity][kSplit][128]
         uint8_t* s_cnt = reinterpret_cast<uint8_t*>(base_ptr + OFF_CNT);      // [2 parity][kSplit][128]
-        const float cmax = __ldg(cmax_ptr);
         const uint32_t lane_taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(slice * kCols);
         uint32_t u = 0, tpar = 0;
         float xn_next = 0.0f;
         uint32_t old_next = 0;
-        if ((size_t)blockIdx.x * BM + r < n) {
-            xn_next = __ldg(xnorm + (size_t)blockIdx.x * BM + r);
-            if (slice == 0 && assign) old_next = assign[(size_t)blockIdx.x * BM + r];
+        // tiles of stopped textures are skipped (by all three roles alike)
+        auto next_live = [&](uint32_t tt) {
+            while (tt < num_tiles && !live(tt)) tt += gridDim.x;
+            return tt;
+        };
+        float cmax = BATCH ? 0.0f : __ldg(cmax_ptr);
+        uint32_t cmax_tex = BATCH ? 0xffffffffu : 0u;
+        const uint32_t t_first = next_live(blockIdx.x);
+        if (t_first < num_tiles && (size_t)t_first * BM + r < n) {
+            xn_next = __ldg(xnorm + (size_t)t_first * BM + r);
+            if (slice == 0 && assign) old_next = assign[(size_t)t_first * BM + r];
         }
         // threshold below which a score cannot belong to the reference argmin, given the best score m
         auto threshold = [&](float m, float xn, float e_dot, bool& bad) -> float {
@@ -324,13 +384,19 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
             if (thr == 0.0f) thr = -FLT_MIN;
             return thr;
         };
-        for (uint32_t t = blockIdx.x; t < num_tiles; t += gridDim.x, tpar ^= 1) {
+        for (uint32_t t = t_first, t_next; t < num_tiles; t = t_next, tpar ^= 1) {
+            t_next = next_live(t + gridDim.x);
+            const uint32_t tex = tex_of(t);
+            if (BATCH && tex != cmax_tex) {
+                cmax_tex = tex;
+                cmax = __ldg(cmax_ptr + (size_t)tex * bt.cmax_stride);
+            }
             const size_t row = (size_t)t * BM + r;
             const float xn = xn_next;
             const uint32_t old_c = old_next;
             {   // prefetch the next tile's |x'| (and previous assignment) so its DRAM latency hides behind this tile
-                const size_t nrow = row + (size_t)gridDim.x * BM;
-                const bool has = t + gridDim.x < num_tiles && nrow < n;
+                const size_t nrow = (size_t)t_next * BM + r;
+                const bool has = t_next < num_tiles && nrow < n;
                 xn_next = has ? __ldg(xnorm + nrow) : 0.0f;
                 if (slice == 0 && assign) old_next = has ? assign[nrow] : 0u;
             }
@@ -430,7 +496,7 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                 if (!ovf && total == 1 && assign) {
                     // a single candidate is the exact argmin: final
                     const uint32_t c = w[0] & 0xffffu;
-                    if (flags && old_c != c) flags[0] = 1u;
+                    if (flags && old_c != c) flags[(size_t)tex * bt.flags_stride] = 1u;
                     assign[row] = c;
                 } else {
                     if (!ovf && total >= 1 && total <= (uint32_t)kMaxCand) {
@@ -513,7 +579,13 @@ __global__ void __launch_bounds__(256) prep_blocks_kernel(const float* __restric
 // cmax = max_c |c'| (rounded up).
 __global__ void __launch_bounds__(64) prep_centroids_kernel(const float* __restrict__ cent, uint32_t K, const float* __restrict__ mu,
                                                             float* __restrict__ b_main, float* __restrict__ b_ext,
-                                                            unsigned int* __restrict__ cmax_bits) {
+                                                            unsigned int* __restrict__ cmax_bits, size_t small_stride) {
+    // texture blockIdx.y of a lock-step batch: operands stacked gridDim.x rows apart, mu / cmax small_stride bytes apart
+    cent += (size_t)blockIdx.y * K * 64;
+    b_main += (size_t)blockIdx.y * gridDim.x * 64;
+    b_ext += (size_t)blockIdx.y * gridDim.x * 8;
+    mu = reinterpret_cast<const float*>(reinterpret_cast<const uint8_t*>(mu) + (size_t)blockIdx.y * small_stride);
+    cmax_bits = reinterpret_cast<unsigned int*>(reinterpret_cast<uint8_t*>(cmax_bits) + (size_t)blockIdx.y * small_stride);
     const uint32_t c = blockIdx.x;
     const int i = threadIdx.x;
     float v = 0.0f;
@@ -709,7 +781,10 @@ __global__ void __launch_bounds__(kRrThreads, 2) rerank_sparse_kernel(const floa
                                                                       uint32_t K, const uint4* __restrict__ cand,
                                                                       const uint32_t* __restrict__ amb_list, unsigned int* amb_count,
                                                                       unsigned int* ticket, uint32_t* __restrict__ assign,
-                                                                      uint32_t* __restrict__ flags, unsigned int* __restrict__ stat) {
+                                                                      uint32_t* __restrict__ flags, unsigned int* __restrict__ stat,
+                                                                      TcBatch bt) {
+    const float* const cent_base = cent;
+    uint32_t* const flags_base = flags;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int g = lane >> 1, h = lane & 1;
     const uint32_t total = __ldcg(amb_count);
@@ -719,6 +794,11 @@ __global__ void __launch_bounds__(kRrThreads, 2) rerank_sparse_kernel(const floa
         const uint32_t idx = base + g;
         const bool act = idx < total;
         const size_t row = __ldcg(amb_list + (act ? idx : base));
+        {   // lock-step batch: the row's texture selects the centroid table and the changed flag
+            const uint32_t tex = (uint32_t)(row / bt.rows_per_tex);
+            cent = cent_base + (size_t)tex * K * 64;
+            flags = flags_base ? flags_base + (size_t)tex * bt.flags_stride : nullptr;
+        }
         const uint4 cw = ldg_nc_v4(cand + row);
         const uint32_t m_raw = cw.w >> 16;
         const bool overflow = act && m_raw == 0xffffu;
@@ -748,11 +828,12 @@ __global__ void __launch_bounds__(kRrThreads, 2) rerank_sparse_kernel(const floa
             const size_t orow = __shfl_sync(0xffffffffu, (unsigned long long)row, src);
             RowHalf ox;
             ox.load_stream(feat + orow * 64, h);
+            const float* ocent = cent_base + (size_t)(orow / bt.rows_per_tex) * K * 64;
             float od = FLT_MAX;
             uint32_t oc = 0;
             for (uint32_t c0 = 0; c0 < K; c0 += 16) {
                 const uint32_t c = c0 + g;
-                const float d = pair_distance(ox, cent + (size_t)(c < K ? c : 0) * 64, h);
+                const float d = pair_distance(ox, ocent + (size_t)(c < K ? c : 0) * 64, h);
                 if (c < K && d < od) {  // ascending c inside the group: strict '<' keeps the first minimum
                     od = d;
                     oc = c;
@@ -852,39 +933,59 @@ cudaError_t launch_tc_prep_centroids(const float* cent, uint32_t K, const float*
                                      float* cmax, cudaStream_t s) {
     cudaError_t e = cudaMemsetAsync(cmax, 0, 4, s);
     if (e != cudaSuccess) return e;
-    prep_centroids_kernel<<<tc_padded_k(K), 64, 0, s>>>(cent, K, mu, b_main, b_ext, reinterpret_cast<unsigned int*>(cmax));
+    prep_centroids_kernel<<<tc_padded_k(K), 64, 0, s>>>(cent, K, mu, b_main, b_ext, reinterpret_cast<unsigned int*>(cmax), 0);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_tc_prep_centroids_batch(const float* cent, uint32_t K, uint32_t n_textures, uint8_t* small, size_t small_stride,
+                                           size_t mu_off, size_t cmax_off, float* b_main, float* b_ext, cudaStream_t s) {
+    cudaError_t e = cudaMemset2DAsync(small + cmax_off, small_stride, 0, 4, n_textures, s);
+    if (e != cudaSuccess) return e;
+    prep_centroids_kernel<<<dim3(tc_padded_k(K), n_textures), 64, 0, s>>>(cent, K, reinterpret_cast<const float*>(small + mu_off), b_main,
+                                                                         b_ext, reinterpret_cast<unsigned int*>(small + cmax_off),
+                                                                         small_stride);
     return cudaGetLastError();
 }
 
 cudaError_t launch_assign_tc(const float* a_prime, const float* xnorm, size_t n, const float* b_main, const float* b_ext,
                              uint32_t K, const float* cmax, uint4* cand, uint32_t* assign, uint32_t* flags, uint32_t* amb_list,
-                             unsigned int* amb_count, const uint32_t* stop, cudaStream_t s) {
+                             unsigned int* amb_count, const uint32_t* stop, cudaStream_t s, const TcBatch* batch) {
     if (n == 0) return cudaSuccess;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(assign_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_TC);
+        cudaError_t e = cudaFuncSetAttribute(assign_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_TC);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(assign_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_TC);
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
     const uint32_t k_pad = tc_padded_k(K);
+    const uint32_t n_tex = batch ? batch->n_textures : 1u;
+    if (batch && (batch->rows_per_tex % BM != 0 || (size_t)batch->rows_per_tex * n_tex != n || batch->k_pad != k_pad))
+        return cudaErrorInvalidValue;  // tiles must not straddle textures
     CUtensorMap tm_a, tm_b, tm_bx;
     if (!make_map(&tm_a, a_prime, 128, n, 64, BM, CU_TENSOR_MAP_SWIZZLE_128B) ||
-        !make_map(&tm_b, b_main, 128, k_pad, 64, BN, CU_TENSOR_MAP_SWIZZLE_128B) ||
-        !make_map(&tm_bx, b_ext, 16, k_pad, 16, BN, CU_TENSOR_MAP_SWIZZLE_32B))
+        !make_map(&tm_b, b_main, 128, (uint64_t)k_pad * n_tex, 64, BN, CU_TENSOR_MAP_SWIZZLE_128B) ||
+        !make_map(&tm_bx, b_ext, 16, (uint64_t)k_pad * n_tex, 16, BN, CU_TENSOR_MAP_SWIZZLE_32B))
         return cudaErrorInvalidValue;
     const uint32_t num_tiles = (uint32_t)((n + BM - 1) / BM);
     const uint32_t num_chunks = k_pad / BN;
     const uint32_t grid = num_tiles < (uint32_t)YUPVQ_NUM_SMS ? num_tiles : (uint32_t)YUPVQ_NUM_SMS;
-    assign_tc_kernel<<<grid, kThreadsTc, SMEM_TC, s>>>(tm_a, tm_b, tm_bx, xnorm, cmax, (uint32_t)n, num_tiles, num_chunks,
-                                                      num_chunks <= 2 ? 1u : 0u, cand, assign, flags, amb_list, amb_count, stop);
+    TcBatch bt = batch ? *batch : tc_single();
+    if (!batch) bt.k_pad = k_pad;
+    if (batch && n_tex > 1)
+        assign_tc_kernel<true><<<grid, kThreadsTc, SMEM_TC, s>>>(tm_a, tm_b, tm_bx, xnorm, cmax, (uint32_t)n, num_tiles, num_chunks,
+                                                                num_chunks <= 2 ? 1u : 0u, cand, assign, flags, amb_list, amb_count, stop, bt);
+    else
+        assign_tc_kernel<false><<<grid, kThreadsTc, SMEM_TC, s>>>(tm_a, tm_b, tm_bx, xnorm, cmax, (uint32_t)n, num_tiles, num_chunks,
+                                                                 num_chunks <= 2 ? 1u : 0u, cand, assign, flags, amb_list, amb_count, stop, bt);
     return cudaGetLastError();
 }
 
 cudaError_t launch_rerank_sparse(const float* feat, const float* cent, uint32_t K, const uint4* cand, const uint32_t* amb_list,
                                  unsigned int* amb_count, unsigned int* ticket, uint32_t* assign, uint32_t* flags,
-                                 unsigned int* stat_pairs, cudaStream_t s) {
+                                 unsigned int* stat_pairs, cudaStream_t s, const TcBatch* batch) {
     rerank_sparse_kernel<<<YUPVQ_NUM_SMS * 2, kRrThreads, 0, s>>>(feat, cent, K, cand, amb_list, amb_count, ticket, assign, flags,
-                                                                 stat_pairs);
+                                                                 stat_pairs, batch ? *batch : tc_single());
     return cudaGetLastError();
 }
 

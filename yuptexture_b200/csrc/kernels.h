@@ -65,6 +65,19 @@ cudaError_t launch_exact_errors(const float* feat, size_t n, const float* cent, 
 // Per pass: B' / folded norms / cmax from the current centroids, the MMA front-end writes one uint4
 // candidate list per block (7 x uint16 + count; count 0xffff = full exact scan), the re-rank turns
 // the lists into assignments with the reference's exact arithmetic.
+// Lock-step batch descriptor: the rows of all textures form one matrix (texture t = rows [t * rows_per_tex, ...),
+// rows_per_tex a multiple of 128), the per-texture centroid operands are stacked in the B buffers (k_pad rows
+// each) and the per-texture scalar words sit at fixed strides.  Single texture: tc_single().
+struct TcBatch {
+    uint32_t tiles_per_tex;   // 128-row tiles per texture
+    uint32_t k_pad;           // rows of b_main / b_ext per texture
+    uint32_t cmax_stride;     // floats between the textures' cmax words
+    uint32_t flags_stride;    // uint32 words between the textures' changed flags
+    uint32_t stop_stride;     // uint32 words between the textures' stop words
+    uint32_t rows_per_tex;    // rows per texture (the re-rank maps a row to its texture's centroids)
+    uint32_t n_textures;
+};
+inline TcBatch tc_single() { return TcBatch{0xffffffffu, 0u, 0u, 0u, 0u, 0xffffffffu, 1u}; }
 bool tc_supported(uint32_t K);
 uint32_t tc_padded_k(uint32_t K);  // rows of b_main / b_ext
 cudaError_t launch_tc_mean(const float* feat, size_t n, double* sums64, float* mu, cudaStream_t s);
@@ -72,6 +85,10 @@ cudaError_t launch_tc_prep_blocks(const float* feat, size_t n, const float* mu, 
                                   cudaStream_t s);
 cudaError_t launch_tc_prep_centroids(const float* cent, uint32_t K, const float* mu, float* b_main, float* b_ext,
                                      float* cmax, cudaStream_t s);
+// batch: texture t reads cent + t*K*64, mu at small + t*small_stride + mu_off, writes rows [t*k_pad, ..) of b_main /
+// b_ext and max-reduces cmax at small + t*small_stride + cmax_off (zeroed here)
+cudaError_t launch_tc_prep_centroids_batch(const float* cent, uint32_t K, uint32_t n_textures, uint8_t* small, size_t small_stride,
+                                           size_t mu_off, size_t cmax_off, float* b_main, float* b_ext, cudaStream_t s);
 // `stop` (may be null): device word; when non-zero the kernel returns at once (Lloyd passes are enqueued
 // ahead of the convergence test, see launch_lloyd_control).
 // assign != null: rows with exactly one candidate get their assignment (and the changed flag) written by the
@@ -80,10 +97,12 @@ cudaError_t launch_tc_prep_centroids(const float* cent, uint32_t K, const float*
 cudaError_t launch_assign_tc(const float* a_prime, const float* xnorm, size_t n, const float* b_main,
                              const float* b_ext, uint32_t K, const float* cmax, uint4* cand, uint32_t* assign,
                              uint32_t* flags, uint32_t* amb_list, unsigned int* amb_count, const uint32_t* stop,
-                             cudaStream_t s);
+                             cudaStream_t s, const TcBatch* batch = nullptr);
+// batch != null: n is the row count of ALL textures, K the per-texture codebook size
 cudaError_t launch_rerank_sparse(const float* feat, const float* cent, uint32_t K, const uint4* cand,
                                  const uint32_t* amb_list, unsigned int* amb_count, unsigned int* ticket,
-                                 uint32_t* assign, uint32_t* flags, unsigned int* stat_pairs, cudaStream_t s);
+                                 uint32_t* assign, uint32_t* flags, unsigned int* stat_pairs, cudaStream_t s,
+                                 const TcBatch* batch = nullptr);
 cudaError_t launch_rerank(const float* feat, size_t n, const float* cent, uint32_t K, const uint4* cand,
                           uint32_t* assign, float* errors, uint32_t* flags, unsigned int* stat_pairs,
                           const uint32_t* stop, cudaStream_t s);
@@ -95,6 +114,21 @@ cudaError_t launch_rerank(const float* feat, size_t n, const float* cent, uint32
 // flags: [0] changed (written by assign), [1] #empty clusters, [2] reseeds (running total).
 cudaError_t launch_accumulate(const float* feat, size_t n, const uint32_t* assign, uint32_t K, int shift,
                               long long* acc, const uint32_t* flags, const uint32_t* stop, cudaStream_t s);
+// lock-step batch: texture t = rows [t * rows_per_tex, ..) of feat / assign, accumulator acc + t * acc_stride (int64 words),
+// fixed-point scale scales[t] (device), changed flag flags[t * flags_stride], stop word stop[t * stop_stride]
+struct AccBatch {
+    uint32_t n_textures;
+    size_t acc_stride;
+    const float* scales;
+    uint32_t flags_stride;
+    uint32_t stop_stride;
+};
+bool accumulate_batch_supported(size_t rows_per_tex, uint32_t K);
+cudaError_t launch_accumulate_batch(const float* feat, size_t rows_per_tex, const uint32_t* assign, uint32_t K, long long* acc,
+                                    const uint32_t* flags, const uint32_t* stop, const AccBatch& bt, cudaStream_t s);
+cudaError_t launch_finalize_centroids_batch(const long long* acc, size_t acc_stride, uint32_t n_textures, uint32_t K,
+                                            const double* inv_scales, float* cent, uint32_t* flags, uint32_t flags_stride,
+                                            const uint32_t* stop, uint32_t stop_stride, cudaStream_t s);
 // centroid = float(sum) * (1.0f / count) (reference src/vq_encoder.cpp:366-368); flags[1] = #empty clusters
 cudaError_t launch_finalize_centroids(const long long* acc, uint32_t K, int shift, float* cent, uint32_t* flags,
                                       const uint32_t* stop, cudaStream_t s);
@@ -105,6 +139,11 @@ cudaError_t launch_count_empty(const long long* acc, uint32_t K, uint32_t* out, 
 // writes the number of empty clusters to ctl[2] and clears flags[0] (changed) and flags[1] (#empty).
 cudaError_t launch_lloyd_control(const long long* acc, uint32_t K, uint32_t iter, uint32_t break_after, uint32_t* flags,
                                  uint32_t* ctl, cudaStream_t s);
+// the same for texture blockIdx.x of a lock-step batch: acc + t * acc_stride, flags + t * flags_stride, ctl + 3 t;
+// *sticky = 1 (if non-null) when a running texture has an empty cluster
+cudaError_t launch_lloyd_control_batch(const long long* acc, size_t acc_stride, uint32_t n_textures, uint32_t K, uint32_t iter,
+                                       uint32_t break_after, uint32_t* flags, uint32_t flags_stride, uint32_t* ctl,
+                                       uint32_t* sticky, cudaStream_t s);
 // serial-semantics reseed of empty clusters (ascending c, first maximum of errors, then zero it)
 cudaError_t launch_reseed_empty(const float* feat, size_t n, float* errors, const long long* acc, uint32_t K,
                                 float* cent, uint32_t* flags, const uint32_t* stop, cudaStream_t s);

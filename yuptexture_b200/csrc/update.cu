@@ -50,21 +50,31 @@ constexpr int kAccChunk = 4096;
 constexpr int kAccMaxK = 4096;
 
 __global__ void __launch_bounds__(kAccThreads, 2)
-accumulate_sorted_kernel(const float* __restrict__ feat, size_t n, const uint32_t* __restrict__ assign, uint32_t K, float scale,
-                         long long* __restrict__ acc, const uint32_t* __restrict__ flags, const uint32_t* __restrict__ stop) {
+accumulate_sorted_kernel(const float* __restrict__ feat_all, size_t n, const uint32_t* __restrict__ assign_all, uint32_t K, float scale1,
+                         long long* __restrict__ acc_all, const uint32_t* __restrict__ flags, const uint32_t* __restrict__ stop,
+                         AccBatch bt) {
+    // Lock-step batch (bt.n_textures > 1): texture t owns rows [t * n, (t + 1) * n) of feat / assign, the accumulator
+    // at acc + t * acc_stride, the scale bt.scales[t] and the flag / stop words at the given strides; chunks are
+    // numbered texture-major, so one launch covers the whole batch.
     extern __shared__ uint32_t sm_acc[];
-    if (stop && __ldg(stop)) return;
+    if (bt.n_textures <= 1 && stop && __ldg(stop)) return;
     uint32_t* hist = sm_acc;                                      // K
     uint32_t* offs = sm_acc + K;                                  // K
     uint16_t* sorted = reinterpret_cast<uint16_t*>(sm_acc + 2 * K);  // kAccChunk
     __shared__ uint32_t warp_tot[kAccThreads / 32 + 1];
     __shared__ uint32_t next_c;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    unsigned long long* sums = reinterpret_cast<unsigned long long*>(acc);
-    unsigned long long* counts = sums + (size_t)K * 64;
-    const size_t n_chunks = (n + kAccChunk - 1) / kAccChunk;
+    const size_t n_chunks = (n + kAccChunk - 1) / kAccChunk;     // per texture
     constexpr int kPer = kAccChunk / kAccThreads;                 // blocks per thread per chunk
-    for (size_t chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x) {
+    for (size_t gchunk = blockIdx.x; gchunk < n_chunks * bt.n_textures; gchunk += gridDim.x) {
+        const uint32_t tex = (uint32_t)(gchunk / n_chunks);
+        if (bt.n_textures > 1 && stop && __ldg(stop + (size_t)tex * bt.stop_stride)) continue;  // uniform across the CTA
+        const size_t chunk = gchunk - (size_t)tex * n_chunks;
+        const float* feat = feat_all + (size_t)tex * n * 64;
+        const uint32_t* assign = assign_all + (size_t)tex * n;
+        const float scale = bt.scales ? __ldg(bt.scales + tex) : scale1;
+        unsigned long long* sums = reinterpret_cast<unsigned long long*>(acc_all) + (size_t)tex * bt.acc_stride;
+        unsigned long long* counts = sums + (size_t)K * 64;
         const size_t first = chunk * kAccChunk;
         const uint32_t len = (uint32_t)((n - first) < (size_t)kAccChunk ? (n - first) : (size_t)kAccChunk);
         for (uint32_t c = tid; c < K; c += kAccThreads) hist[c] = 0;
@@ -158,12 +168,25 @@ accumulate_sorted_kernel(const float* __restrict__ feat, size_t n, const uint32_
         }
         __syncthreads();
     }
-    if (blockIdx.x == 0 && tid == 0 && flags) atomicAdd(sums + (size_t)K * 65, (unsigned long long)flags[0]);
+    if (blockIdx.x == 0 && flags) {
+        for (uint32_t tex = tid; tex < bt.n_textures; tex += kAccThreads) {
+            if (bt.n_textures > 1 && stop && __ldg(stop + (size_t)tex * bt.stop_stride)) continue;
+            unsigned long long* sums = reinterpret_cast<unsigned long long*>(acc_all) + (size_t)tex * bt.acc_stride;
+            atomicAdd(sums + (size_t)K * 65, (unsigned long long)flags[(size_t)tex * bt.flags_stride]);
+        }
+    }
 }
 
+// blockIdx.y = texture of a lock-step batch (strides 0 and inv_scales null for a single texture)
 __global__ void finalize_kernel(const long long* __restrict__ acc, uint32_t K, double inv_scale,
-                                float* __restrict__ cent, uint32_t* __restrict__ flags, const uint32_t* __restrict__ stop) {
-    if (stop && __ldg(stop)) return;
+                                float* __restrict__ cent, uint32_t* __restrict__ flags, const uint32_t* __restrict__ stop,
+                                size_t acc_stride, const double* __restrict__ inv_scales, uint32_t flags_stride,
+                                uint32_t stop_stride) {
+    if (stop && __ldg(stop + (size_t)blockIdx.y * stop_stride)) return;
+    acc += (size_t)blockIdx.y * acc_stride;
+    cent += (size_t)blockIdx.y * K * 64;
+    flags += (size_t)blockIdx.y * flags_stride;
+    if (inv_scales) inv_scale = inv_scales[blockIdx.y];
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= (size_t)K * 64) return;
     const uint32_t c = (uint32_t)(i >> 6);
@@ -196,6 +219,36 @@ __global__ void lloyd_control_kernel(const long long* __restrict__ acc, uint32_t
         ctl[1] += 1u;     // assignment passes run
         ctl[2] = total;   // empty clusters of this pass
         if (!changed && iter > break_after) ctl[0] = 1u;  // stop: this pass' update and every later pass are skipped
+        flags[0] = 0u;
+        flags[1] = 0u;
+    }
+}
+
+// Lock-step batch: one CTA per texture does what lloyd_control_kernel does for texture blockIdx.x (accumulators,
+// flag words and control words are strided per texture).  `sticky` (may be null) is set when a texture that is
+// still running has an empty cluster: block-sharded runs cannot reseed on the device (the winner lives on
+// another GPU), the host then redoes the batch with the synchronous loop.
+__global__ void lloyd_control_batch_kernel(const long long* __restrict__ acc, size_t acc_stride, uint32_t K, uint32_t iter,
+                                           uint32_t break_after, uint32_t* __restrict__ flags, uint32_t flags_stride,
+                                           uint32_t* __restrict__ ctl_all, uint32_t* __restrict__ sticky) {
+    __shared__ unsigned int total;
+    acc += (size_t)blockIdx.x * acc_stride;
+    flags += (size_t)blockIdx.x * flags_stride;
+    uint32_t* ctl = ctl_all + (size_t)blockIdx.x * 3;
+    if (ctl[0]) return;
+    if (threadIdx.x == 0) total = 0;
+    __syncthreads();
+    unsigned int local = 0;
+    for (uint32_t c = threadIdx.x; c < K; c += blockDim.x) local += acc[(size_t)K * 64 + c] == 0 ? 1u : 0u;
+    local = warp_sum(local);
+    if ((threadIdx.x & 31) == 0 && local) atomicAdd(&total, local);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const bool changed = acc[(size_t)K * 65] != 0;
+        ctl[1] += 1u;
+        ctl[2] = total;
+        if (!changed && iter > break_after) ctl[0] = 1u;
+        else if (total && sticky) *sticky = 1u;
         flags[0] = 0u;
         flags[1] = 0u;
     }
@@ -323,7 +376,8 @@ cudaError_t launch_accumulate(const float* feat, size_t n, const uint32_t* assig
         }
         size_t chunks = (n + kAccChunk - 1) / kAccChunk;
         size_t grid = chunks < (size_t)YUPVQ_NUM_SMS * 2 ? chunks : (size_t)YUPVQ_NUM_SMS * 2;
-        accumulate_sorted_kernel<<<(unsigned)grid, kAccThreads, smem, s>>>(feat, n, assign, K, ldexpf(1.0f, shift), acc, flags, stop);
+        accumulate_sorted_kernel<<<(unsigned)grid, kAccThreads, smem, s>>>(feat, n, assign, K, ldexpf(1.0f, shift), acc, flags, stop,
+                                                                          AccBatch{1u, 0, nullptr, 0u, 0u});
         return cudaGetLastError();
     }
     size_t blocks = (n * 32 + 255) / 256;
@@ -335,7 +389,31 @@ cudaError_t launch_accumulate(const float* feat, size_t n, const uint32_t* assig
 
 cudaError_t launch_finalize_centroids(const long long* acc, uint32_t K, int shift, float* cent, uint32_t* flags,
                                       const uint32_t* stop, cudaStream_t s) {
-    finalize_kernel<<<(K * 64 + 255) / 256, 256, 0, s>>>(acc, K, ldexp(1.0, -shift), cent, flags, stop);
+    finalize_kernel<<<(K * 64 + 255) / 256, 256, 0, s>>>(acc, K, ldexp(1.0, -shift), cent, flags, stop, 0, nullptr, 0u, 0u);
+    return cudaGetLastError();
+}
+
+bool accumulate_batch_supported(size_t rows_per_tex, uint32_t K) { return K <= (uint32_t)kAccMaxK && rows_per_tex >= (size_t)kAccChunk; }
+
+cudaError_t launch_accumulate_batch(const float* feat, size_t rows_per_tex, const uint32_t* assign, uint32_t K, long long* acc,
+                                    const uint32_t* flags, const uint32_t* stop, const AccBatch& bt, cudaStream_t s) {
+    if (!accumulate_batch_supported(rows_per_tex, K)) return cudaErrorInvalidValue;
+    const size_t smem = (size_t)K * 8 + (size_t)kAccChunk * 2;
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(accumulate_sorted_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+    }
+    size_t chunks = (rows_per_tex + kAccChunk - 1) / kAccChunk * bt.n_textures;
+    size_t grid = chunks < (size_t)YUPVQ_NUM_SMS * 2 ? chunks : (size_t)YUPVQ_NUM_SMS * 2;
+    accumulate_sorted_kernel<<<(unsigned)grid, kAccThreads, smem, s>>>(feat, rows_per_tex, assign, K, 1.0f, acc, flags, stop, bt);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_finalize_centroids_batch(const long long* acc, size_t acc_stride, uint32_t n_textures, uint32_t K,
+                                            const double* inv_scales, float* cent, uint32_t* flags, uint32_t flags_stride,
+                                            const uint32_t* stop, uint32_t stop_stride, cudaStream_t s) {
+    finalize_kernel<<<dim3((K * 64 + 255) / 256, n_textures), 256, 0, s>>>(acc, K, 1.0, cent, flags, stop, acc_stride, inv_scales,
+                                                                           flags_stride, stop_stride);
     return cudaGetLastError();
 }
 
@@ -347,6 +425,13 @@ cudaError_t launch_count_empty(const long long* acc, uint32_t K, uint32_t* out, 
 cudaError_t launch_lloyd_control(const long long* acc, uint32_t K, uint32_t iter, uint32_t break_after, uint32_t* flags,
                                  uint32_t* ctl, cudaStream_t s) {
     lloyd_control_kernel<<<1, 256, 0, s>>>(acc, K, iter, break_after, flags, ctl);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_lloyd_control_batch(const long long* acc, size_t acc_stride, uint32_t n_textures, uint32_t K, uint32_t iter,
+                                       uint32_t break_after, uint32_t* flags, uint32_t flags_stride, uint32_t* ctl,
+                                       uint32_t* sticky, cudaStream_t s) {
+    lloyd_control_batch_kernel<<<n_textures, 256, 0, s>>>(acc, acc_stride, K, iter, break_after, flags, flags_stride, ctl, sticky);
     return cudaGetLastError();
 }
 
