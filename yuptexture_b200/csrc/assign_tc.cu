@@ -168,6 +168,23 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t sbo_bytes
 // kind::f16, D = f32, A/B = bf16, both K-major, M = 128, N = 256 (cute::UMMA::InstrDescriptor)
 constexpr uint32_t kIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
 
+// (tile, texture) walk of one CTA through the batch without a division per tile
+struct TileWalk {
+    uint32_t t, tex, off, step, tpt;
+    __device__ __forceinline__ TileWalk(uint32_t t0, uint32_t step_, uint32_t tpt_, bool batch)
+        : t(t0), tex(batch ? t0 / tpt_ : 0u), off(0u), step(step_), tpt(batch ? tpt_ : 0xffffffffu) {
+        off = batch ? t0 - tex * tpt_ : 0u;
+    }
+    __device__ __forceinline__ void advance() {
+        t += step;
+        off += step;
+        while (off >= tpt) {
+            off -= tpt;
+            ++tex;
+        }
+    }
+};
+
 // ---- the front-end kernel -----------------------------------------------------------------------------
 template <bool BATCH>
 __global__ void __launch_bounds__(kThreadsTc, 1)
@@ -187,10 +204,8 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
     // with flags the epilogue writes)
     uint32_t chk_tex = 0xffffffffu;
     bool chk_live = true;
-    auto tex_of = [&](uint32_t tt) -> uint32_t { return BATCH ? tt / bt.tiles_per_tex : 0u; };
-    auto live = [&](uint32_t tt) {
+    auto live = [&](uint32_t x) {   // x = texture index
         if (!BATCH || !stop) return true;
-        const uint32_t x = tt / bt.tiles_per_tex;
         if (x != chk_tex) {
             chk_tex = x;
             chk_live = __ldg(stop + (size_t)x * bt.stop_stride) == 0u;
@@ -246,9 +261,9 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                 cur_tex = 0;
                 bgen = 1;
             }
-            for (uint32_t t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-                const uint32_t tex = tex_of(t);
-                if (!live(t)) continue;
+            for (TileWalk w(blockIdx.x, gridDim.x, bt.tiles_per_tex, BATCH); w.t < num_tiles; w.advance()) {
+                const uint32_t t = w.t, tex = w.tex;
+                if (!live(tex)) continue;
                 const uint32_t sa = it & 1, pa = (it >> 1) & 1;
                 ++it;
                 mbar_wait(bar(BAR_EMPTY_A + sa), pa ^ 1);
@@ -290,9 +305,9 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
         if (lane == 0) {
             uint32_t it = 0, u = 0, cur_tex = 0xffffffffu, bgen = 0;
             const uint64_t ones_desc = make_desc(base + OFF_ONES, 256, 6);
-            for (uint32_t t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-                const uint32_t tex = tex_of(t);
-                if (!live(t)) continue;
+            for (TileWalk w(blockIdx.x, gridDim.x, bt.tiles_per_tex, BATCH); w.t < num_tiles; w.advance()) {
+                const uint32_t tex = w.tex;
+                if (!live(tex)) continue;
                 const bool first_of_tex = tex != cur_tex;   // wait for this texture's resident B
                 if (first_of_tex) {
                     cur_tex = tex;
@@ -300,7 +315,12 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                 }
                 // last tile this CTA runs on this texture: hand the resident B back to the producer afterwards
                 // (a texture is live or stopped as a whole, so the next tile of the same texture is live too)
-                const bool last_of_tex = BATCH && !(t + gridDim.x < num_tiles && (t + gridDim.x) / bt.tiles_per_tex == tex);
+                bool last_of_tex = false;
+                if (BATCH) {
+                    TileWalk nx = w;
+                    nx.advance();
+                    last_of_tex = !(nx.t < num_tiles && nx.tex == tex);
+                }
                 const uint32_t sa = it & 1, pa = (it >> 1) & 1;
                 ++it;
                 mbar_wait(bar(BAR_FULL_A + sa), pa);
@@ -362,13 +382,17 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
         float xn_next = 0.0f;
         uint32_t old_next = 0;
         // tiles of stopped textures are skipped (by all three roles alike)
-        auto next_live = [&](uint32_t tt) {
-            while (tt < num_tiles && !live(tt)) tt += gridDim.x;
-            return tt;
+        // (tile, texture) walk without a division per tile: the epilogue is ALU-issue bound
+        TileWalk w(blockIdx.x, gridDim.x, bt.tiles_per_tex, BATCH);
+        auto next_live = [&](bool step) {
+            if (step) w.advance();
+            while (w.t < num_tiles && !live(w.tex)) w.advance();
+            return w.t;
         };
         float cmax = BATCH ? 0.0f : __ldg(cmax_ptr);
         uint32_t cmax_tex = BATCH ? 0xffffffffu : 0u;
-        const uint32_t t_first = next_live(blockIdx.x);
+        const uint32_t t_first = next_live(false);
+        uint32_t tex = w.tex;
         if (t_first < num_tiles && (size_t)t_first * BM + r < n) {
             xn_next = __ldg(xnorm + (size_t)t_first * BM + r);
             if (slice == 0 && assign) old_next = assign[(size_t)t_first * BM + r];
@@ -384,9 +408,9 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
             if (thr == 0.0f) thr = -FLT_MIN;
             return thr;
         };
-        for (uint32_t t = t_first, t_next; t < num_tiles; t = t_next, tpar ^= 1) {
-            t_next = next_live(t + gridDim.x);
-            const uint32_t tex = tex_of(t);
+        for (uint32_t t = t_first, t_next, tex_next; t < num_tiles; t = t_next, tex = tex_next, tpar ^= 1) {
+            t_next = next_live(true);
+            tex_next = w.tex;
             if (BATCH && tex != cmax_tex) {
                 cmax_tex = tex;
                 cmax = __ldg(cmax_ptr + (size_t)tex * bt.cmax_stride);
