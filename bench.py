@@ -163,8 +163,17 @@ def run_ours(args, rank, world, local_rank):
         dist.broadcast(uid, 0)
         enc.comm_init(uid.cpu().numpy(), world, rank)
 
-    # synthetic inputs (every rank generates the same textures: seeds are fixed)
-    textures = [make_texture(1000 + t) for t in range(n_tex)]
+    # synthetic inputs (fixed seeds): texture t is generated on rank t % world and broadcast, every rank holds all of them
+    textures = []
+    for t in range(n_tex):
+        if world == 1:
+            textures.append(make_texture(1000 + t))
+            continue
+        buf = torch.empty(n * 8, dtype=torch.uint8, device=dev)
+        if t % world == rank:
+            buf.copy_(torch.from_numpy(make_texture(1000 + t).reshape(-1).copy()))
+        dist.broadcast(buf, t % world)
+        textures.append(buf.cpu().numpy().reshape(n, 8))
     pinned_in = [torch.from_numpy(t.reshape(-1).copy()).pin_memory() for t in textures]
     dev_in = [p.to(dev) for p in pinned_in]
     from yuptexture_b200 import sharding
@@ -237,7 +246,7 @@ def run_ours(args, rank, world, local_rank):
         # dominant kernel: the tcgen05 assignment front-end (assign_tc_kernel), every launch of it inside one
         # more real step bracketed by CUDA events on the library's stream (yupvq_profile)
         ms_a = ms_fe / max(1, n_fe)
-        blocks_per_launch = n_local if world > 1 else n
+        blocks_per_launch = n_local * n_tex if world > 1 else n   # the lock-step batch launches the front-end once for all textures
         flop_alg = 2.0 * blocks_per_launch * k * 64          # 2 K D per block per pass
         split = 3                                            # xh.ch + xh.cl + xl.ch bf16 partial products
         achieved = split * flop_alg / (ms_a * 1e-3) / 1e12 if ms_a > 0 else 0.0
