@@ -170,3 +170,44 @@ def test_multi_gpu_sharded_matches_single_gpu():
                        capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert "multi_gpu_check ok" in r.stdout
+
+
+# ---- A21: the SAD metric (vq_Metric == SAD), all-integer: bit-exact end to end -------------------------------
+
+def test_sad_metric_golden(enc, golden_pipeline):
+    """The reference's own SAD-metric BuildCodebook / QuantizeBlocks output (tests/golden/make_golden.py)."""
+    from yuptexture_b200 import binding
+    g = golden_pipeline
+    px = g["sad_px"]
+    cfg = binding.make_config(codebook=32, max_iterations=32, seed=50, metric=binding.METRIC_SAD)
+    cent, st = enc.build_codebook(px, 3, cfg)
+    assert bits_equal(cent, g["sad_centroids"])
+    idx, _ = enc.quantize_blocks(px, 3, cent, metric=binding.METRIC_SAD)
+    assert bits_equal(idx, g["sad_indices"])
+    assert st.lloyd_passes >= 1
+
+
+@pytest.mark.parametrize("case", ["rgb_bc1", "rgba_bc3", "checker_bc1", "const_bc1", "grey_bc4"])
+def test_sad_metric_matches_oracle(enc, oracle, case):
+    """Whole SAD path through the C ABI vs the CPU restatement: centroids, pass count and indices identical
+    (integer arithmetic: no tolerance), incl. duplicate-heavy textures (empty clusters -> reseed) and K > 512."""
+    from yuptexture_b200 import binding
+    if case == "rgb_bc1":
+        bc, fmt, ch, k = synth.bc1_encode(synth.ldr_rgb(512, 512, seed=3)), 1, 3, 600
+    elif case == "rgba_bc3":
+        bc, fmt, ch, k = synth.bc3_encode(synth.ldr_rgba(384, 256, seed=4)), 3, 4, 128
+    elif case == "checker_bc1":
+        bc, fmt, ch, k = synth.bc1_encode(synth.checker_rgb(256, 256)), 1, 3, 64
+    elif case == "const_bc1":
+        bc, fmt, ch, k = synth.bc1_encode(synth.constant_rgb(128, 128)), 1, 3, 16
+    else:
+        img = synth.ldr_rgb(256, 256, seed=8)[..., :1]
+        bc, fmt, ch, k = synth._chunked(synth._bc4_block, synth.image_to_blocks(img).reshape(-1, 16)), 4, 1, 32
+    n = len(bc)
+    px = oracle.decode_bcn(bc, fmt, ch)
+    cfg = binding.make_config(codebook=k, max_iterations=12, seed=77, metric=binding.METRIC_SAD)
+    cent, idx, st = enc.encode_bcn(bc, n, fmt, ch, cfg)
+    c_ref, passes = oracle.build_codebook(px, ch, k, 12, 77, metric=oracle.METRIC_SAD)
+    assert bits_equal(cent, c_ref)
+    assert st.lloyd_passes == passes
+    assert bits_equal(idx, oracle.quantize_blocks(px, ch, c_ref, metric=oracle.METRIC_SAD))

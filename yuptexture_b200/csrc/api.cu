@@ -515,6 +515,50 @@ int run_lloyd(yupvq_ctx* ctx, const Blocks& b, size_t n_total, size_t first_bloc
     return 0;
 }
 
+// ---- A21: SAD-metric Lloyd (src/vq_encoder.cpp:380-430) ---------------------------------------------------------
+// b.planes = the pixel planes, b.feat = the same bytes as integer-valued fp32 rows (launch_sad_expand); cent (K x 64
+// fp32, integer-valued) holds the seed blocks on entry and the final pixel centroids on exit.  Every pass is
+// enqueued without a host round trip, exactly like the Oklab loop; all arithmetic is integer, so the result is
+// bit-identical to the reference.
+int run_lloyd_sad(yupvq_ctx* ctx, const Blocks& b, uint32_t K, uint32_t max_iter, float* cent, yupvq_stats* stats) {
+    const size_t n = b.n;
+    CK(ctx->assign.ensure(std::max<size_t>(1, n) * 4));
+    CK(ctx->errors.ensure(std::max<size_t>(1, n) * 4));
+    const size_t acc_words = (size_t)K * 65 + 1;
+    CK(ctx->acc.ensure(acc_words * 8));
+    CK(ctx->cent_px.ensure((size_t)K * 16 * b.ch));
+    uint32_t* flags = ctx->small.as<uint32_t>();
+    uint32_t* ctl = flags + F_CTL;
+    uint32_t* assign = ctx->assign.as<uint32_t>();
+    float* errors = ctx->errors.as<float>();
+    long long* acc = ctx->acc.as<long long>();
+    CK(cudaMemsetAsync(assign, 0, n * 4, ctx->stream));  // assignments(numBlocks, 0), :316
+    CK(cudaMemsetAsync(flags, 0, F_WORDS * 4, ctx->stream));
+    for (uint32_t iter = 0; iter < max_iter; ++iter) {
+        LAUNCH(launch_sad_pack(cent, K, b.ch, ctx->cent_px.as<uint8_t>(), ctx->stream));
+        LAUNCH(launch_sad_assign(b.planes, b.stride, n, b.ch, ctx->cent_px.as<uint8_t>(), K, assign, errors, flags, ctl, ctx->stream));
+        CK(cudaMemsetAsync(acc, 0, acc_words * 8, ctx->stream));
+        LAUNCH(launch_accumulate(b.feat, n, assign, K, 0, acc, flags, ctl, ctx->stream));   // shift 0: exact integer sums
+        LAUNCH(launch_lloyd_control(acc, K, iter, 0u, flags, ctl, ctx->stream));            // !hasChanged && iter > 0 (:395)
+        LAUNCH(launch_sad_finalize(acc, K, cent, flags, ctl, ctx->stream));
+        LAUNCH(launch_reseed_empty(b.feat, n, errors, acc, K, cent, flags, ctl, ctx->stream));  // :423-427, ascending c
+        if ((iter == 3 || iter == 7 || iter == 15) && iter + 1 < max_iter) {
+            CK(cudaMemcpyAsync(ctx->h_small, ctl, 4, cudaMemcpyDeviceToHost, ctx->stream));
+            CK(cudaStreamSynchronize(ctx->stream));
+            if (ctx->h_small[0]) break;
+        }
+    }
+    LAUNCH(launch_sad_pack(cent, K, b.ch, ctx->cent_px.as<uint8_t>(), ctx->stream));
+    CK(cudaMemcpyAsync(ctx->h_small, ctl + 1, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(ctx->h_small + 1, flags + F_RESEEDS, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (stats) {
+        stats->lloyd_passes = ctx->h_small[0];
+        stats->reseeds = ctx->h_small[1];
+    }
+    return 0;
+}
+
 void init_stats(yupvq_stats* s) {
     if (s) std::memset(s, 0, sizeof(*s));
 }
@@ -556,7 +600,13 @@ int build_codebook_device(yupvq_ctx* ctx, const Blocks& all, size_t n_total, con
     LAUNCH(launch_gather_rows_f32(b.feat, ctx->seed_idx.as<uint32_t>(), K, 64, ctx->cent.as<float>(), ctx->stream));
     *t_seed1 = tm.mark();
     const int metric = hdr ? YUPVQ_METRIC_OKLAB : cfg->metric;
-    if (metric != YUPVQ_METRIC_OKLAB) return ctx->fail("SAD metric Lloyd is not built yet");
+    if (metric == YUPVQ_METRIC_SAD) {
+        // the caller built b.feat with launch_sad_expand: the gathered seed rows are the seed pixel blocks
+        if (run_lloyd_sad(ctx, b, K, cfg->max_iterations, ctx->cent.as<float>(), stats)) return 1;
+        *t_lloyd1 = tm.mark();
+        *t_fin1 = tm.mark();   // the centroids already are pixel blocks (no colour conversion on this path)
+        return 0;
+    }
     if (run_lloyd(ctx, b, n_total, 0, K, cfg->max_iterations, hdr ? 1u : 0u, cfg->assign_mode, ctx->cent.as<float>(), stats))
         return 1;
     *t_lloyd1 = tm.mark();
@@ -572,7 +622,14 @@ int build_codebook_device(yupvq_ctx* ctx, const Blocks& all, size_t n_total, con
 }
 
 // QuantizeBlocks on device data: centroids (pixel/float, device) -> Oklab -> one assignment pass.
-int quantize_device(yupvq_ctx* ctx, const Blocks& all, const void* cent_px_dev, uint32_t K, bool hdr, int assign_mode) {
+int quantize_device(yupvq_ctx* ctx, const Blocks& all, const void* cent_px_dev, uint32_t K, bool hdr, int assign_mode,
+                    int metric = YUPVQ_METRIC_OKLAB) {
+    if (!hdr && metric == YUPVQ_METRIC_SAD) {  // src/vq_encoder.cpp:473-484
+        CK(ctx->out_idx.ensure(std::max<size_t>(1, all.n) * 4));
+        LAUNCH(launch_sad_assign(all.planes, all.stride, all.n, all.ch, reinterpret_cast<const uint8_t*>(cent_px_dev), K,
+                                 ctx->out_idx.as<uint32_t>(), nullptr, nullptr, nullptr, ctx->stream));
+        return 0;
+    }
     CK(ctx->cent_feat.ensure((size_t)K * 256));
     if (hdr) LAUNCH(launch_floats_to_features(reinterpret_cast<const float*>(cent_px_dev), K, all.ch, ctx->cent_feat.as<float>(), ctx->stream));
     else LAUNCH(launch_pixels_to_features(reinterpret_cast<const uint8_t*>(cent_px_dev), K, all.ch, nullptr, 0, ctx->cent_feat.as<float>(), ctx->stream));
@@ -758,6 +815,8 @@ int yupvq_encode_bcn(yupvq_ctx* ctx, const uint8_t* bc_blocks, size_t n_blocks, 
     CK(ctx->feat.ensure(n_blocks * 256));
     LAUNCH(launch_decode_bcn(reinterpret_cast<const uint8_t*>(bc_dev), n_blocks, bc_format, channels,
                              ctx->planes.as<uint4>(), n_blocks, ctx->feat.as<float>(), nullptr, ctx->stream));
+    if (cfg->metric == YUPVQ_METRIC_SAD)  // SAD path: the "features" are the pixel bytes themselves (sad.cu)
+        LAUNCH(launch_sad_expand(ctx->planes.as<uint4>(), n_blocks, n_blocks, channels, ctx->feat.as<float>(), ctx->stream));
     const int t2 = tm.mark();
     Blocks all;
     all.n = n_blocks;
@@ -767,7 +826,7 @@ int yupvq_encode_bcn(yupvq_ctx* ctx, const uint8_t* bc_blocks, size_t n_blocks, 
     all.feat = ctx->feat.as<float>();
     int ts0, ts1, tl1, tf1;
     if (build_codebook_device(ctx, all, n_blocks, cfg, false, stats, tm, &ts0, &ts1, &tl1, &tf1)) return 1;
-    if (quantize_device(ctx, all, ctx->cent_px.p, cfg->codebook_size, false, cfg->assign_mode)) return 1;
+    if (quantize_device(ctx, all, ctx->cent_px.p, cfg->codebook_size, false, cfg->assign_mode, cfg->metric)) return 1;
     const int t3 = tm.mark();
     if (from_device(ctx, out_pixel_centroids, ctx->cent_px.p, (size_t)cfg->codebook_size * 16 * channels)) return 1;
     if (from_device(ctx, out_indices, ctx->out_idx.p, n_blocks * 4)) return 1;
@@ -879,6 +938,8 @@ int yupvq_build_codebook(yupvq_ctx* ctx, const uint8_t* pixel_blocks, size_t n_b
     CK(ctx->feat.ensure(n_blocks * 256));
     LAUNCH(launch_pixels_to_features(reinterpret_cast<const uint8_t*>(px_dev), n_blocks, channels,
                                      ctx->planes.as<uint4>(), n_blocks, ctx->feat.as<float>(), ctx->stream));
+    if (cfg->metric == YUPVQ_METRIC_SAD)
+        LAUNCH(launch_sad_expand(ctx->planes.as<uint4>(), n_blocks, n_blocks, channels, ctx->feat.as<float>(), ctx->stream));
     Blocks all;
     all.n = n_blocks;
     all.ch = channels;
@@ -911,21 +972,30 @@ int yupvq_quantize_blocks(yupvq_ctx* ctx, const uint8_t* pixel_blocks, size_t n_
     ctx->tc_feat = nullptr;
     if (n_blocks == 0) return 0;  // reference returns {} (:449)
     if (channels < 1 || channels > 4) return ctx->fail("channels must be 1..4");
-    if (metric != YUPVQ_METRIC_OKLAB) return ctx->fail("SAD metric quantise is not built yet");
+    if (metric != YUPVQ_METRIC_OKLAB && metric != YUPVQ_METRIC_SAD) return ctx->fail("unknown metric %d", metric);
     Timer tm(ctx);
     const int t0 = tm.mark();
     const void* px_dev = nullptr;
     if (to_device(ctx, pixel_blocks, n_blocks * 16 * channels, ctx->in_bytes, &px_dev)) return 1;
     CK(ctx->feat.ensure(n_blocks * 256));
-    LAUNCH(launch_pixels_to_features(reinterpret_cast<const uint8_t*>(px_dev), n_blocks, channels, nullptr, 0,
-                                     ctx->feat.as<float>(), ctx->stream));
+    const bool sad = metric == YUPVQ_METRIC_SAD;
+    if (sad) CK(ctx->planes.ensure(n_blocks * 16 * channels));
+    LAUNCH(launch_pixels_to_features(reinterpret_cast<const uint8_t*>(px_dev), n_blocks, channels,
+                                     sad ? ctx->planes.as<uint4>() : nullptr, sad ? n_blocks : 0, ctx->feat.as<float>(), ctx->stream));
     const void* c_dev = nullptr;
     if (to_device(ctx, pixel_centroids, (size_t)codebook_size * 16 * channels, ctx->cent_px, &c_dev)) return 1;
+    if (sad && ((uintptr_t)c_dev & 15)) {  // the SAD kernel reads centroids as uint4
+        CK(ctx->cent_px.ensure((size_t)codebook_size * 16 * channels));
+        CK(cudaMemcpyAsync(ctx->cent_px.p, c_dev, (size_t)codebook_size * 16 * channels, cudaMemcpyDeviceToDevice, ctx->stream));
+        c_dev = ctx->cent_px.p;
+    }
     Blocks all;
     all.n = n_blocks;
     all.ch = channels;
+    all.planes = sad ? ctx->planes.as<uint4>() : nullptr;
+    all.stride = n_blocks;
     all.feat = ctx->feat.as<float>();
-    if (quantize_device(ctx, all, c_dev, codebook_size, false, assign_mode)) return 1;
+    if (quantize_device(ctx, all, c_dev, codebook_size, false, assign_mode, metric)) return 1;
     if (from_device(ctx, out_indices, ctx->out_idx.p, n_blocks * 4)) return 1;
     const int t1 = tm.mark();
     CK(cudaStreamSynchronize(ctx->stream));

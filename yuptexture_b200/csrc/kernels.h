@@ -151,4 +151,15 @@ cudaError_t launch_reseed_empty(const float* feat, size_t n, float* errors, cons
 cudaError_t launch_argmax_error(const float* errors, size_t n, uint32_t* out2, cudaStream_t s);
 cudaError_t launch_max_abs(const float* x, size_t n, uint32_t* out_bits, cudaStream_t s);
 
+// ---- sad.cu : A21, SAD-metric Lloyd (all integer, bit-exact) ---------------------------------------------
+// argmin over K pixel-block centroids (K x 16*ch bytes) of sum |a - b|; errors[i] = the minimum (as float)
+cudaError_t launch_sad_assign(const uint4* planes, size_t stride, size_t n, int ch, const uint8_t* cent_px, uint32_t K,
+                              uint32_t* assign, float* errors, uint32_t* flags, const uint32_t* stop, cudaStream_t s);
+// pixel planes -> N x 64 fp32 rows (integer-valued, zero padded): the rows the shared accumulate / reseed kernels read
+cudaError_t launch_sad_expand(const uint4* planes, size_t stride, size_t n, int ch, float* rows, cudaStream_t s);
+cudaError_t launch_sad_pack(const float* cent_f, uint32_t K, int ch, uint8_t* cent_px, cudaStream_t s);
+// centroid byte = sum / count (truncating); flags[1] = #empty clusters
+cudaError_t launch_sad_finalize(const long long* acc, uint32_t K, float* cent_f, uint32_t* flags, const uint32_t* stop,
+                                cudaStream_t s);
+
 }  // namespace yupvq
