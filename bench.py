@@ -250,9 +250,13 @@ def run_ours(args, rank, world, local_rank):
         flop_alg = 2.0 * blocks_per_launch * k * 64          # 2 K D per block per pass
         split = 3                                            # xh.ch + xh.cl + xl.ch bf16 partial products
         achieved = split * flop_alg / (ms_a * 1e-3) / 1e12 if ms_a > 0 else 0.0
+        traffic = None
+        tpath = os.path.join(ROOT, "profiles", "r01d_traffic.json")
+        if world == 1 and os.path.exists(tpath):  # DRAM bytes per launch of the same kernel on the same config, from the committed ncu capture
+            traffic = json.load(open(tpath))["assign_tc_kernel"]["dram_bytes_per_launch"]
         roofline = {"bound": "tensor", "kernel": "assign_tc_kernel (N x K x 64 contraction as 3 bf16 partial products + argmax epilogue)",
                     "achieved": achieved, "peak": pk["bf16_tflops_sustained"], "unit": "TFLOP/s",
-                    "frac": achieved / pk["bf16_tflops_sustained"], "traffic": None,
+                    "frac": achieved / pk["bf16_tflops_sustained"], "traffic": traffic,
                     "peak_source": pk["src"] + " bf16 sustained (kernel timed inside a step)",
                     "ms_per_launch": ms_a, "launches_timed": n_fe, "flop_per_launch_algorithmic": flop_alg, "bf16_split": split,
                     "achieved_unsplit": flop_alg / (ms_a * 1e-3) / 1e12 if ms_a > 0 else 0.0,

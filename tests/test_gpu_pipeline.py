@@ -211,3 +211,54 @@ def test_sad_metric_matches_oracle(enc, oracle, case):
     assert bits_equal(cent, c_ref)
     assert st.lloyd_passes == passes
     assert bits_equal(idx, oracle.quantize_blocks(px, ch, c_ref, metric=oracle.METRIC_SAD))
+
+
+def test_config3_full_size(enc, oracle):
+    """BASELINE config 3: 4096x4096 RGBA with alpha as BC3 (1,048,576 16-byte blocks, 4-channel vectors), K = 512.
+    Size-independent checks as for config 2: exact argmin on a stride sample given the returned centroids,
+    idempotent quantise, determinism; plus the same through BC7 (mode 6) on a quarter-size texture."""
+    from yuptexture_b200 import binding
+    img = synth.ldr_rgba(4096, 4096, seed=5)
+    bc = synth.bc3_encode(img)
+    n = len(bc)
+    cfg = binding.make_config(quality=0.8, max_iterations=16, seed=43)
+    cent, idx, st = enc.encode_bcn(bc, n, 3, 4, cfg)
+    assert st.n_blocks == n and idx.max() < 512 and 1 <= st.lloyd_passes <= 16
+    sel = np.arange(0, n, 64)
+    px_s = oracle.decode_bcn(bc[sel], 3, 4)
+    assert bits_equal(enc.decode_bcn(bc[sel], 3, 4), px_s)
+    i_ref, _ = oracle.assign(oracle.pixels_to_oklab(px_s, 4), oracle.pixels_to_oklab(cent, 4))
+    assert np.array_equal(idx[sel], i_ref)
+    cent_b, idx_b, _ = enc.encode_bcn(bc, n, 3, 4, cfg)
+    assert bits_equal(cent_b, cent) and bits_equal(idx_b, idx)
+    assert recon_psnr(px_s, cent, idx[sel]) > 15.0   # alpha has 10 % of its pixels forced to 0 / 255
+    # BC7
+    bc7 = synth.bc7_encode_mode6(synth.ldr_rgba(2048, 2048, seed=6))
+    n7 = len(bc7)
+    cent7, idx7, _ = enc.encode_bcn(bc7, n7, 7, 4, cfg)
+    sel7 = np.arange(0, n7, 32)
+    px7 = oracle.decode_bcn(bc7[sel7], 7, 4)
+    assert bits_equal(enc.decode_bcn(bc7[sel7], 7, 4), px7)
+    i7, _ = oracle.assign(oracle.pixels_to_oklab(px7, 4), oracle.pixels_to_oklab(cent7, 4))
+    assert np.array_equal(idx7[sel7], i7)
+
+
+def test_config4_full_size(enc, oracle):
+    """BASELINE config 4: 4096x2048 float HDR skybox (524,288 blocks), quality 1.0 -> K = 1024 (the streamed-
+    centroid front-end: four 256-centroid chunks), HDR break rule.  Checks: indices == the oracle's exact
+    QuantizeBlocksHDR on a stride sample given the returned float centroids, determinism, index range."""
+    from yuptexture_b200 import binding
+    w, h = 4096, 2048
+    img = synth.hdr_rgb(w, h, seed=11)
+    cfg = binding.make_config(quality=1.0, max_iterations=12, seed=44)
+    assert cfg.codebook_size == 1024
+    cent, idx, st = enc.encode_hdr(img, w, h, 3, cfg)
+    n = (w // 4) * (h // 4)
+    assert st.n_blocks == n and idx.max() < 1024 and 2 <= st.lloyd_passes <= 12
+    px = synth.image_to_blocks(img)
+    sel = np.arange(0, n, 64)
+    assert np.array_equal(idx[sel], oracle.quantize_blocks_hdr(px[sel], 3, cent))
+    cent_b, idx_b, _ = enc.encode_hdr(img, w, h, 3, cfg)
+    assert bits_equal(cent_b, cent) and bits_equal(idx_b, idx)
+    # the codebook represents the image: mean squared error well below the image variance
+    assert np.mean((cent[idx[sel]] - px[sel]) ** 2) < 0.5 * np.var(px[sel])
