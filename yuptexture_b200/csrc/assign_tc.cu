@@ -434,8 +434,6 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                 mbar_wait(bar(BAR_TFULL + acc), pacc);
                 tc_fence_after();
                 const uint32_t taddr = lane_taddr + acc * BN;
-                // TMEM reads are double-buffered (two 32-column register tiles): the load of the next tile is
-                // in flight while the current one is reduced, across the pass-1 / pass-2 boundary as well.
                 uint32_t va[32], vb[32];
                 float m0 = -INFINITY, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
                 auto reduce_max = [&](const uint32_t (&v)[32]) {
@@ -447,13 +445,18 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                         m3 = fmax3(m3, __uint_as_float(v[i + 6]), __uint_as_float(v[i + 7]));
                     }
                 };
-                // ---- pass 1: maximum score over this thread's columns
+                // ---- one read of the accumulator: both 32-column register tiles of this thread's slice are loaded,
+                // the stage goes back to the MMA warp at once (the next chunk's MMAs run under the whole reduction /
+                // sweep below), and both passes work from registers.
                 tc_ld32(taddr, va);
-                tc_wait_ld(va);
                 tc_ld32(taddr + 32, vb);
-                reduce_max(va);
+                tc_wait_ld(va);
                 tc_wait_ld(vb);
-                tc_ld32(taddr, va);  // first tile of pass 2
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar(BAR_TEMPTY + acc));
+                // ---- pass 1 (registers): maximum score over this thread's columns
+                reduce_max(va);
                 reduce_max(vb);
                 const float m_prev = m_run;
                 m_run = fmaxf(fmax3(m_run, m0, m1), fmaxf(m2, m3));
@@ -481,15 +484,8 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                     }
                 };
                 const uint32_t cbase = j * BN + slice * kCols;
-                tc_wait_ld(va);
-                tc_ld32(taddr + 32, vb);
                 sweep(va, cbase);
-                tc_wait_ld(vb);
                 sweep(vb, cbase + 32);
-                // release the accumulator stage to the MMA warp
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(bar(BAR_TEMPTY + acc));
             }
             // ---- the four slices of a row meet.  Lists, maxima and counts are double buffered by tile parity,
             // so one barrier per tile is enough.  count 100 = list overflow.
