@@ -68,6 +68,7 @@ struct yupvq_ctx {
     DevBuf cent_px, cent_feat, out_idx;                // finalize / quantize
     // tensor engine (assign_tc.cu): per block set A', |x'|, mu; per pass B', folded norms, candidates
     DevBuf tc_a, tc_xnorm, tc_small, tc_b, tc_bx, tc_cand, tc_amb;
+    DevBuf tc_chg, delta_ctl;  // delta update: (row, previous centroid) lists; counter / mode words
     // lock-step batch (yupvq_encode_bcn_batch_sharded): per-texture slices of one buffer each
     DevBuf bt_feat, bt_tca, bt_xnorm, bt_tcsmall, bt_assign, bt_errors, bt_cent, bt_acc, bt_misc, bt_centpx, bt_cent0;
     const float* tc_feat = nullptr;                    // block set the A' buffer was built from
@@ -365,7 +366,8 @@ int tc_prepare_view(yupvq_ctx* ctx, const float* feat, size_t n, const TcView& v
 }
 
 int assign_blocks(yupvq_ctx* ctx, const float* feat, size_t n, const float* cent, uint32_t K, int mode, uint32_t* assign,
-                  float* errors, uint32_t* flags, const uint32_t* stop = nullptr, const TcView* view = nullptr) {
+                  float* errors, uint32_t* flags, const uint32_t* stop = nullptr, const TcView* view = nullptr,
+                  const TcBatch* delta = nullptr) {
     if (mode == YUPVQ_ASSIGN_TENSOR && !tc_supported(K))
         return ctx->fail("tensor assignment needs 1 <= K <= 65535 and a driver with cuTensorMapEncodeTiled (K = %u)", K);
     if (!use_tensor(mode, n, K)) {
@@ -397,10 +399,10 @@ int assign_blocks(yupvq_ctx* ctx, const float* feat, size_t n, const float* cent
         if (prof) cudaEventRecord(ctx->pev[ctx->pev_used++], ctx->stream);
         LAUNCH(launch_assign_tc(tc_a, tc_xnorm, n, ctx->tc_b.as<float>(), ctx->tc_bx.as<float>(),
                                 K, reinterpret_cast<const float*>(sm + TC_CMAX), ctx->tc_cand.as<uint4>(), assign, flags,
-                                ctx->tc_amb.as<uint32_t>(), small + F_AMB, stop, ctx->stream));
+                                ctx->tc_amb.as<uint32_t>(), small + F_AMB, stop, ctx->stream, delta));
         if (prof) cudaEventRecord(ctx->pev[ctx->pev_used++], ctx->stream);
         LAUNCH(launch_rerank_sparse(feat, cent, K, ctx->tc_cand.as<uint4>(), ctx->tc_amb.as<uint32_t>(), small + F_AMB,
-                                    small + F_AMB + 1, assign, flags, small + F_PAIRS, ctx->stream));
+                                    small + F_AMB + 1, assign, flags, small + F_PAIRS, ctx->stream, delta));
     }
     return 0;
 }
@@ -455,11 +457,34 @@ int run_lloyd(yupvq_ctx* ctx, const Blocks& b, size_t n_total, size_t first_bloc
         const uint32_t* stopk = (dbg_async0 & 4) ? nullptr : ctl;
         CK(cudaMemsetAsync(ctl, 0, 12 + 8, ctx->stream));  // stop, passes, empty | ambiguous-row count, ticket
         CK(cudaMemsetAsync(flags, 0, 8, ctx->stream));  // changed, empty
+        // Delta update (tensor engine): the assignment kernels list the rows that moved; from the second pass on the
+        // update touches only those (exact: integer sums), unless more than a quarter of the blocks moved.
+        static const bool no_delta = getenv("YUPVQ_NO_DELTA") != nullptr;  // A/B timing and tests
+        const bool delta = tensor && !no_delta && n < 0xffffffffull;
+        TcBatch dl = tc_single();
+        uint32_t* dctl = nullptr;
+        if (delta) {
+            CK(ctx->tc_chg.ensure(std::max<size_t>(1, n) * 8));
+            CK(ctx->delta_ctl.ensure(256));
+            dctl = ctx->delta_ctl.as<uint32_t>();
+            CK(cudaMemsetAsync(dctl, 0, 256, ctx->stream));
+            dl.chg_rows = ctx->tc_chg.as<uint32_t>();
+            dl.chg_old = dl.chg_rows + n;
+            dl.chg_count = dctl;
+        }
         for (uint32_t iter = 0; iter < max_iter; ++iter) {
             // tensor mode computes errors[] lazily (they only feed the empty-cluster reseed)
-            if (assign_blocks(ctx, b.feat, n, cent, K, assign_mode, assign, tensor ? nullptr : errors, flags, stopk)) return 1;
-            CK(cudaMemsetAsync(acc, 0, acc_words * 8, ctx->stream));
-            LAUNCH(launch_accumulate(b.feat, n, assign, K, shift, acc, flags, stopk, ctx->stream));
+            if (assign_blocks(ctx, b.feat, n, cent, K, assign_mode, assign, tensor ? nullptr : errors, flags, stopk, nullptr,
+                              delta ? &dl : nullptr))
+                return 1;
+            if (delta) {
+                LAUNCH(launch_acc_prepare(acc, K, n, iter == 0 ? 1u : 0u, dctl, stopk, ctx->stream));
+                LAUNCH(launch_accumulate(b.feat, n, assign, K, shift, acc, flags, stopk, ctx->stream, dctl));
+                LAUNCH(launch_accumulate_delta(b.feat, assign, K, shift, acc, dl.chg_rows, dl.chg_old, dctl, flags, stopk, ctx->stream));
+            } else {
+                CK(cudaMemsetAsync(acc, 0, acc_words * 8, ctx->stream));
+                LAUNCH(launch_accumulate(b.feat, n, assign, K, shift, acc, flags, stopk, ctx->stream));
+            }
             LAUNCH(launch_lloyd_control(acc, K, iter, break_after, flags, ctl, ctx->stream));
             static const int dbg_async2 = getenv("YUPVQ_ASYNC_DBG") ? atoi(getenv("YUPVQ_ASYNC_DBG")) : 0;
             if (tensor && !(dbg_async2 & 2))  // errors[i] = distance to the assigned centroid, before the update (:336); only if a reseed needs them
@@ -468,6 +493,12 @@ int run_lloyd(yupvq_ctx* ctx, const Blocks& b, size_t n_total, size_t first_bloc
             LAUNCH(launch_reseed_empty(b.feat, n, errors, acc, K, cent, flags, stopk, ctx->stream));
             static const int dbg_async = getenv("YUPVQ_ASYNC_DBG") ? atoi(getenv("YUPVQ_ASYNC_DBG")) : 0;
             if (dbg_async & 1) CK(cudaStreamSynchronize(ctx->stream));
+            if ((dbg_async & 8) && delta) {  // per-pass delta statistics (debug)
+                uint32_t w[2];
+                CK(cudaMemcpyAsync(w, dctl + 32, 8, cudaMemcpyDeviceToHost, ctx->stream));
+                CK(cudaStreamSynchronize(ctx->stream));
+                fprintf(stderr, "pass %u: moved %u of %zu rows, mode %s\n", iter, w[0], n, w[1] ? "full" : "delta");
+            }
             if ((iter == 3 || iter == 7 || iter == 15) && iter + 1 < max_iter) {
                 CK(cudaMemcpyAsync(ctx->h_small, ctl, 4, cudaMemcpyDeviceToHost, ctx->stream));
                 CK(cudaStreamSynchronize(ctx->stream));
@@ -733,7 +764,7 @@ void yupvq_destroy(yupvq_ctx* ctx) {
                       &ctx->errors, &ctx->cent, &ctx->acc, &ctx->cent_px, &ctx->cent_feat, &ctx->out_idx,
                       &ctx->tc_a, &ctx->tc_xnorm, &ctx->tc_small, &ctx->tc_b, &ctx->tc_bx, &ctx->tc_cand, &ctx->tc_amb,
                       &ctx->bt_feat, &ctx->bt_tca, &ctx->bt_xnorm, &ctx->bt_tcsmall, &ctx->bt_assign, &ctx->bt_errors,
-                      &ctx->bt_cent, &ctx->bt_acc, &ctx->bt_misc, &ctx->bt_centpx, &ctx->bt_cent0};
+                      &ctx->bt_cent, &ctx->bt_acc, &ctx->bt_misc, &ctx->bt_centpx, &ctx->bt_cent0, &ctx->tc_chg, &ctx->delta_ctl};
     for (DevBuf* b : bufs) b->release();
     if (ctx->h_small) cudaFreeHost(ctx->h_small);
     for (auto& ev : ctx->ev)

@@ -408,7 +408,10 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
             if (thr == 0.0f) thr = -FLT_MIN;
             return thr;
         };
+        bool moved = false;
+        uint32_t pend_mask = 0, pend_base = 0, pend_row = 0, pend_old = 0;
         for (uint32_t t = t_first, t_next, tex_next; t < num_tiles; t = t_next, tex = tex_next, tpar ^= 1) {
+            moved = false;
             t_next = next_live(true);
             tex_next = w.tex;
             if (BATCH && tex != cmax_tex) {
@@ -513,10 +516,12 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                         w[total >> 1] |= c << (16 * (total & 1));
                     }
                 }
+                moved = false;
                 if (!ovf && total == 1 && assign) {
                     // a single candidate is the exact argmin: final
                     const uint32_t c = w[0] & 0xffffu;
-                    if (flags && old_c != c) flags[(size_t)tex * bt.flags_stride] = 1u;
+                    moved = old_c != c;
+                    if (flags && moved) flags[(size_t)tex * bt.flags_stride] = 1u;
                     assign[row] = c;
                 } else {
                     if (!ovf && total >= 1 && total <= (uint32_t)kMaxCand) {
@@ -528,6 +533,30 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                     cand[row] = make_uint4(w[0], w[1], w[2], w[3]);
                     if (amb_list) amb_list[atomicAdd(amb_count, 1u)] = (uint32_t)row;
                 }
+            }
+            if (!BATCH && bt.chg_count && slice == 0) {
+                // delta update: (row, previous centroid) of every row that moved -- one atomic per warp and tile, and
+                // its result is only consumed one tile later, so the round trip to L2 hides behind the next tile
+                if (pend_mask) {
+                    const uint32_t slot = __shfl_sync(0xffffffffu, pend_base, __ffs(pend_mask) - 1) +
+                                          (uint32_t)__popc(pend_mask & ((1u << lane) - 1u));
+                    if (pend_mask & (1u << lane)) {
+                        bt.chg_rows[slot] = pend_row;
+                        bt.chg_old[slot] = pend_old;
+                    }
+                }
+                pend_mask = __ballot_sync(0xffffffffu, moved);
+                pend_row = (uint32_t)row;
+                pend_old = old_c;
+                if (pend_mask && lane == __ffs(pend_mask) - 1) pend_base = atomicAdd(bt.chg_count, (unsigned)__popc(pend_mask));
+            }
+        }
+        if (!BATCH && bt.chg_count && slice == 0 && pend_mask) {
+            const uint32_t slot = __shfl_sync(0xffffffffu, pend_base, __ffs(pend_mask) - 1) +
+                                  (uint32_t)__popc(pend_mask & ((1u << lane) - 1u));
+            if (pend_mask & (1u << lane)) {
+                bt.chg_rows[slot] = pend_row;
+                bt.chg_old[slot] = pend_old;
             }
         }
     }
@@ -875,7 +904,15 @@ __global__ void __launch_bounds__(kRrThreads, 2) rerank_sparse_kernel(const floa
             }
         }
         if (act && h == 0) {
-            if (flags && assign[row] != bc) flags[0] = 1u;
+            const uint32_t prev = assign[row];
+            if (prev != bc) {
+                if (flags) flags[0] = 1u;
+                if (bt.chg_count) {  // delta update (about 1 % of the rows come through here)
+                    const uint32_t slot = atomicAdd(bt.chg_count, 1u);
+                    bt.chg_rows[slot] = (uint32_t)row;
+                    bt.chg_old[slot] = prev;
+                }
+            }
             assign[row] = bc;
         }
     }
@@ -980,7 +1017,7 @@ cudaError_t launch_assign_tc(const float* a_prime, const float* xnorm, size_t n,
     }
     const uint32_t k_pad = tc_padded_k(K);
     const uint32_t n_tex = batch ? batch->n_textures : 1u;
-    if (batch && (batch->rows_per_tex % BM != 0 || (size_t)batch->rows_per_tex * n_tex != n || batch->k_pad != k_pad))
+    if (batch && n_tex > 1 && (batch->rows_per_tex % BM != 0 || (size_t)batch->rows_per_tex * n_tex != n || batch->k_pad != k_pad))
         return cudaErrorInvalidValue;  // tiles must not straddle textures
     CUtensorMap tm_a, tm_b, tm_bx;
     if (!make_map(&tm_a, a_prime, 128, n, 64, BM, CU_TENSOR_MAP_SWIZZLE_128B) ||
@@ -991,7 +1028,7 @@ cudaError_t launch_assign_tc(const float* a_prime, const float* xnorm, size_t n,
     const uint32_t num_chunks = k_pad / BN;
     const uint32_t grid = num_tiles < (uint32_t)YUPVQ_NUM_SMS ? num_tiles : (uint32_t)YUPVQ_NUM_SMS;
     TcBatch bt = batch ? *batch : tc_single();
-    if (!batch) bt.k_pad = k_pad;
+    if (!batch || n_tex <= 1) bt.k_pad = k_pad;
     if (batch && n_tex > 1)
         assign_tc_kernel<true><<<grid, kThreadsTc, SMEM_TC, s>>>(tm_a, tm_b, tm_bx, xnorm, cmax, (uint32_t)n, num_tiles, num_chunks,
                                                                 num_chunks <= 2 ? 1u : 0u, cand, assign, flags, amb_list, amb_count, stop, bt);

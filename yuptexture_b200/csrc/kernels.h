@@ -76,8 +76,13 @@ struct TcBatch {
     uint32_t stop_stride;     // uint32 words between the textures' stop words
     uint32_t rows_per_tex;    // rows per texture (the re-rank maps a row to its texture's centroids)
     uint32_t n_textures;
+    // delta update (single texture only; null = off): every row whose assignment changes is appended as
+    // (row, previous centroid) so the update touches only those rows (launch_accumulate_delta)
+    uint32_t* chg_rows;
+    uint32_t* chg_old;
+    unsigned int* chg_count;
 };
-inline TcBatch tc_single() { return TcBatch{0xffffffffu, 0u, 0u, 0u, 0u, 0xffffffffu, 1u}; }
+inline TcBatch tc_single() { return TcBatch{0xffffffffu, 0u, 0u, 0u, 0u, 0xffffffffu, 1u, nullptr, nullptr, nullptr}; }
 bool tc_supported(uint32_t K);
 uint32_t tc_padded_k(uint32_t K);  // rows of b_main / b_ext
 cudaError_t launch_tc_mean(const float* feat, size_t n, double* sums64, float* mu, cudaStream_t s);
@@ -113,7 +118,8 @@ cudaError_t launch_rerank(const float* feat, size_t n, const float* cent, uint32
 // buffer is what gets all-reduced when blocks are sharded across GPUs.
 // flags: [0] changed (written by assign), [1] #empty clusters, [2] reseeds (running total).
 cudaError_t launch_accumulate(const float* feat, size_t n, const uint32_t* assign, uint32_t K, int shift,
-                              long long* acc, const uint32_t* flags, const uint32_t* stop, cudaStream_t s);
+                              long long* acc, const uint32_t* flags, const uint32_t* stop, cudaStream_t s,
+                              const uint32_t* dctl = nullptr);
 // lock-step batch: texture t = rows [t * rows_per_tex, ..) of feat / assign, accumulator acc + t * acc_stride (int64 words),
 // fixed-point scale scales[t] (device), changed flag flags[t * flags_stride], stop word stop[t * stop_stride]
 struct AccBatch {
@@ -123,6 +129,19 @@ struct AccBatch {
     uint32_t flags_stride;
     uint32_t stop_stride;
 };
+// Delta update.  dctl (uint32 words, own cache lines): [0] changed-row counter the assignment kernels append to,
+// [32] rows to process this pass, [33] mode (1 = full recompute, 0 = delta).
+//   launch_acc_prepare     decides the mode for this pass (full on pass 0 / when more than n/4 rows changed / when the
+//                          list is off), zeroes the accumulator for a full pass and always the changed word, moves the
+//                          counter to [32] and clears it;
+//   launch_accumulate      (full) runs only when dctl == null or dctl[33] == 1;
+//   launch_accumulate_delta runs only when dctl[33] == 0: sums[new] += x, sums[old] -= x, counts likewise, for the
+//                          listed rows -- exact, because the sums are integers.
+cudaError_t launch_acc_prepare(long long* acc, uint32_t K, size_t n, uint32_t force_full, uint32_t* dctl, const uint32_t* stop,
+                               cudaStream_t s);
+cudaError_t launch_accumulate_delta(const float* feat, const uint32_t* assign, uint32_t K, int shift, long long* acc,
+                                    const uint32_t* chg_rows, const uint32_t* chg_old, const uint32_t* dctl,
+                                    const uint32_t* flags, const uint32_t* stop, cudaStream_t s);
 bool accumulate_batch_supported(size_t rows_per_tex, uint32_t K);
 cudaError_t launch_accumulate_batch(const float* feat, size_t rows_per_tex, const uint32_t* assign, uint32_t K, long long* acc,
                                     const uint32_t* flags, const uint32_t* stop, const AccBatch& bt, cudaStream_t s);

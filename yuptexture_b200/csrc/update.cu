@@ -22,8 +22,9 @@ namespace {
 __global__ void __launch_bounds__(256) accumulate_kernel(const float* __restrict__ feat, size_t n,
                                                          const uint32_t* __restrict__ assign, uint32_t K, float scale,
                                                          long long* __restrict__ acc, const uint32_t* __restrict__ flags,
-                                                         const uint32_t* __restrict__ stop) {
+                                                         const uint32_t* __restrict__ stop, const uint32_t* __restrict__ dctl) {
     if (stop && __ldg(stop)) return;
+    if (dctl && dctl[33] == 0u) return;  // this pass is a delta update
     const int lane = threadIdx.x & 31;
     const size_t warp = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const size_t n_warps = ((size_t)gridDim.x * blockDim.x) >> 5;
@@ -52,12 +53,13 @@ constexpr int kAccMaxK = 4096;
 __global__ void __launch_bounds__(kAccThreads, 2)
 accumulate_sorted_kernel(const float* __restrict__ feat_all, size_t n, const uint32_t* __restrict__ assign_all, uint32_t K, float scale1,
                          long long* __restrict__ acc_all, const uint32_t* __restrict__ flags, const uint32_t* __restrict__ stop,
-                         AccBatch bt) {
+                         AccBatch bt, const uint32_t* __restrict__ dctl) {
     // Lock-step batch (bt.n_textures > 1): texture t owns rows [t * n, (t + 1) * n) of feat / assign, the accumulator
     // at acc + t * acc_stride, the scale bt.scales[t] and the flag / stop words at the given strides; chunks are
     // numbered texture-major, so one launch covers the whole batch.
     extern __shared__ uint32_t sm_acc[];
     if (bt.n_textures <= 1 && stop && __ldg(stop)) return;
+    if (dctl && dctl[33] == 0u) return;  // this pass is a delta update
     uint32_t* hist = sm_acc;                                      // K
     uint32_t* offs = sm_acc + K;                                  // K
     uint16_t* sorted = reinterpret_cast<uint16_t*>(sm_acc + 2 * K);  // kAccChunk
@@ -175,6 +177,178 @@ accumulate_sorted_kernel(const float* __restrict__ feat_all, size_t n, const uin
             atomicAdd(sums + (size_t)K * 65, (unsigned long long)flags[(size_t)tex * bt.flags_stride]);
         }
     }
+}
+
+// ---- delta update ----------------------------------------------------------------------------------------------
+// After the first passes only a few percent of the blocks change centroid.  Because the sums are integers,
+// sums[new] += x, sums[old] -= x over the changed rows gives exactly the accumulator a full recompute would give,
+// while reading only those rows.  The assignment kernels append (row, previous centroid) for every row they move.
+constexpr int kDeltaThreads = 512;
+constexpr int kDeltaRows = 2048;           // listed rows per chunk -> 2 * kDeltaRows signed entries
+constexpr int kDeltaMaxK = 4096;
+
+// one CTA: decide this pass' mode, zero what has to be zeroed, hand the row count over and rearm the counter
+__global__ void __launch_bounds__(1024) acc_prepare_kernel(long long* __restrict__ acc, uint32_t K, uint32_t full_above,
+                                                           uint32_t force_full, uint32_t* __restrict__ dctl,
+                                                           const uint32_t* __restrict__ stop) {
+    if (stop && __ldg(stop)) return;
+    const uint32_t n_chg = dctl[0];
+    const bool full = force_full || n_chg > full_above;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        dctl[32] = n_chg;
+        dctl[33] = full ? 1u : 0u;
+        dctl[0] = 0u;
+        acc[(size_t)K * 65] = 0;  // the changed word is per pass in both modes
+    }
+    if (full)
+        for (size_t i = threadIdx.x; i < (size_t)K * 65; i += blockDim.x) acc[i] = 0;
+}
+
+__global__ void __launch_bounds__(kDeltaThreads)
+accumulate_delta_kernel(const float* __restrict__ feat, const uint32_t* __restrict__ assign, uint32_t K, float scale,
+                        long long* __restrict__ acc, const uint32_t* __restrict__ chg_rows, const uint32_t* __restrict__ chg_old,
+                        const uint32_t* __restrict__ dctl, const uint32_t* __restrict__ flags, const uint32_t* __restrict__ stop) {
+    // A chunk of listed rows becomes 2 signed entries per row (+x for the new centroid, -x for the old one); the
+    // entries are counting-sorted by centroid in shared memory and every half-warp then walks a contiguous slice
+    // of the SORTED entries, 8 independent row loads in flight at a time, emitting one 64-bit RED per column at
+    // the end of each run of equal centroids.  Chunk size adapts to the list length: long lists use big chunks
+    // (long runs, few REDs), short lists small ones (all SMs busy, short dependent chains).
+    extern __shared__ uint32_t sm_acc[];
+    if (stop && __ldg(stop)) return;
+    if (dctl[33] != 0u) return;  // this pass is a full recompute
+    const uint32_t n_use = dctl[32];
+    uint32_t chunk_rows = n_use / gridDim.x + 1;
+    chunk_rows = chunk_rows < 128u ? 128u : (chunk_rows > (uint32_t)kDeltaRows ? (uint32_t)kDeltaRows : chunk_rows);
+    uint32_t* hist = sm_acc;                                          // K
+    uint32_t* offs = sm_acc + K;                                      // K
+    uint32_t* rows_s = sm_acc + 2 * K;                                // kDeltaRows
+    uint16_t* sorted = reinterpret_cast<uint16_t*>(sm_acc + 2 * K + kDeltaRows);   // 2 * kDeltaRows entry ids
+    uint16_t* cent_s = sorted + 2 * kDeltaRows;                                    // centroid of each sorted entry
+    __shared__ uint32_t warp_tot[kDeltaThreads / 32 + 1];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    unsigned long long* sums = reinterpret_cast<unsigned long long*>(acc);
+    unsigned long long* counts = sums + (size_t)K * 64;
+    const uint32_t n_chunks = (n_use + chunk_rows - 1) / chunk_rows;
+    constexpr int kPer = kDeltaRows / kDeltaThreads;
+    for (uint32_t chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x) {
+        const uint32_t first = chunk * chunk_rows;
+        const uint32_t len = n_use - first < chunk_rows ? n_use - first : chunk_rows;
+        for (uint32_t c = tid; c < K; c += kDeltaThreads) hist[c] = 0;
+        __syncthreads();
+        uint32_t a_new[kPer], a_old[kPer], r_new[kPer], r_old[kPer];
+#pragma unroll
+        for (int k = 0; k < kPer; ++k) {
+            const uint32_t i = (uint32_t)k * kDeltaThreads + tid;
+            a_new[k] = a_old[k] = 0xffffffffu;
+            r_new[k] = r_old[k] = 0u;
+            if (i < len) {
+                const uint32_t row = chg_rows[first + i];
+                rows_s[i] = row;
+                a_old[k] = chg_old[first + i];
+                a_new[k] = assign[row];
+                if (a_new[k] < K) r_new[k] = atomicAdd(&hist[a_new[k]], 1u);
+                if (a_old[k] < K) r_old[k] = atomicAdd(&hist[a_old[k]], 1u);
+            }
+        }
+        __syncthreads();
+        {   // exclusive scan of hist -> offs
+            const uint32_t per = (K + kDeltaThreads - 1) / kDeltaThreads;
+            const uint32_t b0 = tid * per;
+            uint32_t local = 0;
+            for (uint32_t c = b0; c < b0 + per && c < K; ++c) local += hist[c];
+            uint32_t incl = local;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += t;
+            }
+            if (lane == 31) warp_tot[wid] = incl;
+            __syncthreads();
+            if (wid == 0) {
+                uint32_t w = lane < kDeltaThreads / 32 ? warp_tot[lane] : 0u, wi = w;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const uint32_t t = __shfl_up_sync(0xffffffffu, wi, o);
+                    if (lane >= o) wi += t;
+                }
+                if (lane < kDeltaThreads / 32) warp_tot[lane] = wi - w;
+            }
+            __syncthreads();
+            uint32_t run = warp_tot[wid] + incl - local;
+            for (uint32_t c = b0; c < b0 + per && c < K; ++c) {
+                offs[c] = run;
+                run += hist[c];
+            }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < kPer; ++k) {
+            const uint32_t i = (uint32_t)k * kDeltaThreads + tid;
+            if (a_new[k] < K) {
+                const uint32_t p = offs[a_new[k]] + r_new[k];
+                sorted[p] = (uint16_t)(2u * i);        // + x
+                cent_s[p] = (uint16_t)a_new[k];
+            }
+            if (a_old[k] < K) {
+                const uint32_t p = offs[a_old[k]] + r_old[k];
+                sorted[p] = (uint16_t)(2u * i + 1u);   // - x
+                cent_s[p] = (uint16_t)a_old[k];
+            }
+        }
+        __syncthreads();
+        // half-warp hwid walks sorted entries [p0, p1); lane l of the half-warp owns columns 4l .. 4l+3
+        const uint32_t total = offs[K - 1] + hist[K - 1];   // == 2 * len unless an id was out of range (dropped)
+        const uint32_t hwid = (uint32_t)tid >> 4, l16 = (uint32_t)tid & 15u;
+        constexpr uint32_t kHalfWarps = kDeltaThreads / 16;
+        const uint32_t per_hw = (total + kHalfWarps - 1) / kHalfWarps;
+        const uint32_t p0 = hwid * per_hw, p1 = p0 + per_hw < total ? p0 + per_hw : total;
+        const float4* rows = reinterpret_cast<const float4*>(feat) + l16;
+        long long s0 = 0, s1 = 0, s2 = 0, s3 = 0, cnt = 0;
+        uint32_t cur = 0xffffffffu;
+        auto flush = [&]() {
+            if (cur != 0xffffffffu) {
+                unsigned long long* dst = sums + (size_t)cur * 64 + 4 * l16;
+                atomicAdd(dst + 0, (unsigned long long)s0);
+                atomicAdd(dst + 1, (unsigned long long)s1);
+                atomicAdd(dst + 2, (unsigned long long)s2);
+                atomicAdd(dst + 3, (unsigned long long)s3);
+                if (l16 == 0 && cnt != 0) atomicAdd(counts + cur, (unsigned long long)cnt);
+            }
+            s0 = s1 = s2 = s3 = cnt = 0;
+        };
+        for (uint32_t p = p0; p < p1; p += 8) {
+            float4 v[8];
+            uint32_t e[8], c[8];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                const bool ok = p + q < p1;
+                e[q] = ok ? sorted[p + q] : 0u;
+                c[q] = ok ? cent_s[p + q] : 0xffffffffu;
+                v[q] = ok ? __ldg(rows + (size_t)rows_s[e[q] >> 1] * 16) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                if (p + q < p1) {
+                    if (c[q] != cur) {
+                        flush();
+                        cur = c[q];
+                    }
+                    const bool neg = (e[q] & 1u) != 0u;
+                    const long long f0 = __float2ll_rn(__fmul_rn(v[q].x, scale)), f1 = __float2ll_rn(__fmul_rn(v[q].y, scale));
+                    const long long f2 = __float2ll_rn(__fmul_rn(v[q].z, scale)), f3 = __float2ll_rn(__fmul_rn(v[q].w, scale));
+                    s0 += neg ? -f0 : f0;
+                    s1 += neg ? -f1 : f1;
+                    s2 += neg ? -f2 : f2;
+                    s3 += neg ? -f3 : f3;
+                    cnt += neg ? -1 : 1;
+                }
+            }
+        }
+        flush();
+        __syncthreads();
+    }
+    if (blockIdx.x == 0 && tid == 0 && flags) atomicAdd(sums + (size_t)K * 65, (unsigned long long)flags[0]);
 }
 
 // blockIdx.y = texture of a lock-step batch (strides 0 and inv_scales null for a single texture)
@@ -365,7 +539,7 @@ __global__ void max_abs_kernel(const float* __restrict__ x, size_t n, uint32_t* 
 }  // namespace
 
 cudaError_t launch_accumulate(const float* feat, size_t n, const uint32_t* assign, uint32_t K, int shift,
-                              long long* acc, const uint32_t* flags, const uint32_t* stop, cudaStream_t s) {
+                              long long* acc, const uint32_t* flags, const uint32_t* stop, cudaStream_t s, const uint32_t* dctl) {
     if (K <= (uint32_t)kAccMaxK && n >= (size_t)kAccChunk) {
         const size_t smem = (size_t)K * 8 + (size_t)kAccChunk * 2;
         static size_t attr_smem = 0;
@@ -377,19 +551,42 @@ cudaError_t launch_accumulate(const float* feat, size_t n, const uint32_t* assig
         size_t chunks = (n + kAccChunk - 1) / kAccChunk;
         size_t grid = chunks < (size_t)YUPVQ_NUM_SMS * 2 ? chunks : (size_t)YUPVQ_NUM_SMS * 2;
         accumulate_sorted_kernel<<<(unsigned)grid, kAccThreads, smem, s>>>(feat, n, assign, K, ldexpf(1.0f, shift), acc, flags, stop,
-                                                                          AccBatch{1u, 0, nullptr, 0u, 0u});
+                                                                          AccBatch{1u, 0, nullptr, 0u, 0u}, dctl);
         return cudaGetLastError();
     }
     size_t blocks = (n * 32 + 255) / 256;
     if (blocks > (size_t)YUPVQ_NUM_SMS * 16) blocks = (size_t)YUPVQ_NUM_SMS * 16;
     if (blocks < 1) blocks = 1;
-    accumulate_kernel<<<(unsigned)blocks, 256, 0, s>>>(feat, n, assign, K, ldexpf(1.0f, shift), acc, flags, stop);
+    accumulate_kernel<<<(unsigned)blocks, 256, 0, s>>>(feat, n, assign, K, ldexpf(1.0f, shift), acc, flags, stop, dctl);
     return cudaGetLastError();
 }
 
 cudaError_t launch_finalize_centroids(const long long* acc, uint32_t K, int shift, float* cent, uint32_t* flags,
                                       const uint32_t* stop, cudaStream_t s) {
     finalize_kernel<<<(K * 64 + 255) / 256, 256, 0, s>>>(acc, K, ldexp(1.0, -shift), cent, flags, stop, 0, nullptr, 0u, 0u);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_acc_prepare(long long* acc, uint32_t K, size_t n, uint32_t force_full, uint32_t* dctl, const uint32_t* stop,
+                               cudaStream_t s) {
+    if (K > (uint32_t)kDeltaMaxK) force_full = 1u;
+    acc_prepare_kernel<<<1, 1024, 0, s>>>(acc, K, (uint32_t)(n / 4), force_full, dctl, stop);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_accumulate_delta(const float* feat, const uint32_t* assign, uint32_t K, int shift, long long* acc,
+                                    const uint32_t* chg_rows, const uint32_t* chg_old, const uint32_t* dctl,
+                                    const uint32_t* flags, const uint32_t* stop, cudaStream_t s) {
+    if (K > (uint32_t)kDeltaMaxK) return cudaSuccess;  // launch_acc_prepare forces full passes
+    const size_t smem = (size_t)K * 8 + (size_t)kDeltaRows * 4 + (size_t)kDeltaRows * 4 + (size_t)kDeltaRows * 4;
+    static size_t attr_smem = 0;
+    if (smem > 48 * 1024 && smem > attr_smem) {
+        cudaError_t e = cudaFuncSetAttribute(accumulate_delta_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        attr_smem = smem;
+    }
+    accumulate_delta_kernel<<<YUPVQ_NUM_SMS, kDeltaThreads, smem, s>>>(feat, assign, K, ldexpf(1.0f, shift), acc, chg_rows, chg_old,
+                                                                          dctl, flags, stop);
     return cudaGetLastError();
 }
 
@@ -405,7 +602,7 @@ cudaError_t launch_accumulate_batch(const float* feat, size_t rows_per_tex, cons
     }
     size_t chunks = (rows_per_tex + kAccChunk - 1) / kAccChunk * bt.n_textures;
     size_t grid = chunks < (size_t)YUPVQ_NUM_SMS * 2 ? chunks : (size_t)YUPVQ_NUM_SMS * 2;
-    accumulate_sorted_kernel<<<(unsigned)grid, kAccThreads, smem, s>>>(feat, rows_per_tex, assign, K, 1.0f, acc, flags, stop, bt);
+    accumulate_sorted_kernel<<<(unsigned)grid, kAccThreads, smem, s>>>(feat, rows_per_tex, assign, K, 1.0f, acc, flags, stop, bt, nullptr);
     return cudaGetLastError();
 }
 
