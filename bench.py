@@ -97,12 +97,31 @@ def cpu_reference_step(px_sample, threads):
     if refbind.available():
         t0 = time.perf_counter()
         cent, _, _ = refbind.build_codebook(px_sample, 3, 1, QUALITY, MAX_ITER, SEED, threads=threads)
-        refbind.quantize_blocks(px_sample, 3, cent, threads=threads)
-        return time.perf_counter() - t0, "reference"
+        idx = refbind.quantize_blocks(px_sample, 3, cent, threads=threads)
+        idx = idx[0] if isinstance(idx, tuple) else idx
+        return time.perf_counter() - t0, "reference", cent, idx
     t0 = time.perf_counter()
     cent, _ = orcbind.build_codebook(px_sample, 3, k, MAX_ITER, SEED, threads=1)
-    orcbind.quantize_blocks(px_sample, 3, cent)
-    return time.perf_counter() - t0, "port"
+    idx = orcbind.quantize_blocks(px_sample, 3, cent)
+    return time.perf_counter() - t0, "port", cent, idx
+
+
+def parity_report(enc, px, cent_ref, idx_ref):
+    """SURVEY 8d parity gates on the CPU sample, GPU path vs the CPU reference output of the same sample and seed."""
+    from oracle import orcbind
+    from yuptexture_b200 import binding, synth
+    k = len(cent_ref)
+    cfg = binding.make_config(codebook=k, max_iterations=MAX_ITER, seed=SEED)
+    cent, st = enc.build_codebook(px, 3, cfg)
+    idx, _ = enc.quantize_blocks(px, 3, cent)
+    idx_on_ref, _ = enc.quantize_blocks(px, 3, cent_ref)            # indices given the reference's centroids
+    cfg0 = binding.make_config(codebook=k, max_iterations=0, seed=SEED)
+    seeds_gpu, _ = enc.build_codebook(px, 3, cfg0)
+    seeds_cpu, _ = orcbind.build_codebook(px, 3, k, 0, SEED)         # the pinned restatement (seeds only: cheap)
+    return {"sample_blocks": int(len(px)), "index_agreement_given_reference_centroids": float((idx_on_ref == idx_ref).mean()),
+            "seed_list_identical": bool(np.array_equal(seeds_gpu, seeds_cpu)),
+            "psnr_db_gpu": float(synth.psnr_u8(cent[idx], px)), "psnr_db_reference": float(synth.psnr_u8(cent_ref[idx_ref], px)),
+            "lloyd_passes_gpu": int(st.lloyd_passes)}
 
 
 def cpu_sample_pixels(bc):
@@ -124,7 +143,7 @@ def run_reference(args, rank, world):
     t0 = time.perf_counter()
     kind = "port"
     for _ in range(args.steps):
-        _, kind = cpu_reference_step(px, threads)
+        _, kind = cpu_reference_step(px, threads)[:2]
     dt = (time.perf_counter() - t0) / max(1, args.steps)
     value = len(px) / dt
     sample = f"{CPU_SAMPLE}x{CPU_SAMPLE} crop ({len(px)} blocks) of the 4096^2 BC1 bench texture per step, K=512, 32 iterations max"
@@ -264,7 +283,8 @@ def run_ours(args, rank, world, local_rank):
         # bounded CPU sample of the same workload on this box's host cores
         px = cpu_sample_pixels(textures[0])
         threads = os.cpu_count() or 1
-        dt, kind = cpu_reference_step(px, threads)
+        dt, kind, cent_ref, idx_ref = cpu_reference_step(px, threads)
+        parity = parity_report(enc, px, cent_ref, idx_ref)
         cpu = {"value": len(px) / dt, "unit": "blocks/s", "cores": threads if kind == "reference" else 1, "kind": kind,
                "sample": f"{CPU_SAMPLE}x{CPU_SAMPLE} crop ({len(px)} blocks) of the bench texture, one pass, "
                          f"BuildCodebook+QuantizeBlocks {dt:.2f} s"}
@@ -289,6 +309,7 @@ def run_ours(args, rank, world, local_rank):
             "gpu_launches": launches,
             "roofline": roofline,
             "cpu_baseline": cpu,
+            "parity": parity,
             "clocks": clocks.summary(),
         }
         print(json.dumps(out))
