@@ -284,7 +284,9 @@ def run_ours(args, rank, world, local_rank):
         px = cpu_sample_pixels(textures[0])
         threads = os.cpu_count() or 1
         dt, kind, cent_ref, idx_ref = cpu_reference_step(px, threads)
-        parity = parity_report(enc, px, cent_ref, idx_ref)
+        solo = binding.Encoder(local_rank)   # no communicator: the parity sample is a single-GPU call on rank 0 only
+        parity = parity_report(solo, px, cent_ref, idx_ref)
+        solo.close()
         cpu = {"value": len(px) / dt, "unit": "blocks/s", "cores": threads if kind == "reference" else 1, "kind": kind,
                "sample": f"{CPU_SAMPLE}x{CPU_SAMPLE} crop ({len(px)} blocks) of the bench texture, one pass, "
                          f"BuildCodebook+QuantizeBlocks {dt:.2f} s"}

@@ -70,7 +70,7 @@ struct yupvq_ctx {
     DevBuf tc_a, tc_xnorm, tc_small, tc_b, tc_bx, tc_cand, tc_amb;
     DevBuf tc_chg, delta_ctl;  // delta update: (row, previous centroid) lists; counter / mode words
     // lock-step batch (yupvq_encode_bcn_batch_sharded): per-texture slices of one buffer each
-    DevBuf bt_feat, bt_tca, bt_xnorm, bt_tcsmall, bt_assign, bt_errors, bt_cent, bt_acc, bt_misc, bt_centpx, bt_cent0;
+    DevBuf bt_feat, bt_tca, bt_xnorm, bt_tcsmall, bt_assign, bt_errors, bt_cent, bt_acc, bt_misc, bt_centpx, bt_cent0, bt_acc_local;
     const float* tc_feat = nullptr;                    // block set the A' buffer was built from
     size_t tc_n = 0;
     uint64_t rerank_pairs = 0;
@@ -764,7 +764,7 @@ void yupvq_destroy(yupvq_ctx* ctx) {
                       &ctx->errors, &ctx->cent, &ctx->acc, &ctx->cent_px, &ctx->cent_feat, &ctx->out_idx,
                       &ctx->tc_a, &ctx->tc_xnorm, &ctx->tc_small, &ctx->tc_b, &ctx->tc_bx, &ctx->tc_cand, &ctx->tc_amb,
                       &ctx->bt_feat, &ctx->bt_tca, &ctx->bt_xnorm, &ctx->bt_tcsmall, &ctx->bt_assign, &ctx->bt_errors,
-                      &ctx->bt_cent, &ctx->bt_acc, &ctx->bt_misc, &ctx->bt_centpx, &ctx->bt_cent0, &ctx->tc_chg, &ctx->delta_ctl};
+                      &ctx->bt_cent, &ctx->bt_acc, &ctx->bt_misc, &ctx->bt_centpx, &ctx->bt_cent0, &ctx->tc_chg, &ctx->delta_ctl, &ctx->bt_acc_local};
     for (DevBuf* b : bufs) b->release();
     if (ctx->h_small) cudaFreeHost(ctx->h_small);
     for (auto& ev : ctx->ev)
@@ -1753,7 +1753,11 @@ int yupvq_encode_bcn_batch_sharded(yupvq_ctx* ctx, const uint8_t* const* bc_bloc
     auto assign_fused = [&](const float* cent_all, uint32_t* out, uint32_t* fl, const uint32_t* stop) -> int {
         uint8_t* sm = ctx->bt_tcsmall.as<uint8_t>();
         TcBatch b = tb;
-        if (!fl) b.flags_stride = 0;
+        if (!fl) {  // the quantise pass: no changed flags, no moved-row list
+            b.flags_stride = 0;
+            b.chg_rows = b.chg_old = nullptr;
+            b.chg_count = nullptr;
+        }
         if (!stop) b.stop_stride = 0;
         LAUNCH(launch_tc_prep_centroids_batch(cent_all, K, (uint32_t)T, sm, TC_SMALL_BYTES, TC_MU, TC_CMAX, ctx->tc_b.as<float>(),
                                               ctx->tc_bx.as<float>(), ctx->stream));
@@ -1770,11 +1774,42 @@ int yupvq_encode_bcn_batch_sharded(yupvq_ctx* ctx, const uint8_t* const* bc_bloc
     auto run_async_fused = [&](bool* redo) -> int {
         *redo = false;
         if (reset_state()) return 1;
+        // Delta update: this rank's partial sums persist in bt_acc_local and are adjusted by the rows that
+        // moved; a copy goes through the all-reduce.  One list and one mode for the whole batch.
+        static const bool no_delta = getenv("YUPVQ_NO_DELTA") != nullptr;
+        const bool delta = !no_delta && delta_batch_supported(K, (uint32_t)T);
+        long long* acc_loc = ctx->bt_acc.as<long long>();
+        uint32_t* dctl = nullptr;
+        tb.chg_rows = tb.chg_old = nullptr;
+        tb.chg_count = nullptr;
+        if (delta) {
+            CK(ctx->tc_chg.ensure(T * nl * 8));
+            CK(ctx->delta_ctl.ensure(256));
+            dctl = ctx->delta_ctl.as<uint32_t>();
+            CK(cudaMemsetAsync(dctl, 0, 256, ctx->stream));
+            tb.chg_rows = ctx->tc_chg.as<uint32_t>();
+            tb.chg_old = tb.chg_rows + T * nl;
+            tb.chg_count = dctl;
+            if (ctx->comm) {
+                CK(ctx->bt_acc_local.ensure(T * acc_words * 8));
+                acc_loc = ctx->bt_acc_local.as<long long>();
+            }
+        }
         for (uint32_t iter = 0; iter < cfg->max_iterations; ++iter) {
-            CK(cudaMemsetAsync(ctx->bt_acc.p, 0, T * acc_words * 8, ctx->stream));
             if (assign_fused(ctx->bt_cent.as<float>(), ctx->bt_assign.as<uint32_t>(), tflags_d, ctl_d)) return 1;
-            LAUNCH(launch_accumulate_batch(ctx->bt_feat.as<float>(), n_local, ctx->bt_assign.as<uint32_t>(), K, ctx->bt_acc.as<long long>(),
-                                           tflags_d, ctl_d, ab, ctx->stream));
+            if (delta) {
+                LAUNCH(launch_acc_prepare_batch(acc_loc, K, T * n_local, iter == 0 ? 1u : 0u, dctl, ab, ctx->stream));
+                LAUNCH(launch_accumulate_batch(ctx->bt_feat.as<float>(), n_local, ctx->bt_assign.as<uint32_t>(), K, acc_loc, tflags_d, ctl_d,
+                                               ab, ctx->stream, dctl));
+                LAUNCH(launch_accumulate_delta(ctx->bt_feat.as<float>(), ctx->bt_assign.as<uint32_t>(), K, 0, acc_loc, tb.chg_rows, tb.chg_old,
+                                               dctl, tflags_d, ctl_d, ctx->stream, &ab, (uint32_t)n_local));
+                if (ctx->comm)
+                    CK(cudaMemcpyAsync(ctx->bt_acc.p, acc_loc, T * acc_words * 8, cudaMemcpyDeviceToDevice, ctx->stream));
+            } else {
+                CK(cudaMemsetAsync(ctx->bt_acc.p, 0, T * acc_words * 8, ctx->stream));
+                LAUNCH(launch_accumulate_batch(ctx->bt_feat.as<float>(), n_local, ctx->bt_assign.as<uint32_t>(), K, ctx->bt_acc.as<long long>(),
+                                               tflags_d, ctl_d, ab, ctx->stream));
+            }
             if (ctx->comm && ctx->nccl.all_reduce_sum_i64(ctx->comm, ctx->bt_acc.as<long long>(), T * acc_words, ctx->stream))
                 return ctx->fail("ncclAllReduce(sum) failed");
             LAUNCH(launch_lloyd_control_batch(ctx->bt_acc.as<long long>(), acc_words, (uint32_t)T, K, iter, 0u, tflags_d, 4u, ctl_d,

@@ -534,7 +534,7 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                     if (amb_list) amb_list[atomicAdd(amb_count, 1u)] = (uint32_t)row;
                 }
             }
-            if (!BATCH && bt.chg_count && slice == 0) {
+            if (bt.chg_count && slice == 0) {
                 // delta update: (row, previous centroid) of every row that moved -- one atomic per warp and tile, and
                 // its result is only consumed one tile later, so the round trip to L2 hides behind the next tile
                 if (pend_mask) {
@@ -551,7 +551,7 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                 if (pend_mask && lane == __ffs(pend_mask) - 1) pend_base = atomicAdd(bt.chg_count, (unsigned)__popc(pend_mask));
             }
         }
-        if (!BATCH && bt.chg_count && slice == 0 && pend_mask) {
+        if (bt.chg_count && slice == 0 && pend_mask) {
             const uint32_t slot = __shfl_sync(0xffffffffu, pend_base, __ffs(pend_mask) - 1) +
                                   (uint32_t)__popc(pend_mask & ((1u << lane) - 1u));
             if (pend_mask & (1u << lane)) {

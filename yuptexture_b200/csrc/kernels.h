@@ -76,7 +76,7 @@ struct TcBatch {
     uint32_t stop_stride;     // uint32 words between the textures' stop words
     uint32_t rows_per_tex;    // rows per texture (the re-rank maps a row to its texture's centroids)
     uint32_t n_textures;
-    // delta update (single texture only; null = off): every row whose assignment changes is appended as
+    // delta update (null = off): every row whose assignment changes is appended as
     // (row, previous centroid) so the update touches only those rows (launch_accumulate_delta)
     uint32_t* chg_rows;
     uint32_t* chg_old;
@@ -141,10 +141,16 @@ cudaError_t launch_acc_prepare(long long* acc, uint32_t K, size_t n, uint32_t fo
                                cudaStream_t s);
 cudaError_t launch_accumulate_delta(const float* feat, const uint32_t* assign, uint32_t K, int shift, long long* acc,
                                     const uint32_t* chg_rows, const uint32_t* chg_old, const uint32_t* dctl,
-                                    const uint32_t* flags, const uint32_t* stop, cudaStream_t s);
+                                    const uint32_t* flags, const uint32_t* stop, cudaStream_t s,
+                                    const AccBatch* batch = nullptr, uint32_t rows_per_tex = 0xffffffffu);
+// lock-step batch: one list / one mode for all textures (needs K * n_textures <= 4096, else every pass is full)
+bool delta_batch_supported(uint32_t K, uint32_t n_textures);
+cudaError_t launch_acc_prepare_batch(long long* acc, uint32_t K, size_t total_rows, uint32_t force_full, uint32_t* dctl,
+                                     const AccBatch& bt, cudaStream_t s);
 bool accumulate_batch_supported(size_t rows_per_tex, uint32_t K);
 cudaError_t launch_accumulate_batch(const float* feat, size_t rows_per_tex, const uint32_t* assign, uint32_t K, long long* acc,
-                                    const uint32_t* flags, const uint32_t* stop, const AccBatch& bt, cudaStream_t s);
+                                    const uint32_t* flags, const uint32_t* stop, const AccBatch& bt, cudaStream_t s,
+                                    const uint32_t* dctl = nullptr);
 cudaError_t launch_finalize_centroids_batch(const long long* acc, size_t acc_stride, uint32_t n_textures, uint32_t K,
                                             const double* inv_scales, float* cent, uint32_t* flags, uint32_t flags_stride,
                                             const uint32_t* stop, uint32_t stop_stride, cudaStream_t s);

@@ -188,9 +188,10 @@ constexpr int kDeltaRows = 2048;           // listed rows per chunk -> 2 * kDelt
 constexpr int kDeltaMaxK = 4096;
 
 // one CTA: decide this pass' mode, zero what has to be zeroed, hand the row count over and rearm the counter
+// (lock-step batch: n_textures accumulators acc_stride words apart share one list and one mode)
 __global__ void __launch_bounds__(1024) acc_prepare_kernel(long long* __restrict__ acc, uint32_t K, uint32_t full_above,
                                                            uint32_t force_full, uint32_t* __restrict__ dctl,
-                                                           const uint32_t* __restrict__ stop) {
+                                                           const uint32_t* __restrict__ stop, uint32_t n_textures, size_t acc_stride) {
     if (stop && __ldg(stop)) return;
     const uint32_t n_chg = dctl[0];
     const bool full = force_full || n_chg > full_above;
@@ -199,23 +200,27 @@ __global__ void __launch_bounds__(1024) acc_prepare_kernel(long long* __restrict
         dctl[32] = n_chg;
         dctl[33] = full ? 1u : 0u;
         dctl[0] = 0u;
-        acc[(size_t)K * 65] = 0;  // the changed word is per pass in both modes
     }
+    for (uint32_t t = threadIdx.x; t < n_textures; t += blockDim.x) acc[(size_t)t * acc_stride + (size_t)K * 65] = 0;  // changed word: per pass
     if (full)
-        for (size_t i = threadIdx.x; i < (size_t)K * 65; i += blockDim.x) acc[i] = 0;
+        for (uint32_t t = 0; t < n_textures; ++t)
+            for (size_t i = threadIdx.x; i < (size_t)K * 65; i += blockDim.x) acc[(size_t)t * acc_stride + i] = 0;
 }
 
 __global__ void __launch_bounds__(kDeltaThreads)
-accumulate_delta_kernel(const float* __restrict__ feat, const uint32_t* __restrict__ assign, uint32_t K, float scale,
+accumulate_delta_kernel(const float* __restrict__ feat, const uint32_t* __restrict__ assign, uint32_t K1, float scale1,
                         long long* __restrict__ acc, const uint32_t* __restrict__ chg_rows, const uint32_t* __restrict__ chg_old,
-                        const uint32_t* __restrict__ dctl, const uint32_t* __restrict__ flags, const uint32_t* __restrict__ stop) {
+                        const uint32_t* __restrict__ dctl, const uint32_t* __restrict__ flags, const uint32_t* __restrict__ stop,
+                        AccBatch bt, uint32_t rows_per_tex) {
+    // lock-step batch: rows are global (texture = row / rows_per_tex), the sort key is texture * K1 + centroid
+    const uint32_t K = K1 * bt.n_textures;
     // A chunk of listed rows becomes 2 signed entries per row (+x for the new centroid, -x for the old one); the
     // entries are counting-sorted by centroid in shared memory and every half-warp then walks a contiguous slice
     // of the SORTED entries, 8 independent row loads in flight at a time, emitting one 64-bit RED per column at
     // the end of each run of equal centroids.  Chunk size adapts to the list length: long lists use big chunks
     // (long runs, few REDs), short lists small ones (all SMs busy, short dependent chains).
     extern __shared__ uint32_t sm_acc[];
-    if (stop && __ldg(stop)) return;
+    if (bt.n_textures <= 1 && stop && __ldg(stop)) return;
     if (dctl[33] != 0u) return;  // this pass is a full recompute
     const uint32_t n_use = dctl[32];
     uint32_t chunk_rows = n_use / gridDim.x + 1;
@@ -227,8 +232,7 @@ accumulate_delta_kernel(const float* __restrict__ feat, const uint32_t* __restri
     uint16_t* cent_s = sorted + 2 * kDeltaRows;                                    // centroid of each sorted entry
     __shared__ uint32_t warp_tot[kDeltaThreads / 32 + 1];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    unsigned long long* sums = reinterpret_cast<unsigned long long*>(acc);
-    unsigned long long* counts = sums + (size_t)K * 64;
+    unsigned long long* sums_all = reinterpret_cast<unsigned long long*>(acc);
     const uint32_t n_chunks = (n_use + chunk_rows - 1) / chunk_rows;
     constexpr int kPer = kDeltaRows / kDeltaThreads;
     for (uint32_t chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x) {
@@ -245,10 +249,14 @@ accumulate_delta_kernel(const float* __restrict__ feat, const uint32_t* __restri
             if (i < len) {
                 const uint32_t row = chg_rows[first + i];
                 rows_s[i] = row;
-                a_old[k] = chg_old[first + i];
-                a_new[k] = assign[row];
-                if (a_new[k] < K) r_new[k] = atomicAdd(&hist[a_new[k]], 1u);
-                if (a_old[k] < K) r_old[k] = atomicAdd(&hist[a_old[k]], 1u);
+                const uint32_t kbase = (row / rows_per_tex) * K1;
+                const uint32_t co = chg_old[first + i], cn = assign[row];
+                if (co < K1 && cn < K1 && kbase < K) {
+                    a_old[k] = kbase + co;
+                    a_new[k] = kbase + cn;
+                    r_new[k] = atomicAdd(&hist[a_new[k]], 1u);
+                    r_old[k] = atomicAdd(&hist[a_old[k]], 1u);
+                }
             }
         }
         __syncthreads();
@@ -306,14 +314,18 @@ accumulate_delta_kernel(const float* __restrict__ feat, const uint32_t* __restri
         const float4* rows = reinterpret_cast<const float4*>(feat) + l16;
         long long s0 = 0, s1 = 0, s2 = 0, s3 = 0, cnt = 0;
         uint32_t cur = 0xffffffffu;
+        float scale = scale1;
         auto flush = [&]() {
             if (cur != 0xffffffffu) {
-                unsigned long long* dst = sums + (size_t)cur * 64 + 4 * l16;
+                const uint32_t tex = cur / K1, cc = cur - tex * K1;
+                unsigned long long* sums = sums_all + (size_t)tex * bt.acc_stride;
+                unsigned long long* counts = sums + (size_t)K1 * 64;
+                unsigned long long* dst = sums + (size_t)cc * 64 + 4 * l16;
                 atomicAdd(dst + 0, (unsigned long long)s0);
                 atomicAdd(dst + 1, (unsigned long long)s1);
                 atomicAdd(dst + 2, (unsigned long long)s2);
                 atomicAdd(dst + 3, (unsigned long long)s3);
-                if (l16 == 0 && cnt != 0) atomicAdd(counts + cur, (unsigned long long)cnt);
+                if (l16 == 0 && cnt != 0) atomicAdd(counts + cc, (unsigned long long)cnt);
             }
             s0 = s1 = s2 = s3 = cnt = 0;
         };
@@ -333,6 +345,7 @@ accumulate_delta_kernel(const float* __restrict__ feat, const uint32_t* __restri
                     if (c[q] != cur) {
                         flush();
                         cur = c[q];
+                        if (bt.scales) scale = __ldg(bt.scales + cur / K1);
                     }
                     const bool neg = (e[q] & 1u) != 0u;
                     const long long f0 = __float2ll_rn(__fmul_rn(v[q].x, scale)), f1 = __float2ll_rn(__fmul_rn(v[q].y, scale));
@@ -348,7 +361,12 @@ accumulate_delta_kernel(const float* __restrict__ feat, const uint32_t* __restri
         flush();
         __syncthreads();
     }
-    if (blockIdx.x == 0 && tid == 0 && flags) atomicAdd(sums + (size_t)K * 65, (unsigned long long)flags[0]);
+    if (blockIdx.x == 0 && flags) {
+        for (uint32_t tex = tid; tex < bt.n_textures; tex += kDeltaThreads) {
+            if (bt.n_textures > 1 && stop && __ldg(stop + (size_t)tex * bt.stop_stride)) continue;
+            atomicAdd(sums_all + (size_t)tex * bt.acc_stride + (size_t)K1 * 65, (unsigned long long)flags[(size_t)tex * bt.flags_stride]);
+        }
+    }
 }
 
 // blockIdx.y = texture of a lock-step batch (strides 0 and inv_scales null for a single texture)
@@ -570,15 +588,26 @@ cudaError_t launch_finalize_centroids(const long long* acc, uint32_t K, int shif
 cudaError_t launch_acc_prepare(long long* acc, uint32_t K, size_t n, uint32_t force_full, uint32_t* dctl, const uint32_t* stop,
                                cudaStream_t s) {
     if (K > (uint32_t)kDeltaMaxK) force_full = 1u;
-    acc_prepare_kernel<<<1, 1024, 0, s>>>(acc, K, (uint32_t)(n / 4), force_full, dctl, stop);
+    acc_prepare_kernel<<<1, 1024, 0, s>>>(acc, K, (uint32_t)(n / 4), force_full, dctl, stop, 1u, 0);
+    return cudaGetLastError();
+}
+
+bool delta_batch_supported(uint32_t K, uint32_t n_textures) { return (size_t)K * n_textures <= (size_t)kDeltaMaxK; }
+
+cudaError_t launch_acc_prepare_batch(long long* acc, uint32_t K, size_t total_rows, uint32_t force_full, uint32_t* dctl,
+                                     const AccBatch& bt, cudaStream_t s) {
+    if (!delta_batch_supported(K, bt.n_textures)) force_full = 1u;
+    acc_prepare_kernel<<<1, 1024, 0, s>>>(acc, K, (uint32_t)(total_rows / 4), force_full, dctl, nullptr, bt.n_textures, bt.acc_stride);
     return cudaGetLastError();
 }
 
 cudaError_t launch_accumulate_delta(const float* feat, const uint32_t* assign, uint32_t K, int shift, long long* acc,
                                     const uint32_t* chg_rows, const uint32_t* chg_old, const uint32_t* dctl,
-                                    const uint32_t* flags, const uint32_t* stop, cudaStream_t s) {
-    if (K > (uint32_t)kDeltaMaxK) return cudaSuccess;  // launch_acc_prepare forces full passes
-    const size_t smem = (size_t)K * 8 + (size_t)kDeltaRows * 4 + (size_t)kDeltaRows * 4 + (size_t)kDeltaRows * 4;
+                                    const uint32_t* flags, const uint32_t* stop, cudaStream_t s, const AccBatch* batch,
+                                    uint32_t rows_per_tex) {
+    const AccBatch bt = batch ? *batch : AccBatch{1u, 0, nullptr, 0u, 0u};
+    if ((size_t)K * bt.n_textures > (size_t)kDeltaMaxK) return cudaSuccess;  // launch_acc_prepare forces full passes
+    const size_t smem = (size_t)K * bt.n_textures * 8 + (size_t)kDeltaRows * 4 + (size_t)kDeltaRows * 4 + (size_t)kDeltaRows * 4;
     static size_t attr_smem = 0;
     if (smem > 48 * 1024 && smem > attr_smem) {
         cudaError_t e = cudaFuncSetAttribute(accumulate_delta_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -586,14 +615,15 @@ cudaError_t launch_accumulate_delta(const float* feat, const uint32_t* assign, u
         attr_smem = smem;
     }
     accumulate_delta_kernel<<<YUPVQ_NUM_SMS, kDeltaThreads, smem, s>>>(feat, assign, K, ldexpf(1.0f, shift), acc, chg_rows, chg_old,
-                                                                          dctl, flags, stop);
+                                                                      dctl, flags, stop, bt, batch ? rows_per_tex : 0xffffffffu);
     return cudaGetLastError();
 }
 
 bool accumulate_batch_supported(size_t rows_per_tex, uint32_t K) { return K <= (uint32_t)kAccMaxK && rows_per_tex >= (size_t)kAccChunk; }
 
 cudaError_t launch_accumulate_batch(const float* feat, size_t rows_per_tex, const uint32_t* assign, uint32_t K, long long* acc,
-                                    const uint32_t* flags, const uint32_t* stop, const AccBatch& bt, cudaStream_t s) {
+                                    const uint32_t* flags, const uint32_t* stop, const AccBatch& bt, cudaStream_t s,
+                                    const uint32_t* dctl) {
     if (!accumulate_batch_supported(rows_per_tex, K)) return cudaErrorInvalidValue;
     const size_t smem = (size_t)K * 8 + (size_t)kAccChunk * 2;
     if (smem > 48 * 1024) {
@@ -602,7 +632,7 @@ cudaError_t launch_accumulate_batch(const float* feat, size_t rows_per_tex, cons
     }
     size_t chunks = (rows_per_tex + kAccChunk - 1) / kAccChunk * bt.n_textures;
     size_t grid = chunks < (size_t)YUPVQ_NUM_SMS * 2 ? chunks : (size_t)YUPVQ_NUM_SMS * 2;
-    accumulate_sorted_kernel<<<(unsigned)grid, kAccThreads, smem, s>>>(feat, rows_per_tex, assign, K, 1.0f, acc, flags, stop, bt, nullptr);
+    accumulate_sorted_kernel<<<(unsigned)grid, kAccThreads, smem, s>>>(feat, rows_per_tex, assign, K, 1.0f, acc, flags, stop, bt, dctl);
     return cudaGetLastError();
 }
 
