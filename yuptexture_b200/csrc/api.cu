@@ -1534,22 +1534,26 @@ int yupvq_encode_bcn_batch_sharded(yupvq_ctx* ctx, const uint8_t* const* bc_bloc
         if ((int)(t % (size_t)R) != rank) continue;
         const void* bc_dev = nullptr;
         if (to_device(ctx, bc_blocks[t], n_total * bb, ctx->in_bytes, &bc_dev)) return 1;
+        // pixel planes only: the seeding reads nothing else, and the fp64 colour conversion (the expensive part of the
+        // decode) is then done for the K chosen blocks instead of the whole texture
         CK(ctx->planes.ensure(n_total * 16 * channels));
-        CK(ctx->feat.ensure(n_total * 256));
         LAUNCH(launch_decode_bcn(reinterpret_cast<const uint8_t*>(bc_dev), n_total, bc_format, channels,
-                                 ctx->planes.as<uint4>(), n_total, ctx->feat.as<float>(), nullptr, ctx->stream));
+                                 ctx->planes.as<uint4>(), n_total, nullptr, nullptr, ctx->stream));
         Blocks all;
         all.n = n_total;
         all.ch = channels;
         all.planes = ctx->planes.as<uint4>();
         all.stride = n_total;
-        all.feat = ctx->feat.as<float>();
+        all.feat = nullptr;
         size_t n_used;
         Draws dr = make_draws(n_total, K, 1.0f, cfg->seed ? cfg->seed + t : 0, &n_used);
         uint32_t rounds = 0;
         if (run_seeding(ctx, all, K, dr, false, stats ? &rounds : nullptr)) return 1;
         seed_rounds += rounds;
-        LAUNCH(launch_gather_rows_f32(all.feat, ctx->seed_idx.as<uint32_t>(), K, 64, cent_t(t), ctx->stream));
+        CK(ctx->cent_px.ensure((size_t)K * 16 * channels));
+        LAUNCH(launch_planes_to_blocks(all.planes, all.stride, ctx->seed_idx.as<uint32_t>(), K, channels, ctx->cent_px.as<uint8_t>(),
+                                       ctx->stream));
+        LAUNCH(launch_pixels_to_features(ctx->cent_px.as<uint8_t>(), K, channels, nullptr, 0, cent_t(t), ctx->stream));
     }
     if (ctx->comm && ctx->nccl.all_reduce_sum_i64(ctx->comm, ctx->bt_cent.as<long long>(), T * (size_t)K * 32, ctx->stream))
         return ctx->fail("ncclAllReduce(seed rows) failed");
