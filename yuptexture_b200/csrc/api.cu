@@ -9,6 +9,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <functional>
 #include <numeric>
 #include <random>
 #include <string>
@@ -53,7 +54,7 @@ struct yupvq_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
     std::string err;
-    cudaEvent_t ev[10] = {};
+    cudaEvent_t ev[12] = {};
     cudaEvent_t ev_user[2] = {};
     uint32_t launches = 0;
     uint32_t reseeds_sharded = 0;
@@ -597,8 +598,11 @@ void init_stats(yupvq_stats* s) {
 // Shared tail of the LDR paths: seeding + Lloyd + centroid -> pixel conversion on a device block set.
 // `all` is the full block set; when sampling is active the subset is gathered first.
 // Leaves K x 16*ch uint8 pixel centroids in ctx->cent_px.
+// `late_features` (optional): builds all.feat AFTER the seeding -- LDR seeding reads only the pixel planes, and it runs
+// faster while they are the only thing in L2 (the 256 MB feature write would evict them); used when no sampling is active.
 int build_codebook_device(yupvq_ctx* ctx, const Blocks& all, size_t n_total, const yupvq_config* cfg, bool hdr,
-                          yupvq_stats* stats, Timer& tm, int* t_seed0, int* t_seed1, int* t_lloyd1, int* t_fin1) {
+                          yupvq_stats* stats, Timer& tm, int* t_seed0, int* t_seed1, int* t_lloyd1, int* t_fin1,
+                          const std::function<int()>& late_features = nullptr) {
     const uint32_t K = cfg->codebook_size;
     size_t n_used = 0;
     Draws dr = make_draws(all.n, K, cfg->sample_ratio, cfg->seed, &n_used);
@@ -625,6 +629,7 @@ int build_codebook_device(yupvq_ctx* ctx, const Blocks& all, size_t n_total, con
     uint32_t rounds = 0;
     if (run_seeding(ctx, b, K, dr, hdr, stats ? &rounds : nullptr)) return 1;
     if (stats) stats->seed_rounds = rounds;
+    if (late_features && late_features()) return 1;
     // seeds -> Oklab centroids: PixelBlockToOklabBlock(pixelCentroids[i]) (:324-326) equals the
     // feature row of the chosen block (same pixels, same conversion).
     CK(ctx->cent.ensure((size_t)K * 256));
@@ -844,10 +849,27 @@ int yupvq_encode_bcn(yupvq_ctx* ctx, const uint8_t* bc_blocks, size_t n_blocks, 
     const int t1 = tm.mark();
     CK(ctx->planes.ensure(n_blocks * 16 * channels));
     CK(ctx->feat.ensure(n_blocks * 256));
-    LAUNCH(launch_decode_bcn(reinterpret_cast<const uint8_t*>(bc_dev), n_blocks, bc_format, channels,
-                             ctx->planes.as<uint4>(), n_blocks, ctx->feat.as<float>(), nullptr, ctx->stream));
-    if (cfg->metric == YUPVQ_METRIC_SAD)  // SAD path: the "features" are the pixel bytes themselves (sad.cu)
+    // Without sampling the decode is split: pixel planes now (all the seeding reads), Oklab features after the seeding.
+    static const bool no_split = getenv("YUPVQ_NO_SPLIT_DECODE") != nullptr;  // A/B timing
+    const bool sampling = cfg->sample_ratio < 1.0f && cfg->sample_ratio > 0.0f;
+    const bool split = !sampling && !no_split;
+    const bool sad = cfg->metric == YUPVQ_METRIC_SAD;
+    LAUNCH(launch_decode_bcn(reinterpret_cast<const uint8_t*>(bc_dev), n_blocks, bc_format, channels, ctx->planes.as<uint4>(), n_blocks,
+                             (split || sad) ? nullptr : ctx->feat.as<float>(), nullptr, ctx->stream));
+    if (sad && !split)  // SAD path: the "features" are the pixel bytes themselves (sad.cu)
         LAUNCH(launch_sad_expand(ctx->planes.as<uint4>(), n_blocks, n_blocks, channels, ctx->feat.as<float>(), ctx->stream));
+    float ms_late = 0.f;
+    int tl0 = -1, tl1e = -1;
+    std::function<int()> late;
+    if (split)
+        late = [&]() -> int {
+            tl0 = tm.mark();
+            if (sad) LAUNCH(launch_sad_expand(ctx->planes.as<uint4>(), n_blocks, n_blocks, channels, ctx->feat.as<float>(), ctx->stream));
+            else LAUNCH(launch_decode_bcn(reinterpret_cast<const uint8_t*>(bc_dev), n_blocks, bc_format, channels, nullptr, 0,
+                                          ctx->feat.as<float>(), nullptr, ctx->stream));
+            tl1e = tm.mark();
+            return 0;
+        };
     const int t2 = tm.mark();
     Blocks all;
     all.n = n_blocks;
@@ -856,7 +878,7 @@ int yupvq_encode_bcn(yupvq_ctx* ctx, const uint8_t* bc_blocks, size_t n_blocks, 
     all.stride = n_blocks;
     all.feat = ctx->feat.as<float>();
     int ts0, ts1, tl1, tf1;
-    if (build_codebook_device(ctx, all, n_blocks, cfg, false, stats, tm, &ts0, &ts1, &tl1, &tf1)) return 1;
+    if (build_codebook_device(ctx, all, n_blocks, cfg, false, stats, tm, &ts0, &ts1, &tl1, &tf1, late)) return 1;
     if (quantize_device(ctx, all, ctx->cent_px.p, cfg->codebook_size, false, cfg->assign_mode, cfg->metric)) return 1;
     const int t3 = tm.mark();
     if (from_device(ctx, out_pixel_centroids, ctx->cent_px.p, (size_t)cfg->codebook_size * 16 * channels)) return 1;
@@ -864,9 +886,10 @@ int yupvq_encode_bcn(yupvq_ctx* ctx, const uint8_t* bc_blocks, size_t n_blocks, 
     const int t4 = tm.mark();
     CK(cudaStreamSynchronize(ctx->stream));
     if (stats) {
+        if (tl0 >= 0) ms_late = tm.ms(tl0, tl1e);   // the feature half of the split decode ran inside the seeding window
         stats->ms_h2d = tm.ms(t0, t1);
-        stats->ms_decode = tm.ms(t1, t2);
-        stats->ms_seed = tm.ms(ts0, ts1);
+        stats->ms_decode = tm.ms(t1, t2) + ms_late;
+        stats->ms_seed = tm.ms(ts0, ts1) - ms_late;
         stats->ms_lloyd = tm.ms(ts1, tl1);
         stats->ms_finalize = tm.ms(tl1, tf1);
         stats->ms_quantize = tm.ms(tf1, t3);
