@@ -1434,27 +1434,35 @@ int yupvq_encode_bcn_sharded(yupvq_ctx* ctx, const uint8_t* bc_blocks, size_t n_
     const int t1 = tm.mark();
     // Whole texture decoded on every rank (8-16 MiB in): seeding is replicated and integer-exact, so
     // all ranks pick the same seeds with no communication.
+    // pixel planes of the whole texture (all the seeding reads); Oklab features only for the K seed blocks and,
+    // after the seeding, for this rank's shard
     CK(ctx->planes.ensure(n_total * 16 * channels));
-    CK(ctx->feat.ensure(n_total * 256));
+    CK(ctx->feat.ensure(std::max<size_t>(1, n_local) * 256));
     LAUNCH(launch_decode_bcn(reinterpret_cast<const uint8_t*>(bc_dev), n_total, bc_format, channels,
-                             ctx->planes.as<uint4>(), n_total, ctx->feat.as<float>(), nullptr, ctx->stream));
+                             ctx->planes.as<uint4>(), n_total, nullptr, nullptr, ctx->stream));
     const int t2 = tm.mark();
     Blocks all;
     all.n = n_total;
     all.ch = channels;
     all.planes = ctx->planes.as<uint4>();
     all.stride = n_total;
-    all.feat = ctx->feat.as<float>();
+    all.feat = nullptr;
     size_t n_used;
     Draws dr = make_draws(n_total, K, 1.0f, cfg->seed, &n_used);
     uint32_t rounds = 0;
     if (run_seeding(ctx, all, K, dr, false, stats ? &rounds : nullptr)) return 1;
     CK(ctx->cent.ensure((size_t)K * 256));
-    LAUNCH(launch_gather_rows_f32(all.feat, ctx->seed_idx.as<uint32_t>(), K, 64, ctx->cent.as<float>(), ctx->stream));
+    CK(ctx->cent_px.ensure((size_t)K * 16 * channels));
+    LAUNCH(launch_planes_to_blocks(all.planes, all.stride, ctx->seed_idx.as<uint32_t>(), K, channels, ctx->cent_px.as<uint8_t>(),
+                                   ctx->stream));
+    LAUNCH(launch_pixels_to_features(ctx->cent_px.as<uint8_t>(), K, channels, nullptr, 0, ctx->cent.as<float>(), ctx->stream));
+    if (n_local)
+        LAUNCH(launch_decode_bcn(reinterpret_cast<const uint8_t*>(bc_dev) + first_block * bc_block_bytes(bc_format), n_local, bc_format,
+                                 channels, nullptr, 0, ctx->feat.as<float>(), nullptr, ctx->stream));
     const int t3 = tm.mark();
     Blocks mine = all;
     mine.n = n_local;
-    mine.feat = all.feat + first_block * 64;
+    mine.feat = ctx->feat.as<float>();
     mine.planes = all.planes + first_block;  // stride unchanged
     if (run_lloyd(ctx, mine, n_total, first_block, K, cfg->max_iterations, 0u, cfg->assign_mode, ctx->cent.as<float>(), stats)) return 1;
     const int t4 = tm.mark();
