@@ -127,6 +127,28 @@ int main(int argc, char** argv) {
         const auto bc3 = comp.DecompressToBCn(s3, i3);
         CHECK(i3.compressionFlags == (COMPRESSION_FLAGS_VQ_BYPASSED | COMPRESSION_FLAGS_ZSTD_BYPASSED) && bc3.size() == 16 * 8);
 
+        // vq_Metric == SAD (the example's BC4 / BC5 / BC7 presets, example/example.cpp:260-277): all-integer path
+        {
+            CompressionParams ps = p;
+            ps.vq_Metric = DistanceMetric::SAD_SIMD;
+            CompressionConfig cs;
+            cs.maxIterations = 8;
+            cs.SetQuality(0.5f);
+            cs.metric = DistanceMetric::SAD_SIMD;
+            VQEncoder es(cs);
+            es.SetFormat(BCFormat::BC1);
+            es.SetSeed(42);
+            std::vector<std::vector<uint8_t>> cs_cent;
+            const VQCodebook cbs = es.BuildCodebook(blocks, CH, cs_cent, ps);
+            const auto is = es.QuantizeBlocks(blocks, CH, cs_cent, ps);
+            CHECK(cbs.entries.size() == 128 && cs_cent.size() == 128 && is.size() == blocks.size());
+            dump(out + "/sad_centroids.u8", flat(cs_cent));
+            dump(out + "/sad_indices.u32", is);
+            const auto ss = comp.Compress(img.data(), W, H, CH, ps);
+            TextureInfo isad;
+            CHECK(comp.DecompressToBCn(ss, isad).size() == bc.size() && isad.storedCodebookEntries == 128);
+        }
+
         // RGBA through BC3 and BC7
         const auto rgba = make_rgb(128, 128, 4);
         for (BCFormat f : {BCFormat::BC3, BCFormat::BC7}) {

@@ -47,3 +47,14 @@ def test_cpp_api_hdr_matches_oracle(dumped, oracle):
     # device pow() vs glibc pow() on arbitrary floats can differ in the last bit of a feature, which can
     # flip an exact near-tie: require >= 99.99 % agreement (north_star's bar), expect 100 %
     assert (idx == i_ref).mean() >= 0.9999
+
+
+def test_cpp_api_sad_metric_matches_oracle(dumped, oracle):
+    """DistanceMetric::SAD through VQEncoder::BuildCodebook / QuantizeBlocks: all-integer, so the C++ API's output
+    is bit-identical to the CPU restatement of the reference's SAD path for the same seed."""
+    px = np.fromfile(dumped / "ldr_blocks.u8", np.uint8).reshape(-1, 48)
+    cent = np.fromfile(dumped / "sad_centroids.u8", np.uint8).reshape(-1, 48)
+    idx = np.fromfile(dumped / "sad_indices.u32", np.uint32)
+    c_ref, _ = oracle.build_codebook(px, 3, 128, 8, 42, metric=oracle.METRIC_SAD)
+    assert np.array_equal(cent, c_ref)
+    assert np.array_equal(idx, oracle.quantize_blocks(px, 3, c_ref, metric=oracle.METRIC_SAD))

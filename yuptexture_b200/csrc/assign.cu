@@ -67,16 +67,17 @@ __global__ void __launch_bounds__(kTile) assign_exact_kernel(const float* __rest
 __global__ void exact_errors_kernel(const float* __restrict__ feat, size_t n, const float* __restrict__ cent,
                                     const uint32_t* __restrict__ assign, float* __restrict__ errors,
                                     const uint32_t* __restrict__ stop, const uint32_t* __restrict__ n_empty) {
+    // launched every pass but needed only when a cluster came out empty: a small grid keeps the early exit cheap
     if ((stop && __ldg(stop)) || (n_empty && __ldg(n_empty) == 0)) return;
-    const size_t blk = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (blk >= n) return;
-    const float4* x = reinterpret_cast<const float4*>(feat) + blk * 16;
-    const float4* c = reinterpret_cast<const float4*>(cent) + (size_t)assign[blk] * 16;
-    DistAcc acc;
-    acc.reset();
+    for (size_t blk = (size_t)blockIdx.x * blockDim.x + threadIdx.x; blk < n; blk += (size_t)gridDim.x * blockDim.x) {
+        const float4* x = reinterpret_cast<const float4*>(feat) + blk * 16;
+        const float4* c = reinterpret_cast<const float4*>(cent) + (size_t)assign[blk] * 16;
+        DistAcc acc;
+        acc.reset();
 #pragma unroll
-    for (int i = 0; i < 8; ++i) acc.step(x[2 * i], x[2 * i + 1], c[2 * i], c[2 * i + 1]);
-    errors[blk] = acc.finish();
+        for (int i = 0; i < 8; ++i) acc.step(x[2 * i], x[2 * i + 1], c[2 * i], c[2 * i + 1]);
+        errors[blk] = acc.finish();
+    }
 }
 
 }  // namespace
@@ -91,7 +92,9 @@ cudaError_t launch_assign_exact(const float* feat, size_t n, const float* cent, 
 cudaError_t launch_exact_errors(const float* feat, size_t n, const float* cent, const uint32_t* assign, float* errors,
                                 const uint32_t* stop, const uint32_t* n_empty, cudaStream_t s) {
     if (n == 0) return cudaSuccess;
-    exact_errors_kernel<<<(unsigned)((n + 127) / 128), 128, 0, s>>>(feat, n, cent, assign, errors, stop, n_empty);
+    size_t grid = (n + 127) / 128;
+    if (grid > (size_t)YUPVQ_NUM_SMS * 8) grid = (size_t)YUPVQ_NUM_SMS * 8;
+    exact_errors_kernel<<<(unsigned)grid, 128, 0, s>>>(feat, n, cent, assign, errors, stop, n_empty);
     return cudaGetLastError();
 }
 

@@ -311,7 +311,14 @@ __device__ __forceinline__ T warp_incl_scan(T v, int lane) {
 
 // HDR == false: CH uint4 planes per block, SAD^2, uint64 sums.  HDR == true: 64-float rows, weighted L2, double sums.
 // Exchange words in st.partial: [0, 2W) warp words (LDR uses the first W), then the pick word.
-template <bool HDR, int CH, bool MDREG>
+// TRI (LDR, MDREG): triangle-inequality skip.  SAD is a metric, so with s_j the seed nearest to block j and
+// d_j = SAD(j, s_j):  SAD(new, s_j) >= 2 d_j  =>  SAD(j, new) >= d_j  =>  min(d^2, minDistSq[j]) is unchanged and the
+// block's pixels need not be read at all.  Every CTA keeps the pixel blocks of all seeds chosen so far in shared
+// memory and computes the K' <= 1023 distances new-seed -> earlier-seed at the top of a round (one per thread); a
+// lane keeps (min SAD, nearest seed ordinal) packed in one register per block instead of the squared float, which
+// is recomputed on demand (float(d) * float(d) is monotone in d, so the minimum of the rounded squares is the rounded
+// square of the minimum).  Values, sums and picks are bit-identical to the plain update.
+template <bool HDR, int CH, bool MDREG, bool TRI = false>
 __global__ void __launch_bounds__(kPThreads, 1)
 seed_persistent_kernel(SeedState st, const uint4* __restrict__ planes, size_t stride, const float* __restrict__ feat, size_t n,
                        size_t bpw, int cseg, uint32_t K) {
@@ -345,6 +352,11 @@ seed_persistent_kernel(SeedState st, const uint4* __restrict__ planes, size_t st
     float md[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) md[i] = FLT_MAX;  // seed_init_kernel wrote the same value to min_dist
+    uint32_t msnr[8];                             // TRI: [nearest seed ordinal : 16 | min SAD : 16], 0xffff = none yet
+#pragma unroll
+    for (int i = 0; i < 8; ++i) msnr[i] = 0xffffu;
+    uint4* const seeds_s = s_cache + (size_t)cseg * kPWarps * CH * 32;          // TRI: [K][CH] pixel blocks of the seeds
+    uint32_t* const tri_s = reinterpret_cast<uint32_t*>(seeds_s + (size_t)K * CH);  // TRI: SAD(new seed, seed q)
     // per-lane constants of the update loop
     unsigned int vmask = 0;
 #pragma unroll
@@ -397,7 +409,65 @@ seed_persistent_kernel(SeedState st, const uint4* __restrict__ planes, size_t st
                 return __fmul_rn(d, d);
             }
         };
-        if (MDREG && !HDR) {
+        if (TRI && MDREG && !HDR) {
+            const uint32_t o = round - 1;             // ordinal of the seed applied in this round
+            if (tid < (int)o) {
+                unsigned int sad = 0;
+#pragma unroll
+                for (int q = 0; q < CH; ++q) {
+                    const uint4 v = seeds_s[(size_t)tid * CH + q];
+                    sad = __vsadu4(v.x, sp[q].x) + sad;
+                    sad = __vsadu4(v.y, sp[q].y) + sad;
+                    sad = __vsadu4(v.z, sp[q].z) + sad;
+                    sad = __vsadu4(v.w, sp[q].w) + sad;
+                }
+                tri_s[tid] = sad;
+            }
+            if (tid == 0) {                                          // read from the next round on (barriers in between)
+#pragma unroll
+                for (int q = 0; q < CH; ++q) seeds_s[(size_t)o * CH + q] = sp[q];
+            }
+            __syncthreads();
+            unsigned int loc32 = 0;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                if ((vmask >> i) & 1u) {
+                    uint32_t ms = msnr[i] & 0xffffu;
+                    const bool skip = ms != 0xffffu && tri_s[msnr[i] >> 16] >= 2u * ms;
+                    if (!skip) {
+                        unsigned int sad = 0;
+                        if (i < cseg) {
+#pragma unroll
+                            for (int q = 0; q < CH; ++q) {
+                                const uint4 v = sc[(i * CH + q) * 32];
+                                sad = __vsadu4(v.x, sp[q].x) + sad;
+                                sad = __vsadu4(v.y, sp[q].y) + sad;
+                                sad = __vsadu4(v.z, sp[q].z) + sad;
+                                sad = __vsadu4(v.w, sp[q].w) + sad;
+                            }
+                        } else {
+#pragma unroll
+                            for (int q = 0; q < CH; ++q) {
+                                const uint4 v = ldg_nc_v4(gp[q] + i * 32);
+                                sad = __vsadu4(v.x, sp[q].x) + sad;
+                                sad = __vsadu4(v.y, sp[q].y) + sad;
+                                sad = __vsadu4(v.z, sp[q].z) + sad;
+                                sad = __vsadu4(v.w, sp[q].w) + sad;
+                            }
+                        }
+                        if (sad < ms) {                                        // std::min(d * d, minDistSq[j]) moved
+                            ms = sad;
+                            msnr[i] = sad | (o << 16);
+                            const float d = (float)sad;
+                            __stcg(mdp + i * 32, __fmul_rn(d, d));
+                        }
+                    }
+                    const float dm = (float)ms;
+                    loc32 += __float2uint_rn(__fmul_rn(dm, dm));
+                }
+            }
+            local = (ACC)loc32;
+        } else if (MDREG && !HDR) {
             // minimum distances live in registers (nseg <= 8): no loads that could alias the stores, so the
             // pixel loads of all segments are free to be issued early; a value is stored (for the leader's
             // level-2 search) only when it changed.  Addresses and validity are precomputed: about 25
@@ -701,6 +771,11 @@ cudaError_t launch_seed_persistent(const SeedState& st, const uint4* planes, siz
     bpw = (bpw + 31) / 32 * 32;
     if (!hdr && bpw * kPWarps >= ((size_t)1 << 19)) return cudaErrorNotSupported;  // CTA partial must fit 48 bits
     const bool mdreg = bpw / 32 <= 8;
+    // Measured on config 2 (B200): the skip makes the seeding SLOWER (4.41 ms against 3.84 ms) -- the extra barrier and
+    // table per round cost more than the skipped loads save, because a warp only saves a load when all 32 of its
+    // (noisy, 48-dimensional) blocks pass the bound.  Kept opt-in for smoother inputs; results are identical either way.
+    static const bool want_tri = getenv("YUPVQ_SEED_TRI") != nullptr;
+    const bool tri = !hdr && mdreg && K <= (uint32_t)kPThreads && want_tri;
     const void* fn = nullptr;
     if (hdr) fn = mdreg ? (const void*)seed_persistent_kernel<true, 1, true> : (const void*)seed_persistent_kernel<true, 1, false>;
     else if (ch == 1) fn = mdreg ? (const void*)seed_persistent_kernel<false, 1, true> : (const void*)seed_persistent_kernel<false, 1, false>;
@@ -708,18 +783,25 @@ cudaError_t launch_seed_persistent(const SeedState& st, const uint4* planes, siz
     else if (ch == 3) fn = mdreg ? (const void*)seed_persistent_kernel<false, 3, true> : (const void*)seed_persistent_kernel<false, 3, false>;
     else if (ch == 4) fn = mdreg ? (const void*)seed_persistent_kernel<false, 4, true> : (const void*)seed_persistent_kernel<false, 4, false>;
     else return cudaErrorInvalidValue;
-    // shared-memory resident segments per warp: as many as fit in ~200 KB
+    if (tri) {
+        if (ch == 1) fn = (const void*)seed_persistent_kernel<false, 1, true, true>;
+        else if (ch == 2) fn = (const void*)seed_persistent_kernel<false, 2, true, true>;
+        else if (ch == 3) fn = (const void*)seed_persistent_kernel<false, 3, true, true>;
+        else fn = (const void*)seed_persistent_kernel<false, 4, true, true>;
+    }
+    // shared-memory resident segments per warp: as many as fit in ~200 KB (after the seed table of the TRI variant)
     int cseg = 0;
     size_t smem = 0;
     if (!hdr) {
         const size_t seg_bytes = (size_t)kPWarps * 32 * ch * 16;
-        cseg = (int)((200u * 1024u) / seg_bytes);
+        const size_t tri_bytes = tri ? (size_t)K * ch * 16 + (size_t)K * 4 : 0;
+        cseg = (int)((200u * 1024u - tri_bytes) / seg_bytes);
         if ((size_t)cseg > bpw / 32) cseg = (int)(bpw / 32);
         static const char* no_cache = getenv("YUPVQ_SEED_NO_SMEM");
         if (no_cache) cseg = 0;
-        smem = (size_t)cseg * seg_bytes;
-        static bool attr[12] = {};  // dynamic + static shared memory may exceed the 48 KB default: always opt in
-        const int ai = ch * 2 + (mdreg ? 1 : 0);
+        smem = (size_t)cseg * seg_bytes + tri_bytes;
+        static bool attr[24] = {};  // dynamic + static shared memory may exceed the 48 KB default: always opt in
+        const int ai = ch * 2 + (mdreg ? 1 : 0) + (tri ? 12 : 0);
         if (smem > 0 && !attr[ai]) {
             cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(200u * 1024u));
             if (e != cudaSuccess) return e;
