@@ -73,6 +73,7 @@ struct yupvq_ctx {
     // lock-step batch (yupvq_encode_bcn_batch_sharded): per-texture slices of one buffer each
     DevBuf bt_feat, bt_tca, bt_xnorm, bt_tcsmall, bt_assign, bt_errors, bt_cent, bt_acc, bt_misc, bt_centpx, bt_cent0, bt_acc_local;
     const float* tc_feat = nullptr;                    // block set the A' buffer was built from
+    int tc_rgb = 0;                                    // 1: channels are 1 or 3 (alpha feature constant): 48-column tensor operands
     size_t tc_n = 0;
     uint64_t rerank_pairs = 0;
     uint32_t* h_small = nullptr;                       // pinned: flags + status readback
@@ -343,7 +344,7 @@ int tc_prepare_blocks(yupvq_ctx* ctx, const float* feat, size_t n) {
     LAUNCH(launch_tc_mean(feat, n, reinterpret_cast<double*>(sm + TC_SUMS), reinterpret_cast<float*>(sm + TC_MU), ctx->stream));
     ++ctx->launches;  // launch_tc_mean is two kernels
     LAUNCH(launch_tc_prep_blocks(feat, n, reinterpret_cast<const float*>(sm + TC_MU), ctx->tc_a.as<float>(),
-                                 ctx->tc_xnorm.as<float>(), ctx->stream));
+                                 ctx->tc_xnorm.as<float>(), ctx->stream, ctx->tc_rgb));
     ctx->tc_feat = feat;
     ctx->tc_n = n;
     return 0;
@@ -362,7 +363,7 @@ struct TcView {
 int tc_prepare_view(yupvq_ctx* ctx, const float* feat, size_t n, const TcView& v) {
     LAUNCH(launch_tc_mean(feat, n, reinterpret_cast<double*>(v.small + TC_SUMS), reinterpret_cast<float*>(v.small + TC_MU), ctx->stream));
     ++ctx->launches;
-    LAUNCH(launch_tc_prep_blocks(feat, n, reinterpret_cast<const float*>(v.small + TC_MU), v.a, v.xnorm, ctx->stream));
+    LAUNCH(launch_tc_prep_blocks(feat, n, reinterpret_cast<const float*>(v.small + TC_MU), v.a, v.xnorm, ctx->stream, ctx->tc_rgb));
     return 0;
 }
 
@@ -384,13 +385,15 @@ int assign_blocks(yupvq_ctx* ctx, const float* feat, size_t n, const float* cent
     float* tc_a = view ? view->a : ctx->tc_a.as<float>();
     float* tc_xnorm = view ? view->xnorm : ctx->tc_xnorm.as<float>();
     LAUNCH(launch_tc_prep_centroids(cent, K, reinterpret_cast<const float*>(sm + TC_MU), ctx->tc_b.as<float>(),
-                                    ctx->tc_bx.as<float>(), reinterpret_cast<float*>(sm + TC_CMAX), ctx->stream));
+                                    ctx->tc_bx.as<float>(), reinterpret_cast<float*>(sm + TC_CMAX), ctx->stream, ctx->tc_rgb));
+    TcBatch tcb = delta ? *delta : tc_single();
+    tcb.rgb = (uint32_t)ctx->tc_rgb;
     uint32_t* small = ctx->small.as<uint32_t>();
     if (errors) {
         // errors[] wanted for every block: dense candidate lists + dense re-rank
         LAUNCH(launch_assign_tc(tc_a, tc_xnorm, n, ctx->tc_b.as<float>(), ctx->tc_bx.as<float>(),
                                 K, reinterpret_cast<const float*>(sm + TC_CMAX), ctx->tc_cand.as<uint4>(), nullptr, nullptr, nullptr,
-                                nullptr, stop, ctx->stream));
+                                nullptr, stop, ctx->stream, &tcb));
         LAUNCH(launch_rerank(feat, n, cent, K, ctx->tc_cand.as<uint4>(), assign, errors, flags, small + F_PAIRS, stop, ctx->stream));
     } else {
         // the front-end finishes single-candidate blocks itself; the exact re-rank sees only the ambiguous ones
@@ -400,10 +403,10 @@ int assign_blocks(yupvq_ctx* ctx, const float* feat, size_t n, const float* cent
         if (prof) cudaEventRecord(ctx->pev[ctx->pev_used++], ctx->stream);
         LAUNCH(launch_assign_tc(tc_a, tc_xnorm, n, ctx->tc_b.as<float>(), ctx->tc_bx.as<float>(),
                                 K, reinterpret_cast<const float*>(sm + TC_CMAX), ctx->tc_cand.as<uint4>(), assign, flags,
-                                ctx->tc_amb.as<uint32_t>(), small + F_AMB, stop, ctx->stream, delta));
+                                ctx->tc_amb.as<uint32_t>(), small + F_AMB, stop, ctx->stream, &tcb));
         if (prof) cudaEventRecord(ctx->pev[ctx->pev_used++], ctx->stream);
         LAUNCH(launch_rerank_sparse(feat, cent, K, ctx->tc_cand.as<uint4>(), ctx->tc_amb.as<uint32_t>(), small + F_AMB,
-                                    small + F_AMB + 1, assign, flags, small + F_PAIRS, ctx->stream, delta));
+                                    small + F_AMB + 1, assign, flags, small + F_PAIRS, ctx->stream, &tcb));
     }
     return 0;
 }
@@ -683,6 +686,13 @@ int check_cfg(yupvq_ctx* ctx, const yupvq_config* cfg, size_t n, int ch) {
     return 0;
 }
 
+// Features built by our own decode / conversion kernels carry alpha == 1.0f exactly when the input has 1 or 3 channels
+// (convert.cu block_features / float path), so the 16 alpha columns vanish after centring: 48-column tensor operands.
+int rgb_layout(int channels) {
+    static const bool off = getenv("YUPVQ_NO_RGB48") != nullptr;  // A/B timing and tests
+    return (!off && (channels == 1 || channels == 3)) ? 1 : 0;
+}
+
 struct Scope {  // selects the context's device for the duration of a call
     int prev = 0;
     explicit Scope(int dev) {
@@ -840,6 +850,7 @@ int yupvq_encode_bcn(yupvq_ctx* ctx, const uint8_t* bc_blocks, size_t n_blocks, 
     init_stats(stats);
     ctx->launches = 0;
     ctx->tc_feat = nullptr;
+    ctx->tc_rgb = rgb_layout(channels);
     if (check_cfg(ctx, cfg, n_blocks, channels)) return 1;
     if (!bc_supported(bc_format)) return ctx->fail("BC format %d is not supported on the LDR VQ path", bc_format);
     Timer tm(ctx);
@@ -908,6 +919,7 @@ int yupvq_encode_hdr(yupvq_ctx* ctx, const float* image, uint32_t width, uint32_
     init_stats(stats);
     ctx->launches = 0;
     ctx->tc_feat = nullptr;
+    ctx->tc_rgb = rgb_layout(channels);
     const size_t n_blocks = (size_t)((width + 3) / 4) * ((height + 3) / 4);
     if (check_cfg(ctx, cfg, n_blocks, channels)) return 1;
     Timer tm(ctx);
@@ -983,6 +995,7 @@ int yupvq_build_codebook(yupvq_ctx* ctx, const uint8_t* pixel_blocks, size_t n_b
     init_stats(stats);
     ctx->launches = 0;
     ctx->tc_feat = nullptr;
+    ctx->tc_rgb = rgb_layout(channels);
     if (check_cfg(ctx, cfg, n_blocks, channels)) return 1;
     Timer tm(ctx);
     const int t0 = tm.mark();
@@ -1024,6 +1037,7 @@ int yupvq_quantize_blocks(yupvq_ctx* ctx, const uint8_t* pixel_blocks, size_t n_
     init_stats(stats);
     ctx->launches = 0;
     ctx->tc_feat = nullptr;
+    ctx->tc_rgb = rgb_layout(channels);
     if (n_blocks == 0) return 0;  // reference returns {} (:449)
     if (channels < 1 || channels > 4) return ctx->fail("channels must be 1..4");
     if (metric != YUPVQ_METRIC_OKLAB && metric != YUPVQ_METRIC_SAD) return ctx->fail("unknown metric %d", metric);
@@ -1069,6 +1083,7 @@ int yupvq_build_codebook_hdr(yupvq_ctx* ctx, const float* float_blocks, size_t n
     init_stats(stats);
     ctx->launches = 0;
     ctx->tc_feat = nullptr;
+    ctx->tc_rgb = rgb_layout(channels);
     if (n_blocks == 0) return 0;  // reference returns {} (:517)
     if (check_cfg(ctx, cfg, n_blocks, channels)) return 1;
     Timer tm(ctx);
@@ -1106,6 +1121,7 @@ int yupvq_quantize_blocks_hdr(yupvq_ctx* ctx, const float* float_blocks, size_t 
     init_stats(stats);
     ctx->launches = 0;
     ctx->tc_feat = nullptr;
+    ctx->tc_rgb = rgb_layout(channels);
     if (n_blocks == 0) return 0;  // :631
     if (channels < 1 || channels > 4) return ctx->fail("channels must be 1..4");
     Timer tm(ctx);
@@ -1233,6 +1249,7 @@ int yupvq_assign(yupvq_ctx* ctx, const float* features, size_t n_blocks, const f
     init_stats(stats);
     ctx->launches = 0;
     ctx->tc_feat = nullptr;
+    ctx->tc_rgb = 0;
     if (n_blocks == 0) return 0;
     const void* f_dev = nullptr;
     const void* c_dev = nullptr;
@@ -1268,6 +1285,7 @@ int yupvq_seed_ldr(yupvq_ctx* ctx, const uint8_t* pixel_blocks, size_t n_blocks,
     Scope scope(ctx->device);
     ctx->launches = 0;
     ctx->tc_feat = nullptr;
+    ctx->tc_rgb = 0;
     if (channels < 1 || channels > 4) return ctx->fail("channels must be 1..4");
     if (n_blocks == 0 || codebook_size == 0) return ctx->fail("empty input");
     const void* px_dev = nullptr;
@@ -1296,6 +1314,7 @@ int yupvq_seed_hdr(yupvq_ctx* ctx, const float* features, size_t n_blocks, uint3
     Scope scope(ctx->device);
     ctx->launches = 0;
     ctx->tc_feat = nullptr;
+    ctx->tc_rgb = 0;
     if (n_blocks == 0 || codebook_size == 0) return ctx->fail("empty input");
     const void* f_dev = nullptr;
     if (to_device(ctx, features, n_blocks * 256, ctx->feat, &f_dev)) return 1;
@@ -1319,6 +1338,7 @@ int yupvq_update_centroids(yupvq_ctx* ctx, const float* features, size_t n_block
     Scope scope(ctx->device);
     ctx->launches = 0;
     ctx->tc_feat = nullptr;
+    ctx->tc_rgb = 0;
     const uint32_t K = codebook_size;
     if (n_blocks == 0 || K == 0) return ctx->fail("empty input");
     const void* f_dev = nullptr;
@@ -1372,6 +1392,7 @@ int yupvq_gather_codebook(yupvq_ctx* ctx, const uint8_t* codebook, uint32_t n_en
     Scope scope(ctx->device);
     ctx->launches = 0;
     ctx->tc_feat = nullptr;
+    ctx->tc_rgb = 0;
     if (block_size != 8 && block_size != 16) return ctx->fail("block_size must be 8 or 16");
     if (n_blocks == 0) return 0;
     const void* cb_dev = nullptr;
@@ -1421,6 +1442,7 @@ int yupvq_encode_bcn_sharded(yupvq_ctx* ctx, const uint8_t* bc_blocks, size_t n_
     init_stats(stats);
     ctx->launches = 0;
     ctx->tc_feat = nullptr;
+    ctx->tc_rgb = rgb_layout(channels);
     if (check_cfg(ctx, cfg, n_total, channels)) return 1;
     if (!bc_supported(bc_format)) return ctx->fail("BC format %d is not supported on the LDR VQ path", bc_format);
     if (first_block + n_local > n_total) return ctx->fail("shard [%zu, %zu) exceeds %zu blocks", first_block, first_block + n_local, n_total);
@@ -1514,6 +1536,7 @@ int yupvq_encode_bcn_batch_sharded(yupvq_ctx* ctx, const uint8_t* const* bc_bloc
     init_stats(stats);
     ctx->launches = 0;
     ctx->tc_feat = nullptr;
+    ctx->tc_rgb = rgb_layout(channels);
     if (check_cfg(ctx, cfg, n_total, channels)) return 1;
     if (!bc_blocks || n_textures == 0) return ctx->fail("no textures");
     if (n_textures > 4096) return ctx->fail("too many textures in one batch (%zu > 4096)", n_textures);
@@ -1794,8 +1817,9 @@ int yupvq_encode_bcn_batch_sharded(yupvq_ctx* ctx, const uint8_t* const* bc_bloc
             b.chg_count = nullptr;
         }
         if (!stop) b.stop_stride = 0;
+        b.rgb = (uint32_t)ctx->tc_rgb;
         LAUNCH(launch_tc_prep_centroids_batch(cent_all, K, (uint32_t)T, sm, TC_SMALL_BYTES, TC_MU, TC_CMAX, ctx->tc_b.as<float>(),
-                                              ctx->tc_bx.as<float>(), ctx->stream));
+                                              ctx->tc_bx.as<float>(), ctx->stream, ctx->tc_rgb));
         const bool prof = ctx->profile && ctx->pev_used + 2 <= ctx->pev.size();
         if (prof) cudaEventRecord(ctx->pev[ctx->pev_used++], ctx->stream);
         LAUNCH(launch_assign_tc(ctx->bt_tca.as<float>(), ctx->bt_xnorm.as<float>(), T * n_local, ctx->tc_b.as<float>(), ctx->tc_bx.as<float>(),

@@ -341,15 +341,29 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                     const uint32_t d_tmem = tmem_base + acc * BN;
                     // xl.ch + xh.cl + xh.ch: twelve K = 16 steps over the two 128-byte halves of each operand row
                     // (small terms first), then the folded norm
+                    if (bt.rgb) {
+                        // 48 colour columns: xl.ch and xh.cl over three K-steps each, xh.ch over four -- the fourth holds
+                        // the ones / folded-norm columns
 #pragma unroll
-                    for (int k = 0; k < 12; ++k) {
-                        const int seg = k >> 2;
-                        const uint32_t koff = (seg == 0 ? A_HALF_BYTES : 0u) + (uint32_t)(k & 3) * 32u;
-                        const uint32_t boff = (seg == 1 ? B_HALF_BYTES : 0u) + (uint32_t)(k & 3) * 32u;
-                        tc_mma_bf16(d_tmem, make_desc(a_addr + koff, 1024, 2), make_desc(b_addr + boff, 1024, 2), kIdesc,
-                                    k > 0 ? 1u : 0u);
+                        for (int k = 0; k < 10; ++k) {
+                            const int seg = k < 3 ? 0 : (k < 6 ? 1 : 2);
+                            const uint32_t kk = (uint32_t)(k < 3 ? k : (k < 6 ? k - 3 : k - 6)) * 32u;
+                            const uint32_t koff = (seg == 0 ? A_HALF_BYTES : 0u) + kk;
+                            const uint32_t boff = (seg == 1 ? B_HALF_BYTES : 0u) + kk;
+                            tc_mma_bf16(d_tmem, make_desc(a_addr + koff, 1024, 2), make_desc(b_addr + boff, 1024, 2), kIdesc,
+                                        k > 0 ? 1u : 0u);
+                        }
+                    } else {
+#pragma unroll
+                        for (int k = 0; k < 12; ++k) {
+                            const int seg = k >> 2;
+                            const uint32_t koff = (seg == 0 ? A_HALF_BYTES : 0u) + (uint32_t)(k & 3) * 32u;
+                            const uint32_t boff = (seg == 1 ? B_HALF_BYTES : 0u) + (uint32_t)(k & 3) * 32u;
+                            tc_mma_bf16(d_tmem, make_desc(a_addr + koff, 1024, 2), make_desc(b_addr + boff, 1024, 2), kIdesc,
+                                        k > 0 ? 1u : 0u);
+                        }
+                        tc_mma_bf16(d_tmem, ones_desc, make_desc(b_addr + 2 * B_HALF_BYTES, 256, 6), kIdesc, 1u);
                     }
-                    tc_mma_bf16(d_tmem, ones_desc, make_desc(b_addr + 2 * B_HALF_BYTES, 256, 6), kIdesc, 1u);
                     tc_commit(bar(BAR_TFULL + acc));
                     if (!resident_b || last_of_tex) tc_commit(bar(BAR_EMPTY_B + sb));
                 }
@@ -595,8 +609,9 @@ __global__ void mean_kernel(const double* __restrict__ sums, double inv_n, float
 }
 
 // A' row (256 B) = [bf16 hi of w (x - mu) x 64 | bf16 lo x 64],  xnorm = |w (x - mu)| (rounded up a little)
+// rgb: row = [hi: 16 x (L a b) | 1 1 1 0..0 (16) || lo: 16 x (L a b) | 0..0 (16)]  (the alpha column is exactly zero)
 __global__ void __launch_bounds__(256) prep_blocks_kernel(const float* __restrict__ feat, size_t n, const float* __restrict__ mu,
-                                                          float* __restrict__ a_prime, float* __restrict__ xnorm) {
+                                                          float* __restrict__ a_prime, float* __restrict__ xnorm, int rgb) {
     const size_t row = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 4;   // 16 threads per row
     const int q = threadIdx.x & 15;                                            // pixel == float4 index
     float ss = 0.0f;
@@ -614,9 +629,17 @@ __global__ void __launch_bounds__(256) prep_blocks_kernel(const float* __restric
         split_bf16(o.y, h1, l1);
         split_bf16(o.z, h2, l2);
         split_bf16(o.w, h3, l3);
-        uint2* dst = reinterpret_cast<uint2*>(a_prime) + row * 32 + q;          // 32 x 8 B per row
-        dst[0] = make_uint2((uint32_t)h0 | ((uint32_t)h1 << 16), (uint32_t)h2 | ((uint32_t)h3 << 16));
-        dst[16] = make_uint2((uint32_t)l0 | ((uint32_t)l1 << 16), (uint32_t)l2 | ((uint32_t)l3 << 16));
+        if (rgb) {
+            uint16_t* r16 = reinterpret_cast<uint16_t*>(a_prime) + row * 128;   // 128 bf16 per row
+            r16[3 * q] = h0; r16[3 * q + 1] = h1; r16[3 * q + 2] = h2;
+            r16[64 + 3 * q] = l0; r16[64 + 3 * q + 1] = l1; r16[64 + 3 * q + 2] = l2;
+            r16[48 + q] = q < 3 ? (uint16_t)0x3f80u : (uint16_t)0u;             // bf16 1.0 multiplies the folded norm terms
+            r16[112 + q] = 0;
+        } else {
+            uint2* dst = reinterpret_cast<uint2*>(a_prime) + row * 32 + q;      // 32 x 8 B per row
+            dst[0] = make_uint2((uint32_t)h0 | ((uint32_t)h1 << 16), (uint32_t)h2 | ((uint32_t)h3 << 16));
+            dst[16] = make_uint2((uint32_t)l0 | ((uint32_t)l1 << 16), (uint32_t)l2 | ((uint32_t)l3 << 16));
+        }
     }
 #pragma unroll
     for (int o = 8; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
@@ -628,7 +651,7 @@ __global__ void __launch_bounds__(256) prep_blocks_kernel(const float* __restric
 // cmax = max_c |c'| (rounded up).
 __global__ void __launch_bounds__(64) prep_centroids_kernel(const float* __restrict__ cent, uint32_t K, const float* __restrict__ mu,
                                                             float* __restrict__ b_main, float* __restrict__ b_ext,
-                                                            unsigned int* __restrict__ cmax_bits, size_t small_stride) {
+                                                            unsigned int* __restrict__ cmax_bits, size_t small_stride, int rgb) {
     // texture blockIdx.y of a lock-step batch: operands stacked gridDim.x rows apart, mu / cmax small_stride bytes apart
     cent += (size_t)blockIdx.y * K * 64;
     b_main += (size_t)blockIdx.y * gridDim.x * 64;
@@ -646,8 +669,19 @@ __global__ void __launch_bounds__(64) prep_centroids_kernel(const float* __restr
     uint16_t hi16, lo16;
     split_bf16(v, hi16, lo16);
     uint16_t* brow = reinterpret_cast<uint16_t*>(b_main) + (size_t)c * 128;
-    brow[i] = hi16;
-    brow[64 + i] = lo16;
+    if (rgb) {
+        // colour columns packed first; the alpha column is dropped from the product (x' is exactly 0 there) but stays in
+        // the norm below, which is the true |c'|^2
+        if ((i & 3) != 3) {
+            brow[3 * (i >> 2) + (i & 3)] = hi16;
+            brow[64 + 3 * (i >> 2) + (i & 3)] = lo16;
+        } else {
+            brow[112 + (i >> 2)] = 0;
+        }
+    } else {
+        brow[i] = hi16;
+        brow[64 + i] = lo16;
+    }
     __shared__ double red[2];
     double ss = (double)v * (double)v;
 #pragma unroll
@@ -666,6 +700,7 @@ __global__ void __launch_bounds__(64) prep_centroids_kernel(const float* __restr
             e = -1.0e30f;
         }
         reinterpret_cast<uint16_t*>(b_ext)[(size_t)c * 16 + i] = __bfloat16_as_ushort(__float2bfloat16_rn(e));
+        if (rgb) brow[48 + i] = __bfloat16_as_ushort(__float2bfloat16_rn(e));   // folded norm inside the hi half
     }
     if (i == 0 && c < K) {
         const float nrm = (float)sqrt(red[0] + red[1]) * 1.0001f;
@@ -980,27 +1015,27 @@ cudaError_t launch_tc_mean(const float* feat, size_t n, double* sums64, float* m
     return cudaGetLastError();
 }
 
-cudaError_t launch_tc_prep_blocks(const float* feat, size_t n, const float* mu, float* a_prime, float* xnorm, cudaStream_t s) {
+cudaError_t launch_tc_prep_blocks(const float* feat, size_t n, const float* mu, float* a_prime, float* xnorm, cudaStream_t s, int rgb) {
     if (n == 0) return cudaSuccess;
-    prep_blocks_kernel<<<(unsigned)((n * 16 + 255) / 256), 256, 0, s>>>(feat, n, mu, a_prime, xnorm);
+    prep_blocks_kernel<<<(unsigned)((n * 16 + 255) / 256), 256, 0, s>>>(feat, n, mu, a_prime, xnorm, rgb);
     return cudaGetLastError();
 }
 
 cudaError_t launch_tc_prep_centroids(const float* cent, uint32_t K, const float* mu, float* b_main, float* b_ext,
-                                     float* cmax, cudaStream_t s) {
+                                     float* cmax, cudaStream_t s, int rgb) {
     cudaError_t e = cudaMemsetAsync(cmax, 0, 4, s);
     if (e != cudaSuccess) return e;
-    prep_centroids_kernel<<<tc_padded_k(K), 64, 0, s>>>(cent, K, mu, b_main, b_ext, reinterpret_cast<unsigned int*>(cmax), 0);
+    prep_centroids_kernel<<<tc_padded_k(K), 64, 0, s>>>(cent, K, mu, b_main, b_ext, reinterpret_cast<unsigned int*>(cmax), 0, rgb);
     return cudaGetLastError();
 }
 
 cudaError_t launch_tc_prep_centroids_batch(const float* cent, uint32_t K, uint32_t n_textures, uint8_t* small, size_t small_stride,
-                                           size_t mu_off, size_t cmax_off, float* b_main, float* b_ext, cudaStream_t s) {
+                                           size_t mu_off, size_t cmax_off, float* b_main, float* b_ext, cudaStream_t s, int rgb) {
     cudaError_t e = cudaMemset2DAsync(small + cmax_off, small_stride, 0, 4, n_textures, s);
     if (e != cudaSuccess) return e;
     prep_centroids_kernel<<<dim3(tc_padded_k(K), n_textures), 64, 0, s>>>(cent, K, reinterpret_cast<const float*>(small + mu_off), b_main,
                                                                          b_ext, reinterpret_cast<unsigned int*>(small + cmax_off),
-                                                                         small_stride);
+                                                                         small_stride, rgb);
     return cudaGetLastError();
 }
 

@@ -81,19 +81,25 @@ struct TcBatch {
     uint32_t* chg_rows;
     uint32_t* chg_old;
     unsigned int* chg_count;
+    // 1 = the operands were prepared in the 48-column layout (see launch_tc_prep_blocks): 10 MMAs per tile-chunk
+    uint32_t rgb;
 };
-inline TcBatch tc_single() { return TcBatch{0xffffffffu, 0u, 0u, 0u, 0u, 0xffffffffu, 1u, nullptr, nullptr, nullptr}; }
+inline TcBatch tc_single() { return TcBatch{0xffffffffu, 0u, 0u, 0u, 0u, 0xffffffffu, 1u, nullptr, nullptr, nullptr, 0u}; }
 bool tc_supported(uint32_t K);
 uint32_t tc_padded_k(uint32_t K);  // rows of b_main / b_ext
 cudaError_t launch_tc_mean(const float* feat, size_t n, double* sums64, float* mu, cudaStream_t s);
+// rgb != 0 (textures without an alpha channel: the alpha feature is the constant 1.0, so its 16 centred columns are
+// exactly zero in every block): the 48 colour columns are packed first and the folded norm terms take three of the 16
+// freed columns of the hi half, so a tile-chunk needs 3 + 3 + 4 = 10 K-steps instead of 13.  Both operands and the
+// front-end launch must agree on the flag.
 cudaError_t launch_tc_prep_blocks(const float* feat, size_t n, const float* mu, float* a_prime, float* xnorm,
-                                  cudaStream_t s);
+                                  cudaStream_t s, int rgb = 0);
 cudaError_t launch_tc_prep_centroids(const float* cent, uint32_t K, const float* mu, float* b_main, float* b_ext,
-                                     float* cmax, cudaStream_t s);
+                                     float* cmax, cudaStream_t s, int rgb = 0);
 // batch: texture t reads cent + t*K*64, mu at small + t*small_stride + mu_off, writes rows [t*k_pad, ..) of b_main /
 // b_ext and max-reduces cmax at small + t*small_stride + cmax_off (zeroed here)
 cudaError_t launch_tc_prep_centroids_batch(const float* cent, uint32_t K, uint32_t n_textures, uint8_t* small, size_t small_stride,
-                                           size_t mu_off, size_t cmax_off, float* b_main, float* b_ext, cudaStream_t s);
+                                           size_t mu_off, size_t cmax_off, float* b_main, float* b_ext, cudaStream_t s, int rgb = 0);
 // `stop` (may be null): device word; when non-zero the kernel returns at once (Lloyd passes are enqueued
 // ahead of the convergence test, see launch_lloyd_control).
 // assign != null: rows with exactly one candidate get their assignment (and the changed flag) written by the
