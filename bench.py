@@ -270,8 +270,10 @@ def run_ours(args, rank, world, local_rank):
         split = 3                                            # xh.ch + xh.cl + xl.ch bf16 partial products
         achieved = split * flop_alg / (ms_a * 1e-3) / 1e12 if ms_a > 0 else 0.0
         traffic = None
-        tpath = os.path.join(ROOT, "profiles", "r01d_traffic.json")
-        if world == 1 and os.path.exists(tpath):  # DRAM bytes per launch of the same kernel on the same config, from the committed ncu capture
+        import glob
+        tfiles = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_traffic.json")))
+        tpath = tfiles[-1] if tfiles else ""
+        if world == 1 and tpath:  # DRAM bytes per launch of the same kernel on the same config, from the committed ncu capture
             traffic = json.load(open(tpath))["assign_tc_kernel"]["dram_bytes_per_launch"]
         roofline = {"bound": "tensor", "kernel": "assign_tc_kernel (N x K x 64 contraction as 3 bf16 partial products + argmax epilogue)",
                     "achieved": achieved, "peak": pk["bf16_tflops_sustained"], "unit": "TFLOP/s",
