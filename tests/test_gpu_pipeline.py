@@ -135,13 +135,15 @@ def test_errors_are_reported(enc):
         enc.encode_bcn(np.zeros(8, np.uint8), 1, 1, 5, cfg)
 
 
-def test_lockstep_batch_equals_per_texture_calls(enc):
+@pytest.mark.parametrize("w,h", [(256, 512), (200, 264)])
+def test_lockstep_batch_equals_per_texture_calls(enc, w, h):
     """yupvq_encode_bcn_batch_sharded on one GPU (no communicator, the whole texture as the shard): every
     texture's centroids and indices are bit-identical to yupvq_encode_bcn with seed + t -- the lock-step
-    schedule, the per-texture operand views and the host-side convergence test change nothing."""
+    schedule, the per-texture operand views and the device-side convergence test change nothing.
+    256x512 (8192 blocks, tile-aligned) takes the whole-batch launches; 200x264 (3300 blocks) the per-texture ones."""
     from yuptexture_b200 import binding
-    texs = [synth.bc1_encode(synth.ldr_rgb(256, 512, seed=31 + t)) for t in range(3)]
-    texs.append(synth.bc1_encode(np.full((256, 512, 3), 77, np.uint8)))   # flat: converges at once, leaves the set early
+    texs = [synth.bc1_encode(synth.ldr_rgb(w, h, seed=31 + t)) for t in range(3)]
+    texs.append(synth.bc1_encode(np.full((h, w, 3), 77, np.uint8)))   # flat: converges at once, leaves the set early
     n, k = len(texs[0]), 128
     cfg = binding.make_config(codebook=k, max_iterations=12, seed=5, assign_mode=binding.ASSIGN_TENSOR)
     cents, idxs, st = enc.encode_bcn_batch_sharded(texs, n, 0, n, 1, 3, cfg)
