@@ -506,6 +506,43 @@ seed_persistent_kernel(SeedState st, const uint4* __restrict__ planes, size_t st
                 }
             }
             local = (ACC)loc32;
+        } else if (TRI && MDREG && HDR) {
+            // Triangle-inequality skip on the Oklab metric: sqrt(d) is a norm distance, so with s_j the seed nearest to
+            // block j:  d(new, s_j) >= 4 md_j  =>  d(j, new) >= md_j  =>  the minimum is unchanged and the 256-byte
+            // feature row is not read.  The factor 4.001 keeps the implication true for the fp32-computed distances
+            // (64 non-negative terms: relative error < 1e-5), so values, sums and picks stay bit-identical.  The
+            // distances new seed -> earlier seeds are recomputed by every CTA (one per thread, rows are L2-resident).
+            const uint32_t o = round - 1;
+            float* const tri_f = reinterpret_cast<float*>(s_cache);
+            uint32_t* const seedlist_s = reinterpret_cast<uint32_t*>(tri_f + K);
+            if (tid < (int)o) {
+                const float4* x = reinterpret_cast<const float4*>(feat) + (size_t)seedlist_s[tid] * 16;
+                DistAcc acc;
+                acc.reset();
+#pragma unroll
+                for (int k = 0; k < 8; ++k) acc.step(x[2 * k], x[2 * k + 1], s_seedf[2 * k], s_seedf[2 * k + 1]);
+                tri_f[tid] = acc.finish();
+            }
+            if (tid == 0) seedlist_s[o] = seed;   // read from the next round on (barriers in between)
+            __syncthreads();
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const size_t j = wbase + (size_t)i * 32 + lane;
+                if ((vmask >> i) & 1u) {
+                    float m = md[i];
+                    const bool skip = msnr[i] != 0xffffu && tri_f[msnr[i]] >= 4.001f * m;
+                    if (!skip) {
+                        const float d = block_dist(i, j);
+                        if (d < m) {                                               // std::min(d, minDistSq[j]) moved
+                            m = d;
+                            md[i] = d;
+                            msnr[i] = o;
+                            __stcg(mdp + i * 32, d);
+                        }
+                    }
+                    local += (ACC)m;
+                }
+            }
         } else if (MDREG) {
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
@@ -774,8 +811,12 @@ cudaError_t launch_seed_persistent(const SeedState& st, const uint4* planes, siz
     // Measured on config 2 (B200): the skip makes the seeding SLOWER (4.41 ms against 3.84 ms) -- the extra barrier and
     // table per round cost more than the skipped loads save, because a warp only saves a load when all 32 of its
     // (noisy, 48-dimensional) blocks pass the bound.  Kept opt-in for smoother inputs; results are identical either way.
+    // The Oklab (HDR) variant is on by default: its rows are 256 bytes (the round is HBM-bound) and neighbouring
+    // blocks of real images are similar, so whole warps skip (YUPVQ_SEED_NO_TRI=1 turns it off for A/B).
     static const bool want_tri = getenv("YUPVQ_SEED_TRI") != nullptr;
+    static const bool no_tri = getenv("YUPVQ_SEED_NO_TRI") != nullptr;
     const bool tri = !hdr && mdreg && K <= (uint32_t)kPThreads && want_tri;
+    const bool tri_hdr = hdr && mdreg && K <= (uint32_t)kPThreads && !no_tri;
     const void* fn = nullptr;
     if (hdr) fn = mdreg ? (const void*)seed_persistent_kernel<true, 1, true> : (const void*)seed_persistent_kernel<true, 1, false>;
     else if (ch == 1) fn = mdreg ? (const void*)seed_persistent_kernel<false, 1, true> : (const void*)seed_persistent_kernel<false, 1, false>;
@@ -783,6 +824,7 @@ cudaError_t launch_seed_persistent(const SeedState& st, const uint4* planes, siz
     else if (ch == 3) fn = mdreg ? (const void*)seed_persistent_kernel<false, 3, true> : (const void*)seed_persistent_kernel<false, 3, false>;
     else if (ch == 4) fn = mdreg ? (const void*)seed_persistent_kernel<false, 4, true> : (const void*)seed_persistent_kernel<false, 4, false>;
     else return cudaErrorInvalidValue;
+    if (tri_hdr) fn = (const void*)seed_persistent_kernel<true, 1, true, true>;
     if (tri) {
         if (ch == 1) fn = (const void*)seed_persistent_kernel<false, 1, true, true>;
         else if (ch == 2) fn = (const void*)seed_persistent_kernel<false, 2, true, true>;
@@ -806,6 +848,15 @@ cudaError_t launch_seed_persistent(const SeedState& st, const uint4* planes, siz
             cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(200u * 1024u));
             if (e != cudaSuccess) return e;
             attr[ai] = true;
+        }
+    }
+    if (tri_hdr) {  // distances to the earlier seeds + their block indices
+        smem = (size_t)K * 8;
+        static bool attr_hdr = false;
+        if (smem > 40 * 1024 && !attr_hdr) {
+            cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(64u * 1024u));
+            if (e != cudaSuccess) return e;
+            attr_hdr = true;
         }
     }
     SeedState st_copy = st;
