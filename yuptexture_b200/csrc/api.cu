@@ -1003,10 +1003,23 @@ int yupvq_build_codebook(yupvq_ctx* ctx, const uint8_t* pixel_blocks, size_t n_b
     if (to_device(ctx, pixel_blocks, n_blocks * 16 * channels, ctx->in_bytes, &px_dev)) return 1;
     CK(ctx->planes.ensure(n_blocks * 16 * channels));
     CK(ctx->feat.ensure(n_blocks * 256));
-    LAUNCH(launch_pixels_to_features(reinterpret_cast<const uint8_t*>(px_dev), n_blocks, channels,
-                                     ctx->planes.as<uint4>(), n_blocks, ctx->feat.as<float>(), ctx->stream));
-    if (cfg->metric == YUPVQ_METRIC_SAD)
+    // as in yupvq_encode_bcn: pixel planes before the seeding, features after it (no sampling)
+    static const bool no_split = getenv("YUPVQ_NO_SPLIT_DECODE") != nullptr;
+    const bool sampling = cfg->sample_ratio < 1.0f && cfg->sample_ratio > 0.0f;
+    const bool split = !sampling && !no_split;
+    const bool sad = cfg->metric == YUPVQ_METRIC_SAD;
+    LAUNCH(launch_pixels_to_features(reinterpret_cast<const uint8_t*>(px_dev), n_blocks, channels, ctx->planes.as<uint4>(), n_blocks,
+                                     (split || sad) ? nullptr : ctx->feat.as<float>(), ctx->stream));
+    if (sad && !split)
         LAUNCH(launch_sad_expand(ctx->planes.as<uint4>(), n_blocks, n_blocks, channels, ctx->feat.as<float>(), ctx->stream));
+    std::function<int()> late;
+    if (split)
+        late = [&]() -> int {
+            if (sad) LAUNCH(launch_sad_expand(ctx->planes.as<uint4>(), n_blocks, n_blocks, channels, ctx->feat.as<float>(), ctx->stream));
+            else LAUNCH(launch_pixels_to_features(reinterpret_cast<const uint8_t*>(px_dev), n_blocks, channels, nullptr, 0,
+                                                  ctx->feat.as<float>(), ctx->stream));
+            return 0;
+        };
     Blocks all;
     all.n = n_blocks;
     all.ch = channels;
@@ -1014,7 +1027,7 @@ int yupvq_build_codebook(yupvq_ctx* ctx, const uint8_t* pixel_blocks, size_t n_b
     all.stride = n_blocks;
     all.feat = ctx->feat.as<float>();
     int ts0, ts1, tl1, tf1;
-    if (build_codebook_device(ctx, all, n_blocks, cfg, false, stats, tm, &ts0, &ts1, &tl1, &tf1)) return 1;
+    if (build_codebook_device(ctx, all, n_blocks, cfg, false, stats, tm, &ts0, &ts1, &tl1, &tf1, late)) return 1;
     if (from_device(ctx, out_pixel_centroids, ctx->cent_px.p, (size_t)cfg->codebook_size * 16 * channels)) return 1;
     const int t4 = tm.mark();
     CK(cudaStreamSynchronize(ctx->stream));

@@ -357,6 +357,11 @@ seed_persistent_kernel(SeedState st, const uint4* __restrict__ planes, size_t st
     for (int i = 0; i < 8; ++i) msnr[i] = 0xffffu;
     uint4* const seeds_s = s_cache + (size_t)cseg * kPWarps * CH * 32;          // TRI: [K][CH] pixel blocks of the seeds
     uint32_t* const tri_s = reinterpret_cast<uint32_t*>(seeds_s + (size_t)K * CH);  // TRI: SAD(new seed, seed q)
+    if (TRI && HDR) {   // "seed q is nearest to one of this CTA's blocks" bits (after the distance and index tables)
+        uint32_t* used0 = reinterpret_cast<uint32_t*>(s_cache) + 2 * (size_t)K;
+        for (uint32_t i = tid; i < (K + 31) / 32; i += kPThreads) used0[i] = 0u;
+        __syncthreads();
+    }
     // per-lane constants of the update loop
     unsigned int vmask = 0;
 #pragma unroll
@@ -512,10 +517,13 @@ seed_persistent_kernel(SeedState st, const uint4* __restrict__ planes, size_t st
             // feature row is not read.  The factor 4.001 keeps the implication true for the fp32-computed distances
             // (64 non-negative terms: relative error < 1e-5), so values, sums and picks stay bit-identical.  The
             // distances new seed -> earlier seeds are recomputed by every CTA (one per thread, rows are L2-resident).
+            // Only the seeds that are (or once were) nearest to one of THIS CTA's blocks are needed: a CTA covers a
+            // contiguous stripe of the image, so that is a small part of the list (bit mask in shared memory).
             const uint32_t o = round - 1;
             float* const tri_f = reinterpret_cast<float*>(s_cache);
             uint32_t* const seedlist_s = reinterpret_cast<uint32_t*>(tri_f + K);
-            if (tid < (int)o) {
+            uint32_t* const used_s = seedlist_s + K;                               // K / 32 words (zeroed before round 1)
+            if (tid < (int)o && ((used_s[tid >> 5] >> (tid & 31)) & 1u)) {
                 const float4* x = reinterpret_cast<const float4*>(feat) + (size_t)seedlist_s[tid] * 16;
                 DistAcc acc;
                 acc.reset();
@@ -525,6 +533,7 @@ seed_persistent_kernel(SeedState st, const uint4* __restrict__ planes, size_t st
             }
             if (tid == 0) seedlist_s[o] = seed;   // read from the next round on (barriers in between)
             __syncthreads();
+            bool took = false;
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
                 const size_t j = wbase + (size_t)i * 32 + lane;
@@ -537,12 +546,14 @@ seed_persistent_kernel(SeedState st, const uint4* __restrict__ planes, size_t st
                             m = d;
                             md[i] = d;
                             msnr[i] = o;
+                            took = true;
                             __stcg(mdp + i * 32, d);
                         }
                     }
                     local += (ACC)m;
                 }
             }
+            if (__any_sync(0xffffffffu, took) && lane == 0) atomicOr(&used_s[o >> 5], 1u << (o & 31));
         } else if (MDREG) {
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
@@ -851,7 +862,7 @@ cudaError_t launch_seed_persistent(const SeedState& st, const uint4* planes, siz
         }
     }
     if (tri_hdr) {  // distances to the earlier seeds + their block indices
-        smem = (size_t)K * 8;
+        smem = (size_t)K * 8 + ((size_t)K + 31) / 32 * 4;
         static bool attr_hdr = false;
         if (smem > 40 * 1024 && !attr_hdr) {
             cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(64u * 1024u));
