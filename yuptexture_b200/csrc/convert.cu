@@ -43,44 +43,89 @@ __device__ __forceinline__ uint32_t texel_byte(const uint32_t (&w)[4 * CH], int 
 }
 
 // VQEncoder::PixelBlockToOklabBlock (src/vq_encoder.cpp:96-102) on a pixel block held as packed
-// words.  Conversions are de-duplicated through a 4-entry cache: a BC1/BC3 block has at most four
-// distinct colours, so it costs four double-precision conversions instead of sixteen.
+// words.  A BC1/BC3 block has at most four distinct colours, so the conversions are de-duplicated, in three
+// steps that keep the warp converged through the fp64 code: (1) integer only: every texel gets the slot of its
+// colour in a 4-entry key list, or an overflow bit once the block has shown a fifth colour; (2) slot j is
+// converted by all lanes together while any lane of the warp has more than j colours; (3) texels pick their slot,
+// overflow texels are converted one by one (BC7 / raw pixel blocks with many colours, no worse than a plain loop).
+template <int CH>
+__device__ __forceinline__ uint32_t texel_rgb_key(const uint32_t (&w)[4 * CH], int p) {
+    if (CH <= 2) return texel_byte<CH>(w, p, 0) * 0x010101u;
+    return texel_byte<CH>(w, p, 0) | (texel_byte<CH>(w, p, 1) << 8) | (texel_byte<CH>(w, p, 2) << 16);
+}
+
 template <int CH>
 __device__ __forceinline__ void block_features(const uint32_t (&w)[4 * CH], float4 (&f)[16]) {
-    uint32_t key[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
-    float3 val[4];
-    int next = 0;
+    uint32_t key[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};  // never equals a 24-bit key
+    uint32_t slots = 0, overflow = 0;
+    int count = 0;
 #pragma unroll
     for (int p = 0; p < 16; ++p) {
-        uint32_t r, g, b;
-        float alpha = 1.0f;
-        if (CH == 1) {
-            r = g = b = texel_byte<CH>(w, p, 0);
-        } else if (CH == 2) {
-            r = g = b = texel_byte<CH>(w, p, 0);
-            alpha = __fdiv_rn((float)texel_byte<CH>(w, p, 1), 255.0f);
-        } else {
-            r = texel_byte<CH>(w, p, 0);
-            g = texel_byte<CH>(w, p, 1);
-            b = texel_byte<CH>(w, p, 2);
-            if (CH == 4) alpha = __fdiv_rn((float)texel_byte<CH>(w, p, 3), 255.0f);
-        }
-        const uint32_t k = r | (g << 8) | (b << 16);
-        float3 o;
-        if (k == key[0]) o = val[0];
-        else if (k == key[1]) o = val[1];
-        else if (k == key[2]) o = val[2];
-        else if (k == key[3]) o = val[3];
-        else {
-            o = srgb8_to_oklab(r, g, b);
+        const uint32_t k = texel_rgb_key<CH>(w, p);
+        uint32_t s;
+        if (k == key[0]) s = 0;
+        else if (k == key[1]) s = 1;
+        else if (k == key[2]) s = 2;
+        else if (k == key[3]) s = 3;
+        else if (count < 4) {
+            s = (uint32_t)count;
 #pragma unroll
             for (int j = 0; j < 4; ++j)
-                if (j == next) {
-                    key[j] = k;
-                    val[j] = o;
-                }
-            next = (next + 1) & 3;
+                if (j == count) key[j] = k;
+            ++count;
+        } else {
+            s = 0;
+            overflow |= 1u << p;
         }
+        slots |= s << (2 * p);
+    }
+    float3 val[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        val[j] = make_float3(0.f, 0.f, 0.f);
+        if (__any_sync(__activemask(), count > j)) {
+            const uint32_t k = count > j ? key[j] : 0u;
+            val[j] = srgb8_to_oklab(k & 255u, (k >> 8) & 255u, (k >> 16) & 255u);
+        }
+    }
+#pragma unroll
+    for (int p = 0; p < 16; ++p) {
+        const uint32_t s = (slots >> (2 * p)) & 3u;
+        float3 o = s == 0 ? val[0] : s == 1 ? val[1] : s == 2 ? val[2] : val[3];
+        if (overflow & (1u << p)) {
+            const uint32_t k = texel_rgb_key<CH>(w, p);
+            o = srgb8_to_oklab(k & 255u, (k >> 8) & 255u, (k >> 16) & 255u);
+        }
+        float alpha = 1.0f;
+        if (CH == 2) alpha = __fdiv_rn((float)texel_byte<CH>(w, p, 1), 255.0f);
+        if (CH == 4) alpha = __fdiv_rn((float)texel_byte<CH>(w, p, 3), 255.0f);
+        f[p] = make_float4(o.x, o.y, o.z, alpha);
+    }
+}
+
+// The same features for a block whose colours come from a 4-entry palette (BC1, BC3 colour part): the four
+// palette colours are converted by every lane at the same point of the program, then selected per texel by the
+// 2-bit index.  block_features' cache makes the same four conversions per block, but the lanes of a warp miss at
+// different texels, so the warp walks the fp64 conversion at nearly all sixteen positions; here it walks it four
+// times.  Same function on the same bytes, so the features are bit-identical.
+template <int CH>
+__device__ __forceinline__ void palette_features(const uint32_t (&pal)[4], uint32_t sel, const uint32_t (&w)[4 * CH],
+                                                 float4 (&f)[16]) {
+    float3 val[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        uint32_t r = pal[j] & 255u, g = (pal[j] >> 8) & 255u, b = (pal[j] >> 16) & 255u;
+        if (CH == 1) r = g = b;       // 1-channel output of BC1/BC3 takes B (pack_block)
+        else if (CH == 2) g = b = r;  // 2-channel output takes (R, G): colour from R, alpha from G
+        val[j] = srgb8_to_oklab(r, g, b);
+    }
+#pragma unroll
+    for (int p = 0; p < 16; ++p) {
+        const uint32_t k = (sel >> (2 * p)) & 3u;
+        const float3 o = k == 0 ? val[0] : k == 1 ? val[1] : k == 2 ? val[2] : val[3];
+        float alpha = 1.0f;
+        if (CH == 2) alpha = __fdiv_rn((float)texel_byte<CH>(w, p, 1), 255.0f);
+        if (CH == 4) alpha = __fdiv_rn((float)texel_byte<CH>(w, p, 3), 255.0f);
         f[p] = make_float4(o.x, o.y, o.z, alpha);
     }
 }
@@ -178,8 +223,8 @@ __global__ void __launch_bounds__(kTile) decode_bcn_kernel(const uint8_t* __rest
 
     if (valid) {
         uint32_t t[16];
+        uint32_t pal[4] = {0, 0, 0, 0};
         if (FMT == YUPVQ_FMT_BC1) {
-            uint32_t pal[4];
             bc1_palette(raw.x, true, pal);
 #pragma unroll
             for (int p = 0; p < 16; ++p) {
@@ -187,7 +232,7 @@ __global__ void __launch_bounds__(kTile) decode_bcn_kernel(const uint8_t* __rest
                 t[p] = k == 0 ? pal[0] : k == 1 ? pal[1] : k == 2 ? pal[2] : pal[3];
             }
         } else if (FMT == YUPVQ_FMT_BC3) {
-            uint32_t pal[4], a[16];
+            uint32_t a[16];
             bc1_palette(raw.z, false, pal);
             bc4_decode(raw.x, raw.y, a);
 #pragma unroll
@@ -217,7 +262,11 @@ __global__ void __launch_bounds__(kTile) decode_bcn_kernel(const uint8_t* __rest
 #pragma unroll
             for (int i = 0; i < 4 * CH; ++i) dst[i] = w[i];
         }
-        if (feat) block_features<CH>(w, f);
+        if (feat) {
+            if (FMT == YUPVQ_FMT_BC1) palette_features<CH>(pal, raw.y, w, f);
+            else if (FMT == YUPVQ_FMT_BC3) palette_features<CH>(pal, raw.w, w, f);
+            else block_features<CH>(w, f);
+        }
     }
     if (feat) store_features_tile(f, valid, tile, feat, tile_first, n);
 }
