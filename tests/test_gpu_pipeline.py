@@ -92,6 +92,23 @@ def test_fast_mode_sampling_golden(enc, golden_pipeline):
     assert abs(p_gpu - p_ref) <= 0.25  # small sample (102 blocks for 32 clusters): looser bound
 
 
+@pytest.mark.parametrize("n", [4133, 300000, 1048576])
+def test_bc1_palette_form_seeding_equals_pixel_path(enc, oracle, n):
+    """BC1 input with 3-channel output is seeded from the 20-byte palette form of the blocks (seed.cu PAL variant);
+    the two-call interface on the decoded pixel blocks is seeded from the pixel planes.  Random BC1 bytes put half of
+    the blocks in 3-colour mode (index 3 = black), the sizes cover ragged warps and every resident segment."""
+    from yuptexture_b200 import binding
+    rng = np.random.default_rng(n)
+    bc = rng.integers(0, 256, size=(n, 8), dtype=np.uint8)
+    bc[: n // 4, 4:] = rng.integers(0, 256, size=(n // 4, 1), dtype=np.uint8)  # some low-variety index patterns
+    cfg = binding.make_config(codebook=256, max_iterations=0, seed=7)
+    cent, idx, st = enc.encode_bcn(bc, n, 1, 3, cfg)
+    px = oracle.decode_bcn(bc, 1, 3)
+    cent_b, _ = enc.build_codebook(px, 3, cfg)
+    assert bits_equal(cent_b, cent)
+    assert st.seed_rounds == 255
+
+
 def test_config2_full_size(enc, oracle):
     """BASELINE config 2: 4096x4096 BC1 (1,048,576 blocks), K = 512.  Size-independent checks:
     decode and seeds equal the oracle's, indices equal the exact assignment given the returned

@@ -62,6 +62,7 @@ struct yupvq_ctx {
     // device arena (grow-only, reused across calls)
     DevBuf in_bytes;    // staged input (BCn bytes / pixel blocks / float image or blocks)
     DevBuf planes;      // uint8 pixel planes (ch planes of uint4)
+    DevBuf pal5;        // BC1 input, 3 channels: palette form of the blocks for the seeding (5 planes of uint32)
     DevBuf feat;        // N x 64 fp32 features
     DevBuf s_planes, s_feat, s_rows;  // fast-mode sampled subset
     DevBuf min_dist, partial, seed_idx, canon, small;  // seeding
@@ -209,6 +210,8 @@ struct Blocks {        // device-resident block set
     const uint4* planes = nullptr;  // null for HDR
     size_t stride = 0;
     const float* feat = nullptr;
+    const uint32_t* pal5 = nullptr;  // optional: the same blocks in BC1 palette form (seeding only), 5 planes
+    size_t pal_stride = 0;
 };
 
 int fixed_shift(size_t n_total, float max_abs) {
@@ -226,6 +229,17 @@ int fixed_shift(size_t n_total, float max_abs) {
 }
 
 // ---- K2: seeding -----------------------------------------------------------------------------------
+// BC1 input with 3-channel output: the seeding works from the 20-byte palette form of the blocks, which fits in
+// shared memory whole (seed.cu, PAL variant).  `all` must describe exactly the n blocks at bc_dev.
+int attach_palette_form(yupvq_ctx* ctx, Blocks& all, const void* bc_dev, int bc_format, int channels) {
+    if (bc_format != YUPVQ_BC1 || channels != 3 || all.n == 0) return 0;
+    CK(ctx->pal5.ensure(all.n * 20));
+    LAUNCH(launch_bc1_palette_planes(reinterpret_cast<const uint8_t*>(bc_dev), all.n, ctx->pal5.as<uint32_t>(), all.n, ctx->stream));
+    all.pal5 = ctx->pal5.as<uint32_t>();
+    all.pal_stride = all.n;
+    return 0;
+}
+
 int run_seeding(yupvq_ctx* ctx, const Blocks& b, uint32_t K, const Draws& dr, bool hdr, uint32_t* out_rounds) {
     const size_t n = b.n;
     const int grid = (int)seed_grid_for(n);
@@ -247,7 +261,7 @@ int run_seeding(yupvq_ctx* ctx, const Blocks& b, uint32_t K, const Draws& dr, bo
     // one persistent cooperative kernel for all K-1 rounds; per-round launches only where that is not possible
     static const bool per_round = getenv("YUPVQ_SEED_PER_ROUND") != nullptr;  // A/B timing and tests
     cudaError_t pe = per_round ? cudaErrorNotSupported
-                               : launch_seed_persistent(st, b.planes, b.stride, b.feat, n, b.ch, hdr, K, ctx->stream);
+                               : launch_seed_persistent(st, b.planes, b.stride, b.feat, n, b.ch, hdr, K, ctx->stream, b.pal5, b.pal_stride);
     if (pe == cudaSuccess) {
         if (K > 1) ++ctx->launches;
     } else if (pe == cudaErrorNotSupported || pe == cudaErrorCooperativeLaunchTooLarge) {
@@ -622,6 +636,8 @@ int build_codebook_device(yupvq_ctx* ctx, const Blocks& all, size_t n_total, con
         b.planes = hdr ? nullptr : ctx->s_planes.as<uint4>();
         b.stride = n_used;
         b.feat = ctx->s_feat.as<float>();
+        b.pal5 = nullptr;  // the palette form describes the full set, not the gathered subset
+        b.pal_stride = 0;
         n_total = n_used;
     }
     if (stats) {
@@ -779,7 +795,7 @@ void yupvq_destroy(yupvq_ctx* ctx) {
                       &ctx->errors, &ctx->cent, &ctx->acc, &ctx->cent_px, &ctx->cent_feat, &ctx->out_idx,
                       &ctx->tc_a, &ctx->tc_xnorm, &ctx->tc_small, &ctx->tc_b, &ctx->tc_bx, &ctx->tc_cand, &ctx->tc_amb,
                       &ctx->bt_feat, &ctx->bt_tca, &ctx->bt_xnorm, &ctx->bt_tcsmall, &ctx->bt_assign, &ctx->bt_errors,
-                      &ctx->bt_cent, &ctx->bt_acc, &ctx->bt_misc, &ctx->bt_centpx, &ctx->bt_cent0, &ctx->tc_chg, &ctx->delta_ctl, &ctx->bt_acc_local};
+                      &ctx->bt_cent, &ctx->bt_acc, &ctx->bt_misc, &ctx->bt_centpx, &ctx->bt_cent0, &ctx->tc_chg, &ctx->delta_ctl, &ctx->bt_acc_local, &ctx->pal5};
     for (DevBuf* b : bufs) b->release();
     if (ctx->h_small) cudaFreeHost(ctx->h_small);
     for (auto& ev : ctx->ev)
@@ -888,6 +904,7 @@ int yupvq_encode_bcn(yupvq_ctx* ctx, const uint8_t* bc_blocks, size_t n_blocks, 
     all.planes = ctx->planes.as<uint4>();
     all.stride = n_blocks;
     all.feat = ctx->feat.as<float>();
+    if (!sampling && attach_palette_form(ctx, all, bc_dev, bc_format, channels)) return 1;
     int ts0, ts1, tl1, tf1;
     if (build_codebook_device(ctx, all, n_blocks, cfg, false, stats, tm, &ts0, &ts1, &tl1, &tf1, late)) return 1;
     if (quantize_device(ctx, all, ctx->cent_px.p, cfg->codebook_size, false, cfg->assign_mode, cfg->metric)) return 1;
@@ -1482,6 +1499,7 @@ int yupvq_encode_bcn_sharded(yupvq_ctx* ctx, const uint8_t* bc_blocks, size_t n_
     all.planes = ctx->planes.as<uint4>();
     all.stride = n_total;
     all.feat = nullptr;
+    if (attach_palette_form(ctx, all, bc_dev, bc_format, channels)) return 1;
     size_t n_used;
     Draws dr = make_draws(n_total, K, 1.0f, cfg->seed, &n_used);
     uint32_t rounds = 0;
@@ -1612,6 +1630,7 @@ int yupvq_encode_bcn_batch_sharded(yupvq_ctx* ctx, const uint8_t* const* bc_bloc
         all.planes = ctx->planes.as<uint4>();
         all.stride = n_total;
         all.feat = nullptr;
+        if (attach_palette_form(ctx, all, bc_dev, bc_format, channels)) return 1;
         size_t n_used;
         Draws dr = make_draws(n_total, K, 1.0f, cfg->seed ? cfg->seed + t : 0, &n_used);
         uint32_t rounds = 0;

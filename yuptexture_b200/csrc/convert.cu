@@ -513,6 +513,47 @@ cudaError_t launch_decode_bcn(const uint8_t* bc, size_t n, int fmt, int ch, uint
     }
 }
 
+// BC1 blocks -> the compact form the K-Means++ seeding keeps resident in shared memory (seed.cu, PAL variant): five
+// 32-bit planes per block -- the four palette entries of R, of G and of B (byte j = entry j), and the sixteen 2-bit
+// indices widened to PRMT selector nibbles (texels 0-7, texels 8-15).  20 bytes describe the same 48 pixel bytes the
+// planes hold (3-channel output of a BC1 block: R, G, B of the decoded texel; entry 3 of 3-colour mode is black).
+__global__ void __launch_bounds__(256) bc1_palette_planes_kernel(const uint8_t* __restrict__ bc, size_t n,
+                                                                 uint32_t* __restrict__ pal5, size_t stride, int aligned) {
+    const size_t blk = (size_t)blockIdx.x * 256 + threadIdx.x;
+    if (blk >= n) return;
+    uint32_t lo, idx;
+    if (aligned) {
+        const uint2 v = __ldg(reinterpret_cast<const uint2*>(bc) + blk);
+        lo = v.x;
+        idx = v.y;
+    } else {
+        const uint8_t* p = bc + blk * 8;
+        lo = p[0] | (p[1] << 8) | (p[2] << 16) | ((uint32_t)p[3] << 24);
+        idx = p[4] | (p[5] << 8) | (p[6] << 16) | ((uint32_t)p[7] << 24);
+    }
+    uint32_t pal[4];
+    bc1_palette(lo, true, pal);
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+        pal5[c * stride + blk] = ((pal[0] >> (8 * c)) & 255u) | (((pal[1] >> (8 * c)) & 255u) << 8) |
+                                 (((pal[2] >> (8 * c)) & 255u) << 16) | (((pal[3] >> (8 * c)) & 255u) << 24);
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        uint32_t x = (idx >> (16 * h)) & 0xffffu;  // 8 two-bit indices -> 8 nibbles
+        x = (x | (x << 8)) & 0x00ff00ffu;
+        x = (x | (x << 4)) & 0x0f0f0f0fu;
+        x = (x | (x << 2)) & 0x33333333u;
+        pal5[(3 + h) * stride + blk] = x;
+    }
+}
+
+cudaError_t launch_bc1_palette_planes(const uint8_t* bc, size_t n, uint32_t* pal5, size_t stride, cudaStream_t s) {
+    if (n == 0) return cudaSuccess;
+    const int aligned = ((reinterpret_cast<uintptr_t>(bc) & 7u) == 0) ? 1 : 0;
+    bc1_palette_planes_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(bc, n, pal5, stride, aligned);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_pixels_to_features(const uint8_t* px_blocks, size_t n, int ch, uint4* planes, size_t plane_stride,
                                       float* feat, cudaStream_t s) {
     if (n == 0) return cudaSuccess;

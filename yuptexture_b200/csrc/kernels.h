@@ -45,8 +45,12 @@ cudaError_t launch_seed_init(const SeedState& st, size_t n, uint32_t first_idx, 
 cudaError_t launch_seed_round_ldr(const SeedState& st, const uint4* planes, size_t plane_stride, size_t n, int ch,
                                   uint32_t round, uint32_t K, cudaStream_t s);
 // all K-1 rounds in one cooperative launch; cudaErrorNotSupported -> use the per-round launches
+// pal5 (optional, ch == 3 only): the blocks in BC1 palette form (launch_bc1_palette_planes), 5 planes of pal_stride words
 cudaError_t launch_seed_persistent(const SeedState& st, const uint4* planes, size_t plane_stride, const float* feat, size_t n,
-                                   int ch, bool hdr, uint32_t K, cudaStream_t s);
+                                   int ch, bool hdr, uint32_t K, cudaStream_t s, const uint32_t* pal5 = nullptr,
+                                   size_t pal_stride = 0);
+// convert.cu: BC1 blocks -> 5 x uint32 palette planes (R, G, B palette bytes; selector nibbles of texels 0-7, 8-15)
+cudaError_t launch_bc1_palette_planes(const uint8_t* bc, size_t n, uint32_t* pal5, size_t stride, cudaStream_t s);
 cudaError_t launch_seed_round_hdr(const SeedState& st, const float* feat, size_t n, uint32_t round, uint32_t K,
                                   cudaStream_t s);
 

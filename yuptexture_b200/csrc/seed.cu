@@ -754,6 +754,231 @@ seed_persistent_kernel(SeedState st, const uint4* __restrict__ planes, size_t st
 #endif
 }
 
+// ---- K2p: K-Means++ seeding of BC1 blocks from their palette form ---------------------------------------------------
+// Same rounds, same integer sums, same picks as seed_persistent_kernel<false, 3, true> (reference :287-313), for the
+// one input the headline path has: BC1 blocks with 3-channel output.  Two things change.
+//  (1) Data.  A BC1 block is 20 bytes in palette form (convert.cu bc1_palette_planes_kernel: the four palette entries
+//      of R, G, B and sixteen selector nibbles), so ALL blocks of a CTA are resident in shared memory (160 KiB) and
+//      the minimum distances live in registers: a round reads and writes no global memory except the exchange words.
+//      A lane rebuilds the 48 pixel bytes channel by channel with 12 PRMTs and feeds 12 VABSDIFF4 against the seed
+//      rebuilt the same way; SAD adds the same 48 |a - b| in another order.
+//  (2) The chain of a round.  The generic kernel publishes 32 warp words per CTA with a release (its min_dist stores must
+//      be visible to the leader's level-2 search), the leader scans 4736 words with three CTA barriers, reads the
+//      owner warp's min_dist from L2 and publishes the pick; every CTA then fetches the seed's pixels: five dependent
+//      L2 round trips.  Here the search goes to the data instead: each CTA publishes ONE tagged word (its total), one
+//      warp of the leader scans the <= 160 words and posts the residual target in the owning CTA's mailbox; that
+//      CTA finds the block in its own registers (warp totals are still in shared memory) and publishes the pick
+//      TOGETHER with the seed's 20 bytes taken from its shared memory.  Three round trips, every message a
+//      self-validating tagged 64-bit word (16-bit round tag + 48-bit payload): no fences, no min_dist array.
+constexpr int kQMailbox = 256, kQMailStride = 16, kQPick = 4096;  // u64 offsets in SeedState::partial (CTA words at 0)
+constexpr unsigned int kEvtPick = 1, kEvtOwner = 2;
+
+__global__ void __launch_bounds__(kPThreads, 1)
+seed_palette_kernel(SeedState st, const uint32_t* __restrict__ pal5, size_t pstride, size_t n, size_t bpw, uint32_t K) {
+    extern __shared__ uint4 s_cache[];                 // [warp][8 segments][5 words][32 lanes]
+    __shared__ unsigned long long s_w[kPWarps];        // warp totals, then their inclusive prefix
+    __shared__ unsigned long long s_pickw[5];
+    __shared__ unsigned long long s_resid;
+    __shared__ unsigned int s_evt;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int G = gridDim.x;
+    const size_t gw = (size_t)blockIdx.x * kPWarps + wid;
+    const size_t wbase = gw * bpw;
+    const size_t wend = wbase + bpw < n ? wbase + bpw : n;  // may be <= wbase: empty warp
+    const int nseg = (int)(bpw / 32);
+    unsigned long long* const cta_words = st.partial;
+    unsigned long long* const mailbox = st.partial + kQMailbox + (size_t)blockIdx.x * kQMailStride;
+    unsigned long long* const pickw = st.partial + kQPick;
+    const bool leader = blockIdx.x == 0;
+
+    uint32_t* const pc = reinterpret_cast<uint32_t*>(s_cache) + (size_t)wid * 8 * 5 * 32 + lane;
+    for (int i = 0; i < nseg; ++i) {
+        const size_t j = wbase + (size_t)i * 32 + lane;
+#pragma unroll
+        for (int q = 0; q < 5; ++q) pc[(i * 5 + q) * 32] = j < wend ? __ldg(pal5 + q * pstride + j) : 0u;
+    }
+    __syncwarp();
+    unsigned int vmask = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+        if (i < nseg && wbase + (size_t)i * 32 + lane < wend) vmask |= 1u << i;
+    // minDistSq[j] as the integer value of the reference's float: uint(float(sad) * float(sad)), monotone in sad
+    uint32_t msq[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) msq[i] = 0xffffffffu;
+    uint32_t c[5];
+    {
+        const uint32_t seed = st.seed_idx[0];
+#pragma unroll
+        for (int q = 0; q < 5; ++q) c[q] = __ldg(pal5 + q * pstride + seed);
+    }
+    for (uint32_t round = 1; round < K; ++round) {
+        const unsigned long long tag = (unsigned long long)round << kTagShift;
+        const double canon_u = (leader && wid == 0) ? st.canon[round - 1] : 0.0;  // fetched early: off the critical path
+        // ---- (1) the new seed's pixels, channel-planar: sp[q] = channel q of texels 0-3, 4-7, 8-11, 12-15
+        uint4 sp[3];
+        {
+            const uint32_t s1 = c[3] >> 16, s3 = c[4] >> 16;
+#pragma unroll
+            for (int q = 0; q < 3; ++q)
+                sp[q] = make_uint4(__byte_perm(c[q], 0u, c[3]), __byte_perm(c[q], 0u, s1), __byte_perm(c[q], 0u, c[4]),
+                                   __byte_perm(c[q], 0u, s3));
+        }
+        // ---- (2) min-distance update, all operands in shared memory and registers
+        unsigned int loc32 = 0;  // at most 8 values < 2^28
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            if ((vmask >> i) & 1u) {
+                const uint32_t sa = pc[(i * 5 + 3) * 32], sb = pc[(i * 5 + 4) * 32];
+                const uint32_t s1 = sa >> 16, s3 = sb >> 16;
+                unsigned int sad = 0;
+#pragma unroll
+                for (int q = 0; q < 3; ++q) {
+                    const uint32_t pw = pc[(i * 5 + q) * 32];
+                    sad = __vsadu4(__byte_perm(pw, 0u, sa), sp[q].x) + sad;
+                    sad = __vsadu4(__byte_perm(pw, 0u, s1), sp[q].y) + sad;
+                    sad = __vsadu4(__byte_perm(pw, 0u, sb), sp[q].z) + sad;
+                    sad = __vsadu4(__byte_perm(pw, 0u, s3), sp[q].w) + sad;
+                }
+                const float d = (float)sad;                                    // BlockDistanceSAD returns float(sad)
+                const uint32_t sq = __float2uint_rn(__fmul_rn(d, d));          // d * d, an integer-valued float
+                msq[i] = sq < msq[i] ? sq : msq[i];                            // std::min(d * d, minDistSq[j])
+                loc32 += msq[i];
+            }
+        }
+        const unsigned long long wt = warp_sum((unsigned long long)loc32);
+        if (lane == 0) s_w[wid] = wt;
+        __syncthreads();
+        if (wid == 0) {
+            const unsigned long long incl_w = warp_incl_scan<unsigned long long>(s_w[lane], lane);
+            s_w[lane] = incl_w;
+            if (lane == 31) st_relaxed_u64(cta_words + blockIdx.x, tag | incl_w);   // CTA total < 2^48 (launcher)
+            if (leader) {
+                // ---- (3) leader warp: all CTA totals -> S, target, owning CTA, residual
+                unsigned long long v[kPPer];
+                for (;;) {
+                    bool ok = true;
+#pragma unroll
+                    for (int k = 0; k < kPPer; ++k) {
+                        const int idx = lane * kPPer + k;
+                        unsigned long long w = tag;
+                        if (idx < G) w = ld_relaxed_u64(cta_words + idx);
+                        ok = ok && (w >> kTagShift) == (unsigned long long)round;
+                        v[k] = w & kPayloadMask;
+                    }
+                    if (__all_sync(0xffffffffu, ok)) break;
+                }
+                unsigned long long thread_tot = 0;
+#pragma unroll
+                for (int k = 0; k < kPPer; ++k) thread_tot += v[k];
+                const unsigned long long incl = warp_incl_scan<unsigned long long>(thread_tot, lane);
+                const unsigned long long S = __shfl_sync(0xffffffffu, incl, 31);
+                if (S == 0) {  // reference :299-302: fill the rest with seed 0 and stop
+                    for (uint32_t rr = round + lane; rr < K; rr += 32) st.seed_idx[rr] = st.seed_idx[0];
+                    if (lane == 0) st.status[0] = round;
+                    if (lane < 5) st_relaxed_u64(pickw + lane, tag | kStopBit);
+                } else {
+                    const double p = __dadd_rn(__dmul_rn(canon_u, (double)S), 0.0);
+                    // first j with prefix_j >= p  <=>  prefix_j >= ceil(p) on exact integers
+                    const unsigned long long target = (unsigned long long)(p <= 0.0 ? 0.0 : ceil(p));
+                    unsigned long long cum = incl - thread_tot;
+                    int hit = -1;
+#pragma unroll
+                    for (int k = 0; k < kPPer; ++k) {
+                        if (lane * kPPer + k < G && hit < 0) {
+                            if (cum + v[k] >= target) hit = k;
+                            else cum += v[k];
+                        }
+                    }
+                    const unsigned int hb = __ballot_sync(0xffffffffu, hit >= 0);
+                    int f = hb ? __ffs(hb) - 1 : (G - 1) / kPPer;                // no hit: cannot happen on exact integers
+                    int hk = __shfl_sync(0xffffffffu, hit, f);
+                    if (hk < 0) hk = (G - 1) % kPPer;
+                    const unsigned long long before = __shfl_sync(0xffffffffu, cum, f);
+                    const unsigned long long resid = target > before ? target - before : 0ull;
+                    if (lane == 0) {
+                        st.status[1] = round;                                    // rounds that drew a sample
+                        st_relaxed_u64(st.partial + kQMailbox + (size_t)(f * kPPer + hk) * kQMailStride, tag | resid);
+                    }
+                }
+            }
+        }
+        // ---- (4) wait for the pick; the CTA whose mailbox is posted first finds the block and publishes it
+        bool owner_done = false;
+        for (;;) {
+            if (wid == 0) {
+                unsigned long long w = 0;
+                unsigned int b;
+                for (;;) {
+                    if (lane < 5) w = ld_relaxed_u64(pickw + lane);
+                    else if (lane == 5 && !owner_done) w = ld_relaxed_u64(mailbox);
+                    const bool ok = lane < 6 && (w >> kTagShift) == (unsigned long long)round;
+                    b = __ballot_sync(0xffffffffu, ok);
+                    if ((b & 0x1fu) == 0x1fu || (b & 0x20u)) break;
+                }
+                if ((b & 0x1fu) == 0x1fu) {
+                    if (lane < 5) s_pickw[lane] = w;
+                    if (lane == 0) s_evt = kEvtPick;
+                } else {
+                    if (lane == 5) s_resid = w & kPayloadMask;
+                    if (lane == 0) s_evt = kEvtOwner;
+                    owner_done = true;
+                }
+            }
+            __syncthreads();
+            if (s_evt == kEvtPick) break;
+            {   // owner: first block (in block order) whose inclusive prefix inside this CTA reaches the residual
+                const unsigned long long resid = s_resid;
+                const unsigned int wb = __ballot_sync(0xffffffffu, s_w[lane] >= resid);
+                const int ow = wb ? __ffs(wb) - 1 : kPWarps - 1;
+                if (wid == ow) {
+                    const unsigned long long r = resid - (ow ? s_w[ow - 1] : 0ull);
+                    unsigned long long run = 0;
+                    bool found = false;
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const unsigned long long val = ((vmask >> i) & 1u) ? (unsigned long long)msq[i] : 0ull;
+                        const unsigned long long incl = warp_incl_scan<unsigned long long>(val, lane);
+                        const unsigned long long tot = __shfl_sync(0xffffffffu, incl, 31);
+                        const unsigned int hb = __ballot_sync(0xffffffffu, run + incl >= r);
+                        if (!found && hb) {
+                            const int f = __ffs(hb) - 1;
+                            if (lane == f) {
+                                const size_t chosen = wbase + (size_t)i * 32 + lane;
+                                uint32_t e[5];
+#pragma unroll
+                                for (int q = 0; q < 5; ++q) e[q] = pc[(i * 5 + q) * 32];
+                                st.seed_idx[round] = (uint32_t)chosen;
+                                st_relaxed_u64(pickw + 0, tag | (unsigned long long)chosen);
+                                st_relaxed_u64(pickw + 1, tag | (unsigned long long)e[0] | ((unsigned long long)(e[1] & 0xffffu) << 32));
+                                st_relaxed_u64(pickw + 2, tag | (unsigned long long)(e[1] >> 16) | ((unsigned long long)e[2] << 16));
+                                st_relaxed_u64(pickw + 3, tag | (unsigned long long)e[3] | ((unsigned long long)(e[4] & 0xffffu) << 32));
+                                st_relaxed_u64(pickw + 4, tag | (unsigned long long)(e[4] >> 16));
+                            }
+                            found = true;
+                        }
+                        run += tot;
+                    }
+                    if (!found && lane == 0) {  // cannot happen (r <= warp total); never leave the grid waiting
+                        st.seed_idx[round] = (uint32_t)(n - 1);
+#pragma unroll
+                        for (int q = 0; q < 5; ++q) st_relaxed_u64(pickw + q, tag | kStopBit);
+                        st.status[0] = round;
+                    }
+                }
+            }
+            __syncthreads();
+        }
+        const unsigned long long p0 = s_pickw[0], p1 = s_pickw[1], p2 = s_pickw[2], p3 = s_pickw[3], p4 = s_pickw[4];
+        if (p0 & kStopBit) return;
+        c[0] = (uint32_t)(p1 & 0xffffffffull);
+        c[1] = (uint32_t)((p1 >> 32) & 0xffffull) | ((uint32_t)(p2 & 0xffffull) << 16);
+        c[2] = (uint32_t)((p2 >> 16) & 0xffffffffull);
+        c[3] = (uint32_t)(p3 & 0xffffffffull);
+        c[4] = (uint32_t)((p3 >> 32) & 0xffffull) | ((uint32_t)(p4 & 0xffffull) << 16);
+    }
+}
+
 inline size_t chunk_for(size_t n, int grid) {
     size_t c = (n + grid - 1) / grid;
     return (c + kThreads - 1) / kThreads * kThreads;
@@ -801,7 +1026,7 @@ cudaError_t launch_seed_round_ldr(const SeedState& st, const uint4* planes, size
 }
 
 cudaError_t launch_seed_persistent(const SeedState& st, const uint4* planes, size_t plane_stride, const float* feat, size_t n,
-                                   int ch, bool hdr, uint32_t K, cudaStream_t s) {
+                                   int ch, bool hdr, uint32_t K, cudaStream_t s, const uint32_t* pal5, size_t pal_stride) {
     if (K <= 1) return cudaSuccess;
     static int sms = 0, coop = -1;
     if (coop < 0) {
@@ -841,6 +1066,20 @@ cudaError_t launch_seed_persistent(const SeedState& st, const uint4* planes, siz
         else if (ch == 2) fn = (const void*)seed_persistent_kernel<false, 2, true, true>;
         else if (ch == 3) fn = (const void*)seed_persistent_kernel<false, 3, true, true>;
         else fn = (const void*)seed_persistent_kernel<false, 4, true, true>;
+    }
+    // BC1 input in palette form: its own kernel (A/B: YUPVQ_SEED_NO_PAL=1 keeps the pixel-plane kernel)
+    static const bool no_pal = getenv("YUPVQ_SEED_NO_PAL") != nullptr;
+    if (pal5 != nullptr && !hdr && ch == 3 && mdreg && !tri && !no_pal && K <= 0xffffu) {
+        const size_t smem_pal = (size_t)kPWarps * 8 * 5 * 32 * 4;  // 160 KiB
+        static bool attr_pal = false;
+        if (!attr_pal) {
+            cudaError_t e = cudaFuncSetAttribute(seed_palette_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_pal);
+            if (e != cudaSuccess) return e;
+            attr_pal = true;
+        }
+        SeedState st_pal = st;
+        void* pargs[] = {&st_pal, (void*)&pal5, &pal_stride, &n, &bpw, &K};
+        return cudaLaunchCooperativeKernel((const void*)seed_palette_kernel, dim3((unsigned)g), dim3(kPThreads), pargs, smem_pal, s);
     }
     // shared-memory resident segments per warp: as many as fit in ~200 KB (after the seed table of the TRI variant)
     int cseg = 0;
