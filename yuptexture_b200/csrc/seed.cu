@@ -776,7 +776,7 @@ constexpr unsigned int kEvtPick = 1, kEvtOwner = 2;
 __global__ void __launch_bounds__(kPThreads, 1)
 seed_palette_kernel(SeedState st, const uint32_t* __restrict__ pal5, size_t pstride, size_t n, size_t bpw, uint32_t K) {
     extern __shared__ uint4 s_cache[];                 // [warp][8 segments][5 words][32 lanes]
-    __shared__ unsigned long long s_w[kPWarps];        // warp totals, then their inclusive prefix
+    __shared__ unsigned long long s_w[kPWarps];        // warp totals of the round
     __shared__ unsigned long long s_pickw[5];
     __shared__ unsigned long long s_resid;
     __shared__ unsigned int s_evt;
@@ -802,17 +802,29 @@ seed_palette_kernel(SeedState st, const uint32_t* __restrict__ pal5, size_t pstr
 #pragma unroll
     for (int i = 0; i < 8; ++i)
         if (i < nseg && wbase + (size_t)i * 32 + lane < wend) vmask |= 1u << i;
-    // minDistSq[j] as the integer value of the reference's float: uint(float(sad) * float(sad)), monotone in sad
-    uint32_t msq[8];
+    // minDistSq[j] = float(sad) * float(sad) is monotone in sad, so a lane keeps the minimum SAD per block and the
+    // running sum of the (integer-valued) squares of its blocks, which only moves when a minimum moves
+    auto sq_of = [](uint32_t sad) -> uint32_t {
+        const float d = (float)sad;                                            // BlockDistanceSAD returns float(sad)
+        return __float2uint_rn(__fmul_rn(d, d));                               // d * d, an integer-valued float < 2^28
+    };
+    uint32_t ms[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) msq[i] = 0xffffffffu;
+    for (int i = 0; i < 8; ++i) ms[i] = 0xffffffffu;
+    uint32_t lsum = 0;  // at most 8 values < 2^28
     uint32_t c[5];
     {
         const uint32_t seed = st.seed_idx[0];
 #pragma unroll
         for (int q = 0; q < 5; ++q) c[q] = __ldg(pal5 + q * pstride + seed);
     }
+#ifdef YUPVQ_SEED_TIMING
+    long long q_upd = 0, q_bar = 0, q_lead = 0, q_poll = 0, q_own = 0, t0 = 0, t1;
+#endif
     for (uint32_t round = 1; round < K; ++round) {
+#ifdef YUPVQ_SEED_TIMING
+        t0 = clock64();
+#endif
         const unsigned long long tag = (unsigned long long)round << kTagShift;
         const double canon_u = (leader && wid == 0) ? st.canon[round - 1] : 0.0;  // fetched early: off the critical path
         // ---- (1) the new seed's pixels, channel-planar: sp[q] = channel q of texels 0-3, 4-7, 8-11, 12-15
@@ -825,7 +837,6 @@ seed_palette_kernel(SeedState st, const uint32_t* __restrict__ pal5, size_t pstr
                                    __byte_perm(c[q], 0u, s3));
         }
         // ---- (2) min-distance update, all operands in shared memory and registers
-        unsigned int loc32 = 0;  // at most 8 values < 2^28
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
             if ((vmask >> i) & 1u) {
@@ -840,19 +851,24 @@ seed_palette_kernel(SeedState st, const uint32_t* __restrict__ pal5, size_t pstr
                     sad = __vsadu4(__byte_perm(pw, 0u, sb), sp[q].z) + sad;
                     sad = __vsadu4(__byte_perm(pw, 0u, s3), sp[q].w) + sad;
                 }
-                const float d = (float)sad;                                    // BlockDistanceSAD returns float(sad)
-                const uint32_t sq = __float2uint_rn(__fmul_rn(d, d));          // d * d, an integer-valued float
-                msq[i] = sq < msq[i] ? sq : msq[i];                            // std::min(d * d, minDistSq[j])
-                loc32 += msq[i];
+                if (sad < ms[i]) {                                             // std::min(d * d, minDistSq[j]) moved
+                    lsum += sq_of(sad) - (ms[i] == 0xffffffffu ? 0u : sq_of(ms[i]));
+                    ms[i] = sad;
+                }
             }
         }
-        const unsigned long long wt = warp_sum((unsigned long long)loc32);
+        // warp total < 2^36: two hardware reductions over the 16-bit halves
+        const unsigned long long wt = ((unsigned long long)__reduce_add_sync(0xffffffffu, lsum >> 16) << 16) +
+                                      (unsigned long long)__reduce_add_sync(0xffffffffu, lsum & 0xffffu);
         if (lane == 0) s_w[wid] = wt;
+        TICK(q_upd);
         __syncthreads();
+        TICK(q_bar);
         if (wid == 0) {
-            const unsigned long long incl_w = warp_incl_scan<unsigned long long>(s_w[lane], lane);
-            s_w[lane] = incl_w;
-            if (lane == 31) st_relaxed_u64(cta_words + blockIdx.x, tag | incl_w);   // CTA total < 2^48 (launcher)
+            const unsigned long long wv = s_w[lane];   // < 2^36; CTA total < 2^41
+            const unsigned long long cta_total = ((unsigned long long)__reduce_add_sync(0xffffffffu, (unsigned int)(wv >> 20)) << 20) +
+                                                 (unsigned long long)__reduce_add_sync(0xffffffffu, (unsigned int)(wv & 0xfffffu));
+            if (lane == 0) st_relaxed_u64(cta_words + blockIdx.x, tag | cta_total);
             if (leader) {
                 // ---- (3) leader warp: all CTA totals -> S, target, owning CTA, residual
                 unsigned long long v[kPPer];
@@ -903,6 +919,7 @@ seed_palette_kernel(SeedState st, const uint32_t* __restrict__ pal5, size_t pstr
                 }
             }
         }
+        TICK(q_lead);
         // ---- (4) wait for the pick; the CTA whose mailbox is posted first finds the block and publishes it
         bool owner_done = false;
         for (;;) {
@@ -926,18 +943,22 @@ seed_palette_kernel(SeedState st, const uint32_t* __restrict__ pal5, size_t pstr
                 }
             }
             __syncthreads();
+            TICK(q_poll);
             if (s_evt == kEvtPick) break;
             {   // owner: first block (in block order) whose inclusive prefix inside this CTA reaches the residual
                 const unsigned long long resid = s_resid;
-                const unsigned int wb = __ballot_sync(0xffffffffu, s_w[lane] >= resid);
+                const unsigned long long wtot = s_w[lane];
+                const unsigned long long wincl = warp_incl_scan<unsigned long long>(wtot, lane);
+                const unsigned int wb = __ballot_sync(0xffffffffu, wincl >= resid);
                 const int ow = wb ? __ffs(wb) - 1 : kPWarps - 1;
+                const unsigned long long before_w = __shfl_sync(0xffffffffu, wincl - wtot, ow);
                 if (wid == ow) {
-                    const unsigned long long r = resid - (ow ? s_w[ow - 1] : 0ull);
+                    const unsigned long long r = resid - before_w;
                     unsigned long long run = 0;
                     bool found = false;
 #pragma unroll
                     for (int i = 0; i < 8; ++i) {
-                        const unsigned long long val = ((vmask >> i) & 1u) ? (unsigned long long)msq[i] : 0ull;
+                        const unsigned long long val = ((vmask >> i) & 1u) ? (unsigned long long)sq_of(ms[i]) : 0ull;
                         const unsigned long long incl = warp_incl_scan<unsigned long long>(val, lane);
                         const unsigned long long tot = __shfl_sync(0xffffffffu, incl, 31);
                         const unsigned int hb = __ballot_sync(0xffffffffu, run + incl >= r);
@@ -968,6 +989,7 @@ seed_palette_kernel(SeedState st, const uint32_t* __restrict__ pal5, size_t pstr
                 }
             }
             __syncthreads();
+            TICK(q_own);
         }
         const unsigned long long p0 = s_pickw[0], p1 = s_pickw[1], p2 = s_pickw[2], p3 = s_pickw[3], p4 = s_pickw[4];
         if (p0 & kStopBit) return;
@@ -977,6 +999,11 @@ seed_palette_kernel(SeedState st, const uint32_t* __restrict__ pal5, size_t pstr
         c[3] = (uint32_t)(p3 & 0xffffffffull);
         c[4] = (uint32_t)((p3 >> 32) & 0xffffull) | ((uint32_t)(p4 & 0xffffull) << 16);
     }
+#ifdef YUPVQ_SEED_TIMING
+    if (tid == 0 && (blockIdx.x == 0 || blockIdx.x == 77))
+        printf("cta %d: cycles/round update %lld, barrier %lld, leader %lld, poll %lld, owner %lld\n", blockIdx.x, q_upd / (K - 1),
+               q_bar / (K - 1), q_lead / (K - 1), q_poll / (K - 1), q_own / (K - 1));
+#endif
 }
 
 inline size_t chunk_for(size_t n, int grid) {
