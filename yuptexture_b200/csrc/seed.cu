@@ -770,6 +770,19 @@ seed_persistent_kernel(SeedState st, const uint4* __restrict__ planes, size_t st
 //      CTA finds the block in its own registers (warp totals are still in shared memory) and publishes the pick
 //      TOGETHER with the seed's 20 bytes taken from its shared memory.  Three round trips, every message a
 //      self-validating tagged 64-bit word (16-bit round tag + 48-bit payload): no fences, no min_dist array.
+// PRMT with raw selector nibbles (all in 0..3 here, upper 16 bits ignored by the hardware): __byte_perm would mask the
+// selector first.  VABSDIFF4 with the accumulate operand spelled out: one instruction per four byte pairs.
+__device__ __forceinline__ uint32_t prmt_lo(uint32_t a, uint32_t sel) {
+    uint32_t d;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(0u), "r"(sel));
+    return d;
+}
+__device__ __forceinline__ uint32_t sad4_acc(uint32_t a, uint32_t b, uint32_t acc) {
+    uint32_t d;
+    asm("vabsdiff4.u32.u32.u32.add %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(acc));
+    return d;
+}
+
 constexpr int kQMailbox = 256, kQMailStride = 16, kQPick = 4096;  // u64 offsets in SeedState::partial (CTA words at 0)
 constexpr unsigned int kEvtPick = 1, kEvtOwner = 2;
 
@@ -833,8 +846,7 @@ seed_palette_kernel(SeedState st, const uint32_t* __restrict__ pal5, size_t pstr
             const uint32_t s1 = c[3] >> 16, s3 = c[4] >> 16;
 #pragma unroll
             for (int q = 0; q < 3; ++q)
-                sp[q] = make_uint4(__byte_perm(c[q], 0u, c[3]), __byte_perm(c[q], 0u, s1), __byte_perm(c[q], 0u, c[4]),
-                                   __byte_perm(c[q], 0u, s3));
+                sp[q] = make_uint4(prmt_lo(c[q], c[3]), prmt_lo(c[q], s1), prmt_lo(c[q], c[4]), prmt_lo(c[q], s3));
         }
         // ---- (2) min-distance update, all operands in shared memory and registers
 #pragma unroll
@@ -842,15 +854,16 @@ seed_palette_kernel(SeedState st, const uint32_t* __restrict__ pal5, size_t pstr
             if ((vmask >> i) & 1u) {
                 const uint32_t sa = pc[(i * 5 + 3) * 32], sb = pc[(i * 5 + 4) * 32];
                 const uint32_t s1 = sa >> 16, s3 = sb >> 16;
-                unsigned int sad = 0;
+                uint32_t part[3];  // one accumulate chain per channel
 #pragma unroll
                 for (int q = 0; q < 3; ++q) {
                     const uint32_t pw = pc[(i * 5 + q) * 32];
-                    sad = __vsadu4(__byte_perm(pw, 0u, sa), sp[q].x) + sad;
-                    sad = __vsadu4(__byte_perm(pw, 0u, s1), sp[q].y) + sad;
-                    sad = __vsadu4(__byte_perm(pw, 0u, sb), sp[q].z) + sad;
-                    sad = __vsadu4(__byte_perm(pw, 0u, s3), sp[q].w) + sad;
+                    part[q] = sad4_acc(prmt_lo(pw, sa), sp[q].x, 0u);
+                    part[q] = sad4_acc(prmt_lo(pw, s1), sp[q].y, part[q]);
+                    part[q] = sad4_acc(prmt_lo(pw, sb), sp[q].z, part[q]);
+                    part[q] = sad4_acc(prmt_lo(pw, s3), sp[q].w, part[q]);
                 }
+                const unsigned int sad = part[0] + part[1] + part[2];
                 if (sad < ms[i]) {                                             // std::min(d * d, minDistSq[j]) moved
                     lsum += sq_of(sad) - (ms[i] == 0xffffffffu ? 0u : sq_of(ms[i]));
                     ms[i] = sad;
