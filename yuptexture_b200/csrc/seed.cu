@@ -967,21 +967,37 @@ seed_palette_kernel(SeedState st, const uint32_t* __restrict__ pal5, size_t pstr
                 const unsigned long long before_w = __shfl_sync(0xffffffffu, wincl - wtot, ow);
                 if (wid == ow) {
                     const unsigned long long r = resid - before_w;
+                    // segment totals by hardware reduction (independent, pipelined), then ONE scan inside the segment
+                    // that holds the residual
+                    uint32_t v32[8];
                     unsigned long long run = 0;
-                    bool found = false;
+                    int si = -1;
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) v32[i] = ((vmask >> i) & 1u) ? sq_of(ms[i]) : 0u;
 #pragma unroll
                     for (int i = 0; i < 8; ++i) {
-                        const unsigned long long val = ((vmask >> i) & 1u) ? (unsigned long long)sq_of(ms[i]) : 0ull;
-                        const unsigned long long incl = warp_incl_scan<unsigned long long>(val, lane);
-                        const unsigned long long tot = __shfl_sync(0xffffffffu, incl, 31);
+                        const unsigned long long tot = ((unsigned long long)__reduce_add_sync(0xffffffffu, v32[i] >> 16) << 16) +
+                                                       (unsigned long long)__reduce_add_sync(0xffffffffu, v32[i] & 0xffffu);
+                        if (si < 0) {
+                            if (run + tot >= r) si = i;
+                            else run += tot;
+                        }
+                    }
+                    bool found = false;
+                    if (si >= 0) {
+                        uint32_t v = 0;
+#pragma unroll
+                        for (int i = 0; i < 8; ++i)
+                            if (i == si) v = v32[i];
+                        const unsigned long long incl = warp_incl_scan<unsigned long long>((unsigned long long)v, lane);
                         const unsigned int hb = __ballot_sync(0xffffffffu, run + incl >= r);
-                        if (!found && hb) {
-                            const int f = __ffs(hb) - 1;
-                            if (lane == f) {
-                                const size_t chosen = wbase + (size_t)i * 32 + lane;
+                        if (hb) {
+                            found = true;
+                            if (lane == __ffs(hb) - 1) {
+                                const size_t chosen = wbase + (size_t)si * 32 + lane;
                                 uint32_t e[5];
 #pragma unroll
-                                for (int q = 0; q < 5; ++q) e[q] = pc[(i * 5 + q) * 32];
+                                for (int q = 0; q < 5; ++q) e[q] = pc[(si * 5 + q) * 32];
                                 st.seed_idx[round] = (uint32_t)chosen;
                                 st_relaxed_u64(pickw + 0, tag | (unsigned long long)chosen);
                                 st_relaxed_u64(pickw + 1, tag | (unsigned long long)e[0] | ((unsigned long long)(e[1] & 0xffffu) << 32));
@@ -989,9 +1005,7 @@ seed_palette_kernel(SeedState st, const uint32_t* __restrict__ pal5, size_t pstr
                                 st_relaxed_u64(pickw + 3, tag | (unsigned long long)e[3] | ((unsigned long long)(e[4] & 0xffffu) << 32));
                                 st_relaxed_u64(pickw + 4, tag | (unsigned long long)(e[4] >> 16));
                             }
-                            found = true;
                         }
-                        run += tot;
                     }
                     if (!found && lane == 0) {  // cannot happen (r <= warp total); never leave the grid waiting
                         st.seed_idx[round] = (uint32_t)(n - 1);
