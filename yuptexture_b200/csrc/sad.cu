@@ -24,11 +24,19 @@ namespace {
 constexpr int kSadThreads = 256;
 constexpr int kSadChunk = 512;  // centroids staged in shared memory at a time
 
+// VABSDIFF4.U8.ACC with the accumulate operand spelled out: `__vsadu4(a, b) + acc` compiles to a zero-accumulate
+// VABSDIFF4 plus an IADD3 tree, i.e. ~1.6 integer instructions per four byte pairs instead of one.
+__device__ __forceinline__ uint32_t sad4_acc(uint32_t a, uint32_t b, uint32_t acc) {
+    uint32_t d;
+    asm("vabsdiff4.u32.u32.u32.add %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(acc));
+    return d;
+}
+
 __device__ __forceinline__ uint32_t sad16(const uint4& a, const uint4& b, uint32_t acc) {
-    acc = __vsadu4(a.x, b.x) + acc;
-    acc = __vsadu4(a.y, b.y) + acc;
-    acc = __vsadu4(a.z, b.z) + acc;
-    acc = __vsadu4(a.w, b.w) + acc;
+    acc = sad4_acc(a.x, b.x, acc);
+    acc = sad4_acc(a.y, b.y, acc);
+    acc = sad4_acc(a.z, b.z, acc);
+    acc = sad4_acc(a.w, b.w, acc);
     return acc;
 }
 
