@@ -25,6 +25,20 @@ namespace {
 constexpr int kThreads = 256;
 constexpr int kMaxGrid = YUPVQ_NUM_SMS * 8;
 
+// PRMT with raw selector nibbles (all in 0..3 here, upper 16 bits ignored by the hardware): __byte_perm would mask the
+// selector first.  VABSDIFF4 with the accumulate operand spelled out: one instruction per four byte pairs.
+__device__ __forceinline__ uint32_t prmt_lo(uint32_t a, uint32_t sel) {
+    uint32_t d;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(0u), "r"(sel));
+    return d;
+}
+__device__ __forceinline__ uint32_t sad4_acc(uint32_t a, uint32_t b, uint32_t acc) {
+    uint32_t d;
+    asm("vabsdiff4.u32.u32.u32.add %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(acc));
+    return d;
+}
+
+
 __global__ void seed_init_kernel(float* min_dist, size_t n, unsigned int* counter, uint32_t* status, uint32_t* seed_idx,
                                  uint32_t first_idx) {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -191,10 +205,10 @@ __global__ void __launch_bounds__(kThreads) seed_round_ldr_kernel(SeedState st, 
 #pragma unroll
         for (int q = 0; q < CH; ++q) {
             const uint4 v = planes[q * stride + j];
-            sad = __vsadu4(v.x, sp[q].x) + sad;
-            sad = __vsadu4(v.y, sp[q].y) + sad;
-            sad = __vsadu4(v.z, sp[q].z) + sad;
-            sad = __vsadu4(v.w, sp[q].w) + sad;
+            sad = sad4_acc(v.x, sp[q].x, sad);
+            sad = sad4_acc(v.y, sp[q].y, sad);
+            sad = sad4_acc(v.z, sp[q].z, sad);
+            sad = sad4_acc(v.w, sp[q].w, sad);
         }
         const float d = (float)sad;                       // BlockDistanceSAD returns float(sad)
         const float m = fminf(__fmul_rn(d, d), st.min_dist[j]);  // std::min(d * d, minDistSq[j])
@@ -405,10 +419,10 @@ seed_persistent_kernel(SeedState st, const uint4* __restrict__ planes, size_t st
 #pragma unroll
                 for (int q = 0; q < CH; ++q) {
                     const uint4 v = i < cseg ? s_cache[((wid * cseg + i) * CH + q) * 32 + lane] : ldg_nc_v4(planes + q * stride + j);
-                    sad = __vsadu4(v.x, sp[q].x) + sad;
-                    sad = __vsadu4(v.y, sp[q].y) + sad;
-                    sad = __vsadu4(v.z, sp[q].z) + sad;
-                    sad = __vsadu4(v.w, sp[q].w) + sad;
+                    sad = sad4_acc(v.x, sp[q].x, sad);
+                    sad = sad4_acc(v.y, sp[q].y, sad);
+                    sad = sad4_acc(v.z, sp[q].z, sad);
+                    sad = sad4_acc(v.w, sp[q].w, sad);
                 }
                 const float d = (float)sad;                                    // BlockDistanceSAD returns float(sad)
                 return __fmul_rn(d, d);
@@ -421,10 +435,10 @@ seed_persistent_kernel(SeedState st, const uint4* __restrict__ planes, size_t st
 #pragma unroll
                 for (int q = 0; q < CH; ++q) {
                     const uint4 v = seeds_s[(size_t)tid * CH + q];
-                    sad = __vsadu4(v.x, sp[q].x) + sad;
-                    sad = __vsadu4(v.y, sp[q].y) + sad;
-                    sad = __vsadu4(v.z, sp[q].z) + sad;
-                    sad = __vsadu4(v.w, sp[q].w) + sad;
+                    sad = sad4_acc(v.x, sp[q].x, sad);
+                    sad = sad4_acc(v.y, sp[q].y, sad);
+                    sad = sad4_acc(v.z, sp[q].z, sad);
+                    sad = sad4_acc(v.w, sp[q].w, sad);
                 }
                 tri_s[tid] = sad;
             }
@@ -445,19 +459,19 @@ seed_persistent_kernel(SeedState st, const uint4* __restrict__ planes, size_t st
 #pragma unroll
                             for (int q = 0; q < CH; ++q) {
                                 const uint4 v = sc[(i * CH + q) * 32];
-                                sad = __vsadu4(v.x, sp[q].x) + sad;
-                                sad = __vsadu4(v.y, sp[q].y) + sad;
-                                sad = __vsadu4(v.z, sp[q].z) + sad;
-                                sad = __vsadu4(v.w, sp[q].w) + sad;
+                                sad = sad4_acc(v.x, sp[q].x, sad);
+                                sad = sad4_acc(v.y, sp[q].y, sad);
+                                sad = sad4_acc(v.z, sp[q].z, sad);
+                                sad = sad4_acc(v.w, sp[q].w, sad);
                             }
                         } else {
 #pragma unroll
                             for (int q = 0; q < CH; ++q) {
                                 const uint4 v = ldg_nc_v4(gp[q] + i * 32);
-                                sad = __vsadu4(v.x, sp[q].x) + sad;
-                                sad = __vsadu4(v.y, sp[q].y) + sad;
-                                sad = __vsadu4(v.z, sp[q].z) + sad;
-                                sad = __vsadu4(v.w, sp[q].w) + sad;
+                                sad = sad4_acc(v.x, sp[q].x, sad);
+                                sad = sad4_acc(v.y, sp[q].y, sad);
+                                sad = sad4_acc(v.z, sp[q].z, sad);
+                                sad = sad4_acc(v.w, sp[q].w, sad);
                             }
                         }
                         if (sad < ms) {                                        // std::min(d * d, minDistSq[j]) moved
@@ -486,19 +500,19 @@ seed_persistent_kernel(SeedState st, const uint4* __restrict__ planes, size_t st
 #pragma unroll
                         for (int q = 0; q < CH; ++q) {
                             const uint4 v = sc[(i * CH + q) * 32];
-                            sad = __vsadu4(v.x, sp[q].x) + sad;
-                            sad = __vsadu4(v.y, sp[q].y) + sad;
-                            sad = __vsadu4(v.z, sp[q].z) + sad;
-                            sad = __vsadu4(v.w, sp[q].w) + sad;
+                            sad = sad4_acc(v.x, sp[q].x, sad);
+                            sad = sad4_acc(v.y, sp[q].y, sad);
+                            sad = sad4_acc(v.z, sp[q].z, sad);
+                            sad = sad4_acc(v.w, sp[q].w, sad);
                         }
                     } else {
 #pragma unroll
                         for (int q = 0; q < CH; ++q) {
                             const uint4 v = ldg_nc_v4(gp[q] + i * 32);
-                            sad = __vsadu4(v.x, sp[q].x) + sad;
-                            sad = __vsadu4(v.y, sp[q].y) + sad;
-                            sad = __vsadu4(v.z, sp[q].z) + sad;
-                            sad = __vsadu4(v.w, sp[q].w) + sad;
+                            sad = sad4_acc(v.x, sp[q].x, sad);
+                            sad = sad4_acc(v.y, sp[q].y, sad);
+                            sad = sad4_acc(v.z, sp[q].z, sad);
+                            sad = sad4_acc(v.w, sp[q].w, sad);
                         }
                     }
                     const float d = (float)sad;                                // BlockDistanceSAD returns float(sad)
@@ -770,19 +784,6 @@ seed_persistent_kernel(SeedState st, const uint4* __restrict__ planes, size_t st
 //      CTA finds the block in its own registers (warp totals are still in shared memory) and publishes the pick
 //      TOGETHER with the seed's 20 bytes taken from its shared memory.  Three round trips, every message a
 //      self-validating tagged 64-bit word (16-bit round tag + 48-bit payload): no fences, no min_dist array.
-// PRMT with raw selector nibbles (all in 0..3 here, upper 16 bits ignored by the hardware): __byte_perm would mask the
-// selector first.  VABSDIFF4 with the accumulate operand spelled out: one instruction per four byte pairs.
-__device__ __forceinline__ uint32_t prmt_lo(uint32_t a, uint32_t sel) {
-    uint32_t d;
-    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(0u), "r"(sel));
-    return d;
-}
-__device__ __forceinline__ uint32_t sad4_acc(uint32_t a, uint32_t b, uint32_t acc) {
-    uint32_t d;
-    asm("vabsdiff4.u32.u32.u32.add %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(acc));
-    return d;
-}
-
 constexpr int kQMailbox = 256, kQMailStride = 16, kQPick = 4096;  // u64 offsets in SeedState::partial (CTA words at 0)
 constexpr unsigned int kEvtPick = 1, kEvtOwner = 2;
 
