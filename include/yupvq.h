@@ -189,9 +189,13 @@ YUPVQ_API int yupvq_gather_codebook(yupvq_ctx* ctx, const uint8_t* codebook, uin
  * file) hands the 128 bytes to every rank, then every rank calls yupvq_comm_init. */
 YUPVQ_API int yupvq_comm_unique_id(yupvq_ctx* ctx, uint8_t out_id[128]);
 YUPVQ_API int yupvq_comm_init(yupvq_ctx* ctx, const uint8_t id[128], int n_ranks, int rank);
+/* Only the two *_sharded entry points below use the communicator.  Every other call on a context that has one
+ * (yupvq_encode_bcn, yupvq_build_codebook[_hdr], yupvq_encode_bcn_batch, ...) stays rank-local: ranks may encode
+ * unrelated textures with them at the same time. */
 /* Block-sharded LDR VQ: this rank holds blocks [first_block, first_block + n_local) of a texture
  * of n_total blocks; the whole texture's BCn bytes are passed on every rank (seeding is replicated
- * and integer-exact, so every rank draws the same seeds with no communication).  Per Lloyd pass
+ * and integer-exact, so every rank draws the same seeds with no communication; with cfg->seed == 0 rank 0 draws
+ * the std::random_device value and broadcasts it, so the ranks still share one RNG stream).  Per Lloyd pass
  * the K x 64 fixed-point sums, K counts and the changed flag are all-reduced over NCCL.
  * out_indices receives this rank's n_local indices. */
 YUPVQ_API int yupvq_encode_bcn_sharded(yupvq_ctx* ctx, const uint8_t* bc_blocks, size_t n_total, size_t first_block,

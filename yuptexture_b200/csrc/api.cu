@@ -16,10 +16,36 @@
 #include <vector>
 
 #include "../../include/yupvq.h"
+#include "host_util.h"
 #include "kernels.h"
 #include "nccl_dyn.h"
 
 using namespace yupvq;
+
+namespace yupvq {
+const DebugOpts& debug_opts() {
+    static const DebugOpts opts = [] {   // parsed once (thread-safe static initialisation)
+        DebugOpts o;
+        auto on = [](const char* name) { return getenv(name) != nullptr; };
+        o.seed_per_round = on("YUPVQ_SEED_PER_ROUND");
+        o.seed_tri = on("YUPVQ_SEED_TRI");
+        o.seed_no_tri = on("YUPVQ_SEED_NO_TRI");
+        o.seed_no_pal = on("YUPVQ_SEED_NO_PAL");
+        o.seed_no_smem = on("YUPVQ_SEED_NO_SMEM");
+        o.seed_no_cluster = on("YUPVQ_SEED_NO_CLUSTER");
+        o.lloyd_sync = on("YUPVQ_LLOYD_SYNC");
+        o.no_delta = on("YUPVQ_NO_DELTA");
+        o.no_rgb48 = on("YUPVQ_NO_RGB48");
+        o.no_split_decode = on("YUPVQ_NO_SPLIT_DECODE");
+        o.batch_per_texture = on("YUPVQ_BATCH_PER_TEXTURE");
+        o.no_tail_fuse = on("YUPVQ_NO_TAIL_FUSE");
+        o.no_overlap = on("YUPVQ_NO_OVERLAP");
+        if (const char* v = getenv("YUPVQ_ASYNC_DBG")) o.async_dbg = atoi(v);
+        return o;
+    }();
+    return opts;
+}
+}  // namespace yupvq
 
 namespace {
 
@@ -259,7 +285,7 @@ int run_seeding(yupvq_ctx* ctx, const Blocks& b, uint32_t K, const Draws& dr, bo
     st.grid = grid;
     LAUNCH(launch_seed_init(st, n, dr.first, ctx->stream));
     // one persistent cooperative kernel for all K-1 rounds; per-round launches only where that is not possible
-    static const bool per_round = getenv("YUPVQ_SEED_PER_ROUND") != nullptr;  // A/B timing and tests
+    const bool per_round = debug_opts().seed_per_round;  // A/B timing and tests
     cudaError_t pe = per_round ? cudaErrorNotSupported
                                : launch_seed_persistent(st, b.planes, b.stride, b.feat, n, b.ch, hdr, K, ctx->stream, b.pal5, b.pal_stride);
     if (pe == cudaSuccess) {
@@ -428,8 +454,12 @@ int assign_blocks(yupvq_ctx* ctx, const float* feat, size_t n, const float* cent
 // ---- K3..K5: Lloyd iterations ----------------------------------------------------------------------
 // break_after: LDR breaks on (!changed && iter > 0), HDR on (!changed && iter > 1)
 // (src/vq_encoder.cpp:341 vs :572).  cent (device, K x 64) holds the seeds on entry.
+// `sharded`: b is this rank's block range of a texture spread over the context's communicator (set only by
+// yupvq_encode_bcn_sharded); every other entry point ignores ctx->comm, so contexts with a communicator can
+// still encode independent textures.
 int run_lloyd(yupvq_ctx* ctx, const Blocks& b, size_t n_total, size_t first_block, uint32_t K, uint32_t max_iter,
-              uint32_t break_after, int assign_mode, float* cent, yupvq_stats* stats) {
+              uint32_t break_after, int assign_mode, float* cent, yupvq_stats* stats, bool sharded = false) {
+    if (sharded && !ctx->comm) sharded = false;
     const size_t n = b.n;
     const bool tensor = use_tensor(assign_mode, n, K);
     CK(ctx->assign.ensure(std::max<size_t>(1, n) * 4));
@@ -452,7 +482,7 @@ int run_lloyd(yupvq_ctx* ctx, const Blocks& b, size_t n_total, size_t first_bloc
     CK(cudaStreamSynchronize(ctx->stream));
     float max_abs;
     std::memcpy(&max_abs, ctx->h_small, 4);
-    if (ctx->comm) {
+    if (sharded) {
         // the scale must be identical on every rank: use the global maximum
         CK(cudaMemcpyAsync(flags + F_SPARE, ctx->h_small, 4, cudaMemcpyHostToDevice, ctx->stream));
         if (ctx->nccl.all_reduce_max_u32(ctx->comm, flags + F_SPARE, 1, ctx->stream)) return ctx->fail("ncclAllReduce(max) failed");
@@ -463,22 +493,20 @@ int run_lloyd(yupvq_ctx* ctx, const Blocks& b, size_t n_total, size_t first_bloc
     const int shift = fixed_shift(n_total, max_abs);
 
     uint32_t passes = 0;
-    static const bool force_sync = getenv("YUPVQ_LLOYD_SYNC") != nullptr;  // A/B timing only
-    const bool async_loop = !ctx->comm && !force_sync;
+    const DebugOpts& dbg = debug_opts();
+    const bool async_loop = !sharded && !dbg.lloyd_sync;
     if (async_loop) {
         // Single GPU: every pass is enqueued without a host round trip.  The reference's convergence test
         // (between assign and update) runs on the device (launch_lloyd_control); once it fires, the kernels
         // of that pass' update and of all later passes return immediately.  The host looks at the stop word
         // only a few times, to avoid enqueueing dozens of no-op passes for textures that converge at once.
         uint32_t* ctl = flags + F_CTL;
-        static const int dbg_async0 = getenv("YUPVQ_ASYNC_DBG") ? atoi(getenv("YUPVQ_ASYNC_DBG")) : 0;
-        const uint32_t* stopk = (dbg_async0 & 4) ? nullptr : ctl;
+        const uint32_t* stopk = ctl;
         CK(cudaMemsetAsync(ctl, 0, 12 + 8, ctx->stream));  // stop, passes, empty | ambiguous-row count, ticket
         CK(cudaMemsetAsync(flags, 0, 8, ctx->stream));  // changed, empty
         // Delta update (tensor engine): the assignment kernels list the rows that moved; from the second pass on the
         // update touches only those (exact: integer sums), unless more than a quarter of the blocks moved.
-        static const bool no_delta = getenv("YUPVQ_NO_DELTA") != nullptr;  // A/B timing and tests
-        const bool delta = tensor && !no_delta && n < 0xffffffffull;
+        const bool delta = tensor && !dbg.no_delta && n < 0xffffffffull;
         TcBatch dl = tc_single();
         uint32_t* dctl = nullptr;
         if (delta) {
@@ -504,14 +532,12 @@ int run_lloyd(yupvq_ctx* ctx, const Blocks& b, size_t n_total, size_t first_bloc
                 LAUNCH(launch_accumulate(b.feat, n, assign, K, shift, acc, flags, stopk, ctx->stream));
             }
             LAUNCH(launch_lloyd_control(acc, K, iter, break_after, flags, ctl, ctx->stream));
-            static const int dbg_async2 = getenv("YUPVQ_ASYNC_DBG") ? atoi(getenv("YUPVQ_ASYNC_DBG")) : 0;
-            if (tensor && !(dbg_async2 & 2))  // errors[i] = distance to the assigned centroid, before the update (:336); only if a reseed needs them
+            if (tensor)  // errors[i] = distance to the assigned centroid, before the update (:336); only if a reseed needs them
                 LAUNCH(launch_exact_errors(b.feat, n, cent, assign, errors, stopk, ctl + 2, ctx->stream));
             LAUNCH(launch_finalize_centroids(acc, K, shift, cent, flags, stopk, ctx->stream));
             LAUNCH(launch_reseed_empty(b.feat, n, errors, acc, K, cent, flags, stopk, ctx->stream));
-            static const int dbg_async = getenv("YUPVQ_ASYNC_DBG") ? atoi(getenv("YUPVQ_ASYNC_DBG")) : 0;
-            if (dbg_async & 1) CK(cudaStreamSynchronize(ctx->stream));
-            if ((dbg_async & 8) && delta) {  // per-pass delta statistics (debug)
+            if (dbg.async_dbg & 1) CK(cudaStreamSynchronize(ctx->stream));
+            if ((dbg.async_dbg & 8) && delta) {  // per-pass delta statistics (debug)
                 uint32_t w[2];
                 CK(cudaMemcpyAsync(w, dctl + 32, 8, cudaMemcpyDeviceToHost, ctx->stream));
                 CK(cudaStreamSynchronize(ctx->stream));
@@ -533,7 +559,7 @@ int run_lloyd(yupvq_ctx* ctx, const Blocks& b, size_t n_total, size_t first_bloc
             // speculatively so one sync and one all-reduce per pass carry both.
             CK(cudaMemsetAsync(acc, 0, acc_words * 8, ctx->stream));
             LAUNCH(launch_accumulate(b.feat, n, assign, K, shift, acc, flags, nullptr, ctx->stream));
-            if (ctx->comm && ctx->nccl.all_reduce_sum_i64(ctx->comm, acc, acc_words, ctx->stream)) return ctx->fail("ncclAllReduce(sum) failed");
+            if (sharded && ctx->nccl.all_reduce_sum_i64(ctx->comm, acc, acc_words, ctx->stream)) return ctx->fail("ncclAllReduce(sum) failed");
             LAUNCH(launch_count_empty(acc, K, flags + F_SPARE, ctx->stream));
             CK(cudaMemcpyAsync(ctx->h_small, acc + (size_t)K * 65, 8, cudaMemcpyDeviceToHost, ctx->stream));
             CK(cudaMemcpyAsync(ctx->h_small + 2, flags + F_SPARE, 4, cudaMemcpyDeviceToHost, ctx->stream));
@@ -544,7 +570,7 @@ int run_lloyd(yupvq_ctx* ctx, const Blocks& b, size_t n_total, size_t first_bloc
             if (tensor && ctx->h_small[2] != 0)  // errors[i] = distance to the assigned centroid, before the update (:336)
                 LAUNCH(launch_exact_errors(b.feat, n, cent, assign, errors, nullptr, nullptr, ctx->stream));
             LAUNCH(launch_finalize_centroids(acc, K, shift, cent, flags, nullptr, ctx->stream));
-            if (!ctx->comm) {
+            if (!sharded) {
                 LAUNCH(launch_reseed_empty(b.feat, n, errors, acc, K, cent, flags, nullptr, ctx->stream));
             } else if (reseed_sharded(ctx, b, first_block, K, cent, errors, acc, flags)) {
                 return 1;
@@ -705,8 +731,7 @@ int check_cfg(yupvq_ctx* ctx, const yupvq_config* cfg, size_t n, int ch) {
 // Features built by our own decode / conversion kernels carry alpha == 1.0f exactly when the input has 1 or 3 channels
 // (convert.cu block_features / float path), so the 16 alpha columns vanish after centring: 48-column tensor operands.
 int rgb_layout(int channels) {
-    static const bool off = getenv("YUPVQ_NO_RGB48") != nullptr;  // A/B timing and tests
-    return (!off && (channels == 1 || channels == 3)) ? 1 : 0;
+    return (!debug_opts().no_rgb48 && (channels == 1 || channels == 3)) ? 1 : 0;
 }
 
 struct Scope {  // selects the context's device for the duration of a call
@@ -767,6 +792,7 @@ int yupvq_create(int device, yupvq_ctx** out) {
         return 1;
     }
     Scope scope(device);
+    (void)debug_opts();  // the only place the environment is read
     yupvq_ctx* ctx = new yupvq_ctx();
     ctx->device = device;
     bool ok = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) == cudaSuccess;
@@ -877,7 +903,7 @@ int yupvq_encode_bcn(yupvq_ctx* ctx, const uint8_t* bc_blocks, size_t n_blocks, 
     CK(ctx->planes.ensure(n_blocks * 16 * channels));
     CK(ctx->feat.ensure(n_blocks * 256));
     // Without sampling the decode is split: pixel planes now (all the seeding reads), Oklab features after the seeding.
-    static const bool no_split = getenv("YUPVQ_NO_SPLIT_DECODE") != nullptr;  // A/B timing
+    const bool no_split = debug_opts().no_split_decode;  // A/B timing
     const bool sampling = cfg->sample_ratio < 1.0f && cfg->sample_ratio > 0.0f;
     const bool split = !sampling && !no_split;
     const bool sad = cfg->metric == YUPVQ_METRIC_SAD;
@@ -1021,7 +1047,7 @@ int yupvq_build_codebook(yupvq_ctx* ctx, const uint8_t* pixel_blocks, size_t n_b
     CK(ctx->planes.ensure(n_blocks * 16 * channels));
     CK(ctx->feat.ensure(n_blocks * 256));
     // as in yupvq_encode_bcn: pixel planes before the seeding, features after it (no sampling)
-    static const bool no_split = getenv("YUPVQ_NO_SPLIT_DECODE") != nullptr;
+    const bool no_split = debug_opts().no_split_decode;
     const bool sampling = cfg->sample_ratio < 1.0f && cfg->sample_ratio > 0.0f;
     const bool split = !sampling && !no_split;
     const bool sad = cfg->metric == YUPVQ_METRIC_SAD;
@@ -1501,7 +1527,19 @@ int yupvq_encode_bcn_sharded(yupvq_ctx* ctx, const uint8_t* bc_blocks, size_t n_
     all.feat = nullptr;
     if (attach_palette_form(ctx, all, bc_dev, bc_format, channels)) return 1;
     size_t n_used;
-    Draws dr = make_draws(n_total, K, 1.0f, cfg->seed, &n_used);
+    uint64_t seed = cfg->seed;
+    if (seed == 0 && ctx->comm) {
+        // seed 0 = std::random_device (src/vq_encoder.cpp:24-26): the ranks replicate the seeding, so they must all draw
+        // from ONE stream -- rank 0 draws the mt19937 seed and broadcasts it
+        uint32_t* spare = ctx->small.as<uint32_t>() + F_SPARE;
+        ctx->h_small[8] = (uint32_t)std::random_device{}();
+        CK(cudaMemcpyAsync(spare, ctx->h_small + 8, 4, cudaMemcpyHostToDevice, ctx->stream));
+        if (ctx->nccl.broadcast_bytes(ctx->comm, spare, 4, 0, ctx->stream)) return ctx->fail("ncclBroadcast(seed) failed");
+        CK(cudaMemcpyAsync(ctx->h_small + 8, spare, 4, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+        seed = (1ull << 32) | ctx->h_small[8];   // make_draws seeds mt19937 with the low 32 bits of a non-zero seed
+    }
+    Draws dr = make_draws(n_total, K, 1.0f, seed, &n_used);
     uint32_t rounds = 0;
     if (run_seeding(ctx, all, K, dr, false, stats ? &rounds : nullptr)) return 1;
     CK(ctx->cent.ensure((size_t)K * 256));
@@ -1517,7 +1555,7 @@ int yupvq_encode_bcn_sharded(yupvq_ctx* ctx, const uint8_t* bc_blocks, size_t n_
     mine.n = n_local;
     mine.feat = ctx->feat.as<float>();
     mine.planes = all.planes + first_block;  // stride unchanged
-    if (run_lloyd(ctx, mine, n_total, first_block, K, cfg->max_iterations, 0u, cfg->assign_mode, ctx->cent.as<float>(), stats)) return 1;
+    if (run_lloyd(ctx, mine, n_total, first_block, K, cfg->max_iterations, 0u, cfg->assign_mode, ctx->cent.as<float>(), stats, true)) return 1;
     const int t4 = tm.mark();
     CK(ctx->cent_px.ensure((size_t)K * 16 * channels));
     LAUNCH(launch_oklab_to_pixels(ctx->cent.as<float>(), K, channels, ctx->cent_px.as<uint8_t>(), ctx->stream));
@@ -1684,7 +1722,7 @@ int yupvq_encode_bcn_batch_sharded(yupvq_ctx* ctx, const uint8_t* const* bc_bloc
     uint32_t* sticky_d = tflags_d + 4 * T;
     std::vector<uint32_t> passes(T, 0);
     uint32_t reseeds_async = 0;
-    static const bool force_sync = getenv("YUPVQ_LLOYD_SYNC") != nullptr;  // A/B timing and tests
+    const bool force_sync = debug_opts().lloyd_sync;  // A/B timing and tests
     if (ctx->comm) {  // the seeds, should the pass loop have to be redone synchronously
         CK(ctx->bt_cent0.ensure(T * (size_t)K * 256));
         CK(cudaMemcpyAsync(ctx->bt_cent0.p, ctx->bt_cent.p, T * (size_t)K * 256, cudaMemcpyDeviceToDevice, ctx->stream));
@@ -1804,7 +1842,7 @@ int yupvq_encode_bcn_batch_sharded(yupvq_ctx* ctx, const uint8_t* const* bc_bloc
     // Whole-batch launches: when the shards are tile-aligned the rows of all textures are one matrix, so every kernel
     // of a pass is launched ONCE for the batch (the front-end reloads its resident centroid operand when a CTA crosses
     // into the next texture) -- a pass costs the same handful of launches whatever the number of textures.
-    static const bool no_fuse = getenv("YUPVQ_BATCH_PER_TEXTURE") != nullptr;  // A/B timing and tests
+    const bool no_fuse = debug_opts().batch_per_texture;  // A/B timing and tests
     const uint32_t k_pad = tc_padded_k(K);
     const bool fused = !no_fuse && tensor && n_local > 0 && n_local % 128 == 0 && k_pad <= 512 && accumulate_batch_supported(n_local, K) &&
                        T * n_local < 0xffffffffull;
@@ -1867,7 +1905,7 @@ int yupvq_encode_bcn_batch_sharded(yupvq_ctx* ctx, const uint8_t* const* bc_bloc
         if (reset_state()) return 1;
         // Delta update: this rank's partial sums persist in bt_acc_local and are adjusted by the rows that
         // moved; a copy goes through the all-reduce.  One list and one mode for the whole batch.
-        static const bool no_delta = getenv("YUPVQ_NO_DELTA") != nullptr;
+        const bool no_delta = debug_opts().no_delta;
         const bool delta = !no_delta && delta_batch_supported(K, (uint32_t)T);
         long long* acc_loc = ctx->bt_acc.as<long long>();
         uint32_t* dctl = nullptr;

@@ -42,6 +42,7 @@
 #include <cuda_bf16.h>
 
 #include "common.cuh"
+#include "host_util.h"
 #include "kernels.h"
 
 namespace yupvq {
@@ -970,16 +971,14 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
 EncodeTiledFn encode_fn() {
-    static EncodeTiledFn fn = nullptr;
-    static bool tried = false;
-    if (!tried) {
-        tried = true;
+    static const EncodeTiledFn fn = [] {   // resolved once, thread-safe (C++11 static initialisation)
         void* p = nullptr;
         cudaDriverEntryPointQueryResult q;
         if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
             q == cudaDriverEntryPointSuccess)
-            fn = reinterpret_cast<EncodeTiledFn>(p);
-    }
+            return reinterpret_cast<EncodeTiledFn>(p);
+        return (EncodeTiledFn) nullptr;
+    }();
     return fn;
 }
 
@@ -1043,12 +1042,14 @@ cudaError_t launch_assign_tc(const float* a_prime, const float* xnorm, size_t n,
                              uint32_t K, const float* cmax, uint4* cand, uint32_t* assign, uint32_t* flags, uint32_t* amb_list,
                              unsigned int* amb_count, const uint32_t* stop, cudaStream_t s, const TcBatch* batch) {
     if (n == 0) return cudaSuccess;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(assign_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_TC);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(assign_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_TC);
+    static std::atomic<uint64_t> attr_set{0};  // per device (a process may hold contexts on several GPUs)
+    {
+        const cudaError_t e = once_per_device(attr_set, [] {
+            cudaError_t a = cudaFuncSetAttribute(assign_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_TC);
+            if (a == cudaSuccess) a = cudaFuncSetAttribute(assign_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_TC);
+            return a;
+        });
         if (e != cudaSuccess) return e;
-        attr_set = true;
     }
     const uint32_t k_pad = tc_padded_k(K);
     const uint32_t n_tex = batch ? batch->n_textures : 1u;

@@ -16,6 +16,7 @@
 #include <type_traits>
 
 #include "common.cuh"
+#include "host_util.h"
 #include "kernels.h"
 
 namespace yupvq {
@@ -1083,8 +1084,8 @@ cudaError_t launch_seed_round_ldr(const SeedState& st, const uint4* planes, size
 cudaError_t launch_seed_persistent(const SeedState& st, const uint4* planes, size_t plane_stride, const float* feat, size_t n,
                                    int ch, bool hdr, uint32_t K, cudaStream_t s, const uint32_t* pal5, size_t pal_stride) {
     if (K <= 1) return cudaSuccess;
-    static int sms = 0, coop = -1;
-    if (coop < 0) {
+    int sms = 0, coop = 0;  // per device: queried on every call (a process may hold contexts on several GPUs)
+    {
         int dev = 0;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
@@ -1104,8 +1105,8 @@ cudaError_t launch_seed_persistent(const SeedState& st, const uint4* planes, siz
     // (noisy, 48-dimensional) blocks pass the bound.  Kept opt-in for smoother inputs; results are identical either way.
     // The Oklab (HDR) variant is on by default: its rows are 256 bytes (the round is HBM-bound) and neighbouring
     // blocks of real images are similar, so whole warps skip (YUPVQ_SEED_NO_TRI=1 turns it off for A/B).
-    static const bool want_tri = getenv("YUPVQ_SEED_TRI") != nullptr;
-    static const bool no_tri = getenv("YUPVQ_SEED_NO_TRI") != nullptr;
+    const bool want_tri = debug_opts().seed_tri;
+    const bool no_tri = debug_opts().seed_no_tri;
     const bool tri = !hdr && mdreg && K <= (uint32_t)kPThreads && want_tri;
     const bool tri_hdr = hdr && mdreg && K <= (uint32_t)kPThreads && !no_tri;
     const void* fn = nullptr;
@@ -1123,15 +1124,14 @@ cudaError_t launch_seed_persistent(const SeedState& st, const uint4* planes, siz
         else fn = (const void*)seed_persistent_kernel<false, 4, true, true>;
     }
     // BC1 input in palette form: its own kernel (A/B: YUPVQ_SEED_NO_PAL=1 keeps the pixel-plane kernel)
-    static const bool no_pal = getenv("YUPVQ_SEED_NO_PAL") != nullptr;
+    const bool no_pal = debug_opts().seed_no_pal;
     if (pal5 != nullptr && !hdr && ch == 3 && mdreg && !tri && !no_pal && K <= 0xffffu) {
         const size_t smem_pal = (size_t)kPWarps * 8 * 5 * 32 * 4;  // 160 KiB
-        static bool attr_pal = false;
-        if (!attr_pal) {
-            cudaError_t e = cudaFuncSetAttribute(seed_palette_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_pal);
-            if (e != cudaSuccess) return e;
-            attr_pal = true;
-        }
+        static std::atomic<uint64_t> attr_pal{0};
+        if (cudaError_t e = once_per_device(attr_pal, [&] {
+                return cudaFuncSetAttribute(seed_palette_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_pal);
+            }); e != cudaSuccess)
+            return e;
         SeedState st_pal = st;
         void* pargs[] = {&st_pal, (void*)&pal5, &pal_stride, &n, &bpw, &K};
         return cudaLaunchCooperativeKernel((const void*)seed_palette_kernel, dim3((unsigned)g), dim3(kPThreads), pargs, smem_pal, s);
@@ -1144,25 +1144,24 @@ cudaError_t launch_seed_persistent(const SeedState& st, const uint4* planes, siz
         const size_t tri_bytes = tri ? (size_t)K * ch * 16 + (size_t)K * 4 : 0;
         cseg = (int)((200u * 1024u - tri_bytes) / seg_bytes);
         if ((size_t)cseg > bpw / 32) cseg = (int)(bpw / 32);
-        static const char* no_cache = getenv("YUPVQ_SEED_NO_SMEM");
-        if (no_cache) cseg = 0;
+        if (debug_opts().seed_no_smem) cseg = 0;
         smem = (size_t)cseg * seg_bytes + tri_bytes;
-        static bool attr[24] = {};  // dynamic + static shared memory may exceed the 48 KB default: always opt in
+        static std::atomic<uint64_t> attr[24];  // dynamic + static shared memory may exceed the 48 KB default: always opt in
         const int ai = ch * 2 + (mdreg ? 1 : 0) + (tri ? 12 : 0);
-        if (smem > 0 && !attr[ai]) {
-            cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(200u * 1024u));
-            if (e != cudaSuccess) return e;
-            attr[ai] = true;
-        }
+        if (smem > 0)
+            if (cudaError_t e = once_per_device(attr[ai], [&] {
+                    return cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(200u * 1024u));
+                }); e != cudaSuccess)
+                return e;
     }
     if (tri_hdr) {  // distances to the earlier seeds + their block indices
         smem = (size_t)K * 8 + ((size_t)K + 31) / 32 * 4;
-        static bool attr_hdr = false;
-        if (smem > 40 * 1024 && !attr_hdr) {
-            cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(64u * 1024u));
-            if (e != cudaSuccess) return e;
-            attr_hdr = true;
-        }
+        static std::atomic<uint64_t> attr_hdr{0};
+        if (smem > 40 * 1024)
+            if (cudaError_t e = once_per_device(attr_hdr, [&] {
+                    return cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(64u * 1024u));
+                }); e != cudaSuccess)
+                return e;
     }
     SeedState st_copy = st;
     void* args[] = {&st_copy, (void*)&planes, &plane_stride, (void*)&feat, &n, &bpw, &cseg, &K};

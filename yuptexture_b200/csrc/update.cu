@@ -12,6 +12,7 @@
 #include <cfloat>
 
 #include "common.cuh"
+#include "host_util.h"
 #include "kernels.h"
 
 namespace yupvq {
@@ -554,18 +555,23 @@ __global__ void max_abs_kernel(const float* __restrict__ x, size_t n, uint32_t* 
     if ((threadIdx.x & 31) == 0) atomicMax(out_bits, __float_as_uint(m));
 }
 
+// accumulate_sorted_kernel's dynamic shared memory can exceed the 48 KB default: opt in once per device to the largest
+// size it can ask for (K = kAccMaxK)
+cudaError_t accumulate_sorted_optin() {
+    static std::atomic<uint64_t> done{0};
+    return once_per_device(done, [] {
+        return cudaFuncSetAttribute(accumulate_sorted_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)((size_t)kAccMaxK * 8 + (size_t)kAccChunk * 2));
+    });
+}
+
 }  // namespace
 
 cudaError_t launch_accumulate(const float* feat, size_t n, const uint32_t* assign, uint32_t K, int shift,
                               long long* acc, const uint32_t* flags, const uint32_t* stop, cudaStream_t s, const uint32_t* dctl) {
     if (K <= (uint32_t)kAccMaxK && n >= (size_t)kAccChunk) {
         const size_t smem = (size_t)K * 8 + (size_t)kAccChunk * 2;
-        static size_t attr_smem = 0;
-        if (smem > 48 * 1024 && smem > attr_smem) {
-            cudaError_t e = cudaFuncSetAttribute(accumulate_sorted_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-            if (e != cudaSuccess) return e;
-            attr_smem = smem;
-        }
+        if (cudaError_t e = accumulate_sorted_optin(); e != cudaSuccess) return e;
         size_t chunks = (n + kAccChunk - 1) / kAccChunk;
         size_t grid = chunks < (size_t)YUPVQ_NUM_SMS * 2 ? chunks : (size_t)YUPVQ_NUM_SMS * 2;
         accumulate_sorted_kernel<<<(unsigned)grid, kAccThreads, smem, s>>>(feat, n, assign, K, ldexpf(1.0f, shift), acc, flags, stop,
@@ -608,12 +614,12 @@ cudaError_t launch_accumulate_delta(const float* feat, const uint32_t* assign, u
     const AccBatch bt = batch ? *batch : AccBatch{1u, 0, nullptr, 0u, 0u};
     if ((size_t)K * bt.n_textures > (size_t)kDeltaMaxK) return cudaSuccess;  // launch_acc_prepare forces full passes
     const size_t smem = (size_t)K * bt.n_textures * 8 + (size_t)kDeltaRows * 4 + (size_t)kDeltaRows * 4 + (size_t)kDeltaRows * 4;
-    static size_t attr_smem = 0;
-    if (smem > 48 * 1024 && smem > attr_smem) {
-        cudaError_t e = cudaFuncSetAttribute(accumulate_delta_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        attr_smem = smem;
-    }
+    static std::atomic<uint64_t> attr_delta{0};  // per device; opt in to the largest size the kernel can ask for
+    if (cudaError_t e = once_per_device(attr_delta, [] {
+            return cudaFuncSetAttribute(accumulate_delta_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)((size_t)kDeltaMaxK * 8 + (size_t)kDeltaRows * 12));
+        }); e != cudaSuccess)
+        return e;
     accumulate_delta_kernel<<<YUPVQ_NUM_SMS, kDeltaThreads, smem, s>>>(feat, assign, K, ldexpf(1.0f, shift), acc, chg_rows, chg_old,
                                                                       dctl, flags, stop, bt, batch ? rows_per_tex : 0xffffffffu);
     return cudaGetLastError();
@@ -626,10 +632,7 @@ cudaError_t launch_accumulate_batch(const float* feat, size_t rows_per_tex, cons
                                     const uint32_t* dctl) {
     if (!accumulate_batch_supported(rows_per_tex, K)) return cudaErrorInvalidValue;
     const size_t smem = (size_t)K * 8 + (size_t)kAccChunk * 2;
-    if (smem > 48 * 1024) {
-        cudaError_t e = cudaFuncSetAttribute(accumulate_sorted_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-    }
+    if (cudaError_t e = accumulate_sorted_optin(); e != cudaSuccess) return e;
     size_t chunks = (rows_per_tex + kAccChunk - 1) / kAccChunk * bt.n_textures;
     size_t grid = chunks < (size_t)YUPVQ_NUM_SMS * 2 ? chunks : (size_t)YUPVQ_NUM_SMS * 2;
     accumulate_sorted_kernel<<<(unsigned)grid, kAccThreads, smem, s>>>(feat, rows_per_tex, assign, K, 1.0f, acc, flags, stop, bt, dctl);

@@ -356,8 +356,8 @@ VQCodebook VQEncoder::EncodeCentroids(const std::vector<std::vector<uint8_t>>& p
     VQCodebook cb((uint32_t)BCBlockSize::GetSize(bcFormat), config.codebookSize);
     cb.entries.resize(pixelCentroids.size());
     for (size_t i = 0; i < pixelCentroids.size(); ++i)
-        cb.entries[i] = bcnCompressor.Compress(pixelCentroids[i].data(), 4, 4, channels, bcFormat, 1, params.bcQuality,
-                                               params.alphaThreshold);
+        // CompressSingleBlock passes (numThreads, bcQuality) only: the default alphaThreshold (128) applies, not params'
+        cb.entries[i] = bcnCompressor.Compress(pixelCentroids[i].data(), 4, 4, channels, bcFormat, params.numThreads, params.bcQuality);
     return cb;
 }
 
@@ -366,7 +366,7 @@ VQCodebook VQEncoder::EncodeCentroidsHDR(const std::vector<std::vector<float>>& 
     VQCodebook cb((uint32_t)BCBlockSize::GetSize(bcFormat), config.codebookSize);
     cb.entries.resize(centroids.size());
     for (size_t i = 0; i < centroids.size(); ++i) {
-        cb.entries[i] = bcnCompressor.CompressHDR(centroids[i].data(), 4, 4, channels, bcFormat, 1, params.bcQuality);
+        cb.entries[i] = bcnCompressor.CompressHDR(centroids[i].data(), 4, 4, channels, bcFormat, params.numThreads, params.bcQuality);
         if (cb.entries[i].empty())
             throw std::runtime_error("no HDR block encoder installed (BCnCompressor::SetCodec): cannot build BC6H codebook entries");
     }
