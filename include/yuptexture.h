@@ -101,6 +101,11 @@ public:
         std::function<std::vector<float>(const uint8_t*, uint32_t, uint32_t, uint32_t, BCFormat)> decompressHDR;
     };
     static void SetCodec(const Codec& codec);
+    // Installs the encoders of a block-codec plugin (include/yupcodec.h), e.g. libyupcodec_cmp.so (Compressonator).
+    // Without an explicit call the first use looks for $YUPTEXTURE_CODEC, then for libyupcodec_cmp.so next to
+    // libyuptexture.so.  Returns false (and leaves the current codec) if the library cannot be loaded.
+    static bool LoadCodecLibrary(const char* path);
+    static const char* CodecName();   // "built-in" or the plugin's yupcodec_name()
 
     std::vector<uint8_t> Compress(const uint8_t* inData, uint32_t width, uint32_t height, uint32_t channelCount,
                                   BCFormat format, int numThreads, float quality = 1.0f, uint8_t alphaThreshold = 128,
@@ -163,6 +168,10 @@ public:
                          std::vector<std::vector<float>>& outPixelFloatCentroids, std::vector<uint32_t>& outIndices,
                          const CompressionParams& params);
     yupvq_ctx* Context();  // lazily created
+    // wall-clock milliseconds of the last Encode* / BuildCodebook* call: the device VQ core (incl. its H2D / D2H) and
+    // the K host-side centroid encodes (A16), timed separately
+    double LastVqMs() const { return lastVqMs; }
+    double LastCentroidEncodeMs() const { return lastCentroidMs; }
 
 private:
     CompressionConfig config;
@@ -171,6 +180,7 @@ private:
     uint64_t seed = 0;
     int device = 0;
     yupvq_ctx* ctx = nullptr;
+    double lastVqMs = 0.0, lastCentroidMs = 0.0;
     VQCodebook EncodeCentroids(const std::vector<std::vector<uint8_t>>& pixelCentroids, uint8_t channels,
                                const CompressionParams& params);
     VQCodebook EncodeCentroidsHDR(const std::vector<std::vector<float>>& centroids, uint8_t channels,
@@ -194,8 +204,15 @@ public:
 
     // extension: seed forwarded to the VQEncoder of each Compress call (0 = std::random_device)
     void SetSeed(uint64_t seed) { seed_ = seed; }
+    // extension: stage times of the last Compress / CompressHDR call in wall-clock milliseconds, the breakdown the
+    // reference's example prints around its call (example/example.cpp:293-304)
+    struct Timings {
+        double bcnEncodeMs = 0, vqMs = 0, centroidEncodeMs = 0, zstdMs = 0, totalMs = 0;
+    };
+    const Timings& LastTimings() const { return timings_; }
 
 private:
+    Timings timings_;
     BCnCompressor bcnCompressor;
     struct ZstdContext;
     std::unique_ptr<ZstdContext> zstdCtx;

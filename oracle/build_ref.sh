@@ -18,8 +18,18 @@ L="$R/thirdparty/Compressonator/linux/lib/x64"
 CXXFLAGS="-std=c++17 -O2 -fopenmp -mavx2 -mfma -fPIC -I$R/include -I$R/thirdparty/colorm/include -I$R/thirdparty/Compressonator/include"
 g++ $CXXFLAGS -c "$R/src/vq_encoder.cpp" -o "$OUT/vq_encoder.o"
 g++ $CXXFLAGS -c "$R/src/bcn_compressor.cpp" -o "$OUT/bcn_compressor.o"
-g++ $CXXFLAGS -c "$HERE/ref_harness.cpp" -o "$OUT/ref_harness.o"
-g++ -shared -fopenmp -o "$OUT/libyupref.so" "$OUT/ref_harness.o" "$OUT/vq_encoder.o" "$OUT/bcn_compressor.o" \
+# src/vq_bcn_compressor.cpp (the container: Compress / DecompressToBCn) needs only <zstd.h>: a prototype-only header
+# (oracle/zstd_shim) and the system libzstd.so.1 stand in for the missing submodule
+ZLIB="$(ls /usr/lib/x86_64-linux-gnu/libzstd.so.1 /lib/x86_64-linux-gnu/libzstd.so.1 2>/dev/null | head -1 || true)"
+EXTRA_OBJ=""
+EXTRA_DEF=""
+if [ -n "$ZLIB" ]; then
+  g++ $CXXFLAGS -I"$HERE/zstd_shim" -c "$R/src/vq_bcn_compressor.cpp" -o "$OUT/vq_bcn_compressor.o"
+  EXTRA_OBJ="$OUT/vq_bcn_compressor.o $ZLIB"
+  EXTRA_DEF="-DYUPREF_HAVE_CONTAINER"
+fi
+g++ $CXXFLAGS $EXTRA_DEF -c "$HERE/ref_harness.cpp" -o "$OUT/ref_harness.o"
+g++ -shared -fopenmp -o "$OUT/libyupref.so" "$OUT/ref_harness.o" "$OUT/vq_encoder.o" "$OUT/bcn_compressor.o" $EXTRA_OBJ \
   -Wl,--start-group "$L/libCMP_Compressonator.a" "$L/libCMP_Common.a" "$L/libCMP_Core.a" \
   "$L/libCMP_Core_SSE.a" "$L/libCMP_Core_AVX.a" "$L/libCMP_Core_AVX512.a" -Wl,--end-group -lpthread -ldl
 echo "build_ref: built $OUT/libyupref.so"

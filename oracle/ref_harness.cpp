@@ -14,6 +14,7 @@
 // so the harness uses the access trick from SURVEY.md Appendix C: include every std header the
 // reference header pulls in, then re-include it with `private` defined away.
 #include <random>
+#include <cstdio>
 #include <vector>
 #include <atomic>
 #include <algorithm>
@@ -40,6 +41,9 @@
 #define private public
 #include "vq_encoder.h"
 #undef private
+#ifdef YUPREF_HAVE_CONTAINER
+#include "vq_bcn_compressor.h"   // the container (src/vq_bcn_compressor.cpp), built when libzstd.so.1 is present
+#endif
 
 namespace {
 
@@ -281,6 +285,71 @@ size_t ref_encode_single_block(const uint8_t* px, uint32_t ch, int bc_format, fl
     return v.size();
 }
 
+// One BC6H 4x4 encode as BuildCodebookHDR's finalise step does it (src/vq_encoder.cpp:252-254, :617-620).
+size_t ref_encode_single_block_hdr(const float* px, uint32_t ch, int bc_format, float bc_quality, int threads, uint8_t* out) {
+    BCnCompressor c;
+    auto v = c.CompressHDR(px, 4, 4, ch, static_cast<BCFormat>(bc_format), threads, bc_quality);
+    std::memcpy(out, v.data(), v.size());
+    return v.size();
+}
+
 int ref_num_threads() { return (int)std::thread::hardware_concurrency(); }
+
+// ---- the container: VQBCnCompressor::Compress / CompressHDR / DecompressToBCn (src/vq_bcn_compressor.cpp) ----------
+int ref_have_container() {
+#ifdef YUPREF_HAVE_CONTAINER
+    return 1;
+#else
+    return 0;
+#endif
+}
+
+#ifdef YUPREF_HAVE_CONTAINER
+// params_blob: a CompressionParams (44 bytes, include/vq_bcn_types.h:110-126) filled by the caller.
+// The reference seeds its VQEncoder from std::random_device inside Compress (:136, src/vq_encoder.cpp:24-26), so the
+// stream differs from run to run; times[0] = wall seconds of the call.
+long long ref_compress(const void* image, int is_hdr, uint32_t w, uint32_t h, uint32_t ch, const void* params_blob,
+                       uint8_t* out, size_t out_cap, double* times) {
+    try {
+        CompressionParams p;
+        std::memcpy(static_cast<void*>(&p), params_blob, sizeof(p));
+        VQBCnCompressor c;
+        const double t0 = now_s();
+        // Compress may swizzle its input in place when useVQ is false (src/bcn_compressor.cpp:61-76): work on a copy
+        std::vector<uint8_t> copy;
+        std::vector<uint8_t> s;
+        if (is_hdr) {
+            s = c.CompressHDR(static_cast<const float*>(image), w, h, (uint8_t)ch, p);
+        } else {
+            copy.assign(static_cast<const uint8_t*>(image), static_cast<const uint8_t*>(image) + (size_t)w * h * ch);
+            s = c.Compress(copy.data(), w, h, (uint8_t)ch, p);
+        }
+        if (times) times[0] = now_s() - t0;
+        if (s.size() > out_cap) return -2;
+        std::memcpy(out, s.data(), s.size());
+        return (long long)s.size();
+    } catch (const std::exception& e) {
+        std::fprintf(stderr, "ref_compress: %s\n", e.what());
+        return -1;
+    }
+}
+
+// The reference's DecompressToBCn (:287-361) on any .yupt2 stream; info24 receives the 24-byte TextureInfo.
+long long ref_decompress_to_bcn(const uint8_t* stream, size_t n, uint8_t* out, size_t out_cap, uint8_t* info24, int threads) {
+    try {
+        VQBCnCompressor c;
+        TextureInfo info;
+        const std::vector<uint8_t> v(stream, stream + n);
+        const std::vector<uint8_t> bc = c.DecompressToBCn(v, info, threads);
+        if (info24) std::memcpy(info24, &info, sizeof(TextureInfo));
+        if (bc.size() > out_cap) return -2;
+        std::memcpy(out, bc.data(), bc.size());
+        return (long long)bc.size();
+    } catch (const std::exception& e) {
+        std::fprintf(stderr, "ref_decompress_to_bcn: %s\n", e.what());
+        return -1;
+    }
+}
+#endif
 
 }  // extern "C"

@@ -18,7 +18,8 @@ def dumped(tmp_path_factory):
     if not os.path.exists(EXE):
         subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "yuptexture_b200", "host")])
     out = tmp_path_factory.mktemp("host_api")
-    r = subprocess.run([EXE, str(out)], capture_output=True, text=True, timeout=300)
+    env = dict(os.environ, YUPTEXTURE_CODEC="")   # built-in encoders: this driver also covers the "no BC6H codec" error path
+    r = subprocess.run([EXE, str(out)], capture_output=True, text=True, timeout=300, env=env)
     assert r.returncode == 0 and "HOST_API PASS" in r.stdout, r.stdout + r.stderr
     return out
 

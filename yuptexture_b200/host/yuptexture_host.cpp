@@ -7,12 +7,17 @@
 #include <dlfcn.h>
 
 #include <algorithm>
+#include <chrono>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <memory>
 #include <mutex>
 #include <stdexcept>
+#include <string>
 
+#include "../../include/yupcodec.h"
 #include "../../include/yupvq.h"
 
 namespace {
@@ -186,6 +191,73 @@ void encode_bc7_mode6(const uint8_t* px, uint8_t* out) {  // one subset, 7777.1 
 
 BCnCompressor::Codec g_codec;
 std::mutex g_codec_mutex;
+std::string g_codec_name = "built-in";
+
+double now_ms() {
+    return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+// ---- block-codec plugin (include/yupcodec.h) -------------------------------------------------------------------
+bool install_plugin(const char* path) {
+    void* h = dlopen(path, RTLD_NOW | RTLD_LOCAL);
+    if (!h) return false;
+    auto enc = reinterpret_cast<decltype(&yupcodec_compress)>(dlsym(h, "yupcodec_compress"));
+    auto enc_hdr = reinterpret_cast<decltype(&yupcodec_compress_hdr)>(dlsym(h, "yupcodec_compress_hdr"));
+    auto dec_hdr = reinterpret_cast<decltype(&yupcodec_decompress_hdr)>(dlsym(h, "yupcodec_decompress_hdr"));
+    auto name = reinterpret_cast<decltype(&yupcodec_name)>(dlsym(h, "yupcodec_name"));
+    if (!enc || !enc_hdr || !dec_hdr) {
+        dlclose(h);
+        return false;
+    }
+    BCnCompressor::Codec c;
+    c.compress = [enc](const uint8_t* img, uint32_t w, uint32_t hgt, uint32_t ch, BCFormat f, int threads, float q, uint8_t at, bool flip) {
+        std::vector<uint8_t> out((size_t)((w + 3) / 4) * ((hgt + 3) / 4) * BCBlockSize::GetSize(f));
+        if (enc(img, w, hgt, ch, (int)f, threads, q, at, flip ? 1 : 0, out.data(), out.size())) out.clear();  // empty = failure (:111)
+        return out;
+    };
+    c.compressHDR = [enc_hdr](const float* img, uint32_t w, uint32_t hgt, uint32_t ch, BCFormat f, int threads, float q) {
+        std::vector<uint8_t> out((size_t)((w + 3) / 4) * ((hgt + 3) / 4) * BCBlockSize::GetSize(f));
+        if (enc_hdr(img, w, hgt, ch, (int)f, threads, q, out.data(), out.size())) out.clear();
+        return out;
+    };
+    c.decompressHDR = [dec_hdr](const uint8_t* bc, uint32_t w, uint32_t hgt, uint32_t ch, BCFormat f) {
+        std::vector<float> out((size_t)w * hgt * ch);
+        if (dec_hdr(bc, w, hgt, ch, (int)f, out.data())) out.clear();
+        return out;
+    };
+    std::lock_guard<std::mutex> lock(g_codec_mutex);
+    g_codec = c;
+    g_codec_name = name ? name() : path;
+    return true;   // the handle stays open for the life of the process
+}
+
+// first use: $YUPTEXTURE_CODEC, else libyupcodec_cmp.so next to this library
+void autoload_codec() {
+    static std::once_flag once;
+    std::call_once(once, [] {
+        {
+            std::lock_guard<std::mutex> lock(g_codec_mutex);
+            if (g_codec.compress || g_codec.compressHDR || g_codec.decompressHDR) return;  // SetCodec was called first
+        }
+        if (const char* e = std::getenv("YUPTEXTURE_CODEC")) {
+            if (*e && install_plugin(e)) return;
+            if (!*e) return;   // YUPTEXTURE_CODEC= (empty) keeps the built-in encoders
+        }
+        Dl_info info;
+        if (dladdr(reinterpret_cast<void*>(&autoload_codec), &info) && info.dli_fname) {
+            std::string dir(info.dli_fname);
+            const size_t slash = dir.find_last_of('/');
+            dir = slash == std::string::npos ? std::string(".") : dir.substr(0, slash);
+            install_plugin((dir + "/libyupcodec_cmp.so").c_str());
+        }
+    });
+}
+
+BCnCompressor::Codec current_codec() {
+    autoload_codec();
+    std::lock_guard<std::mutex> lock(g_codec_mutex);
+    return g_codec;
+}
 
 // fetch a 4x4 RGBA tile (edge clamped), expanding 1/2/3-channel sources the way the VQ path reads them
 void fetch_tile(const uint8_t* img, uint32_t w, uint32_t h, uint32_t ch, uint32_t bx, uint32_t by, bool flip, uint8_t* px) {
@@ -204,11 +276,23 @@ void fetch_tile(const uint8_t* img, uint32_t w, uint32_t h, uint32_t ch, uint32_
 void BCnCompressor::SetCodec(const Codec& codec) {
     std::lock_guard<std::mutex> lock(g_codec_mutex);
     g_codec = codec;
+    g_codec_name = (codec.compress || codec.compressHDR || codec.decompressHDR) ? "user (SetCodec)" : "built-in";
+}
+
+bool BCnCompressor::LoadCodecLibrary(const char* path) { return path && install_plugin(path); }
+
+const char* BCnCompressor::CodecName() {
+    autoload_codec();
+    std::lock_guard<std::mutex> lock(g_codec_mutex);
+    static thread_local std::string name;
+    name = g_codec_name;
+    return name.c_str();
 }
 
 std::vector<uint8_t> BCnCompressor::Compress(const uint8_t* inData, uint32_t width, uint32_t height, uint32_t channelCount,
                                              BCFormat format, int numThreads, float quality, uint8_t alphaThreshold, bool flipRGB) {
-    if (g_codec.compress) return g_codec.compress(inData, width, height, channelCount, format, numThreads, quality, alphaThreshold, flipRGB);
+    if (const Codec c = current_codec(); c.compress)
+        return c.compress(inData, width, height, channelCount, format, numThreads, quality, alphaThreshold, flipRGB);
     if (!inData || width == 0 || height == 0 || channelCount < 1 || channelCount > 4) return {};
     if (format != BCFormat::BC1 && format != BCFormat::BC3 && format != BCFormat::BC4 && format != BCFormat::BC5 && format != BCFormat::BC7)
         return {};  // the reference returns an empty vector on failure (src/bcn_compressor.cpp:111)
@@ -233,13 +317,13 @@ std::vector<uint8_t> BCnCompressor::Compress(const uint8_t* inData, uint32_t wid
 
 std::vector<uint8_t> BCnCompressor::CompressHDR(const float* inData, uint32_t width, uint32_t height, uint32_t channelCount,
                                                 BCFormat format, int numThreads, float quality) {
-    if (g_codec.compressHDR) return g_codec.compressHDR(inData, width, height, channelCount, format, numThreads, quality);
-    return {};  // no built-in BC6H encoder: install one with SetCodec
+    if (const Codec c = current_codec(); c.compressHDR) return c.compressHDR(inData, width, height, channelCount, format, numThreads, quality);
+    return {};  // no built-in BC6H encoder: a codec plugin (include/yupcodec.h) or SetCodec supplies one
 }
 
 std::vector<float> BCnCompressor::DecompressHDR(const uint8_t* bcData, uint32_t width, uint32_t height, uint32_t channelCount,
                                                 BCFormat format) {
-    if (g_codec.decompressHDR) return g_codec.decompressHDR(bcData, width, height, channelCount, format);
+    if (const Codec c = current_codec(); c.decompressHDR) return c.decompressHDR(bcData, width, height, channelCount, format);
     return {};
 }
 
@@ -353,23 +437,31 @@ yupvq_ctx* VQEncoder::Context() {
 // K calls of the 4x4 block encoder, reference src/vq_encoder.cpp:432-440 (CompressSingleBlock :248-250)
 VQCodebook VQEncoder::EncodeCentroids(const std::vector<std::vector<uint8_t>>& pixelCentroids, uint8_t channels,
                                       const CompressionParams& params) {
+    const double t0 = now_ms();
     VQCodebook cb((uint32_t)BCBlockSize::GetSize(bcFormat), config.codebookSize);
     cb.entries.resize(pixelCentroids.size());
-    for (size_t i = 0; i < pixelCentroids.size(); ++i)
-        // CompressSingleBlock passes (numThreads, bcQuality) only: the default alphaThreshold (128) applies, not params'
-        cb.entries[i] = bcnCompressor.Compress(pixelCentroids[i].data(), 4, 4, channels, bcFormat, params.numThreads, params.bcQuality);
+    // CompressSingleBlock passes (numThreads, bcQuality) only, so the default alphaThreshold (128) applies, not params'.
+    // One thread per 4x4 call (the result of a single-block encode does not depend on it), the K calls
+    // spread over params.numThreads as in the reference's loop.
+#pragma omp parallel for num_threads(params.numThreads > 0 ? params.numThreads : 1) schedule(dynamic, 8)
+    for (int64_t i = 0; i < (int64_t)pixelCentroids.size(); ++i)
+        cb.entries[i] = bcnCompressor.Compress(pixelCentroids[i].data(), 4, 4, channels, bcFormat, 1, params.bcQuality);
+    lastCentroidMs = now_ms() - t0;
     return cb;
 }
 
 VQCodebook VQEncoder::EncodeCentroidsHDR(const std::vector<std::vector<float>>& centroids, uint8_t channels,
                                          const CompressionParams& params) {
+    const double t0 = now_ms();
     VQCodebook cb((uint32_t)BCBlockSize::GetSize(bcFormat), config.codebookSize);
     cb.entries.resize(centroids.size());
-    for (size_t i = 0; i < centroids.size(); ++i) {
-        cb.entries[i] = bcnCompressor.CompressHDR(centroids[i].data(), 4, 4, channels, bcFormat, params.numThreads, params.bcQuality);
-        if (cb.entries[i].empty())
-            throw std::runtime_error("no HDR block encoder installed (BCnCompressor::SetCodec): cannot build BC6H codebook entries");
-    }
+#pragma omp parallel for num_threads(params.numThreads > 0 ? params.numThreads : 1) schedule(dynamic, 8)
+    for (int64_t i = 0; i < (int64_t)centroids.size(); ++i)
+        cb.entries[i] = bcnCompressor.CompressHDR(centroids[i].data(), 4, 4, channels, bcFormat, 1, params.bcQuality);
+    for (const auto& e : cb.entries)
+        if (e.empty())
+            throw std::runtime_error("no HDR block encoder installed (codec plugin or BCnCompressor::SetCodec): cannot build BC6H codebook entries");
+    lastCentroidMs = now_ms() - t0;
     return cb;
 }
 
@@ -379,8 +471,10 @@ VQCodebook VQEncoder::BuildCodebook(const std::vector<std::vector<uint8_t>>& all
     const std::vector<uint8_t> flat = flatten(allPixelBlocks, per);
     const yupvq_config cfg = make_cfg(config, seed);
     std::vector<uint8_t> cent((size_t)cfg.codebook_size * per);
+    const double t_vq = now_ms();
     if (yupvq_build_codebook(Context(), flat.data(), allPixelBlocks.size(), channels, &cfg, cent.data(), nullptr))
         fail(ctx, "BuildCodebook");
+    lastVqMs = now_ms() - t_vq;
     outPixelCentroids = unflatten(cent, per);
     return EncodeCentroids(outPixelCentroids, channels, params);
 }
@@ -405,8 +499,10 @@ VQCodebook VQEncoder::BuildCodebookHDR(const std::vector<std::vector<float>>& al
     const std::vector<float> flat = flatten(allPixelFloatBlocks, per);
     const yupvq_config cfg = make_cfg(config, seed);
     std::vector<float> cent((size_t)cfg.codebook_size * per);
+    const double t_vq = now_ms();
     if (yupvq_build_codebook_hdr(Context(), flat.data(), allPixelFloatBlocks.size(), channels, &cfg, cent.data(), nullptr))
         fail(ctx, "BuildCodebookHDR");
+    lastVqMs = now_ms() - t_vq;
     outPixelFloatCentroids = unflatten(cent, per);
     return EncodeCentroidsHDR(outPixelFloatCentroids, channels, params);
 }
@@ -430,8 +526,10 @@ VQCodebook VQEncoder::EncodeBCn(const uint8_t* bcData, size_t numBlocks, uint8_t
     const yupvq_config cfg = make_cfg(config, seed);
     std::vector<uint8_t> cent((size_t)cfg.codebook_size * per);
     outIndices.resize(numBlocks);
+    const double t_vq = now_ms();
     if (yupvq_encode_bcn(Context(), bcData, numBlocks, (int)bcFormat, channels, &cfg, cent.data(), outIndices.data(), nullptr))
         fail(ctx, "EncodeBCn");
+    lastVqMs = now_ms() - t_vq;
     outPixelCentroids = unflatten(cent, per);
     return EncodeCentroids(outPixelCentroids, channels, params);
 }
@@ -443,8 +541,10 @@ VQCodebook VQEncoder::EncodeHDR(const float* image, uint32_t width, uint32_t hei
     const yupvq_config cfg = make_cfg(config, seed);
     std::vector<float> cent((size_t)cfg.codebook_size * per);
     outIndices.resize((size_t)((width + 3) / 4) * ((height + 3) / 4));
+    const double t_vq = now_ms();
     if (yupvq_encode_hdr(Context(), image, width, height, channels, &cfg, cent.data(), outIndices.data(), nullptr))
         fail(ctx, "EncodeHDR");
+    lastVqMs = now_ms() - t_vq;
     outPixelFloatCentroids = unflatten(cent, per);
     return EncodeCentroidsHDR(outPixelFloatCentroids, channels, params);
 }
@@ -552,9 +652,12 @@ std::vector<uint8_t> VQBCnCompressor::Compress(const uint8_t* inData, uint32_t w
                                                const CompressionParams& params) {
     TextureInfo info = make_info(width, height, channels, params, COMPRESSION_FLAGS_DEFAULT);
     const bool enableLdm = width >= 4000 || height >= 4000;
+    timings_ = Timings();
+    const double t0 = now_ms();
     auto bcData = bcnCompressor.Compress(inData, width, height, channels, params.bcFormat, params.numThreads, params.bcQuality,
                                          params.alphaThreshold, /*flipRGB=*/!params.useVQ);
     if (bcData.empty()) throw std::runtime_error("BCn compression failed");
+    timings_.bcnEncodeMs = now_ms() - t0;
     std::vector<uint8_t> payload;
     if (info.compressionFlags & COMPRESSION_FLAGS_VQ_BYPASSED) {
         info.storedCodebookEntries = 0;
@@ -568,18 +671,26 @@ std::vector<uint8_t> VQBCnCompressor::Compress(const uint8_t* inData, uint32_t w
         std::vector<uint32_t> indices;
         // the three starred lines of the reference (:142-150) as one device call
         VQCodebook cb = enc.EncodeBCn(bcData.data(), bcData.size() / bs, channels, centroids, indices, params);
+        timings_.vqMs = enc.LastVqMs();
+        timings_.centroidEncodeMs = enc.LastCentroidEncodeMs();
         info.storedCodebookEntries = (uint32_t)cb.entries.size();
         payload = payload_of(cb, indices, bs);
     }
+    const double tz = now_ms();
     if (!(info.compressionFlags & COMPRESSION_FLAGS_ZSTD_BYPASSED))
         payload = compressWithZstd(payload, params.zstdLevel, params.numThreads, enableLdm);
-    return serialise(info, payload);
+    timings_.zstdMs = now_ms() - tz;
+    auto out = serialise(info, payload);
+    timings_.totalMs = now_ms() - t0;
+    return out;
 }
 
 std::vector<uint8_t> VQBCnCompressor::CompressHDR(const float* inData, uint32_t width, uint32_t height, uint8_t channels,
                                                   const CompressionParams& params) {
     TextureInfo info = make_info(width, height, channels, params, COMPRESSION_FLAGS_IS_HDR);
     const bool enableLdm = width >= 4000 || height >= 4000;
+    timings_ = Timings();
+    const double t0 = now_ms();
     std::vector<uint8_t> payload;
     if (info.compressionFlags & COMPRESSION_FLAGS_VQ_BYPASSED) {
         info.storedCodebookEntries = 0;
@@ -592,12 +703,18 @@ std::vector<uint8_t> VQBCnCompressor::CompressHDR(const float* inData, uint32_t 
         std::vector<std::vector<float>> centroids;
         std::vector<uint32_t> indices;
         VQCodebook cb = enc.EncodeHDR(inData, width, height, channels, centroids, indices, params);  // :230-256 on the device
+        timings_.vqMs = enc.LastVqMs();
+        timings_.centroidEncodeMs = enc.LastCentroidEncodeMs();
         info.storedCodebookEntries = (uint32_t)cb.entries.size();
         payload = payload_of(cb, indices, BCBlockSize::GetSize(params.bcFormat));
     }
+    const double tz = now_ms();
     if (!(info.compressionFlags & COMPRESSION_FLAGS_ZSTD_BYPASSED))
         payload = compressWithZstd(payload, params.zstdLevel, params.numThreads, enableLdm);
-    return serialise(info, payload);
+    timings_.zstdMs = now_ms() - tz;
+    auto out = serialise(info, payload);
+    timings_.totalMs = now_ms() - t0;
+    return out;
 }
 
 std::vector<uint8_t> VQBCnCompressor::DecompressToBCn(const std::vector<uint8_t>& compressedData, TextureInfo& outInfo, int) {  // :287-361
@@ -647,3 +764,54 @@ std::vector<float> VQBCnCompressor::DecompressHDR(const std::vector<uint8_t>& co
         throw std::runtime_error("Cannot decompress LDR texture to float data. Use Decompress instead.");
     return bcnCompressor.DecompressHDR(bc.data(), outInfo.width, outInfo.height, outInfo.originalChannelCount, outInfo.format);
 }
+
+// ---- plain-C entry points over the classes (ctypes / FFI callers: bench.py's whole-Compress breakdown) -----------------
+// out_ms[5] = {BCn pre-pass encode, device VQ core, K centroid encodes (A16), zstd, whole call}; returns 0 on success,
+// the stream size in *out_bytes and (if out_stream != null, capacity out_cap) the stream itself.
+extern "C" {
+
+YUPTEXTURE_API const char* yuptexture_codec_name(void) { return BCnCompressor::CodecName(); }
+
+YUPTEXTURE_API int yuptexture_load_codec(const char* path) { return BCnCompressor::LoadCodecLibrary(path) ? 0 : 1; }
+
+YUPTEXTURE_API int yuptexture_compress_timed(const void* image, int is_hdr, uint32_t width, uint32_t height, uint32_t channels,
+                                             const CompressionParams* params, uint64_t seed, double out_ms[5], size_t* out_bytes,
+                                             uint8_t* out_stream, size_t out_cap, char* err, size_t err_cap) {
+    try {
+        static thread_local std::unique_ptr<VQBCnCompressor> comp;   // keeps the device context (and its arena) across calls
+        if (!comp) comp = std::make_unique<VQBCnCompressor>();
+        comp->SetSeed(seed);
+        const std::vector<uint8_t> s = is_hdr ? comp->CompressHDR(static_cast<const float*>(image), width, height, (uint8_t)channels, *params)
+                                              : comp->Compress(static_cast<const uint8_t*>(image), width, height, (uint8_t)channels, *params);
+        const VQBCnCompressor::Timings& t = comp->LastTimings();
+        if (out_ms) {
+            out_ms[0] = t.bcnEncodeMs; out_ms[1] = t.vqMs; out_ms[2] = t.centroidEncodeMs; out_ms[3] = t.zstdMs; out_ms[4] = t.totalMs;
+        }
+        if (out_bytes) *out_bytes = s.size();
+        if (out_stream && out_cap >= s.size()) std::memcpy(out_stream, s.data(), s.size());
+        return 0;
+    } catch (const std::exception& e) {
+        if (err && err_cap) std::snprintf(err, err_cap, "%s", e.what());
+        return 1;
+    }
+}
+
+// VQBCnCompressor::DecompressToBCn on a stream (ours or the reference's); out must hold GetTotalBlocks() * blockSize bytes
+YUPTEXTURE_API int yuptexture_decompress_to_bcn(const uint8_t* stream, size_t stream_bytes, uint8_t* out, size_t out_cap, size_t* out_bytes,
+                                                TextureInfo* out_info, char* err, size_t err_cap) {
+    try {
+        static thread_local std::unique_ptr<VQBCnCompressor> comp;
+        if (!comp) comp = std::make_unique<VQBCnCompressor>();
+        TextureInfo info;
+        const std::vector<uint8_t> bc = comp->DecompressToBCn(std::vector<uint8_t>(stream, stream + stream_bytes), info);
+        if (out_info) *out_info = info;
+        if (out_bytes) *out_bytes = bc.size();
+        if (out && out_cap >= bc.size()) std::memcpy(out, bc.data(), bc.size());
+        return 0;
+    } catch (const std::exception& e) {
+        if (err && err_cap) std::snprintf(err, err_cap, "%s", e.what());
+        return 1;
+    }
+}
+
+}  // extern "C"
