@@ -33,7 +33,7 @@ TEX = 4096          # BASELINE config 2
 QUALITY = 0.8       # -> K = 512
 MAX_ITER = 32
 SEED = 42
-CPU_SAMPLE = 1024   # the reference is timed on a CPU_SAMPLE^2 crop (bounded sample)
+CPU_SAMPLE = 2048   # our arm's cpu_baseline: the reference on a CPU_SAMPLE^2 crop (bounded sample, ~10 s of CPU work)
 
 
 def peaks():
@@ -124,35 +124,81 @@ def parity_report(enc, px, cent_ref, idx_ref):
             "lloyd_passes_gpu": int(st.lloyd_passes)}
 
 
-def cpu_sample_pixels(bc):
-    """Decoded pixel blocks of the top-left CPU_SAMPLE^2 crop of the bench texture."""
+def cpu_sample_pixels(bc, size=None):
+    """Decoded pixel blocks of the top-left size^2 crop of the bench texture."""
     from oracle import orcbind
+    size = size or CPU_SAMPLE
     bx = TEX // 4
-    rows = np.arange(CPU_SAMPLE // 4)[:, None] * bx + np.arange(CPU_SAMPLE // 4)[None, :]
+    rows = np.arange(size // 4)[:, None] * bx + np.arange(size // 4)[None, :]
     return orcbind.decode_bcn(bc[rows.reshape(-1)], 1, 3)
 
 
+def workload_config(n_tex):
+    """The `config` object both arms print (identical keys and values for the same N, so the driver's same_config holds)."""
+    return {"workload": f"BC1 VQ compress of {n_tex} synthetic 4096x4096 texture(s) (BASELINE config 2 per GPU): "
+                        "seeding+Lloyd+assign, K=512, maxIterations=32, Oklab metric",
+            "blocks_per_texture": (TEX // 4) ** 2, "textures": n_tex, "codebook": 512, "max_iterations": MAX_ITER, "seed": SEED}
+
+
 def run_reference(args, rank, world):
+    """The reference's own CPU implementation of the path (oracle/_ref: the unmodified sources; else the CPU port) on all
+    host cores.  `value` comes from ONE full-size pass over the whole 4096^2 texture (BuildCodebook + QuantizeBlocks,
+    src/vq_encoder.cpp:260 / :447) -- the configuration the GPU arm runs, so the two lines are the same workload; the
+    --warmup / --steps passes run on a 1024^2 crop and are reported as the repeatability sample (a full pass is ~30-45 s)."""
     if rank != 0:
         return
+    from oracle import refbind
     bc = make_texture(1000)
-    px = cpu_sample_pixels(bc)
+    px_crop = cpu_sample_pixels(bc, 1024)
     threads = os.cpu_count() or 1
     for _ in range(args.warmup):
-        cpu_reference_step(px, threads)
-    t0 = time.perf_counter()
+        cpu_reference_step(px_crop, threads)
+    per = []
     kind = "port"
     for _ in range(args.steps):
-        _, kind = cpu_reference_step(px, threads)[:2]
-    dt = (time.perf_counter() - t0) / max(1, args.steps)
-    value = len(px) / dt
-    sample = f"{CPU_SAMPLE}x{CPU_SAMPLE} crop ({len(px)} blocks) of the 4096^2 BC1 bench texture per step, K=512, 32 iterations max"
+        dt, kind = cpu_reference_step(px_crop, threads)[:2]
+        per.append(dt)
+    crop_dt = float(np.mean(per)) if per else 0.0
+    # the full-size pass (reference only: the scalar port would take tens of minutes)
+    breakdown = None
+    if kind == "reference":
+        from oracle import orcbind
+        px_full = orcbind.decode_bcn(bc, 1, 3)
+        t0 = time.perf_counter()
+        cent, _, t_build = refbind.build_codebook(px_full, 3, 1, QUALITY, MAX_ITER, SEED, threads=threads)
+        idx, t_quant = refbind.quantize_blocks(px_full, 3, cent, threads=threads)
+        full_dt = time.perf_counter() - t0
+        n_full = len(px_full)
+        # the K centroid encodes (A16) that BuildCodebook's time includes, timed on their own (src/vq_encoder.cpp:432-440)
+        t1 = time.perf_counter()
+        refbind.encode_blocks(cent, 3, 1, 1.0, threads)
+        t_a16 = time.perf_counter() - t1
+        # the whole-texture Compressonator BC1 pre-pass of VQBCnCompressor::Compress (src/vq_bcn_compressor.cpp:94)
+        from yuptexture_b200 import synth
+        img = synth.ldr_rgb(TEX, TEX, seed=1000)
+        t2 = time.perf_counter()
+        refbind.bcn_encode(img, 1, quality=1.0, threads=threads)
+        t_pre = time.perf_counter() - t2
+        breakdown = {"bcn_encode_s": t_pre, "build_codebook_s": t_build, "of_which_centroid_encodes_s": t_a16,
+                     "quantize_blocks_s": t_quant, "vq_core_s": t_build + t_quant - t_a16,
+                     "note": "reference stages of VQBCnCompressor::Compress on the 4096^2 texture (example/example.cpp:293-304 prints the sum); "
+                             "the per-block decode loop (:142-146) and zstd are not timed here"}
+    else:
+        full_dt, n_full = crop_dt, len(px_crop)
+    value = n_full / full_dt
+    sample = (f"value: one full pass over the 4096^2 texture ({n_full} blocks, {full_dt:.1f} s, K=512, 32 iterations max); "
+              f"repeatability: {args.steps} passes on a 1024x1024 crop ({len(px_crop)} blocks), mean {crop_dt * 1e3:.0f} ms "
+              f"(std {float(np.std(per)) * 1e3 if per else 0:.0f} ms) = {len(px_crop) / crop_dt if crop_dt else 0:.0f} blocks/s")
     print(json.dumps({
         "impl": "reference", "metric": "vq_blocks_per_sec", "value": value, "unit": "blocks/s", "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": crop_dt * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "BC1 VQ compress of a synthetic 4096x4096 texture (config 2): K=512, maxIterations=32, Oklab",
-                   "note": "CPU reference timed on a bounded sample"},
+        "config": workload_config(max(1, args.gpus)),
+        "full_size_pass": {"blocks": n_full, "seconds": full_dt, "blocks_per_s": value},
+        "crop_passes": {"blocks": len(px_crop), "ms_mean": crop_dt * 1e3, "blocks_per_s": len(px_crop) / crop_dt if crop_dt else None},
+        "note": "ms_per_step / steps describe the crop passes; value is the full-size pass (the GPU arm's exact workload, one texture; "
+                "the CPU path is per-texture serial, so N textures cost N times this)",
+        "compress_breakdown": breakdown,
         "cpu_baseline": {"value": value, "unit": "blocks/s", "cores": threads if kind == "reference" else 1,
                          "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": "blocks/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -162,7 +208,7 @@ def run_reference(args, rank, world):
 def run_ours(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
-    from yuptexture_b200 import binding
+    from yuptexture_b200 import binding, sharding
 
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
@@ -171,10 +217,11 @@ def run_ours(args, rank, world, local_rank):
     enc = binding.Encoder(local_rank)
     k = binding.codebook_size(QUALITY)
     n = (TEX // 4) ** 2
-    n_tex = world  # weak scaling: one texture's worth of blocks per GPU
+    n_tex = args.textures or world       # default = weak scaling: one texture's worth of blocks per GPU
+    texture_parallel = args.placement == "texture" and world > 1
     cfg = binding.make_config(quality=QUALITY, max_iterations=MAX_ITER, seed=SEED)
 
-    if world > 1:
+    if world > 1 and not texture_parallel:
         uid = torch.zeros(128, dtype=torch.uint8)
         if rank == 0:
             uid = torch.from_numpy(enc.comm_unique_id().copy())
@@ -182,38 +229,61 @@ def run_ours(args, rank, world, local_rank):
         dist.broadcast(uid, 0)
         enc.comm_init(uid.cpu().numpy(), world, rank)
 
-    # synthetic inputs (fixed seeds): texture t is generated on rank t % world and broadcast, every rank holds all of them
-    textures = []
-    for t in range(n_tex):
-        if world == 1:
-            textures.append(make_texture(1000 + t))
-            continue
-        buf = torch.empty(n * 8, dtype=torch.uint8, device=dev)
-        if t % world == rank:
-            buf.copy_(torch.from_numpy(make_texture(1000 + t).reshape(-1).copy()))
-        dist.broadcast(buf, t % world)
-        textures.append(buf.cpu().numpy().reshape(n, 8))
-    pinned_in = [torch.from_numpy(t.reshape(-1).copy()).pin_memory() for t in textures]
-    dev_in = [p.to(dev) for p in pinned_in]
-    from yuptexture_b200 import sharding
     first, n_local = sharding.shard_range(n, world, rank)
-    dev_cent = [torch.empty(k * 48, dtype=torch.uint8, device=dev) for _ in range(n_tex)]
-    dev_idx = [torch.empty(max(1, n_local), dtype=torch.int32, device=dev) for _ in range(n_tex)]
-    host_cent = [torch.empty(k * 48, dtype=torch.uint8).pin_memory() for _ in range(n_tex)]
-    host_idx = [torch.empty(max(1, n_local), dtype=torch.int32).pin_memory() for _ in range(n_tex)]
+    if texture_parallel:
+        first, n_local = 0, n
+    # which textures this rank holds: block-sharded = the whole textures it seeds + its block shard of all the others
+    # (yupvq_encode_bcn_batch_sharded, include/yupvq.h); texture-parallel = whole textures t % world == rank only
+    mine = [t for t in range(n_tex) if t % world == rank]
+    held = mine if texture_parallel else list(range(n_tex))
+
+    # synthetic inputs (fixed seeds 1000 + t); texture t is generated on rank t % world and its bytes (or this rank's shard of
+    # them) are broadcast
+    pinned_in, dev_in, whole, check_full = {}, {}, {}, {}
+    tex0_host = None
+    for t in range(n_tex):
+        owner = t % world
+        if world == 1:
+            full = make_texture(1000 + t)
+        else:
+            buf = torch.empty(n * 8, dtype=torch.uint8, device=dev)
+            if owner == rank:
+                buf.copy_(torch.from_numpy(make_texture(1000 + t).reshape(-1).copy()))
+            if not texture_parallel or t in (0, n_tex - 1):
+                dist.broadcast(buf, owner)
+            full = buf.cpu().numpy().reshape(n, 8) if (owner == rank or not texture_parallel or t in (0, n_tex - 1)) else None
+        if t == 0:
+            tex0_host = full
+        if t in (0, n_tex - 1) and full is not None:
+            check_full[t] = full
+        if t not in held:
+            continue
+        is_whole = texture_parallel or world == 1 or owner == rank
+        part = full if is_whole else full[first:first + n_local]
+        whole[t] = is_whole
+        pinned_in[t] = torch.from_numpy(np.ascontiguousarray(part).reshape(-1).copy()).pin_memory()
+        dev_in[t] = pinned_in[t].to(dev)
+    dev_cent = {t: torch.empty(k * 48, dtype=torch.uint8, device=dev) for t in held}
+    dev_idx = {t: torch.empty(max(1, n_local), dtype=torch.int32, device=dev) for t in held}
+    host_cent = {t: torch.empty(k * 48, dtype=torch.uint8).pin_memory() for t in held}
+    host_idx = {t: torch.empty(max(1, n_local), dtype=torch.int32).pin_memory() for t in held}
 
     def step(resident):
-        if world == 1:
-            src = dev_in[0].data_ptr() if resident else pinned_in[0].numpy()
-            oc = dev_cent[0].data_ptr() if resident else host_cent[0].numpy()
-            oi = dev_idx[0].data_ptr() if resident else host_idx[0].numpy().view(np.uint32)
-            _, _, st = enc.encode_bcn(src, n, 1, 3, cfg, oc, oi)
+        src = (lambda t: dev_in[t].data_ptr()) if resident else (lambda t: pinned_in[t].numpy())
+        oc = (lambda t: dev_cent[t].data_ptr()) if resident else (lambda t: host_cent[t].numpy())
+        oi = (lambda t: dev_idx[t].data_ptr()) if resident else (lambda t: host_idx[t].numpy().view(np.uint32))
+        if world == 1 and n_tex == 1:
+            _, _, st = enc.encode_bcn(src(0), n, 1, 3, cfg, oc(0), oi(0))
             return [st]
-        # N GPUs: N textures in lock step, every texture's blocks sharded over the N GPUs; one all-reduce per pass
-        srcs = [d.data_ptr() for d in dev_in] if resident else [p.numpy() for p in pinned_in]
-        ocs = [d.data_ptr() for d in dev_cent] if resident else [h.numpy() for h in host_cent]
-        ois = [d.data_ptr() for d in dev_idx] if resident else [h.numpy().view(np.uint32) for h in host_idx]
-        _, _, st = enc.encode_bcn_batch_sharded(srcs, n, first, n_local, 1, 3, cfg, ocs, ois)
+        if texture_parallel:   # independent textures, zero collectives: texture t runs whole on rank t % world with seed + t
+            sts = []
+            for t in mine:
+                c = binding.make_config(quality=QUALITY, max_iterations=MAX_ITER, seed=SEED + t)
+                sts.append(enc.encode_bcn(src(t), n, 1, 3, c, oc(t), oi(t))[2])
+            return sts
+        # lock-step batch: every texture's blocks sharded over the GPUs; one all-reduce per pass
+        _, _, st = enc.encode_bcn_batch_sharded([src(t) for t in held], n, first, n_local, 1, 3, cfg, [oc(t) for t in held],
+                                                [oi(t) for t in held], shard_only=[not whole[t] for t in held])
         return [st]
 
     def barrier():
@@ -259,63 +329,103 @@ def run_ours(args, rank, world, local_rank):
     ms_fe, n_fe = enc.profile_read()
     enc.profile(False)
 
+    # ---- multi-GPU parity, carried by every N > 1 line: this rank's outputs of the first and the last texture it holds are
+    # compared bit for bit with a communicator-less single-GPU yupvq_encode_bcn of the same texture and seed
+    multi = None
+    if world > 1:
+        solo = binding.Encoder(local_rank)
+        ok, checked = True, 0
+        for t in sorted({0, n_tex - 1}):
+            if t not in held or t not in check_full:
+                continue
+            c = binding.make_config(quality=QUALITY, max_iterations=MAX_ITER, seed=SEED + t)
+            cent_s, idx_s, _ = solo.encode_bcn(check_full[t], n, 1, 3, c)
+            ok = ok and np.array_equal(dev_cent[t].cpu().numpy().reshape(k, 48), cent_s)
+            ok = ok and np.array_equal(dev_idx[t].cpu().numpy().view(np.uint32)[:n_local], idx_s[first:first + n_local])
+            checked += 1
+        solo.close()
+        tt = torch.tensor([1.0 if ok else 0.0, float(checked), 1.0 if checked else 0.0], dtype=torch.float64, device=dev)
+        mn = tt.clone()
+        dist.all_reduce(mn, op=dist.ReduceOp.MIN)
+        dist.all_reduce(tt, op=dist.ReduceOp.SUM)
+        multi = {"multi_gpu_identical": bool(mn[0] == 1.0), "ranks_checked": int(tt[2]), "comparisons": int(tt[1]),
+                 "what": "centroids and this rank's index shard of textures 0 and T-1 vs a single-GPU yupvq_encode_bcn of the "
+                         "same texture and seed, bit for bit, on every rank that holds them"}
+
     out = None
     if rank == 0:
         pk = peaks()
-        # dominant kernel: the tcgen05 assignment front-end (assign_tc_kernel), every launch of it inside one
-        # more real step bracketed by CUDA events on the library's stream (yupvq_profile)
+        # dominant kernel: the tcgen05 assignment front-end (assign_tc_kernel), every launch of it inside one more real step
+        # bracketed by CUDA events on the library's stream (yupvq_profile)
         ms_a = ms_fe / max(1, n_fe)
-        blocks_per_launch = n_local * n_tex if world > 1 else n   # the lock-step batch launches the front-end once for all textures
-        flop_alg = 2.0 * blocks_per_launch * k * 64          # 2 K D per block per pass
-        split = 3                                            # xh.ch + xh.cl + xl.ch bf16 partial products
-        achieved = split * flop_alg / (ms_a * 1e-3) / 1e12 if ms_a > 0 else 0.0
+        if world > 1 and not texture_parallel:
+            blocks_per_launch = n_local * n_tex          # the lock-step batch launches the front-end once for all textures
+        else:
+            blocks_per_launch = n
+        flop_alg = 2.0 * blocks_per_launch * k * 64        # 2 K D per block per pass
+        # executed MMA work: K = 16 steps per 128 x 256 tile-chunk actually issued for this layout -- 10 for textures without
+        # alpha (48 colour columns + folded norm: 3 + 3 + 4 steps), 13 with alpha (assign_tc.cu, MMA issuer)
+        ksteps = 10
+        flop_exec = 2.0 * blocks_per_launch * k * 16 * ksteps
+        sec = ms_a * 1e-3
+        ach_alg = flop_alg / sec / 1e12 if sec > 0 else 0.0
+        ach_exec = flop_exec / sec / 1e12 if sec > 0 else 0.0
         traffic = None
         import glob
         tfiles = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_traffic.json")))
         tpath = tfiles[-1] if tfiles else ""
-        if world == 1 and tpath:  # DRAM bytes per launch of the same kernel on the same config, from the committed ncu capture
+        if world == 1 and n_tex == 1 and tpath:  # DRAM bytes per launch of the same kernel on the same config, from the committed ncu capture
             traffic = json.load(open(tpath))["assign_tc_kernel"]["dram_bytes_per_launch"]
-        roofline = {"bound": "tensor", "kernel": "assign_tc_kernel (N x K x 64 contraction as 3 bf16 partial products + argmax epilogue)",
-                    "achieved": achieved, "peak": pk["bf16_tflops_sustained"], "unit": "TFLOP/s",
-                    "frac": achieved / pk["bf16_tflops_sustained"], "traffic": traffic,
+        peak = pk["bf16_tflops_sustained"]
+        roofline = {"bound": "tensor", "kernel": "assign_tc_kernel (N x K x 64 contraction as bf16 partial products + argmax epilogue)",
+                    "achieved": ach_alg, "peak": peak, "unit": "TFLOP/s", "frac": ach_alg / peak, "traffic": traffic,
+                    "frac_algorithmic": ach_alg / peak, "achieved_executed": ach_exec, "frac_executed": ach_exec / peak,
+                    "executed_over_algorithmic": 16.0 * ksteps / 64.0,
                     "peak_source": pk["src"] + " bf16 sustained (kernel timed inside a step)",
-                    "ms_per_launch": ms_a, "launches_timed": n_fe, "flop_per_launch_algorithmic": flop_alg, "bf16_split": split,
-                    "achieved_unsplit": flop_alg / (ms_a * 1e-3) / 1e12 if ms_a > 0 else 0.0,
+                    "ms_per_launch": ms_a, "launches_timed": n_fe, "flop_per_launch_algorithmic": flop_alg,
+                    "flop_per_launch_executed": flop_exec, "mma_ksteps_per_tile_chunk": ksteps,
                     "share_of_step": ms_fe / (ms_dev / args.steps) if ms_dev > 0 else None}
-        # bounded CPU sample of the same workload on this box's host cores
-        px = cpu_sample_pixels(textures[0])
-        threads = os.cpu_count() or 1
-        dt, kind, cent_ref, idx_ref = cpu_reference_step(px, threads)
-        solo = binding.Encoder(local_rank)   # no communicator: the parity sample is a single-GPU call on rank 0 only
-        parity = parity_report(solo, px, cent_ref, idx_ref)
-        solo.close()
-        cpu = {"value": len(px) / dt, "unit": "blocks/s", "cores": threads if kind == "reference" else 1, "kind": kind,
-               "sample": f"{CPU_SAMPLE}x{CPU_SAMPLE} crop ({len(px)} blocks) of the bench texture, one pass, "
-                         f"BuildCodebook+QuantizeBlocks {dt:.2f} s"}
-        bytes_in = n * 8 * n_tex
-        bytes_out = (k * 48 + n_local * 4) * n_tex
         phases = ("h2d", "decode", "seed", "lloyd", "finalize", "quantize", "d2h")
+        bytes_in = sum(int(pinned_in[t].numel()) for t in held)
+        bytes_out = (k * 48 + n_local * 4) * len(held)
+        cfgd = workload_config(n_tex)
+        par = "1 GPU" if world == 1 and n_tex == 1 else (
+            f"{n_tex} textures, texture-parallel placement: whole textures on rank t % {world}, zero collectives" if texture_parallel else
+            f"{n_tex} textures in lock step, blocks sharded over {world} GPU(s), seeding texture-parallel, one NCCL all-reduce of "
+            f"{n_tex} x K x 65 int64 per pass; a rank receives whole only the textures it seeds and its block shard of the others")
         out = {
             "metric": "vq_blocks_per_sec", "value": value, "unit": "blocks/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(3, args.warmup), "ms_per_step": ms_dev / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"BC1 VQ compress of {n_tex} synthetic 4096x4096 texture(s) (config 2 per GPU): "
-                                   "seeding+Lloyd+assign, K=512, maxIterations=32, Oklab metric",
-                       "blocks_per_texture": n, "textures": n_tex, "codebook": k,
-                       "parallelism": "1 GPU" if world == 1 else f"{n_tex} textures in lock step, blocks sharded over {world} GPUs, seeding texture-parallel, "
-                                      f"one NCCL all-reduce of {n_tex} x K x 65 int64 per pass",
+            "scaling": "weak" if not args.textures else "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": cfgd,
+            "detail": {"parallelism": par,
                        "l2": "no explicit flush: each step streams a 330 MB working set (features + pixel planes) > 126 MB L2",
                        "lloyd_passes": last.lloyd_passes, "ms_per_texture": ms_dev / args.steps / n_tex,
                        "phases_ms": {p: getattr(last, "ms_" + p) for p in phases},
                        "wall_ms_per_step": wall_dev / args.steps},
             "e2e": {"value": e2e, "unit": "blocks/s", "h2d_bytes_per_step": bytes_in, "d2h_bytes_per_step": bytes_out,
-                    "ms_per_step": ms_e2e / args.steps, "wall_ms_per_step": wall_e2e / args.steps},
+                    "ms_per_step": ms_e2e / args.steps, "wall_ms_per_step": wall_e2e / args.steps,
+                    "note": "rank 0's bytes; pinned host buffers, copies inside the timed region"},
             "gpu_launches": launches,
             "roofline": roofline,
-            "cpu_baseline": cpu,
-            "parity": parity,
             "clocks": clocks.summary(),
         }
+        if multi is not None:
+            out["parity_multi_gpu"] = multi
+        if not args.no_extras:
+            # bounded CPU sample of the same workload on this box's host cores + the SURVEY 8d parity gates on it
+            px = cpu_sample_pixels(tex0_host)
+            threads = os.cpu_count() or 1
+            dt, kind, cent_ref, idx_ref = cpu_reference_step(px, threads)
+            solo = binding.Encoder(local_rank)   # no communicator: the parity sample is a single-GPU call on rank 0 only
+            out["parity"] = parity_report(solo, px, cent_ref, idx_ref)
+            out["cpu_baseline"] = {"value": len(px) / dt, "unit": "blocks/s", "cores": threads if kind == "reference" else 1, "kind": kind,
+                                   "sample": f"{CPU_SAMPLE}x{CPU_SAMPLE} crop ({len(px)} blocks) of the bench texture, one pass, "
+                                             f"BuildCodebook+QuantizeBlocks {dt:.2f} s"}
+            if world == 1:
+                out["decompress_gather"] = gather_report(solo, torch, dev, pk)
+                out["compress_breakdown"] = compress_report()
+            solo.close()
         print(json.dumps(out))
     enc.close()
     if world > 1:
@@ -324,12 +434,60 @@ def run_ours(args, rank, world, local_rank):
     return out
 
 
+def gather_report(enc, torch, dev, pk):
+    """the DecompressToBCn gather bc[i] = codebook[idx[i]] (src/vq_bcn_compressor.cpp:350-358; README.md:18 quotes
+    7-11 ms for 4096x4096 on the CPU).  Device-resident: CUDA events around the C-ABI call; host: the same call with pinned
+    host buffers (4 MB of indices in, 8-16 MB of blocks out over PCIe)."""
+    rep = {"reference_readme_ms_4096": "7-11 (CPU memcpy loop, README.md:18)", "peak_gbs": pk["hbm_gbs"]}
+    rng = np.random.default_rng(5)
+    for name, bs, n in (("bc1_4096", 8, 1 << 20), ("bc7_4096", 16, 1 << 20), ("bc7_16384", 16, 1 << 24)):
+        cb = torch.from_numpy(rng.integers(0, 256, (512, bs), dtype=np.uint8)).to(dev)
+        idx = torch.from_numpy(rng.integers(0, 512, n, dtype=np.int64).astype(np.int32)).to(dev)
+        o = torch.empty(n * bs, dtype=torch.uint8, device=dev)
+        best = 1e9
+        for _ in range(8):
+            enc.timer_start()
+            enc.gather_codebook_raw(cb.data_ptr(), 512, bs, idx.data_ptr(), n, o.data_ptr())
+            best = min(best, enc.timer_stop())
+        ok = bool(torch.equal(o.view(n, bs), cb[idx.long()]))
+        gb = n * (4 + bs) / 1e9
+        rep[name] = {"blocks": n, "block_bytes": bs, "device_us": best * 1e3, "gbs": gb / (best * 1e-3), "frac_of_hbm_peak": gb / (best * 1e-3) / pk["hbm_gbs"],
+                     "correct": ok}
+        if n == 1 << 20:
+            hcb, hidx = cb.cpu().numpy(), idx.cpu().numpy().view(np.uint32)
+            t0 = time.perf_counter()
+            for _ in range(5):
+                enc.gather_codebook(hcb, hidx)
+            rep[name]["host_to_host_ms"] = (time.perf_counter() - t0) / 5 * 1e3
+    return rep
+
+
+def compress_report():
+    """SURVEY 8d: the whole VQBCnCompressor::Compress call on the 4096^2 RGB image with the stages outside the GPU core timed
+    separately -- Compressonator BC1 pre-pass, device VQ core, K centroid encodes (A16), zstd (the reference prints the sum,
+    example/example.cpp:293-304).  Runs through libyuptexture.so (the C++ drop-in) with the Compressonator codec plugin."""
+    from yuptexture_b200 import hostapi, synth
+    if not hostapi.available():
+        return {"unavailable": "libyuptexture.so not built"}
+    img = synth.ldr_rgb(TEX, TEX, seed=1000)
+    threads = os.cpu_count() or 1
+    rep = {"codec": hostapi.codec_name(), "threads": threads}
+    for _ in range(2):   # the second call has a warm device arena
+        rep["stages_ms"] = hostapi.compress_timed(img, bc_format=1, quality=QUALITY, max_iterations=MAX_ITER, use_zstd=True,
+                                                  threads=threads, seed=SEED)
+    return rep
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--textures", type=int, default=0, help="textures per step (default: one per GPU = weak scaling; 64 = BASELINE config 5 as stated)")
+    ap.add_argument("--placement", default="block", choices=["block", "texture"],
+                    help="block: lock-step batch, blocks sharded over the GPUs (headline); texture: whole textures per GPU, no collectives")
+    ap.add_argument("--no-extras", action="store_true", help="skip the CPU sample, parity sample, gather and Compress breakdown legs")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -203,18 +203,22 @@ YUPVQ_API int yupvq_encode_bcn_sharded(yupvq_ctx* ctx, const uint8_t* bc_blocks,
                                        uint8_t* out_pixel_centroids, uint32_t* out_indices, yupvq_stats* stats);
 
 /* Lock-step batch over block shards (BASELINE config 5): n_textures textures of n_total
- * blocks each (every rank passes all of them), this rank owns blocks [first_block, first_block +
- * n_local) of EVERY texture.  Texture t is seeded on rank t % n_ranks (the K seed rows are combined
+ * blocks each, this rank owns blocks [first_block, first_block + n_local) of EVERY texture.
+ * Texture t is seeded on rank t % n_ranks (the K seed rows are combined
  * by one all-reduce), all textures run their Lloyd passes together and ONE all-reduce per pass carries
  * the K x 65 fixed-point sums/counts of the whole batch.  Texture t uses seed cfg->seed + t, as
  * yupvq_encode_bcn_batch does; results are identical to the single-GPU call.  Without a
  * communicator (yupvq_comm_init not called) it is the single-GPU lock-step batch (n_local = n_total).
- * out_pixel_centroids[t]: K x 16*channels bytes; out_indices[t]: n_local indices. */
+ * out_pixel_centroids[t]: K x 16*channels bytes; out_indices[t]: n_local indices.
+ * shard_only (may be NULL = every pointer is a whole texture): shard_only[t] != 0 says bc_blocks[t] points at this
+ * rank's n_local blocks only.  A rank needs the whole texture just for the textures it seeds (t % n_ranks == rank),
+ * so with the flags set its input (and H2D traffic) is n_textures / n_ranks whole textures plus one shard of each of
+ * the others, instead of growing with n_textures. */
 YUPVQ_API int yupvq_encode_bcn_batch_sharded(yupvq_ctx* ctx, const uint8_t* const* bc_blocks, size_t n_textures,
                                              size_t n_total, size_t first_block, size_t n_local, int bc_format,
                                              int channels, const yupvq_config* cfg,
                                              uint8_t* const* out_pixel_centroids, uint32_t* const* out_indices,
-                                             yupvq_stats* stats);
+                                             yupvq_stats* stats, const uint8_t* shard_only);
 
 #ifdef __cplusplus
 }

@@ -205,5 +205,14 @@ def quantize_blocks_hdr(blocks, ch, centroids, threads=8):
     return idx, float(t[0])
 
 
+def encode_blocks(pixel_blocks, ch, fmt, bc_quality=1.0, threads=8):
+    """K calls of the reference's 4x4 encode (CompressSingleBlock, src/vq_encoder.cpp:248-250) -> (K, blockSize) u8."""
+    pixel_blocks = _c(pixel_blocks, np.uint8).reshape(-1, 16 * ch)
+    out = np.zeros((pixel_blocks.shape[0], BLOCK_BYTES[fmt]), np.uint8)
+    for k in range(pixel_blocks.shape[0]):
+        lib().ref_encode_single_block(_p(pixel_blocks[k], _u8p), ch, fmt, bc_quality, threads, _p(out[k], _u8p))
+    return out
+
+
 def num_threads():
     return int(lib().ref_num_threads())

@@ -31,6 +31,11 @@ def golden_pipeline():
 
 
 @pytest.fixture(scope="session")
+def golden_pipeline2():
+    return np.load(os.path.join(GOLDEN, "pipeline2.npz"))
+
+
+@pytest.fixture(scope="session")
 def oracle():
     """CPU restatement (oracle/vq_oracle.cpp), built on demand with g++."""
     from oracle import orcbind

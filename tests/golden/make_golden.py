@@ -156,10 +156,39 @@ def pipeline_vectors():
     np.savez_compressed(os.path.join(OUT, "pipeline.npz"), **out)
 
 
+def pipeline2_vectors():
+    """Round-2 additions (kept in their own file so pipeline.npz stays byte-stable): the fast-mode sampling prologue's
+    seed blocks (maxIterations = 0: shuffle + K-Means++ only, bit-exact on the GPU) and a larger HDR case for a
+    two-sided 0.05 dB gate."""
+    out = {}
+    img = synth.ldr_rgb(64, 64, seed=21)
+    bc = R.bcn_encode(img, 1, quality=0.3, threads=1)
+    px = R.bcn_decode_blocks(bc, 64, 64, 3, 1)
+    out["ratio_px"] = px
+    for ratio, seed in [(0.4, 51), (0.13, 52), (0.9, 53)]:
+        c, _, _ = R.build_codebook(px, 3, 1, 0.17, 0, seed, ratio=ratio, threads=1)
+        out[f"ratio_seeds_{seed}"] = c
+        out[f"ratio_meta_{seed}"] = np.array([ratio, seed, R.codebook_size(0.17)], np.float64)
+    img = synth.hdr_rgb(256, 128, seed=62)
+    px = synth.image_to_blocks(img)
+    q = 0.33
+    out["hdrL_img"] = img
+    out["hdrL_meta"] = np.array([256, 128, 6, 3, R.codebook_size(q), 62, 32], np.int64)
+    out["hdrL_seeds"], _, _ = R.build_codebook_hdr(px, 3, q, 0, 62, threads=1)
+    cent, _, _ = R.build_codebook_hdr(px, 3, q, 32, 62, threads=1)
+    out["hdrL_centroids"] = cent
+    out["hdrL_indices"], _ = R.quantize_blocks_hdr(px, 3, cent, threads=1)
+    np.savez_compressed(os.path.join(OUT, "pipeline2.npz"), **out)
+
+
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "pipeline2":
+        pipeline2_vectors()
+        sys.exit(0)
     decode_vectors()
     colour_vectors()
     pipeline_vectors()
+    pipeline2_vectors()
     for f in sorted(os.listdir(OUT)):
         if f.endswith(".npz"):
             print(f, os.path.getsize(os.path.join(OUT, f)) // 1024, "KiB")

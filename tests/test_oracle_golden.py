@@ -115,3 +115,20 @@ def test_hdr_pipeline(oracle, golden_pipeline, name):
     cent, _ = oracle.build_codebook_hdr(px, ch, k, iters, seed, threads=1)
     assert bits_equal(cent, g[f"{name}_centroids"])
     assert bits_equal(oracle.quantize_blocks_hdr(px, ch, cent), g[f"{name}_indices"])
+
+
+def test_round2_goldens(oracle, golden_pipeline2):
+    """pipeline2.npz: the fast-mode sampling prologue at maxIterations = 0 (shuffle + K-Means++ seeds) and a larger HDR case."""
+    g = golden_pipeline2
+    px = g["ratio_px"]
+    for seed in (51, 52, 53):
+        ratio, s, k = g[f"ratio_meta_{seed}"]
+        c, _ = oracle.build_codebook(px, 3, int(k), 0, int(s), ratio=float(ratio))
+        assert bits_equal(c, g[f"ratio_seeds_{seed}"])
+    w, h, fmt, ch, k, seed, iters = (int(v) for v in g["hdrL_meta"])
+    hp = oracle.gather_tiles_f32(g["hdrL_img"])
+    seeds, _ = oracle.build_codebook_hdr(hp, ch, k, 0, seed)
+    assert bits_equal(seeds, g["hdrL_seeds"])
+    cent, _ = oracle.build_codebook_hdr(hp, ch, k, iters, seed, threads=1)
+    assert bits_equal(cent, g["hdrL_centroids"])
+    assert bits_equal(oracle.quantize_blocks_hdr(hp, ch, cent), g["hdrL_indices"])

@@ -59,6 +59,25 @@ def main():
         ok &= np.array_equal(cents[t], want[t][0]) and np.array_equal(idxs[t], want[t][1][first:first + n_local])
     ok &= st.lloyd_passes == sum(w[2] for w in want)
 
+    # (3) the same batch with shard-only inputs: whole textures only where this rank seeds them (t % world == rank)
+    parts = [bc if t % world == rank else bc[first:first + n_local] for t, bc in enumerate(texs)]
+    cents, idxs, _ = enc.encode_bcn_batch_sharded(parts, n, first, n_local, 1, 3, cfg, shard_only=[t % world != rank for t in range(len(texs))])
+    for t in range(len(texs)):
+        ok &= np.array_equal(cents[t], want[t][0]) and np.array_equal(idxs[t], want[t][1][first:first + n_local])
+    # (4) seed == 0 (std::random_device, the reference's default) on the sharded single-texture path: rank 0's draw is
+    # broadcast, so all ranks must still end with ONE codebook, and the indices must be the exact argmin against it
+    c0 = binding.make_config(codebook=k, max_iterations=iters, seed=0)
+    cent0, idx0, _ = enc.encode_bcn_sharded(texs[0], n, first, n_local, 1, 3, c0)
+    mine = torch.from_numpy(cent0.astype(np.int32)).to(dev)
+    lo, hi = mine.clone(), mine.clone()
+    dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+    dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+    ok &= bool(torch.equal(lo, hi))
+    # (5) a context with a communicator still runs the rank-local entry points on its own (different texture per rank)
+    c5 = binding.make_config(codebook=k, max_iterations=iters, seed=9 + rank % len(texs))
+    cent5, idx5, st5 = enc.encode_bcn(texs[rank % len(texs)], n, 1, 3, c5)
+    ok &= np.array_equal(cent5, want[rank % len(texs)][0]) and np.array_equal(idx5, want[rank % len(texs)][1])
+
     flag = torch.tensor([1 if ok else 0], device=dev)
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     enc.close()

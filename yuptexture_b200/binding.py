@@ -81,7 +81,7 @@ def lib():
         L.yupvq_encode_bcn_sharded.argtypes = [_vp, _vp, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int, C.c_int, cfgp,
                                                _vp, _vp, stp]
         L.yupvq_encode_bcn_batch_sharded.argtypes = [_vp, C.POINTER(_vp), C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t,
-                                                     C.c_int, C.c_int, cfgp, C.POINTER(_vp), C.POINTER(_vp), stp]
+                                                     C.c_int, C.c_int, cfgp, C.POINTER(_vp), C.POINTER(_vp), stp, _vp]
         _lib = L
     return _lib
 
@@ -196,8 +196,10 @@ class Encoder:
         self._ck(self._L.yupvq_profile_read(self._ctx, C.byref(ms), C.byref(n)), "yupvq_profile_read")
         return ms.value, n.value
 
-    def encode_bcn_batch_sharded(self, textures, n_total, first, n_local, fmt, ch, cfg, out_centroids=None, out_indices=None):
-        """Lock-step batch (config 5): `textures` = list of whole-texture BCn arrays or raw device pointers;
+    def encode_bcn_batch_sharded(self, textures, n_total, first, n_local, fmt, ch, cfg, out_centroids=None, out_indices=None,
+                                 shard_only=None):
+        """Lock-step batch (config 5): `textures` = list of whole-texture BCn arrays or raw device pointers
+        (shard_only[t] true: just this rank's blocks [first, first + n_local) of texture t);
         outputs are lists (numpy arrays or raw device pointers), one per texture."""
         t_n = len(textures)
         textures = [x if isinstance(x, int) else _c(x, np.uint8) for x in textures]
@@ -207,8 +209,10 @@ class Encoder:
             out_indices = [np.empty(n_local, np.uint32) for _ in range(t_n)]
         arr = lambda xs: (_vp * t_n)(*[None if x is None else _ptr(x).value for x in xs])
         st = Stats()
+        flags = None if shard_only is None else np.ascontiguousarray([1 if x else 0 for x in shard_only], dtype=np.uint8)
         self._ck(self._L.yupvq_encode_bcn_batch_sharded(self._ctx, arr(textures), t_n, n_total, first, n_local, fmt, ch,
-                                                        C.byref(cfg), arr(out_centroids), arr(out_indices), C.byref(st)),
+                                                        C.byref(cfg), arr(out_centroids), arr(out_indices), C.byref(st),
+                                                        _ptr(flags)),
                  "yupvq_encode_bcn_batch_sharded")
         return out_centroids, out_indices, st
 
@@ -331,6 +335,11 @@ class Encoder:
         self._ck(self._L.yupvq_gather_codebook(self._ctx, _ptr(codebook), n_entries, bs, _ptr(indices), indices.size,
                                                _ptr(out)), "yupvq_gather_codebook")
         return out
+
+    def gather_codebook_raw(self, codebook_ptr, n_entries, block_size, indices_ptr, n_blocks, out_ptr):
+        """yupvq_gather_codebook on raw (device or host) pointers."""
+        self._ck(self._L.yupvq_gather_codebook(self._ctx, _vp(codebook_ptr), n_entries, block_size, _vp(indices_ptr), n_blocks,
+                                               _vp(out_ptr)), "yupvq_gather_codebook")
 
     # ---- multi-GPU
     def comm_unique_id(self):

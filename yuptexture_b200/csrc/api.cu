@@ -1599,7 +1599,7 @@ int yupvq_encode_bcn_sharded(yupvq_ctx* ctx, const uint8_t* bc_blocks, size_t n_
 int yupvq_encode_bcn_batch_sharded(yupvq_ctx* ctx, const uint8_t* const* bc_blocks, size_t n_textures, size_t n_total,
                                    size_t first_block, size_t n_local, int bc_format, int channels,
                                    const yupvq_config* cfg, uint8_t* const* out_pixel_centroids,
-                                   uint32_t* const* out_indices, yupvq_stats* stats) {
+                                   uint32_t* const* out_indices, yupvq_stats* stats, const uint8_t* shard_only) {
     if (!ctx) return 1;
     Scope scope(ctx->device);
     init_stats(stats);
@@ -1655,6 +1655,8 @@ int yupvq_encode_bcn_batch_sharded(yupvq_ctx* ctx, const uint8_t* const* bc_bloc
     CK(cudaMemsetAsync(ctx->bt_cent.p, 0, T * (size_t)K * 256, ctx->stream));
     for (size_t t = 0; t < T; ++t) {
         if ((int)(t % (size_t)R) != rank) continue;
+        if (shard_only && shard_only[t])
+            return ctx->fail("texture %zu is seeded on this rank (t %% n_ranks == rank): its whole BCn data is needed, not a shard", t);
         const void* bc_dev = nullptr;
         if (to_device(ctx, bc_blocks[t], n_total * bb, ctx->in_bytes, &bc_dev)) return 1;
         // pixel planes only: the seeding reads nothing else, and the fp64 colour conversion (the expensive part of the
@@ -1687,11 +1689,13 @@ int yupvq_encode_bcn_batch_sharded(yupvq_ctx* ctx, const uint8_t* const* bc_bloc
     CK(cudaMemsetAsync(maxabs_d, 0, T * 8, ctx->stream));
     for (size_t t = 0; t < T; ++t) {
         const uint8_t* shard_dev = nullptr;
+        // shard_only[t]: the caller passed just blocks [first_block, first_block + n_local) of this texture
+        const uint8_t* shard_src = bc_blocks[t] + ((shard_only && shard_only[t]) ? 0 : first_block * bb);
         if (is_device_ptr(bc_blocks[t])) {
-            shard_dev = bc_blocks[t] + first_block * bb;
+            shard_dev = shard_src;
         } else {
             const void* p = nullptr;
-            if (to_device(ctx, bc_blocks[t] + first_block * bb, nl * bb, ctx->in_bytes, &p)) return 1;
+            if (to_device(ctx, shard_src, nl * bb, ctx->in_bytes, &p)) return 1;
             shard_dev = reinterpret_cast<const uint8_t*>(p);
         }
         if (n_local) {
