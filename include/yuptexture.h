@@ -168,6 +168,9 @@ public:
                          std::vector<std::vector<float>>& outPixelFloatCentroids, std::vector<uint32_t>& outIndices,
                          const CompressionParams& params);
     yupvq_ctx* Context();  // lazily created
+    // Use a context owned by someone else (VQBCnCompressor keeps one across its Compress calls, so the per-call VQEncoder
+    // of the reference's structure, src/vq_bcn_compressor.cpp:136, does not pay for a new device arena each time).
+    void AttachContext(yupvq_ctx* shared);
     // wall-clock milliseconds of the last Encode* / BuildCodebook* call: the device VQ core (incl. its H2D / D2H) and
     // the K host-side centroid encodes (A16), timed separately
     double LastVqMs() const { return lastVqMs; }
@@ -180,6 +183,7 @@ private:
     uint64_t seed = 0;
     int device = 0;
     yupvq_ctx* ctx = nullptr;
+    bool ownsCtx = true;
     double lastVqMs = 0.0, lastCentroidMs = 0.0;
     VQCodebook EncodeCentroids(const std::vector<std::vector<uint8_t>>& pixelCentroids, uint8_t channels,
                                const CompressionParams& params);
@@ -216,7 +220,8 @@ private:
     BCnCompressor bcnCompressor;
     struct ZstdContext;
     std::unique_ptr<ZstdContext> zstdCtx;
-    std::unique_ptr<VQEncoder> gather_;  // owns the device context DecompressToBCn gathers with
+    std::unique_ptr<VQEncoder> gather_;  // owns the device context shared by the Compress calls and the DecompressToBCn gather
+    yupvq_ctx* SharedContext();
     uint64_t seed_ = 0;
     std::vector<uint8_t> compressWithZstd(const std::vector<uint8_t>& payload, int level, int numThreads, bool enableLdm);
 };

@@ -29,7 +29,9 @@ if [ -n "$ZLIB" ]; then
   EXTRA_DEF="-DYUPREF_HAVE_CONTAINER"
 fi
 g++ $CXXFLAGS $EXTRA_DEF -c "$HERE/ref_harness.cpp" -o "$OUT/ref_harness.o"
-g++ -shared -fopenmp -o "$OUT/libyupref.so" "$OUT/ref_harness.o" "$OUT/vq_encoder.o" "$OUT/bcn_compressor.o" $EXTRA_OBJ \
+# -Bsymbolic: the reference's classes carry the same names as the drop-in's (libyuptexture.so); a process that loads both
+# (tests/cpp/dropin_test.cpp) must see every call inside this library bind to the reference's own definitions
+g++ -shared -fopenmp -Wl,-Bsymbolic -o "$OUT/libyupref.so" "$OUT/ref_harness.o" "$OUT/vq_encoder.o" "$OUT/bcn_compressor.o" $EXTRA_OBJ \
   -Wl,--start-group "$L/libCMP_Compressonator.a" "$L/libCMP_Common.a" "$L/libCMP_Core.a" \
   "$L/libCMP_Core_SSE.a" "$L/libCMP_Core_AVX.a" "$L/libCMP_Core_AVX512.a" -Wl,--end-group -lpthread -ldl
 echo "build_ref: built $OUT/libyupref.so"

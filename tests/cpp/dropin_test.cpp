@@ -63,7 +63,7 @@ struct Ref {
 };
 
 static Ref load_ref(const char* path) {
-    void* h = dlopen(path, RTLD_NOW | RTLD_LOCAL);
+    void* h = dlopen(path, RTLD_NOW | RTLD_LOCAL | RTLD_DEEPBIND);   // its classes share names with ours: bind inside first
     if (!h) throw std::runtime_error(std::string("cannot load ") + path + ": " + dlerror());
     Ref r;
     r.compress = (ref_compress_fn)dlsym(h, "ref_compress");

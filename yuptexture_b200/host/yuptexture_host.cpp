@@ -418,7 +418,13 @@ void CompressionConfig::SetQuality(float quality_level) {
 VQEncoder::VQEncoder(const CompressionConfig& cfg) : config(cfg), seed(default_seed()), device(default_device()) {}
 
 VQEncoder::~VQEncoder() {
-    if (ctx) yupvq_destroy(ctx);
+    if (ctx && ownsCtx) yupvq_destroy(ctx);
+}
+
+void VQEncoder::AttachContext(yupvq_ctx* shared) {
+    if (ctx && ownsCtx) yupvq_destroy(ctx);
+    ctx = shared;
+    ownsCtx = false;
 }
 
 void VQEncoder::SetFormat(BCFormat format) { bcFormat = format; }
@@ -575,6 +581,11 @@ struct VQBCnCompressor::ZstdContext {
 VQBCnCompressor::VQBCnCompressor() : zstdCtx(std::make_unique<ZstdContext>()), seed_(default_seed()) {}
 VQBCnCompressor::~VQBCnCompressor() = default;
 
+yupvq_ctx* VQBCnCompressor::SharedContext() {
+    if (!gather_) gather_ = std::make_unique<VQEncoder>();
+    return gather_->Context();
+}
+
 void VQBCnCompressor::LoadDictionary(const uint8_t* dictData, size_t dictSize) {  // :63-78
     Zstd& z = Zstd::get();
     if (zstdCtx->cdict) z.freeCDict(zstdCtx->cdict);
@@ -664,6 +675,7 @@ std::vector<uint8_t> VQBCnCompressor::Compress(const uint8_t* inData, uint32_t w
         payload = std::move(bcData);
     } else {
         VQEncoder enc(vq_config(params, false));
+        enc.AttachContext(SharedContext());
         enc.SetFormat(params.bcFormat);
         enc.SetSeed(seed_);
         const size_t bs = BCBlockSize::GetSize(params.bcFormat);
@@ -698,6 +710,7 @@ std::vector<uint8_t> VQBCnCompressor::CompressHDR(const float* inData, uint32_t 
         if (payload.empty()) throw std::runtime_error("HDR BCn compression failed");
     } else {
         VQEncoder enc(vq_config(params, true));
+        enc.AttachContext(SharedContext());
         enc.SetFormat(params.bcFormat);
         enc.SetSeed(seed_);
         std::vector<std::vector<float>> centroids;
@@ -743,9 +756,8 @@ std::vector<uint8_t> VQBCnCompressor::DecompressToBCn(const std::vector<uint8_t>
     if (payload.size() != cb_bytes + n * sizeof(uint32_t))
         throw std::runtime_error("Decompressed data size mismatch. Expected codebook + indices.");
     // bc[i] = codebook[indices[i]] (:350-358) as a device gather
-    if (!gather_) gather_ = std::make_unique<VQEncoder>();
     std::vector<uint8_t> bc(n * bs);
-    if (yupvq_gather_codebook(gather_->Context(), payload.data(), outInfo.storedCodebookEntries, (uint32_t)bs,
+    if (yupvq_gather_codebook(SharedContext(), payload.data(), outInfo.storedCodebookEntries, (uint32_t)bs,
                               reinterpret_cast<const uint32_t*>(payload.data() + cb_bytes), n, bc.data()))
         throw std::runtime_error(std::string("DecompressToBCn: ") + yupvq_last_error(gather_->Context()));
     return bc;
