@@ -96,6 +96,7 @@ struct yupvq_ctx {
     DevBuf cent_px, cent_feat, out_idx;                // finalize / quantize
     // tensor engine (assign_tc.cu): per block set A', |x'|, mu; per pass B', folded norms, candidates
     DevBuf tc_a, tc_xnorm, tc_small, tc_b, tc_bx, tc_cand, tc_amb;
+    DevBuf tail_scratch;       // fused pass tail: one (max error, index) slot per CTA for the grid-wide reseed arg-max
     DevBuf tc_chg, delta_ctl;  // delta update: (row, previous centroid) lists; counter / mode words
     // lock-step batch (yupvq_encode_bcn_batch_sharded): per-texture slices of one buffer each
     DevBuf bt_feat, bt_tca, bt_xnorm, bt_tcsmall, bt_assign, bt_errors, bt_cent, bt_acc, bt_misc, bt_centpx, bt_cent0, bt_acc_local;
@@ -143,7 +144,8 @@ namespace {
 enum { F_CHANGED = 0, F_EMPTY = 1, F_RESEEDS = 2, F_SPARE = 3, F_SEED_STATUS = 4 /*2 words*/, F_COUNTER = 6, F_MAXABS = 7,
        F_PAIRS = 8 /*2 words*/, F_CTL = 10 /*stop, passes, empty clusters*/, F_AMB = 13 /*count, ticket*/,
        F_WORDS = 16 };
-// tc_small layout (bytes): [0,512) column sums fp64 | [512,768) mu fp32 | [768,772) cmax
+// tc_small layout (bytes): [0,512) column sums fp64 | [512,768) mu fp32 | [768,776) cmax (two words: double-buffered by
+// pass parity in the fused Lloyd loop, word 0 otherwise)
 enum { TC_SUMS = 0, TC_MU = 512, TC_CMAX = 768, TC_SMALL_BYTES = 1024 };
 
 bool is_device_ptr(const void* p) {
@@ -518,7 +520,70 @@ int run_lloyd(yupvq_ctx* ctx, const Blocks& b, size_t n_total, size_t first_bloc
             dl.chg_old = dl.chg_rows + n;
             dl.chg_count = dctl;
         }
-        for (uint32_t iter = 0; iter < max_iter; ++iter) {
+        // Fused pass: four launches per pass -- front-end, re-rank (its last CTA prepares the update), one
+        // update kernel (full or delta, chosen on the device) and one tail kernel (convergence test, finalize, reseed,
+        // operands of the next pass).  Same arithmetic, same results as the separate kernels below (YUPVQ_NO_TAIL_FUSE=1).
+        const bool fused_pass = delta && !dbg.no_tail_fuse && accumulate_auto_supported(n, K, 1u) && K <= 65535u;
+        if (fused_pass) {
+            if (tc_prepare_blocks(ctx, b.feat, n)) return 1;
+            const uint32_t k_pad = tc_padded_k(K);
+            CK(ctx->tc_b.ensure((size_t)k_pad * 256));
+            CK(ctx->tc_bx.ensure((size_t)k_pad * 32));
+            CK(ctx->tc_cand.ensure(std::max<size_t>(1, n) * 16));
+            CK(ctx->tc_amb.ensure(std::max<size_t>(1, n) * 4));
+            CK(ctx->tail_scratch.ensure(4096));
+            uint8_t* sm = ctx->tc_small.as<uint8_t>();
+            CK(cudaMemsetAsync(sm + TC_CMAX, 0, 8, ctx->stream));
+            LAUNCH(launch_tc_prep_centroids(cent, K, reinterpret_cast<const float*>(sm + TC_MU), ctx->tc_b.as<float>(), ctx->tc_bx.as<float>(),
+                                            reinterpret_cast<float*>(sm + TC_CMAX), ctx->stream, ctx->tc_rgb));
+            dl.rgb = (uint32_t)ctx->tc_rgb;
+            AccPrep prep{acc, dctl, K, (uint32_t)(n / 4), 0u, 1u, 0};
+            TailArgs ta{};
+            ta.acc = acc;
+            ta.n_textures = 1;
+            ta.K = K;
+            ta.k_pad = k_pad;
+            ta.break_after = break_after;
+            ta.flags = flags;
+            ta.flags_stride = 0;
+            ta.ctl = ctl;
+            ta.sticky = nullptr;
+            ta.inv_scale = std::ldexp(1.0, -shift);
+            ta.cent = cent;
+            ta.small = sm;
+            ta.mu_off = TC_MU;
+            ta.cmax_off = TC_CMAX;
+            ta.b_main = ctx->tc_b.as<float>();
+            ta.b_ext = ctx->tc_bx.as<float>();
+            ta.rgb = ctx->tc_rgb;
+            ta.feat = b.feat;
+            ta.n_rows = n;
+            ta.assign = assign;
+            ta.errors = errors;
+            ta.scratch_val = ctx->tail_scratch.as<float>();
+            ta.scratch_idx = reinterpret_cast<unsigned long long*>(ctx->tail_scratch.as<uint8_t>() + 2048);
+            for (uint32_t iter = 0; iter < max_iter; ++iter) {
+                const float* cmax = reinterpret_cast<const float*>(sm + TC_CMAX) + (iter & 1u);
+                const bool prof = ctx->profile && ctx->pev_used + 2 <= ctx->pev.size();
+                if (prof) cudaEventRecord(ctx->pev[ctx->pev_used++], ctx->stream);
+                LAUNCH(launch_assign_tc(ctx->tc_a.as<float>(), ctx->tc_xnorm.as<float>(), n, ctx->tc_b.as<float>(), ctx->tc_bx.as<float>(), K, cmax,
+                                        ctx->tc_cand.as<uint4>(), assign, flags, ctx->tc_amb.as<uint32_t>(), flags + F_AMB, stopk, ctx->stream, &dl));
+                if (prof) cudaEventRecord(ctx->pev[ctx->pev_used++], ctx->stream);
+                prep.force_full = iter == 0 ? 1u : 0u;
+                LAUNCH(launch_rerank_sparse(b.feat, cent, K, ctx->tc_cand.as<uint4>(), ctx->tc_amb.as<uint32_t>(), flags + F_AMB, flags + F_AMB + 1,
+                                            assign, flags, flags + F_PAIRS, ctx->stream, &dl, &prep));
+                LAUNCH(launch_accumulate_auto(b.feat, n, assign, K, shift, acc, dl.chg_rows, dl.chg_old, dctl, flags, stopk, ctx->stream));
+                ta.iter = iter;
+                LAUNCH(launch_lloyd_tail(ta, ctx->stream));
+                if (dbg.async_dbg & 1) CK(cudaStreamSynchronize(ctx->stream));
+                if ((iter == 3 || iter == 7 || iter == 15) && iter + 1 < max_iter) {
+                    CK(cudaMemcpyAsync(ctx->h_small, ctl, 4, cudaMemcpyDeviceToHost, ctx->stream));
+                    CK(cudaStreamSynchronize(ctx->stream));
+                    if (ctx->h_small[0]) break;
+                }
+            }
+        }
+        for (uint32_t iter = 0; iter < max_iter && !fused_pass; ++iter) {
             // tensor mode computes errors[] lazily (they only feed the empty-cluster reseed)
             if (assign_blocks(ctx, b.feat, n, cent, K, assign_mode, assign, tensor ? nullptr : errors, flags, stopk, nullptr,
                               delta ? &dl : nullptr))
@@ -821,7 +886,7 @@ void yupvq_destroy(yupvq_ctx* ctx) {
                       &ctx->errors, &ctx->cent, &ctx->acc, &ctx->cent_px, &ctx->cent_feat, &ctx->out_idx,
                       &ctx->tc_a, &ctx->tc_xnorm, &ctx->tc_small, &ctx->tc_b, &ctx->tc_bx, &ctx->tc_cand, &ctx->tc_amb,
                       &ctx->bt_feat, &ctx->bt_tca, &ctx->bt_xnorm, &ctx->bt_tcsmall, &ctx->bt_assign, &ctx->bt_errors,
-                      &ctx->bt_cent, &ctx->bt_acc, &ctx->bt_misc, &ctx->bt_centpx, &ctx->bt_cent0, &ctx->tc_chg, &ctx->delta_ctl, &ctx->bt_acc_local, &ctx->pal5};
+                      &ctx->bt_cent, &ctx->bt_acc, &ctx->bt_misc, &ctx->bt_centpx, &ctx->bt_cent0, &ctx->tc_chg, &ctx->delta_ctl, &ctx->bt_acc_local, &ctx->pal5, &ctx->tail_scratch};
     for (DevBuf* b : bufs) b->release();
     if (ctx->h_small) cudaFreeHost(ctx->h_small);
     for (auto& ev : ctx->ev)
@@ -1928,7 +1993,66 @@ int yupvq_encode_bcn_batch_sharded(yupvq_ctx* ctx, const uint8_t* const* bc_bloc
                 acc_loc = ctx->bt_acc_local.as<long long>();
             }
         }
-        for (uint32_t iter = 0; iter < cfg->max_iterations; ++iter) {
+        // Fused pass for the block-sharded batch (no device reseed there): front-end, re-rank (+ update prologue), one update
+        // kernel, [copy + all-reduce], one tail kernel for all textures (control, finalize, next operands).
+        const bool fuse_tail = ctx->comm && delta && !debug_opts().no_tail_fuse && accumulate_auto_supported(n_local, K, (uint32_t)T);
+        if (fuse_tail) {
+            uint8_t* sm = ctx->bt_tcsmall.as<uint8_t>();
+            CK(cudaMemset2DAsync(sm + TC_CMAX, TC_SMALL_BYTES, 0, 8, T, ctx->stream));
+            LAUNCH(launch_tc_prep_centroids_batch(ctx->bt_cent.as<float>(), K, (uint32_t)T, sm, TC_SMALL_BYTES, TC_MU, TC_CMAX, ctx->tc_b.as<float>(),
+                                                  ctx->tc_bx.as<float>(), ctx->stream, ctx->tc_rgb));
+            TcBatch b = tb;
+            b.rgb = (uint32_t)ctx->tc_rgb;
+            AccPrep prep{acc_loc, dctl, K, (uint32_t)(T * n_local / 4), 0u, (uint32_t)T, acc_words};
+            TailArgs ta{};
+            ta.acc = ctx->bt_acc.as<long long>();
+            ta.acc_stride = acc_words;
+            ta.n_textures = (uint32_t)T;
+            ta.K = K;
+            ta.k_pad = k_pad;
+            ta.break_after = 0u;
+            ta.flags = tflags_d;
+            ta.flags_stride = 4;
+            ta.ctl = ctl_d;
+            ta.sticky = sticky_d;
+            ta.inv_scales = inv_scales_d;
+            ta.cent = ctx->bt_cent.as<float>();
+            ta.small = sm;
+            ta.small_stride = TC_SMALL_BYTES;
+            ta.mu_off = TC_MU;
+            ta.cmax_off = TC_CMAX;
+            ta.b_main = ctx->tc_b.as<float>();
+            ta.b_ext = ctx->tc_bx.as<float>();
+            ta.rgb = ctx->tc_rgb;
+            for (uint32_t iter = 0; iter < cfg->max_iterations; ++iter) {
+                const float* cmax = reinterpret_cast<const float*>(sm + TC_CMAX) + (iter & 1u);
+                const bool prof = ctx->profile && ctx->pev_used + 2 <= ctx->pev.size();
+                if (prof) cudaEventRecord(ctx->pev[ctx->pev_used++], ctx->stream);
+                LAUNCH(launch_assign_tc(ctx->bt_tca.as<float>(), ctx->bt_xnorm.as<float>(), T * n_local, ctx->tc_b.as<float>(), ctx->tc_bx.as<float>(), K,
+                                        cmax, ctx->tc_cand.as<uint4>(), ctx->bt_assign.as<uint32_t>(), tflags_d, ctx->tc_amb.as<uint32_t>(),
+                                        flags + F_AMB, ctl_d, ctx->stream, &b));
+                if (prof) cudaEventRecord(ctx->pev[ctx->pev_used++], ctx->stream);
+                prep.force_full = iter == 0 ? 1u : 0u;
+                LAUNCH(launch_rerank_sparse(ctx->bt_feat.as<float>(), ctx->bt_cent.as<float>(), K, ctx->tc_cand.as<uint4>(), ctx->tc_amb.as<uint32_t>(),
+                                            flags + F_AMB, flags + F_AMB + 1, ctx->bt_assign.as<uint32_t>(), tflags_d, flags + F_PAIRS, ctx->stream,
+                                            &b, &prep));
+                LAUNCH(launch_accumulate_auto(ctx->bt_feat.as<float>(), n_local, ctx->bt_assign.as<uint32_t>(), K, 0, acc_loc, tb.chg_rows, tb.chg_old,
+                                              dctl, tflags_d, ctl_d, ctx->stream, &ab));
+                CK(cudaMemcpyAsync(ctx->bt_acc.p, acc_loc, T * acc_words * 8, cudaMemcpyDeviceToDevice, ctx->stream));
+                if (ctx->nccl.all_reduce_sum_i64(ctx->comm, ctx->bt_acc.as<long long>(), T * acc_words, ctx->stream))
+                    return ctx->fail("ncclAllReduce(sum) failed");
+                ta.iter = iter;
+                LAUNCH(launch_lloyd_tail(ta, ctx->stream));
+                if ((iter == 3 || iter == 7 || iter == 15) && iter + 1 < cfg->max_iterations) {  // all converged / redo needed?
+                    CK(cudaMemcpyAsync(h_words, ctl_d, (7 * T + 1) * 4, cudaMemcpyDeviceToHost, ctx->stream));
+                    CK(cudaStreamSynchronize(ctx->stream));
+                    bool all_stopped = true;
+                    for (size_t t = 0; t < T; ++t) all_stopped = all_stopped && h_words[3 * t] != 0;
+                    if (all_stopped || h_words[7 * T]) break;
+                }
+            }
+        }
+        for (uint32_t iter = 0; iter < cfg->max_iterations && !fuse_tail; ++iter) {
             if (assign_fused(ctx->bt_cent.as<float>(), ctx->bt_assign.as<uint32_t>(), tflags_d, ctl_d)) return 1;
             if (delta) {
                 LAUNCH(launch_acc_prepare_batch(acc_loc, K, T * n_local, iter == 0 ? 1u : 0u, dctl, ab, ctx->stream));

@@ -44,6 +44,7 @@
 #include "common.cuh"
 #include "host_util.h"
 #include "kernels.h"
+#include "tc_prep.cuh"
 
 namespace yupvq {
 
@@ -584,14 +585,6 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
 }
 
 // ---- operand preparation ------------------------------------------------------------------------------
-// two-term bf16 split: v = hi + lo + r, |r| <= 2^-18 |v| (v - hi is exact in fp32)
-__device__ __forceinline__ void split_bf16(float v, uint16_t& hi, uint16_t& lo) {
-    const __nv_bfloat16 h = __float2bfloat16_rn(v);
-    const __nv_bfloat16 l = __float2bfloat16_rn(__fsub_rn(v, __bfloat162float(h)));
-    hi = __bfloat16_as_ushort(h);
-    lo = __bfloat16_as_ushort(l);
-}
-
 // column sums of the N x 64 feature matrix (fp64, atomics: mu only steers the error margin, it never
 // changes a result, so its last bits need not be reproducible)
 __global__ void __launch_bounds__(256) col_sums_kernel(const float* __restrict__ feat, size_t n, double* __restrict__ sums) {
@@ -647,66 +640,24 @@ __global__ void __launch_bounds__(256) prep_blocks_kernel(const float* __restric
     if (row < n && q == 0) xnorm[row] = sqrtf(ss) * 1.0001f;
 }
 
-// B' row (256 B) = [bf16 hi of w (c - mu) x 64 | bf16 lo x 64]; the ext row (32 B = 16 bf16) holds a three-term
-// bf16 split of -|c'|^2 / 2 (24 bits); rows K..K_pad-1 are padding that can never win (score -1e30).
-// cmax = max_c |c'| (rounded up).
-__global__ void __launch_bounds__(64) prep_centroids_kernel(const float* __restrict__ cent, uint32_t K, const float* __restrict__ mu,
-                                                            float* __restrict__ b_main, float* __restrict__ b_ext,
-                                                            unsigned int* __restrict__ cmax_bits, size_t small_stride, int rgb) {
-    // texture blockIdx.y of a lock-step batch: operands stacked gridDim.x rows apart, mu / cmax small_stride bytes apart
+// One warp per centroid row (tc_prep.cuh); blockIdx.y = texture of a lock-step batch: operands stacked k_pad rows
+// apart, mu / cmax small_stride bytes apart.
+__global__ void __launch_bounds__(256) prep_centroids_kernel(const float* __restrict__ cent, uint32_t K, uint32_t k_pad,
+                                                             const float* __restrict__ mu, float* __restrict__ b_main,
+                                                             float* __restrict__ b_ext, unsigned int* __restrict__ cmax_bits,
+                                                             size_t small_stride, int rgb) {
     cent += (size_t)blockIdx.y * K * 64;
-    b_main += (size_t)blockIdx.y * gridDim.x * 64;
-    b_ext += (size_t)blockIdx.y * gridDim.x * 8;
+    b_main += (size_t)blockIdx.y * k_pad * 64;
+    b_ext += (size_t)blockIdx.y * k_pad * 8;
     mu = reinterpret_cast<const float*>(reinterpret_cast<const uint8_t*>(mu) + (size_t)blockIdx.y * small_stride);
     cmax_bits = reinterpret_cast<unsigned int*>(reinterpret_cast<uint8_t*>(cmax_bits) + (size_t)blockIdx.y * small_stride);
-    const uint32_t c = blockIdx.x;
-    const int i = threadIdx.x;
-    float v = 0.0f;
-    if (c < K) {
-        const float w = (i & 3) == 0 ? 2.0f : 1.0f;
-        v = w * (cent[(size_t)c * 64 + i] - mu[i]);
-        if (!isfinite(v)) v = 0.0f;  // a non-finite centroid is handled by the exact scan (its blocks overflow)
-    }
-    uint16_t hi16, lo16;
-    split_bf16(v, hi16, lo16);
-    uint16_t* brow = reinterpret_cast<uint16_t*>(b_main) + (size_t)c * 128;
-    if (rgb) {
-        // colour columns packed first; the alpha column is dropped from the product (x' is exactly 0 there) but stays in
-        // the norm below, which is the true |c'|^2
-        if ((i & 3) != 3) {
-            brow[3 * (i >> 2) + (i & 3)] = hi16;
-            brow[64 + 3 * (i >> 2) + (i & 3)] = lo16;
-        } else {
-            brow[112 + (i >> 2)] = 0;
-        }
-    } else {
-        brow[i] = hi16;
-        brow[64 + i] = lo16;
-    }
-    __shared__ double red[2];
-    double ss = (double)v * (double)v;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
-    if ((i & 31) == 0) red[i >> 5] = ss;
-    __syncthreads();
-    if (i < 16) {
-        float e = 0.0f;
-        if (c < K) {
-            const double nh = -0.5 * (red[0] + red[1]);
-            const float hi = __bfloat162float(__float2bfloat16_rn((float)nh));
-            const float mid = __bfloat162float(__float2bfloat16_rn((float)(nh - (double)hi)));
-            const float lo = __bfloat162float(__float2bfloat16_rn((float)(nh - (double)hi - (double)mid)));
-            e = i == 0 ? hi : (i == 1 ? mid : (i == 2 ? lo : 0.0f));
-        } else if (i == 0) {
-            e = -1.0e30f;
-        }
-        reinterpret_cast<uint16_t*>(b_ext)[(size_t)c * 16 + i] = __bfloat16_as_ushort(__float2bfloat16_rn(e));
-        if (rgb) brow[48 + i] = __bfloat16_as_ushort(__float2bfloat16_rn(e));   // folded norm inside the hi half
-    }
-    if (i == 0 && c < K) {
-        const float nrm = (float)sqrt(red[0] + red[1]) * 1.0001f;
-        atomicMax(cmax_bits, __float_as_uint(nrm));  // non-negative floats order like their bit patterns
-    }
+    const int lane = threadIdx.x & 31;
+    const uint32_t c = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (c >= k_pad) return;
+    const bool real = c < K;
+    const float x0 = real ? cent[(size_t)c * 64 + lane] : 0.0f, x1 = real ? cent[(size_t)c * 64 + 32 + lane] : 0.0f;
+    tc_prep_centroid_warp(x0, x1, real, mu, reinterpret_cast<uint16_t*>(b_main) + (size_t)c * 128,
+                          reinterpret_cast<uint16_t*>(b_ext) + (size_t)c * 16, cmax_bits, rgb, lane);
 }
 
 // ---- exact re-rank ---------------------------------------------------------------------------------------
@@ -867,7 +818,7 @@ __global__ void __launch_bounds__(kRrThreads, 2) rerank_sparse_kernel(const floa
                                                                       const uint32_t* __restrict__ amb_list, unsigned int* amb_count,
                                                                       unsigned int* ticket, uint32_t* __restrict__ assign,
                                                                       uint32_t* __restrict__ flags, unsigned int* __restrict__ stat,
-                                                                      TcBatch bt) {
+                                                                      TcBatch bt, AccPrep prep) {
     const float* const cent_base = cent;
     uint32_t* const flags_base = flags;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -958,11 +909,34 @@ __global__ void __launch_bounds__(kRrThreads, 2) rerank_sparse_kernel(const floa
         if (lane == 0 && pairs) atomicAdd(stat, pairs);
         if (lane == 0 && n_ovf) atomicAdd(stat + 1, n_ovf);
     }
+    __shared__ uint32_t s_last;
+    __threadfence();   // this CTA's moved-row appends are visible before its ticket
     __syncthreads();
-    if (threadIdx.x == 0 && atomicAdd(ticket, 1u) == gridDim.x - 1) {  // every CTA has read the count by now
-        *amb_count = 0;
-        *ticket = 0;
+    if (threadIdx.x == 0) {
+        const bool last = atomicAdd(ticket, 1u) == gridDim.x - 1;  // every CTA has read the count by now
+        if (last) {
+            *amb_count = 0;
+            *ticket = 0;
+        }
+        s_last = last ? 1u : 0u;
     }
+    if (!prep.dctl) return;
+    __syncthreads();
+    if (!s_last) return;
+    // ---- update prologue (== acc_prepare_kernel), by the last CTA: every moved row of this pass has been listed
+    __threadfence();
+    const uint32_t n_chg = __ldcg(prep.dctl);
+    const bool full = prep.force_full || n_chg > prep.full_above;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        prep.dctl[32] = n_chg;
+        prep.dctl[33] = full ? 1u : 0u;
+        prep.dctl[0] = 0u;
+    }
+    for (uint32_t t = threadIdx.x; t < prep.n_textures; t += blockDim.x) prep.acc[(size_t)t * prep.acc_stride + (size_t)prep.K * 65] = 0;
+    if (full)
+        for (uint32_t t = 0; t < prep.n_textures; ++t)
+            for (size_t i = threadIdx.x; i < (size_t)prep.K * 65; i += blockDim.x) prep.acc[(size_t)t * prep.acc_stride + i] = 0;
 }
 
 // ---- host side -------------------------------------------------------------------------------------------
@@ -1024,7 +998,8 @@ cudaError_t launch_tc_prep_centroids(const float* cent, uint32_t K, const float*
                                      float* cmax, cudaStream_t s, int rgb) {
     cudaError_t e = cudaMemsetAsync(cmax, 0, 4, s);
     if (e != cudaSuccess) return e;
-    prep_centroids_kernel<<<tc_padded_k(K), 64, 0, s>>>(cent, K, mu, b_main, b_ext, reinterpret_cast<unsigned int*>(cmax), 0, rgb);
+    const uint32_t k_pad = tc_padded_k(K);
+    prep_centroids_kernel<<<(k_pad + 7) / 8, 256, 0, s>>>(cent, K, k_pad, mu, b_main, b_ext, reinterpret_cast<unsigned int*>(cmax), 0, rgb);
     return cudaGetLastError();
 }
 
@@ -1032,9 +1007,10 @@ cudaError_t launch_tc_prep_centroids_batch(const float* cent, uint32_t K, uint32
                                            size_t mu_off, size_t cmax_off, float* b_main, float* b_ext, cudaStream_t s, int rgb) {
     cudaError_t e = cudaMemset2DAsync(small + cmax_off, small_stride, 0, 4, n_textures, s);
     if (e != cudaSuccess) return e;
-    prep_centroids_kernel<<<dim3(tc_padded_k(K), n_textures), 64, 0, s>>>(cent, K, reinterpret_cast<const float*>(small + mu_off), b_main,
-                                                                         b_ext, reinterpret_cast<unsigned int*>(small + cmax_off),
-                                                                         small_stride, rgb);
+    const uint32_t k_pad = tc_padded_k(K);
+    prep_centroids_kernel<<<dim3((k_pad + 7) / 8, n_textures), 256, 0, s>>>(cent, K, k_pad, reinterpret_cast<const float*>(small + mu_off),
+                                                                           b_main, b_ext, reinterpret_cast<unsigned int*>(small + cmax_off),
+                                                                           small_stride, rgb);
     return cudaGetLastError();
 }
 
@@ -1076,9 +1052,10 @@ cudaError_t launch_assign_tc(const float* a_prime, const float* xnorm, size_t n,
 
 cudaError_t launch_rerank_sparse(const float* feat, const float* cent, uint32_t K, const uint4* cand, const uint32_t* amb_list,
                                  unsigned int* amb_count, unsigned int* ticket, uint32_t* assign, uint32_t* flags,
-                                 unsigned int* stat_pairs, cudaStream_t s, const TcBatch* batch) {
+                                 unsigned int* stat_pairs, cudaStream_t s, const TcBatch* batch, const AccPrep* prep) {
     rerank_sparse_kernel<<<YUPVQ_NUM_SMS * 2, kRrThreads, 0, s>>>(feat, cent, K, cand, amb_list, amb_count, ticket, assign, flags,
-                                                                 stat_pairs, batch ? *batch : tc_single());
+                                                                 stat_pairs, batch ? *batch : tc_single(),
+                                                                 prep ? *prep : AccPrep{nullptr, nullptr, 0u, 0u, 0u, 0u, 0});
     return cudaGetLastError();
 }
 

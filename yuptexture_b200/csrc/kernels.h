@@ -113,11 +113,23 @@ cudaError_t launch_assign_tc(const float* a_prime, const float* xnorm, size_t n,
                              const float* b_ext, uint32_t K, const float* cmax, uint4* cand, uint32_t* assign,
                              uint32_t* flags, uint32_t* amb_list, unsigned int* amb_count, const uint32_t* stop,
                              cudaStream_t s, const TcBatch* batch = nullptr);
+// Optional epilogue of launch_rerank_sparse (fused Lloyd pass): the last CTA to finish does what
+// launch_acc_prepare does -- decides full / delta for this pass' update, zeroes the accumulator(s) for a full pass and
+// the changed word(s), hands the moved-row count over -- so the pass needs no separate launch for it.  dctl == null: off.
+struct AccPrep {
+    long long* acc;
+    uint32_t* dctl;
+    uint32_t K;
+    uint32_t full_above;   // more moved rows than this -> full recompute
+    uint32_t force_full;
+    uint32_t n_textures;
+    size_t acc_stride;
+};
 // batch != null: n is the row count of ALL textures, K the per-texture codebook size
 cudaError_t launch_rerank_sparse(const float* feat, const float* cent, uint32_t K, const uint4* cand,
                                  const uint32_t* amb_list, unsigned int* amb_count, unsigned int* ticket,
                                  uint32_t* assign, uint32_t* flags, unsigned int* stat_pairs, cudaStream_t s,
-                                 const TcBatch* batch = nullptr);
+                                 const TcBatch* batch = nullptr, const AccPrep* prep = nullptr);
 cudaError_t launch_rerank(const float* feat, size_t n, const float* cent, uint32_t K, const uint4* cand,
                           uint32_t* assign, float* errors, uint32_t* flags, unsigned int* stat_pairs,
                           const uint32_t* stop, cudaStream_t s);
@@ -153,6 +165,12 @@ cudaError_t launch_accumulate_delta(const float* feat, const uint32_t* assign, u
                                     const uint32_t* chg_rows, const uint32_t* chg_old, const uint32_t* dctl,
                                     const uint32_t* flags, const uint32_t* stop, cudaStream_t s,
                                     const AccBatch* batch = nullptr, uint32_t rows_per_tex = 0xffffffffu);
+// full or delta update in ONE launch, the mode read from dctl[33] on the device (fused Lloyd pass); batch != null: the
+// lock-step batch (scales from batch->scales, shift ignored)
+bool accumulate_auto_supported(size_t rows_per_tex, uint32_t K, uint32_t n_textures);
+cudaError_t launch_accumulate_auto(const float* feat, size_t rows_per_tex, const uint32_t* assign, uint32_t K, int shift, long long* acc,
+                                   const uint32_t* chg_rows, const uint32_t* chg_old, const uint32_t* dctl, const uint32_t* flags,
+                                   const uint32_t* stop, cudaStream_t s, const AccBatch* batch = nullptr);
 // lock-step batch: one list / one mode for all textures (needs K * n_textures <= 4096, else every pass is full)
 bool delta_batch_supported(uint32_t K, uint32_t n_textures);
 cudaError_t launch_acc_prepare_batch(long long* acc, uint32_t K, size_t total_rows, uint32_t force_full, uint32_t* dctl,
@@ -185,6 +203,37 @@ cudaError_t launch_reseed_empty(const float* feat, size_t n, float* errors, cons
 // out[0] = max error (float bits), out[1] = index of its first occurrence
 cudaError_t launch_argmax_error(const float* errors, size_t n, uint32_t* out2, cudaStream_t s);
 cudaError_t launch_max_abs(const float* x, size_t n, uint32_t* out_bits, cudaStream_t s);
+
+// ---- tail.cu : the fused tail of a Lloyd pass (control + errors-if-needed + finalize + reseed + next pass' operands) ------
+// Strides address texture t of a lock-step batch (n_textures == 1: all strides unused).  cmax is double-buffered by pass
+// parity: the front-end of pass p reads small[cmax_off + 4 * (p & 1)], this kernel max-reduces the next pass' value into slot
+// (iter + 1) & 1 and zeroes slot iter & 1 for the tail after it.  errors == null (or n_textures > 1): no device reseed;
+// `sticky` (may be null) is raised when a running texture has an empty cluster.
+struct TailArgs {
+    const long long* acc;      // (all-reduced) accumulators
+    size_t acc_stride;         // int64 words between textures
+    uint32_t n_textures, K, k_pad, iter, break_after;
+    uint32_t* flags;           // [changed, empty, reseeds, ...] per texture
+    uint32_t flags_stride;
+    uint32_t* ctl;             // [stop, passes, empty clusters] per texture (stride 3)
+    uint32_t* sticky;
+    double inv_scale;          // 2^-shift (single texture)
+    const double* inv_scales;  // per texture (batch), else null
+    float* cent;               // n_textures x K x 64
+    uint8_t* small;            // per-texture scalar block: mu (64 floats) at mu_off, cmax[2] at cmax_off
+    size_t small_stride, mu_off, cmax_off;
+    float* b_main;             // n_textures x k_pad operand rows
+    float* b_ext;
+    int rgb;
+    // single-texture reseed path
+    const float* feat;
+    size_t n_rows;
+    const uint32_t* assign;
+    float* errors;
+    float* scratch_val;        // one word per CTA
+    unsigned long long* scratch_idx;
+};
+cudaError_t launch_lloyd_tail(const TailArgs& args, cudaStream_t s);
 
 // ---- sad.cu : A21, SAD-metric Lloyd (all integer, bit-exact) ---------------------------------------------
 // argmin over K pixel-block centroids (K x 16*ch bytes) of sum |a - b|; errors[i] = the minimum (as float)

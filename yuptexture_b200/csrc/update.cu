@@ -51,10 +51,10 @@ constexpr int kAccThreads = 512;
 constexpr int kAccChunk = 4096;
 constexpr int kAccMaxK = 4096;
 
-__global__ void __launch_bounds__(kAccThreads, 2)
-accumulate_sorted_kernel(const float* __restrict__ feat_all, size_t n, const uint32_t* __restrict__ assign_all, uint32_t K, float scale1,
-                         long long* __restrict__ acc_all, const uint32_t* __restrict__ flags, const uint32_t* __restrict__ stop,
-                         AccBatch bt, const uint32_t* __restrict__ dctl) {
+__device__ __forceinline__ void
+accumulate_sorted_body(const float* __restrict__ feat_all, size_t n, const uint32_t* __restrict__ assign_all, uint32_t K, float scale1,
+                       long long* __restrict__ acc_all, const uint32_t* __restrict__ flags, const uint32_t* __restrict__ stop,
+                       const AccBatch& bt, const uint32_t* __restrict__ dctl) {
     // Lock-step batch (bt.n_textures > 1): texture t owns rows [t * n, (t + 1) * n) of feat / assign, the accumulator
     // at acc + t * acc_stride, the scale bt.scales[t] and the flag / stop words at the given strides; chunks are
     // numbered texture-major, so one launch covers the whole batch.
@@ -180,6 +180,13 @@ accumulate_sorted_kernel(const float* __restrict__ feat_all, size_t n, const uin
     }
 }
 
+__global__ void __launch_bounds__(kAccThreads, 2)
+accumulate_sorted_kernel(const float* __restrict__ feat_all, size_t n, const uint32_t* __restrict__ assign_all, uint32_t K, float scale1,
+                         long long* __restrict__ acc_all, const uint32_t* __restrict__ flags, const uint32_t* __restrict__ stop,
+                         AccBatch bt, const uint32_t* __restrict__ dctl) {
+    accumulate_sorted_body(feat_all, n, assign_all, K, scale1, acc_all, flags, stop, bt, dctl);
+}
+
 // ---- delta update ----------------------------------------------------------------------------------------------
 // After the first passes only a few percent of the blocks change centroid.  Because the sums are integers,
 // sums[new] += x, sums[old] -= x over the changed rows gives exactly the accumulator a full recompute would give,
@@ -208,11 +215,11 @@ __global__ void __launch_bounds__(1024) acc_prepare_kernel(long long* __restrict
             for (size_t i = threadIdx.x; i < (size_t)K * 65; i += blockDim.x) acc[(size_t)t * acc_stride + i] = 0;
 }
 
-__global__ void __launch_bounds__(kDeltaThreads)
-accumulate_delta_kernel(const float* __restrict__ feat, const uint32_t* __restrict__ assign, uint32_t K1, float scale1,
-                        long long* __restrict__ acc, const uint32_t* __restrict__ chg_rows, const uint32_t* __restrict__ chg_old,
-                        const uint32_t* __restrict__ dctl, const uint32_t* __restrict__ flags, const uint32_t* __restrict__ stop,
-                        AccBatch bt, uint32_t rows_per_tex) {
+__device__ __forceinline__ void
+accumulate_delta_body(const float* __restrict__ feat, const uint32_t* __restrict__ assign, uint32_t K1, float scale1,
+                      long long* __restrict__ acc, const uint32_t* __restrict__ chg_rows, const uint32_t* __restrict__ chg_old,
+                      const uint32_t* __restrict__ dctl, const uint32_t* __restrict__ flags, const uint32_t* __restrict__ stop,
+                      const AccBatch& bt, uint32_t rows_per_tex) {
     // lock-step batch: rows are global (texture = row / rows_per_tex), the sort key is texture * K1 + centroid
     const uint32_t K = K1 * bt.n_textures;
     // A chunk of listed rows becomes 2 signed entries per row (+x for the new centroid, -x for the old one); the
@@ -368,6 +375,26 @@ accumulate_delta_kernel(const float* __restrict__ feat, const uint32_t* __restri
             atomicAdd(sums_all + (size_t)tex * bt.acc_stride + (size_t)K1 * 65, (unsigned long long)flags[(size_t)tex * bt.flags_stride]);
         }
     }
+}
+
+__global__ void __launch_bounds__(kDeltaThreads)
+accumulate_delta_kernel(const float* __restrict__ feat, const uint32_t* __restrict__ assign, uint32_t K1, float scale1,
+                        long long* __restrict__ acc, const uint32_t* __restrict__ chg_rows, const uint32_t* __restrict__ chg_old,
+                        const uint32_t* __restrict__ dctl, const uint32_t* __restrict__ flags, const uint32_t* __restrict__ stop,
+                        AccBatch bt, uint32_t rows_per_tex) {
+    accumulate_delta_body(feat, assign, K1, scale1, acc, chg_rows, chg_old, dctl, flags, stop, bt, rows_per_tex);
+}
+
+// One launch for the update of a fused Lloyd pass: the mode word dctl[33] (set by the re-rank's last CTA, AccPrep) selects the
+// full sort-and-own recompute or the delta update; both bodies return at once in the other mode.  n = rows per texture.
+static_assert(kAccThreads == kDeltaThreads, "the combined update kernel runs both bodies with one block shape");
+__global__ void __launch_bounds__(kAccThreads, 2)
+accumulate_auto_kernel(const float* __restrict__ feat, size_t n, const uint32_t* __restrict__ assign, uint32_t K, float scale1,
+                       long long* __restrict__ acc, const uint32_t* __restrict__ chg_rows, const uint32_t* __restrict__ chg_old,
+                       const uint32_t* __restrict__ dctl, const uint32_t* __restrict__ flags, const uint32_t* __restrict__ stop,
+                       AccBatch bt, uint32_t rows_per_tex) {
+    if (dctl[33] != 0u) accumulate_sorted_body(feat, n, assign, K, scale1, acc, flags, stop, bt, dctl);
+    else accumulate_delta_body(feat, assign, K, scale1, acc, chg_rows, chg_old, dctl, flags, stop, bt, rows_per_tex);
 }
 
 // blockIdx.y = texture of a lock-step batch (strides 0 and inv_scales null for a single texture)
@@ -622,6 +649,31 @@ cudaError_t launch_accumulate_delta(const float* feat, const uint32_t* assign, u
         return e;
     accumulate_delta_kernel<<<YUPVQ_NUM_SMS, kDeltaThreads, smem, s>>>(feat, assign, K, ldexpf(1.0f, shift), acc, chg_rows, chg_old,
                                                                       dctl, flags, stop, bt, batch ? rows_per_tex : 0xffffffffu);
+    return cudaGetLastError();
+}
+
+// full or delta update in one launch (see accumulate_auto_kernel); batch == null: one texture of n rows
+bool accumulate_auto_supported(size_t rows_per_tex, uint32_t K, uint32_t n_textures) {
+    return K <= (uint32_t)kAccMaxK && rows_per_tex >= (size_t)kAccChunk && (size_t)K * n_textures <= (size_t)kDeltaMaxK;
+}
+
+cudaError_t launch_accumulate_auto(const float* feat, size_t rows_per_tex, const uint32_t* assign, uint32_t K, int shift, long long* acc,
+                                   const uint32_t* chg_rows, const uint32_t* chg_old, const uint32_t* dctl, const uint32_t* flags,
+                                   const uint32_t* stop, cudaStream_t s, const AccBatch* batch) {
+    const AccBatch bt = batch ? *batch : AccBatch{1u, 0, nullptr, 0u, 0u};
+    if (!accumulate_auto_supported(rows_per_tex, K, bt.n_textures)) return cudaErrorInvalidValue;
+    const size_t smem_full = (size_t)K * 8 + (size_t)kAccChunk * 2;
+    const size_t smem_delta = (size_t)K * bt.n_textures * 8 + (size_t)kDeltaRows * 12;
+    const size_t smem = smem_full > smem_delta ? smem_full : smem_delta;
+    static std::atomic<uint64_t> attr{0};
+    if (cudaError_t e = once_per_device(attr, [] {
+            return cudaFuncSetAttribute(accumulate_auto_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)((size_t)kDeltaMaxK * 8 + (size_t)kDeltaRows * 12));
+        }); e != cudaSuccess)
+        return e;
+    accumulate_auto_kernel<<<YUPVQ_NUM_SMS * 2, kAccThreads, smem, s>>>(feat, rows_per_tex, assign, K, batch ? 1.0f : ldexpf(1.0f, shift), acc,
+                                                                       chg_rows, chg_old, dctl, flags, stop, bt,
+                                                                       batch ? (uint32_t)rows_per_tex : 0xffffffffu);
     return cudaGetLastError();
 }
 
