@@ -454,16 +454,56 @@ __global__ void planes_to_blocks_kernel(const uint4* __restrict__ planes, size_t
     d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
 }
 
-// VQBCnCompressor::DecompressToBCn gather, src/vq_bcn_compressor.cpp:350-358.
+// VQBCnCompressor::DecompressToBCn gather, src/vq_bcn_compressor.cpp:350-358: out[i] = codebook[indices[i]].
+// HBM-bound (4 B read + blockSize B written per block): the codebook (<= 64 KB) is staged in shared memory, a thread takes
+// four consecutive indices with one 16-byte load and writes 4 x blockSize contiguous bytes with streaming stores, so a warp
+// covers 1-2 KB of output per step; grid = a few CTAs per SM, grid-stride.
 template <typename V>
-__global__ void gather_codebook_kernel(const V* __restrict__ codebook, uint32_t n_entries,
-                                       const uint32_t* __restrict__ indices, size_t n, V* __restrict__ out) {
-    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const uint32_t k = indices[i];
-    V v = V();
-    if (k < n_entries) v = codebook[k];
-    out[i] = v;
+__device__ __forceinline__ void st_cs(V* p, const V& v);
+template <>
+__device__ __forceinline__ void st_cs<uint2>(uint2* p, const uint2& v) {
+    asm volatile("st.global.cs.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(v.x), "r"(v.y) : "memory");
+}
+template <>
+__device__ __forceinline__ void st_cs<uint4>(uint4* p, const uint4& v) {
+    asm volatile("st.global.cs.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+template <typename V>
+__global__ void __launch_bounds__(256) gather_codebook_kernel(const V* __restrict__ codebook, uint32_t n_entries,
+                                                              const uint32_t* __restrict__ indices, size_t n, V* __restrict__ out,
+                                                              int staged) {
+    extern __shared__ uint4 gather_smem[];
+    const V* cb = codebook;
+    if (staged) {
+        V* cb_s = reinterpret_cast<V*>(gather_smem);
+        for (uint32_t k = threadIdx.x; k < n_entries; k += blockDim.x) cb_s[k] = codebook[k];
+        __syncthreads();
+        cb = cb_s;
+    }
+    auto fetch = [&](uint32_t k) {   // an out-of-range index leaves the block zero (the reference leaves it default-initialised)
+        V v = V();
+        if (k < n_entries) v = cb[k];
+        return v;
+    };
+    const size_t n4 = n / 4;
+    const bool aligned = (reinterpret_cast<uintptr_t>(indices) & 15u) == 0;
+    for (size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x; g < n4; g += (size_t)gridDim.x * blockDim.x) {
+        uint4 k;
+        if (aligned) {
+            k = ldg_nc_v4(reinterpret_cast<const uint4*>(indices) + g);
+        } else {
+            k = make_uint4(indices[4 * g], indices[4 * g + 1], indices[4 * g + 2], indices[4 * g + 3]);
+        }
+        const V v0 = fetch(k.x), v1 = fetch(k.y), v2 = fetch(k.z), v3 = fetch(k.w);
+        V* o = out + 4 * g;
+        st_cs(o, v0);
+        st_cs(o + 1, v1);
+        st_cs(o + 2, v2);
+        st_cs(o + 3, v3);
+    }
+    if (blockIdx.x == 0)
+        for (size_t i = n4 * 4 + threadIdx.x; i < n; i += blockDim.x) out[i] = fetch(indices[i]);
 }
 
 inline unsigned grid_for(size_t n, int per) { return (unsigned)((n + per - 1) / per); }
@@ -619,14 +659,18 @@ cudaError_t launch_planes_to_blocks(const uint4* planes, size_t plane_stride, co
 cudaError_t launch_gather_codebook(const uint8_t* codebook, uint32_t n_entries, uint32_t block_size,
                                    const uint32_t* indices, size_t n, uint8_t* out, cudaStream_t s) {
     if (n == 0) return cudaSuccess;
+    if (block_size != 8 && block_size != 16) return cudaErrorInvalidValue;
+    const size_t cb_bytes = (size_t)n_entries * block_size;
+    const int staged = cb_bytes <= 48 * 1024 ? 1 : 0;   // the reference's K <= 1024 -> <= 16 KB
+    const size_t smem = staged ? cb_bytes : 0;
+    size_t groups = (n / 4 + 255) / 256;
+    unsigned grid = (unsigned)std::min<size_t>(std::max<size_t>(groups, 1), (size_t)YUPVQ_NUM_SMS * 8);
     if (block_size == 8)
-        gather_codebook_kernel<uint2><<<grid_for(n, 256), 256, 0, s>>>(reinterpret_cast<const uint2*>(codebook), n_entries,
-                                                                       indices, n, reinterpret_cast<uint2*>(out));
-    else if (block_size == 16)
-        gather_codebook_kernel<uint4><<<grid_for(n, 256), 256, 0, s>>>(reinterpret_cast<const uint4*>(codebook), n_entries,
-                                                                       indices, n, reinterpret_cast<uint4*>(out));
+        gather_codebook_kernel<uint2><<<grid, 256, smem, s>>>(reinterpret_cast<const uint2*>(codebook), n_entries, indices, n,
+                                                              reinterpret_cast<uint2*>(out), staged);
     else
-        return cudaErrorInvalidValue;
+        gather_codebook_kernel<uint4><<<grid, 256, smem, s>>>(reinterpret_cast<const uint4*>(codebook), n_entries, indices, n,
+                                                              reinterpret_cast<uint4*>(out), staged);
     return cudaGetLastError();
 }
 
