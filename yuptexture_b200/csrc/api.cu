@@ -40,6 +40,7 @@ const DebugOpts& debug_opts() {
         o.batch_per_texture = on("YUPVQ_BATCH_PER_TEXTURE");
         o.no_tail_fuse = on("YUPVQ_NO_TAIL_FUSE");
         o.no_overlap = on("YUPVQ_NO_OVERLAP");
+        o.tc_v1 = on("YUPVQ_TC_V1") || !on("YUPVQ_TC_V2");   // v2 is opt-in until its GPU validation lands
         if (const char* v = getenv("YUPVQ_ASYNC_DBG")) o.async_dbg = atoi(v);
         return o;
     }();

@@ -55,6 +55,10 @@ constexpr int BN = 256;            // centroids per chunk (MMA N, TMEM columns p
 constexpr int kEpiWarps = 16;      // epilogue warps: 4 TMEM lane quadrants x 4 column slices
 constexpr int kListCap = 4;        // candidates one (row, column slice) thread can record per tile
 constexpr int kThreadsTc = (2 + kEpiWarps) * 32;
+// v2 role layout (MW = merge warps): warps 0-3 = TMA producer, MMA issuer, two idle; warps 4-7 = one merge warp per row
+// quadrant; warps 8-23 = the 16 epilogue warps.  Roles sit on warpgroup boundaries so that setmaxnreg can move registers
+// from the control / merge warpgroups to the epilogue.
+constexpr int kThreadsTc2 = (8 + kEpiWarps) * 32;
 constexpr int kMaxCand = 7;
 
 constexpr uint32_t A_HALF_BYTES = BM * 128;        // 128 rows x 64 bf16 (xh, then xl)
@@ -71,10 +75,12 @@ constexpr uint32_t OFF_ONES = OFF_B + 2 * B_STAGE_BYTES;
 constexpr uint32_t OFF_LIST = OFF_ONES + ONES_BYTES;                 // u16 [2 parity][4 slices][128][kListCap]
 constexpr uint32_t OFF_MAX = OFF_LIST + 2 * 4 * 128 * kListCap * 2;  // float [2 parity][4 slices][128]
 constexpr uint32_t OFF_CNT = OFF_MAX + 2 * 4 * 128 * 4;              // u8 [2 parity][4 slices][128]
-constexpr uint32_t OFF_BAR = OFF_CNT + 2 * 4 * 128;                  // 12 mbarriers + tmem ptr
-constexpr uint32_t SMEM_TC = OFF_BAR + 16 * 8 + 1024 /* alignment slack */;
+constexpr uint32_t OFF_BAR = OFF_CNT + 2 * 4 * 128;                  // 28 mbarriers + tmem ptr
+constexpr uint32_t SMEM_TC = OFF_BAR + 32 * 8 + 1024 /* alignment slack */;
 
-enum { BAR_FULL_A = 0, BAR_EMPTY_A = 2, BAR_FULL_B = 4, BAR_EMPTY_B = 6, BAR_TFULL = 8, BAR_TEMPTY = 10, BAR_COUNT = 12 };
+// MFULL / MEMPTY [tile parity][row quadrant]: epilogue slices -> merge warp hand-over of the per-row candidate lists (v2)
+enum { BAR_FULL_A = 0, BAR_EMPTY_A = 2, BAR_FULL_B = 4, BAR_EMPTY_B = 6, BAR_TFULL = 8, BAR_TEMPTY = 10, BAR_MFULL = 12,
+       BAR_MEMPTY = 20, BAR_COUNT = 28 };
 
 // error model constants (see header comment)
 constexpr float kDotErr = 0.0000152587890625f * 1.5f;                             // 1.5 * 2^-16
@@ -112,19 +118,39 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
         "l"(map), "r"(bar), "r"(c0), "r"(c1)
         : "memory");
 }
+// one lane of a converged warp (elect.sync): the compiler knows the guarded region runs on a single thread with
+// warp-uniform operands, so tcgen05 / TMA operands stay in uniform registers (a `lane == 0` branch makes it wrap every
+// such instruction in a broadcast loop)
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "elect.sync _|p, 0xffffffff;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t"
+        "}\n"
+        : "=r"(pred));
+    return pred != 0;
+}
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
-__device__ __forceinline__ void tc_mma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+// The two shared-memory descriptors travel as (low word, constant high word): stepping an operand along K only adds
+// to the low word's address field (bytes >> 4), so a K-step costs one 32-bit add per operand.
+__device__ __forceinline__ void tc_mma_bf16(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi, uint32_t idesc,
+                                            uint32_t accumulate) {
     asm volatile(
         "{\n\t"
         ".reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+        ".reg .b64 da, db;\n\t"
+        "mov.b64 da, {%1, %2};\n\t"
+        "mov.b64 db, {%3, %4};\n\t"
+        "setp.ne.b32 p, %6, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n\t"
         "}\n" ::"r"(tmem_d),
-        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate)
         : "memory");
 }
 __device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t (&v)[32]) {
@@ -157,7 +183,7 @@ __device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, %0;" ::"n"
 // K-major shared-memory matrix descriptor (cute::UMMA::SmemDescriptor, version 1 == Blackwell).
 // layout: 2 = 128B swizzle (rows of 128 B, 8-row atoms 1024 B apart), 6 = 32B swizzle (rows of 32 B,
 // 8-row atoms 256 B apart).  LBO is unused for swizzled K-major operands.
-__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t sbo_bytes, uint32_t layout) {
+__device__ __forceinline__ constexpr uint64_t make_desc(uint32_t saddr, uint32_t sbo_bytes, uint32_t layout) {
     uint64_t d = 0;
     d |= (uint64_t)((saddr & 0x3ffffu) >> 4);
     d |= (uint64_t)1 << 16;                          // leading byte offset (ignored)
@@ -169,6 +195,23 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t sbo_bytes
 
 // kind::f16, D = f32, A/B = bf16, both K-major, M = 128, N = 256 (cute::UMMA::InstrDescriptor)
 constexpr uint32_t kIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+
+template <int N>
+__device__ __forceinline__ void setmaxnreg_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
+template <int N>
+__device__ __forceinline__ void setmaxnreg_dec() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
+
+// threshold below which a score cannot belong to the reference argmin, given the best score m
+__device__ __forceinline__ float cand_threshold(float m, float xn, float e_dot, bool& bad) {
+    const float d_up = fmaxf(xn * xn - 2.0f * m + 2.0f * e_dot, 0.0f);
+    const float margin = 2.0f * e_dot + kRefRel * d_up;
+    // NaN / Inf anywhere (or only padding columns): no proof possible, take the exact scan
+    if (!(m > -1.0e29f) || !(margin < 1.0e30f)) bad = true;
+    float thr = m - margin;
+    thr = __uint_as_float(__float_as_uint(thr) + (thr > 0.0f ? -1 : (thr < 0.0f ? 1 : 0)));  // one ulp down
+    if (thr == 0.0f) thr = -FLT_MIN;
+    return thr;
+}
 
 // (tile, texture) walk of one CTA through the batch without a division per tile
 struct TileWalk {
@@ -188,14 +231,90 @@ struct TileWalk {
 };
 
 // ---- the front-end kernel -----------------------------------------------------------------------------
-template <bool BATCH>
-__global__ void __launch_bounds__(kThreadsTc, 1)
+// One row's merge of its four column slices (see the epilogue comment below): executed by the slice-0 epilogue thread
+// of the row (MW = false) or by the row quadrant's merge warp (MW = true).  Returns true when the row's assignment moved.
+__device__ __forceinline__ bool merge_row(const uint16_t* __restrict__ lists, const float* __restrict__ s_max,
+                                          const uint8_t* __restrict__ s_cnt, uint32_t tpar, int r, size_t row, float xn, float e_dot,
+                                          uint32_t old_c, uint32_t tex, uint4* __restrict__ cand, uint32_t* __restrict__ assign,
+                                          uint32_t* __restrict__ flags, uint32_t* __restrict__ amb_list, unsigned int* __restrict__ amb_count,
+                                          const TcBatch& bt) {
+    constexpr int kSplit = kEpiWarps / 4;
+    float mq[kSplit];
+#pragma unroll
+    for (int q = 0; q < kSplit; ++q) mq[q] = s_max[(tpar * kSplit + q) * 128 + r];
+    bool any_bad = false;
+    const float m_all = fmaxf(fmaxf(mq[0], mq[1]), fmaxf(mq[2], mq[3]));
+    const float thr_all = cand_threshold(m_all, xn, e_dot, any_bad);
+    // up to 8 candidate ids, 16 bits each, in two 64-bit words (shifts instead of a dynamically indexed array: registers)
+    unsigned long long lo = 0, hi = 0;
+    uint32_t total = 0;
+    bool ovf = any_bad;
+#pragma unroll
+    for (int q = 0; q < kSplit; ++q) {
+        const uint32_t cq = s_cnt[(tpar * kSplit + q) * 128 + r];
+        if (!(mq[q] > thr_all)) continue;      // this slice's best score cannot be the winner's
+        ovf |= cq > (uint32_t)kListCap;
+        // the slice's list: kListCap u16 = one 8-byte word
+        const unsigned long long lw = *reinterpret_cast<const unsigned long long*>(lists + ((tpar * kSplit + q) * 128 + r) * kListCap);
+        for (uint32_t i = 0; i < cq && !ovf && total < 8; ++i, ++total) {
+            const unsigned long long c = (lw >> (16 * i)) & 0xffffull;
+            if (total < 4) lo |= c << (16 * total);
+            else hi |= c << (16 * (total - 4));
+        }
+    }
+    bool moved = false;
+    if (!ovf && total == 1 && assign) {
+        // a single candidate is the exact argmin: final
+        const uint32_t c = (uint32_t)(lo & 0xffffull);
+        moved = old_c != c;
+        if (flags && moved) flags[(size_t)tex * bt.flags_stride] = 1u;
+        assign[row] = c;
+    } else {
+        uint32_t w0 = (uint32_t)lo, w1 = (uint32_t)(lo >> 32), w2 = (uint32_t)hi, w3 = (uint32_t)(hi >> 32);
+        if (!ovf && total >= 1 && total <= (uint32_t)kMaxCand) {
+            w3 = (w3 & 0xffffu) | (total << 16);
+        } else {
+            w0 = w1 = w2 = 0;
+            w3 = 0xffffu << 16;  // empty (NaN) or overflow: full exact scan in the re-rank
+        }
+        cand[row] = make_uint4(w0, w1, w2, w3);
+        if (amb_list) amb_list[atomicAdd(amb_count, 1u)] = (uint32_t)row;
+    }
+    return moved;
+}
+
+// delta update: (row, previous centroid) of every row that moved -- one atomic per warp and tile, and its result is only
+// consumed one tile later, so the round trip to L2 hides behind the next tile
+struct MovedList {
+    uint32_t pend_mask = 0, pend_base = 0, pend_row = 0, pend_old = 0;
+    __device__ __forceinline__ void flush(const TcBatch& bt, int lane) {
+        if (pend_mask) {
+            const uint32_t slot = __shfl_sync(0xffffffffu, pend_base, __ffs(pend_mask) - 1) + (uint32_t)__popc(pend_mask & ((1u << lane) - 1u));
+            if (pend_mask & (1u << lane)) {
+                bt.chg_rows[slot] = pend_row;
+                bt.chg_old[slot] = pend_old;
+            }
+        }
+    }
+    __device__ __forceinline__ void push(const TcBatch& bt, int lane, bool moved, uint32_t row, uint32_t old_c) {
+        flush(bt, lane);
+        pend_mask = __ballot_sync(0xffffffffu, moved);
+        pend_row = row;
+        pend_old = old_c;
+        if (pend_mask && lane == __ffs(pend_mask) - 1) pend_base = atomicAdd(bt.chg_count, (unsigned)__popc(pend_mask));
+    }
+};
+
+template <bool BATCH, bool MW>
+__global__ void __launch_bounds__(MW ? kThreadsTc2 : kThreadsTc, 1)
 assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
                  const __grid_constant__ CUtensorMap tm_bx, const float* __restrict__ xnorm,
                  const float* __restrict__ cmax_ptr, uint32_t n, uint32_t num_tiles, uint32_t num_chunks,
                  uint32_t resident_b, uint4* __restrict__ cand, uint32_t* __restrict__ assign, uint32_t* __restrict__ flags,
                  uint32_t* __restrict__ amb_list, unsigned int* __restrict__ amb_count, const uint32_t* __restrict__ stop,
                  TcBatch bt) {
+    constexpr int kThreadsCta = MW ? kThreadsTc2 : kThreadsTc;
+    constexpr int kEpiBase = MW ? 8 : 2;   // first epilogue warp
     // Lock-step batch (bt.tiles_per_tex < num_tiles): the rows of all textures are one contiguous matrix, tile t belongs
     // to texture t / tiles_per_tex; that texture's centroid operand is rows [tex * k_pad, (tex + 1) * k_pad) of the B maps
     // and its cmax / flags / stop words sit at the given strides.  A CTA reloads its resident B when it crosses
@@ -232,6 +351,10 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
             mbar_init(bar(BAR_TFULL + i), 1);
             mbar_init(bar(BAR_TEMPTY + i), kEpiWarps);
         }
+        for (int i = 0; i < 8; ++i) {
+            mbar_init(bar(BAR_MFULL + i), kEpiWarps / 4);   // the four slice warps of a row quadrant
+            mbar_init(bar(BAR_MEMPTY + i), 1);              // its merge warp
+        }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {  // TMEM: all 512 columns (two 256-column accumulator stages)
@@ -241,13 +364,22 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     // the column of ones that multiplies the folded norm terms (layout-invariant: every element is 1)
-    for (uint32_t i = threadIdx.x; i < ONES_BYTES / 4; i += kThreadsTc) reinterpret_cast<uint32_t*>(base_ptr + OFF_ONES)[i] = 0x3f803f80u;  // bf16 1.0 x 2
+    for (uint32_t i = threadIdx.x; i < ONES_BYTES / 4; i += kThreadsCta) reinterpret_cast<uint32_t*>(base_ptr + OFF_ONES)[i] = 0x3f803f80u;  // bf16 1.0 x 2
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    // v2: registers follow the work (setmaxnreg at the head of each role's branch, so the role's code is compiled against
+    // its own budget): 16 epilogue warps hold two 32-column score tiles each (104), the control and merge warpgroups need
+    // little (48 each): 512 x 104 + 256 x 48 = 65536
+    uint16_t* const lists = reinterpret_cast<uint16_t*>(base_ptr + OFF_LIST);   // [2 parity][4 slices][128][kListCap]
+    float* const s_max = reinterpret_cast<float*>(base_ptr + OFF_MAX);          // [2 parity][4 slices][128]
+    uint8_t* const s_cnt = reinterpret_cast<uint8_t*>(base_ptr + OFF_CNT);      // [2 parity][4 slices][128]
 
+    if (MW && warp < 4) {
+        setmaxnreg_dec<48>();
+    }
     if (warp == 0) {
         // ===== TMA producer ==============================================================================
         if (lane == 0) {
@@ -303,8 +435,8 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
             }
         }
     } else if (warp == 1) {
-        // ===== MMA issuer (one thread) ===================================================================
-        if (lane == 0) {
+        // ===== MMA issuer: the whole warp walks the tiles (uniform control flow), one elected lane issues ========
+        {
             uint32_t it = 0, u = 0, cur_tex = 0xffffffffu, bgen = 0;
             const uint64_t ones_desc = make_desc(base + OFF_ONES, 256, 6);
             for (TileWalk w(blockIdx.x, gridDim.x, bt.tiles_per_tex, BATCH); w.t < num_tiles; w.advance()) {
@@ -341,37 +473,97 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                     tc_fence_after();
                     const uint32_t b_addr = base + OFF_B + sb * B_STAGE_BYTES;
                     const uint32_t d_tmem = tmem_base + acc * BN;
+                    // descriptor words: low = address field (+ the ignored LBO), high = stride / version / swizzle
+                    constexpr uint32_t kHi128 = (uint32_t)(make_desc(0, 1024, 2) >> 32), kHi32 = (uint32_t)(make_desc(0, 256, 6) >> 32);
+                    const uint32_t a_lo = (uint32_t)make_desc(a_addr, 1024, 2), b_lo = (uint32_t)make_desc(b_addr, 1024, 2);
                     // xl.ch + xh.cl + xh.ch: twelve K = 16 steps over the two 128-byte halves of each operand row
                     // (small terms first), then the folded norm
-                    if (bt.rgb) {
-                        // 48 colour columns: xl.ch and xh.cl over three K-steps each, xh.ch over four -- the fourth holds
-                        // the ones / folded-norm columns
+                    if (elect_one()) {   // one elected lane issues the chunk's MMAs and its commits
+                        if (bt.rgb) {
+                            // 48 colour columns: xl.ch and xh.cl over three K-steps each, xh.ch over four -- the fourth
+                            // holds the ones / folded-norm columns
 #pragma unroll
-                        for (int k = 0; k < 10; ++k) {
-                            const int seg = k < 3 ? 0 : (k < 6 ? 1 : 2);
-                            const uint32_t kk = (uint32_t)(k < 3 ? k : (k < 6 ? k - 3 : k - 6)) * 32u;
-                            const uint32_t koff = (seg == 0 ? A_HALF_BYTES : 0u) + kk;
-                            const uint32_t boff = (seg == 1 ? B_HALF_BYTES : 0u) + kk;
-                            tc_mma_bf16(d_tmem, make_desc(a_addr + koff, 1024, 2), make_desc(b_addr + boff, 1024, 2), kIdesc,
-                                        k > 0 ? 1u : 0u);
-                        }
-                    } else {
+                            for (int k = 0; k < 10; ++k) {
+                                const int seg = k < 3 ? 0 : (k < 6 ? 1 : 2);
+                                const uint32_t kk = (uint32_t)(k < 3 ? k : (k < 6 ? k - 3 : k - 6)) * 32u;
+                                const uint32_t koff = (seg == 0 ? A_HALF_BYTES : 0u) + kk;
+                                const uint32_t boff = (seg == 1 ? B_HALF_BYTES : 0u) + kk;
+                                tc_mma_bf16(d_tmem, a_lo + (koff >> 4), kHi128, b_lo + (boff >> 4), kHi128, kIdesc, k > 0 ? 1u : 0u);
+                            }
+                        } else {
 #pragma unroll
-                        for (int k = 0; k < 12; ++k) {
-                            const int seg = k >> 2;
-                            const uint32_t koff = (seg == 0 ? A_HALF_BYTES : 0u) + (uint32_t)(k & 3) * 32u;
-                            const uint32_t boff = (seg == 1 ? B_HALF_BYTES : 0u) + (uint32_t)(k & 3) * 32u;
-                            tc_mma_bf16(d_tmem, make_desc(a_addr + koff, 1024, 2), make_desc(b_addr + boff, 1024, 2), kIdesc,
-                                        k > 0 ? 1u : 0u);
+                            for (int k = 0; k < 12; ++k) {
+                                const int seg = k >> 2;
+                                const uint32_t koff = (seg == 0 ? A_HALF_BYTES : 0u) + (uint32_t)(k & 3) * 32u;
+                                const uint32_t boff = (seg == 1 ? B_HALF_BYTES : 0u) + (uint32_t)(k & 3) * 32u;
+                                tc_mma_bf16(d_tmem, a_lo + (koff >> 4), kHi128, b_lo + (boff >> 4), kHi128, kIdesc, k > 0 ? 1u : 0u);
+                            }
+                            tc_mma_bf16(d_tmem, (uint32_t)ones_desc, kHi32, (uint32_t)make_desc(b_addr + 2 * B_HALF_BYTES, 256, 6), kHi32, kIdesc, 1u);
                         }
-                        tc_mma_bf16(d_tmem, ones_desc, make_desc(b_addr + 2 * B_HALF_BYTES, 256, 6), kIdesc, 1u);
+                        tc_commit(bar(BAR_TFULL + acc));
+                        if (!resident_b || last_of_tex) tc_commit(bar(BAR_EMPTY_B + sb));
                     }
-                    tc_commit(bar(BAR_TFULL + acc));
-                    if (!resident_b || last_of_tex) tc_commit(bar(BAR_EMPTY_B + sb));
+                    __syncwarp();
                 }
-                tc_commit(bar(BAR_EMPTY_A + sa));
+                if (elect_one()) tc_commit(bar(BAR_EMPTY_A + sa));
+                __syncwarp();
             }
         }
+    } else if (MW && warp < 4) {
+        // idle warps of the control warpgroup (they exist so that the roles fall on warpgroup boundaries)
+    } else if (MW && warp < 8) {
+        // ===== merge warps (v2): warp 4 + m merges the four column slices of rows [32 m, 32 m + 32) of every tile ======
+        // The epilogue slices hand their per-row maxima / counts / lists over through shared memory (double buffered by
+        // tile parity) and an mbarrier pair, so no epilogue warp ever waits for a merge: the merge of tile t runs while
+        // the 16 epilogue warps are already sweeping tile t + 1.
+        setmaxnreg_dec<48>();
+        const int m = warp - 4;
+        const int r = m * 32 + lane;
+        TileWalk w(blockIdx.x, gridDim.x, bt.tiles_per_tex, BATCH);
+        auto next_live = [&](bool step) {
+            if (step) w.advance();
+            while (w.t < num_tiles && !live(w.tex)) w.advance();
+            return w.t;
+        };
+        float cmax = BATCH ? 0.0f : __ldg(cmax_ptr);
+        uint32_t cmax_tex = BATCH ? 0xffffffffu : 0u;
+        const uint32_t t_first = next_live(false);
+        uint32_t tex = w.tex;
+        float xn_next = 0.0f;
+        uint32_t old_next = 0;
+        if (t_first < num_tiles && (size_t)t_first * BM + r < n) {
+            xn_next = __ldg(xnorm + (size_t)t_first * BM + r);
+            if (assign) old_next = assign[(size_t)t_first * BM + r];
+        }
+        MovedList ml;
+        uint32_t ti = 0;
+        for (uint32_t t = t_first, t_next, tex_next; t < num_tiles; t = t_next, tex = tex_next, ++ti) {
+            t_next = next_live(true);
+            tex_next = w.tex;
+            if (BATCH && tex != cmax_tex) {
+                cmax_tex = tex;
+                cmax = __ldg(cmax_ptr + (size_t)tex * bt.cmax_stride);
+            }
+            const size_t row = (size_t)t * BM + r;
+            const float xn = xn_next;
+            const uint32_t old_c = old_next;
+            {   // prefetch the next tile's |x'| and previous assignment
+                const size_t nrow = (size_t)t_next * BM + r;
+                const bool has = t_next < num_tiles && nrow < n;
+                xn_next = has ? __ldg(xnorm + nrow) : 0.0f;
+                if (assign) old_next = has ? assign[nrow] : 0u;
+            }
+            const uint32_t tpar = ti & 1u;
+            mbar_wait(bar(BAR_MFULL + tpar * 4 + m), (ti >> 1) & 1u);
+            bool moved = false;
+            if (row < n)
+                moved = merge_row(lists, s_max, s_cnt, tpar, r, row, xn, kDotErr * xn * cmax, old_c, tex, cand, assign, flags, amb_list,
+                                  amb_count, bt);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar(BAR_MEMPTY + tpar * 4 + m));
+            if (bt.chg_count) ml.push(bt, lane, moved, (uint32_t)row, old_c);
+        }
+        if (bt.chg_count) ml.flush(bt, lane);
     } else {
         // ===== epilogue: 16 warps, thread == (TMEM lane, column quarter) =================================
         // Every (row, column slice) thread works on its own: running maximum, threshold and candidate list
@@ -386,14 +578,16 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
         constexpr int kCols = BN / kSplit;           // columns per thread per stage
         constexpr int kTiles = kCols / 32;           // 32-column register tiles per pass
         static_assert(kTiles == 2, "the unrolled load schedule below is written for two tiles per pass");
-        const int ew = warp - 2;
-        const int quad = warp & 3;          // TMEM lane quadrant this warp may access
+        if (MW) setmaxnreg_inc<104>();
+        const int ew = warp - kEpiBase;
+        const int quad = warp & 3;          // TMEM lane quadrant this warp may access (kEpiBase is a multiple of 4 or 2: see r)
         const int slice = ew >> 2;          // which kCols of the stage's 256 columns
         const int r = quad * 32 + lane;     // row inside the tile
-        uint16_t* lists = reinterpret_cast<uint16_t*>(base_ptr + OFF_LIST);   // [2 parity][kSplit][128][kListCap]
-        float* s_max = reinterpret_cast<float*>(base_ptr + OFF_MAX);          // [2 parity][kSplit][128]
-        uint8_t* s_cnt = reinterpret_cast<uint8_t*>(base_ptr + OFF_CNT);      // [2 parity][kSplit][128]
-        const uint32_t lane_taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(slice * kCols);
+        uint32_t lane_taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(slice * kCols);
+        uint32_t tfull0 = bar(BAR_TFULL);
+        // opaque to the optimiser: without this it recomputes both addresses from %tid / the shared window base in every
+        // chunk (about 25 instructions of a 260-instruction loop)
+        asm volatile("" : "+r"(lane_taddr), "+r"(tfull0));
         uint32_t u = 0, tpar = 0;
         float xn_next = 0.0f;
         uint32_t old_next = 0;
@@ -411,29 +605,19 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
         uint32_t tex = w.tex;
         if (t_first < num_tiles && (size_t)t_first * BM + r < n) {
             xn_next = __ldg(xnorm + (size_t)t_first * BM + r);
-            if (slice == 0 && assign) old_next = assign[(size_t)t_first * BM + r];
+            if (!MW && slice == 0 && assign) old_next = assign[(size_t)t_first * BM + r];
         }
-        // threshold below which a score cannot belong to the reference argmin, given the best score m
-        auto threshold = [&](float m, float xn, float e_dot, bool& bad) -> float {
-            const float d_up = fmaxf(xn * xn - 2.0f * m + 2.0f * e_dot, 0.0f);
-            const float margin = 2.0f * e_dot + kRefRel * d_up;
-            // NaN / Inf anywhere (or only padding columns): no proof possible, take the exact scan
-            if (!(m > -1.0e29f) || !(margin < 1.0e30f)) bad = true;
-            float thr = m - margin;
-            thr = __uint_as_float(__float_as_uint(thr) + (thr > 0.0f ? -1 : (thr < 0.0f ? 1 : 0)));  // one ulp down
-            if (thr == 0.0f) thr = -FLT_MIN;
-            return thr;
-        };
-        bool moved = false;
-        uint32_t pend_mask = 0, pend_base = 0, pend_row = 0, pend_old = 0;
-        for (uint32_t t = t_first, t_next, tex_next; t < num_tiles; t = t_next, tex = tex_next, tpar ^= 1) {
-            moved = false;
+        MovedList ml;
+        uint32_t ti = 0;   // tiles this CTA has run (hand-over barrier phases)
+        for (uint32_t t = t_first, t_next, tex_next; t < num_tiles; t = t_next, tex = tex_next, tpar ^= 1, ++ti) {
             t_next = next_live(true);
             tex_next = w.tex;
             if (BATCH && tex != cmax_tex) {
                 cmax_tex = tex;
                 cmax = __ldg(cmax_ptr + (size_t)tex * bt.cmax_stride);
             }
+            // v2: this parity's hand-over buffers are free once the merge warp has consumed the tile before last
+            if (MW) mbar_wait(bar(BAR_MEMPTY + tpar * 4 + quad), ((ti >> 1) & 1u) ^ 1u);
             const size_t row = (size_t)t * BM + r;
             const float xn = xn_next;
             const uint32_t old_c = old_next;
@@ -441,7 +625,7 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                 const size_t nrow = (size_t)t_next * BM + r;
                 const bool has = t_next < num_tiles && nrow < n;
                 xn_next = has ? __ldg(xnorm + nrow) : 0.0f;
-                if (slice == 0 && assign) old_next = has ? assign[nrow] : 0u;
+                if (!MW && slice == 0 && assign) old_next = has ? assign[nrow] : 0u;
             }
             const float e_dot = kDotErr * xn * cmax;
             float m_run = -INFINITY;
@@ -450,7 +634,7 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
             uint16_t* my_list = lists + ((tpar * kSplit + slice) * 128 + r) * kListCap;
             for (uint32_t j = 0; j < num_chunks; ++j, ++u) {
                 const uint32_t acc = u & 1, pacc = (u >> 1) & 1;
-                mbar_wait(bar(BAR_TFULL + acc), pacc);
+                mbar_wait(tfull0 + 8u * acc, pacc);
                 tc_fence_after();
                 const uint32_t taddr = lane_taddr + acc * BN;
                 uint32_t va[32], vb[32];
@@ -473,28 +657,27 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                 tc_wait_ld(vb);
                 tc_fence_before();
                 __syncwarp();
-                if (lane == 0) mbar_arrive(bar(BAR_TEMPTY + acc));
+                if (lane == 0) mbar_arrive(tfull0 + 8u * (BAR_TEMPTY - BAR_TFULL) + 8u * acc);
                 // ---- pass 1 (registers): maximum score over this thread's columns
                 reduce_max(va);
                 reduce_max(vb);
                 const float m_prev = m_run;
                 m_run = fmaxf(fmax3(m_run, m0, m1), fmaxf(m2, m3));
-                const float thr = threshold(m_run, xn, e_dot, local_bad);
+                const float thr = cand_threshold(m_run, xn, e_dot, local_bad);
                 // every candidate recorded in earlier chunks has score <= m_prev: once the threshold has moved
                 // past that, none of them can win any more
                 if (m_prev < thr) cnt = 0;
-                // ---- pass 2: sign-bit sweep, candidates are the columns with (thr - s) < 0.  Four
-                // independent 8-bit funnel-shift chains per tile keep the ALU pipe busy.
+                // ---- pass 2: sign-bit sweep, candidates are the columns with (thr - s) < 0.  Two independent
+                // 16-bit funnel-shift chains per register tile (four per chunk) keep the ALU pipe busy; one multiply-add
+                // joins them.
                 auto sweep = [&](const uint32_t (&v)[32], uint32_t col0) {
-                    uint32_t k0 = 0, k1 = 0, k2 = 0, k3 = 0;
+                    uint32_t k0 = 0, k1 = 0;
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) {
+                    for (int i = 0; i < 16; ++i) {
                         k0 = __funnelshift_l(__float_as_uint(thr - __uint_as_float(v[i])), k0, 1);
-                        k1 = __funnelshift_l(__float_as_uint(thr - __uint_as_float(v[8 + i])), k1, 1);
-                        k2 = __funnelshift_l(__float_as_uint(thr - __uint_as_float(v[16 + i])), k2, 1);
-                        k3 = __funnelshift_l(__float_as_uint(thr - __uint_as_float(v[24 + i])), k3, 1);
+                        k1 = __funnelshift_l(__float_as_uint(thr - __uint_as_float(v[16 + i])), k1, 1);
                     }
-                    uint32_t mask = (k0 << 24) | (k1 << 16) | (k2 << 8) | k3;  // bit 31 - i <-> column col0 + i
+                    uint32_t mask = k0 * 65536u + k1;  // bit 31 - i <-> column col0 + i
                     while (mask) {
                         const int b = __clz(mask);
                         mask &= ~(0x80000000u >> b);
@@ -506,75 +689,24 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                 sweep(va, cbase);
                 sweep(vb, cbase + 32);
             }
-            // ---- the four slices of a row meet.  Lists, maxima and counts are double buffered by tile parity,
-            // so one barrier per tile is enough.  count 100 = list overflow.
+            // ---- the four slices of a row meet.  Lists, maxima and counts are double buffered by tile parity.
+            // count 100 = list overflow.
             s_cnt[(tpar * kSplit + slice) * 128 + r] = (uint8_t)(cnt > (uint32_t)kListCap ? 100u : cnt);
             s_max[(tpar * kSplit + slice) * 128 + r] = m_run;
-            epi_bar();
-            if (slice == 0 && row < n) {
-                float mq[kSplit];
-#pragma unroll
-                for (int q = 0; q < kSplit; ++q) mq[q] = s_max[(tpar * kSplit + q) * 128 + r];
-                bool any_bad = false;
-                const float m_all = fmaxf(fmaxf(mq[0], mq[1]), fmaxf(mq[2], mq[3]));
-                const float thr_all = threshold(m_all, xn, e_dot, any_bad);
-                uint32_t w[4] = {0, 0, 0, 0};
-                uint32_t total = 0;
-                bool ovf = any_bad;
-#pragma unroll
-                for (int q = 0; q < kSplit; ++q) {
-                    const uint32_t cq = s_cnt[(tpar * kSplit + q) * 128 + r];
-                    if (!(mq[q] > thr_all)) continue;      // this slice's best score cannot be the winner's
-                    ovf |= cq > (uint32_t)kListCap;
-                    const uint16_t* lq = lists + ((tpar * kSplit + q) * 128 + r) * kListCap;
-                    for (uint32_t i = 0; i < cq && !ovf && total < 8; ++i, ++total) {
-                        const uint32_t c = lq[i];
-                        w[total >> 1] |= c << (16 * (total & 1));
-                    }
-                }
-                moved = false;
-                if (!ovf && total == 1 && assign) {
-                    // a single candidate is the exact argmin: final
-                    const uint32_t c = w[0] & 0xffffu;
-                    moved = old_c != c;
-                    if (flags && moved) flags[(size_t)tex * bt.flags_stride] = 1u;
-                    assign[row] = c;
-                } else {
-                    if (!ovf && total >= 1 && total <= (uint32_t)kMaxCand) {
-                        w[3] = (w[3] & 0xffffu) | (total << 16);
-                    } else {
-                        w[0] = w[1] = w[2] = 0;
-                        w[3] = 0xffffu << 16;  // empty (NaN) or overflow: full exact scan in the re-rank
-                    }
-                    cand[row] = make_uint4(w[0], w[1], w[2], w[3]);
-                    if (amb_list) amb_list[atomicAdd(amb_count, 1u)] = (uint32_t)row;
-                }
-            }
-            if (bt.chg_count && slice == 0) {
-                // delta update: (row, previous centroid) of every row that moved -- one atomic per warp and tile, and
-                // its result is only consumed one tile later, so the round trip to L2 hides behind the next tile
-                if (pend_mask) {
-                    const uint32_t slot = __shfl_sync(0xffffffffu, pend_base, __ffs(pend_mask) - 1) +
-                                          (uint32_t)__popc(pend_mask & ((1u << lane) - 1u));
-                    if (pend_mask & (1u << lane)) {
-                        bt.chg_rows[slot] = pend_row;
-                        bt.chg_old[slot] = pend_old;
-                    }
-                }
-                pend_mask = __ballot_sync(0xffffffffu, moved);
-                pend_row = (uint32_t)row;
-                pend_old = old_c;
-                if (pend_mask && lane == __ffs(pend_mask) - 1) pend_base = atomicAdd(bt.chg_count, (unsigned)__popc(pend_mask));
+            if (MW) {
+                // v2: hand the tile to the quadrant's merge warp and go on with the next one
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar(BAR_MFULL + tpar * 4 + quad));
+            } else {
+                // v1: one barrier per tile, the slice-0 thread of each row merges
+                epi_bar();
+                bool moved = false;
+                if (slice == 0 && row < n)
+                    moved = merge_row(lists, s_max, s_cnt, tpar, r, row, xn, e_dot, old_c, tex, cand, assign, flags, amb_list, amb_count, bt);
+                if (bt.chg_count && slice == 0) ml.push(bt, lane, moved, (uint32_t)row, old_c);
             }
         }
-        if (bt.chg_count && slice == 0 && pend_mask) {
-            const uint32_t slot = __shfl_sync(0xffffffffu, pend_base, __ffs(pend_mask) - 1) +
-                                  (uint32_t)__popc(pend_mask & ((1u << lane) - 1u));
-            if (pend_mask & (1u << lane)) {
-                bt.chg_rows[slot] = pend_row;
-                bt.chg_old[slot] = pend_old;
-            }
-        }
+        if (!MW && bt.chg_count && slice == 0) ml.flush(bt, lane);
     }
 
     tc_fence_before();
@@ -1021,8 +1153,10 @@ cudaError_t launch_assign_tc(const float* a_prime, const float* xnorm, size_t n,
     static std::atomic<uint64_t> attr_set{0};  // per device (a process may hold contexts on several GPUs)
     {
         const cudaError_t e = once_per_device(attr_set, [] {
-            cudaError_t a = cudaFuncSetAttribute(assign_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_TC);
-            if (a == cudaSuccess) a = cudaFuncSetAttribute(assign_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_TC);
+            cudaError_t a = cudaFuncSetAttribute(assign_tc_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_TC);
+            if (a == cudaSuccess) a = cudaFuncSetAttribute(assign_tc_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_TC);
+            if (a == cudaSuccess) a = cudaFuncSetAttribute(assign_tc_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_TC);
+            if (a == cudaSuccess) a = cudaFuncSetAttribute(assign_tc_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_TC);
             return a;
         });
         if (e != cudaSuccess) return e;
@@ -1041,12 +1175,20 @@ cudaError_t launch_assign_tc(const float* a_prime, const float* xnorm, size_t n,
     const uint32_t grid = num_tiles < (uint32_t)YUPVQ_NUM_SMS ? num_tiles : (uint32_t)YUPVQ_NUM_SMS;
     TcBatch bt = batch ? *batch : tc_single();
     if (!batch || n_tex <= 1) bt.k_pad = k_pad;
-    if (batch && n_tex > 1)
-        assign_tc_kernel<true><<<grid, kThreadsTc, SMEM_TC, s>>>(tm_a, tm_b, tm_bx, xnorm, cmax, (uint32_t)n, num_tiles, num_chunks,
-                                                                num_chunks <= 2 ? 1u : 0u, cand, assign, flags, amb_list, amb_count, stop, bt);
-    else
-        assign_tc_kernel<false><<<grid, kThreadsTc, SMEM_TC, s>>>(tm_a, tm_b, tm_bx, xnorm, cmax, (uint32_t)n, num_tiles, num_chunks,
-                                                                 num_chunks <= 2 ? 1u : 0u, cand, assign, flags, amb_list, amb_count, stop, bt);
+    const uint32_t res_b = num_chunks <= 2 ? 1u : 0u;
+    const bool v1 = debug_opts().tc_v1;   // A/B: the one-barrier-per-tile epilogue without merge warps
+#define YUPVQ_TC_LAUNCH(B, M)                                                                                                      \
+    assign_tc_kernel<B, M><<<grid, (M) ? kThreadsTc2 : kThreadsTc, SMEM_TC, s>>>(tm_a, tm_b, tm_bx, xnorm, cmax, (uint32_t)n, num_tiles, \
+                                                                                num_chunks, res_b, cand, assign, flags, amb_list,       \
+                                                                                amb_count, stop, bt)
+    if (batch && n_tex > 1) {
+        if (v1) YUPVQ_TC_LAUNCH(true, false);
+        else YUPVQ_TC_LAUNCH(true, true);
+    } else {
+        if (v1) YUPVQ_TC_LAUNCH(false, false);
+        else YUPVQ_TC_LAUNCH(false, true);
+    }
+#undef YUPVQ_TC_LAUNCH
     return cudaGetLastError();
 }
 
