@@ -457,12 +457,10 @@ int assign_blocks(yupvq_ctx* ctx, const float* feat, size_t n, const float* cent
 // ---- K3..K5: Lloyd iterations ----------------------------------------------------------------------
 // break_after: LDR breaks on (!changed && iter > 0), HDR on (!changed && iter > 1)
 // (src/vq_encoder.cpp:341 vs :572).  cent (device, K x 64) holds the seeds on entry.
-// `sharded`: b is this rank's block range of a texture spread over the context's communicator (set only by
-// yupvq_encode_bcn_sharded); every other entry point ignores ctx->comm, so contexts with a communicator can
-// still encode independent textures.
-int run_lloyd(yupvq_ctx* ctx, const Blocks& b, size_t n_total, size_t first_block, uint32_t K, uint32_t max_iter,
-              uint32_t break_after, int assign_mode, float* cent, yupvq_stats* stats, bool sharded = false) {
-    if (sharded && !ctx->comm) sharded = false;
+// Always rank-local: ctx->comm is used by the *_sharded entry points only (the lock-step batch), so a context with a
+// communicator can still encode independent textures.
+int run_lloyd(yupvq_ctx* ctx, const Blocks& b, size_t n_total, uint32_t K, uint32_t max_iter, uint32_t break_after, int assign_mode,
+              float* cent, yupvq_stats* stats) {
     const size_t n = b.n;
     const bool tensor = use_tensor(assign_mode, n, K);
     CK(ctx->assign.ensure(std::max<size_t>(1, n) * 4));
@@ -485,19 +483,11 @@ int run_lloyd(yupvq_ctx* ctx, const Blocks& b, size_t n_total, size_t first_bloc
     CK(cudaStreamSynchronize(ctx->stream));
     float max_abs;
     std::memcpy(&max_abs, ctx->h_small, 4);
-    if (sharded) {
-        // the scale must be identical on every rank: use the global maximum
-        CK(cudaMemcpyAsync(flags + F_SPARE, ctx->h_small, 4, cudaMemcpyHostToDevice, ctx->stream));
-        if (ctx->nccl.all_reduce_max_u32(ctx->comm, flags + F_SPARE, 1, ctx->stream)) return ctx->fail("ncclAllReduce(max) failed");
-        CK(cudaMemcpyAsync(ctx->h_small, flags + F_SPARE, 4, cudaMemcpyDeviceToHost, ctx->stream));
-        CK(cudaStreamSynchronize(ctx->stream));
-        std::memcpy(&max_abs, ctx->h_small, 4);
-    }
     const int shift = fixed_shift(n_total, max_abs);
 
     uint32_t passes = 0;
     const DebugOpts& dbg = debug_opts();
-    const bool async_loop = !sharded && !dbg.lloyd_sync;
+    const bool async_loop = !dbg.lloyd_sync;
     if (async_loop) {
         // Single GPU: every pass is enqueued without a host round trip.  The reference's convergence test
         // (between assign and update) runs on the device (launch_lloyd_control); once it fires, the kernels
@@ -625,7 +615,6 @@ int run_lloyd(yupvq_ctx* ctx, const Blocks& b, size_t n_total, size_t first_bloc
             // speculatively so one sync and one all-reduce per pass carry both.
             CK(cudaMemsetAsync(acc, 0, acc_words * 8, ctx->stream));
             LAUNCH(launch_accumulate(b.feat, n, assign, K, shift, acc, flags, nullptr, ctx->stream));
-            if (sharded && ctx->nccl.all_reduce_sum_i64(ctx->comm, acc, acc_words, ctx->stream)) return ctx->fail("ncclAllReduce(sum) failed");
             LAUNCH(launch_count_empty(acc, K, flags + F_SPARE, ctx->stream));
             CK(cudaMemcpyAsync(ctx->h_small, acc + (size_t)K * 65, 8, cudaMemcpyDeviceToHost, ctx->stream));
             CK(cudaMemcpyAsync(ctx->h_small + 2, flags + F_SPARE, 4, cudaMemcpyDeviceToHost, ctx->stream));
@@ -636,11 +625,7 @@ int run_lloyd(yupvq_ctx* ctx, const Blocks& b, size_t n_total, size_t first_bloc
             if (tensor && ctx->h_small[2] != 0)  // errors[i] = distance to the assigned centroid, before the update (:336)
                 LAUNCH(launch_exact_errors(b.feat, n, cent, assign, errors, nullptr, nullptr, ctx->stream));
             LAUNCH(launch_finalize_centroids(acc, K, shift, cent, flags, nullptr, ctx->stream));
-            if (!sharded) {
-                LAUNCH(launch_reseed_empty(b.feat, n, errors, acc, K, cent, flags, nullptr, ctx->stream));
-            } else if (reseed_sharded(ctx, b, first_block, K, cent, errors, acc, flags)) {
-                return 1;
-            }
+            LAUNCH(launch_reseed_empty(b.feat, n, errors, acc, K, cent, flags, nullptr, ctx->stream));
         }
     }
     CK(cudaMemcpyAsync(ctx->h_small, flags + F_RESEEDS, 4, cudaMemcpyDeviceToHost, ctx->stream));
@@ -754,7 +739,7 @@ int build_codebook_device(yupvq_ctx* ctx, const Blocks& all, size_t n_total, con
         *t_fin1 = tm.mark();   // the centroids already are pixel blocks (no colour conversion on this path)
         return 0;
     }
-    if (run_lloyd(ctx, b, n_total, 0, K, cfg->max_iterations, hdr ? 1u : 0u, cfg->assign_mode, ctx->cent.as<float>(), stats))
+    if (run_lloyd(ctx, b, n_total, K, cfg->max_iterations, hdr ? 1u : 0u, cfg->assign_mode, ctx->cent.as<float>(), stats))
         return 1;
     *t_lloyd1 = tm.mark();
     if (hdr) {
@@ -1556,97 +1541,18 @@ int yupvq_comm_init(yupvq_ctx* ctx, const uint8_t id[128], int n_ranks, int rank
     return 0;
 }
 
+// One texture over the ranks of the communicator: the lock-step batch below with a single texture.  Rank 0 seeds
+// (K-Means++ is K-1 dependent rounds: replicating it on every rank would not make it shorter), the seed rows go out with
+// one all-reduce, every rank runs the device-side Lloyd loop on its shard (no host round trip per pass) and ONE all-reduce
+// per pass carries the fixed-point sums and counts.  With seed == 0 only rank 0 draws from std::random_device.
 int yupvq_encode_bcn_sharded(yupvq_ctx* ctx, const uint8_t* bc_blocks, size_t n_total, size_t first_block,
                              size_t n_local, int bc_format, int channels, const yupvq_config* cfg,
                              uint8_t* out_pixel_centroids, uint32_t* out_indices, yupvq_stats* stats) {
     if (!ctx) return 1;
-    Scope scope(ctx->device);
-    init_stats(stats);
-    ctx->launches = 0;
-    ctx->tc_feat = nullptr;
-    ctx->tc_rgb = rgb_layout(channels);
-    if (check_cfg(ctx, cfg, n_total, channels)) return 1;
-    if (!bc_supported(bc_format)) return ctx->fail("BC format %d is not supported on the LDR VQ path", bc_format);
-    if (first_block + n_local > n_total) return ctx->fail("shard [%zu, %zu) exceeds %zu blocks", first_block, first_block + n_local, n_total);
-    if (cfg->sample_ratio < 1.0f && cfg->sample_ratio > 0.0f) return ctx->fail("fast-mode sampling is not supported on the sharded path");
-    if (cfg->metric != YUPVQ_METRIC_OKLAB) return ctx->fail("SAD metric Lloyd is not built yet");
-    const uint32_t K = cfg->codebook_size;
-    Timer tm(ctx);
-    const int t0 = tm.mark();
-    const void* bc_dev = nullptr;
-    if (to_device(ctx, bc_blocks, n_total * bc_block_bytes(bc_format), ctx->in_bytes, &bc_dev)) return 1;
-    const int t1 = tm.mark();
-    // Whole texture decoded on every rank (8-16 MiB in): seeding is replicated and integer-exact, so
-    // all ranks pick the same seeds with no communication.
-    // pixel planes of the whole texture (all the seeding reads); Oklab features only for the K seed blocks and,
-    // after the seeding, for this rank's shard
-    CK(ctx->planes.ensure(n_total * 16 * channels));
-    CK(ctx->feat.ensure(std::max<size_t>(1, n_local) * 256));
-    LAUNCH(launch_decode_bcn(reinterpret_cast<const uint8_t*>(bc_dev), n_total, bc_format, channels,
-                             ctx->planes.as<uint4>(), n_total, nullptr, nullptr, ctx->stream));
-    const int t2 = tm.mark();
-    Blocks all;
-    all.n = n_total;
-    all.ch = channels;
-    all.planes = ctx->planes.as<uint4>();
-    all.stride = n_total;
-    all.feat = nullptr;
-    if (attach_palette_form(ctx, all, bc_dev, bc_format, channels)) return 1;
-    size_t n_used;
-    uint64_t seed = cfg->seed;
-    if (seed == 0 && ctx->comm) {
-        // seed 0 = std::random_device (src/vq_encoder.cpp:24-26): the ranks replicate the seeding, so they must all draw
-        // from ONE stream -- rank 0 draws the mt19937 seed and broadcasts it
-        uint32_t* spare = ctx->small.as<uint32_t>() + F_SPARE;
-        ctx->h_small[8] = (uint32_t)std::random_device{}();
-        CK(cudaMemcpyAsync(spare, ctx->h_small + 8, 4, cudaMemcpyHostToDevice, ctx->stream));
-        if (ctx->nccl.broadcast_bytes(ctx->comm, spare, 4, 0, ctx->stream)) return ctx->fail("ncclBroadcast(seed) failed");
-        CK(cudaMemcpyAsync(ctx->h_small + 8, spare, 4, cudaMemcpyDeviceToHost, ctx->stream));
-        CK(cudaStreamSynchronize(ctx->stream));
-        seed = (1ull << 32) | ctx->h_small[8];   // make_draws seeds mt19937 with the low 32 bits of a non-zero seed
-    }
-    Draws dr = make_draws(n_total, K, 1.0f, seed, &n_used);
-    uint32_t rounds = 0;
-    if (run_seeding(ctx, all, K, dr, false, stats ? &rounds : nullptr)) return 1;
-    CK(ctx->cent.ensure((size_t)K * 256));
-    CK(ctx->cent_px.ensure((size_t)K * 16 * channels));
-    LAUNCH(launch_planes_to_blocks(all.planes, all.stride, ctx->seed_idx.as<uint32_t>(), K, channels, ctx->cent_px.as<uint8_t>(),
-                                   ctx->stream));
-    LAUNCH(launch_pixels_to_features(ctx->cent_px.as<uint8_t>(), K, channels, nullptr, 0, ctx->cent.as<float>(), ctx->stream));
-    if (n_local)
-        LAUNCH(launch_decode_bcn(reinterpret_cast<const uint8_t*>(bc_dev) + first_block * bc_block_bytes(bc_format), n_local, bc_format,
-                                 channels, nullptr, 0, ctx->feat.as<float>(), nullptr, ctx->stream));
-    const int t3 = tm.mark();
-    Blocks mine = all;
-    mine.n = n_local;
-    mine.feat = ctx->feat.as<float>();
-    mine.planes = all.planes + first_block;  // stride unchanged
-    if (run_lloyd(ctx, mine, n_total, first_block, K, cfg->max_iterations, 0u, cfg->assign_mode, ctx->cent.as<float>(), stats, true)) return 1;
-    const int t4 = tm.mark();
-    CK(ctx->cent_px.ensure((size_t)K * 16 * channels));
-    LAUNCH(launch_oklab_to_pixels(ctx->cent.as<float>(), K, channels, ctx->cent_px.as<uint8_t>(), ctx->stream));
-    const int t5 = tm.mark();
-    if (quantize_device(ctx, mine, ctx->cent_px.p, K, false, cfg->assign_mode)) return 1;
-    const int t6 = tm.mark();
-    if (from_device(ctx, out_pixel_centroids, ctx->cent_px.p, (size_t)K * 16 * channels)) return 1;
-    if (from_device(ctx, out_indices, ctx->out_idx.p, n_local * 4)) return 1;
-    const int t7 = tm.mark();
-    CK(cudaStreamSynchronize(ctx->stream));
-    if (stats) {
-        stats->n_blocks = (uint32_t)n_local;
-        stats->codebook_size = K;
-        stats->seed_rounds = rounds;
-        stats->ms_h2d = tm.ms(t0, t1);
-        stats->ms_decode = tm.ms(t1, t2);
-        stats->ms_seed = tm.ms(t2, t3);
-        stats->ms_lloyd = tm.ms(t3, t4);
-        stats->ms_finalize = tm.ms(t4, t5);
-        stats->ms_quantize = tm.ms(t5, t6);
-        stats->ms_d2h = tm.ms(t6, t7);
-        stats->ms_total = tm.ms(t0, t7);
-        stats->gpu_launches = ctx->launches;
-    }
-    return 0;
+    const uint8_t* tex[1] = {bc_blocks};
+    uint8_t* cents[1] = {out_pixel_centroids};
+    uint32_t* idx[1] = {out_indices};
+    return yupvq_encode_bcn_batch_sharded(ctx, tex, 1, n_total, first_block, n_local, bc_format, channels, cfg, cents, idx, stats, nullptr);
 }
 
 
