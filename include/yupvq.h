@@ -189,14 +189,14 @@ YUPVQ_API int yupvq_gather_codebook(yupvq_ctx* ctx, const uint8_t* codebook, uin
  * file) hands the 128 bytes to every rank, then every rank calls yupvq_comm_init. */
 YUPVQ_API int yupvq_comm_unique_id(yupvq_ctx* ctx, uint8_t out_id[128]);
 YUPVQ_API int yupvq_comm_init(yupvq_ctx* ctx, const uint8_t id[128], int n_ranks, int rank);
-/* Only the two *_sharded entry points below use the communicator.  Every other call on a context that has one
+/* Only the *_sharded entry points below use the communicator.  Every other call on a context that has one
  * (yupvq_encode_bcn, yupvq_build_codebook[_hdr], yupvq_encode_bcn_batch, ...) stays rank-local: ranks may encode
  * unrelated textures with them at the same time. */
-/* Block-sharded LDR VQ: this rank holds blocks [first_block, first_block + n_local) of a texture
- * of n_total blocks; the whole texture's BCn bytes are passed on every rank (seeding is replicated
- * and integer-exact, so every rank draws the same seeds with no communication; with cfg->seed == 0 rank 0 draws
- * the std::random_device value and broadcasts it, so the ranks still share one RNG stream).  Per Lloyd pass
- * the K x 64 fixed-point sums, K counts and the changed flag are all-reduced over NCCL.
+/* Block-sharded LDR VQ of ONE texture: this rank holds blocks [first_block, first_block + n_local) of a texture
+ * of n_total blocks; the whole texture's BCn bytes are passed on every rank.  It is the lock-step batch below with a
+ * single texture: rank 0 runs the K-Means++ seeding (with cfg->seed == 0 it alone draws from std::random_device) and
+ * the seed rows go out with one all-reduce; every rank then runs the Lloyd passes on its shard without a host round
+ * trip per pass, and per pass the K x 64 fixed-point sums, K counts and the changed flag are all-reduced over NCCL.
  * out_indices receives this rank's n_local indices. */
 YUPVQ_API int yupvq_encode_bcn_sharded(yupvq_ctx* ctx, const uint8_t* bc_blocks, size_t n_total, size_t first_block,
                                        size_t n_local, int bc_format, int channels, const yupvq_config* cfg,
@@ -219,6 +219,24 @@ YUPVQ_API int yupvq_encode_bcn_batch_sharded(yupvq_ctx* ctx, const uint8_t* cons
                                              int channels, const yupvq_config* cfg,
                                              uint8_t* const* out_pixel_centroids, uint32_t* const* out_indices,
                                              yupvq_stats* stats, const uint8_t* shard_only);
+/* Variants on the two entry points above (src/vq_encoder.cpp:262-284, :380-430): with cfg->sample_ratio in (0, 1)
+ * (fast mode) the ranks split each texture's SAMPLE list instead of the texture -- the list is drawn on the seeding
+ * rank and broadcast -- and with cfg->metric == YUPVQ_METRIC_SAD the integer SAD kernels run; both need the whole
+ * texture on every rank (shard_only must be NULL or all zero).  Results equal yupvq_encode_bcn with seed + t. */
+
+/* HDR images over the ranks (BASELINE config 4; src/vq_encoder.cpp:493-658): n_images float images of width x height
+ * x channels, every rank passes every image whole and receives the index map of its block range
+ * [first_block, first_block + n_local) of each (blocks in row-major 4x4-tile order, as yupvq_encode_hdr).
+ * Image t is seeded on rank t % n_ranks with seed cfg->seed + t; one all-reduce per Lloyd pass; the reference's
+ * `iter > 1` break rule.  out_float_centroids[t]: K x 16*channels floats. */
+YUPVQ_API int yupvq_encode_hdr_batch_sharded(yupvq_ctx* ctx, const float* const* images, size_t n_images, uint32_t width,
+                                             uint32_t height, int channels, size_t first_block, size_t n_local,
+                                             const yupvq_config* cfg, float* const* out_float_centroids,
+                                             uint32_t* const* out_indices, yupvq_stats* stats);
+/* One image: yupvq_encode_hdr_batch_sharded with n_images == 1. */
+YUPVQ_API int yupvq_encode_hdr_sharded(yupvq_ctx* ctx, const float* image, uint32_t width, uint32_t height, int channels,
+                                       size_t first_block, size_t n_local, const yupvq_config* cfg,
+                                       float* out_float_centroids, uint32_t* out_indices, yupvq_stats* stats);
 
 #ifdef __cplusplus
 }

@@ -200,6 +200,60 @@ def test_lockstep_batch_equals_per_texture_calls(enc, w, h):
     assert st.lloyd_passes == total_passes and st.gpu_launches > 0
 
 
+@pytest.mark.parametrize("variant", ["sampled", "sad", "sad_sampled", "sampled_exact"])
+def test_lockstep_batch_variants_equal_per_texture_calls(enc, variant):
+    """The general lock-step batch (fast-mode sampling, SAD metric; src/vq_encoder.cpp:262-284, :380-430) on one GPU
+    without a communicator: every texture bit-identical to yupvq_encode_bcn with seed + t, incl. a flat texture
+    (all clusters but one empty: reseeds) and a 4-channel one."""
+    from yuptexture_b200 import binding
+    kw = dict(codebook=96, max_iterations=10, seed=9)
+    if "sampled" in variant:
+        kw["sample_ratio"] = 0.3
+    if "sad" in variant:
+        kw["metric"] = binding.METRIC_SAD
+    if variant == "sampled_exact":
+        kw["assign_mode"] = binding.ASSIGN_EXACT
+    for fmt, ch, mk in ((1, 3, lambda t: synth.bc1_encode(synth.ldr_rgb(256, 192, seed=61 + t))),
+                        (3, 4, lambda t: synth.bc3_encode(synth.ldr_rgba(128, 256, seed=71 + t)))):
+        texs = [mk(t) for t in range(3)]
+        if fmt == 1:
+            texs.append(synth.bc1_encode(synth.checker_rgb(256, 192)))
+        n = len(texs[0])
+        cfg = binding.make_config(**kw)
+        cents, idxs, st = enc.encode_bcn_batch_sharded(texs, n, 0, n, fmt, ch, cfg)
+        total = 0
+        for t, bc in enumerate(texs):
+            c1 = binding.make_config(**dict(kw, seed=9 + t))
+            cent, idx, s1 = enc.encode_bcn(bc, n, fmt, ch, c1)
+            assert bits_equal(cents[t], cent), (variant, fmt, t)
+            assert bits_equal(idxs[t], idx), (variant, fmt, t)
+            total += s1.lloyd_passes
+        assert st.lloyd_passes == total
+
+
+@pytest.mark.parametrize("ratio", [1.0, 0.4])
+def test_hdr_lockstep_batch_equals_per_image_calls(enc, ratio):
+    """yupvq_encode_hdr_batch_sharded on one GPU without a communicator: centroids and indices of every image
+    bit-identical to yupvq_encode_hdr with seed + t (the `iter > 1` break rule, float centroids, K > 512 included)."""
+    from yuptexture_b200 import binding
+    w, h = 256, 128
+    imgs = [synth.hdr_rgb(w, h, seed=81 + t) for t in range(2)]
+    n = (w // 4) * (h // 4)
+    for k in (64, 600):
+        cfg = binding.make_config(codebook=k, max_iterations=8, seed=21, sample_ratio=ratio)
+        cents, idxs, st = enc.encode_hdr_batch_sharded(imgs, w, h, 3, 0, n, cfg)
+        for t, img in enumerate(imgs):
+            c1 = binding.make_config(codebook=k, max_iterations=8, seed=21 + t, sample_ratio=ratio)
+            cent, idx, _ = enc.encode_hdr(img, w, h, 3, c1)
+            assert bits_equal(cents[t], cent), (k, t)
+            assert bits_equal(idxs[t], idx), (k, t)
+    # the single-image entry point
+    cfg = binding.make_config(codebook=64, max_iterations=8, seed=21, sample_ratio=ratio)
+    cent_a, idx_a, _ = enc.encode_hdr_sharded(imgs[0], w, h, 3, 0, n, cfg)
+    cent_b, idx_b, _ = enc.encode_hdr(imgs[0], w, h, 3, cfg)
+    assert bits_equal(cent_a, cent_b) and bits_equal(idx_a, idx_b)
+
+
 def test_multi_gpu_sharded_matches_single_gpu():
     """Blocks sharded over 2 GPUs (NCCL all-reduce of the fixed-point sums): identical codebooks and
     indices to the single-GPU run, for both the per-texture and the lock-step batch entry points."""

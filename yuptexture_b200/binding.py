@@ -82,6 +82,9 @@ def lib():
                                                _vp, _vp, stp]
         L.yupvq_encode_bcn_batch_sharded.argtypes = [_vp, C.POINTER(_vp), C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t,
                                                      C.c_int, C.c_int, cfgp, C.POINTER(_vp), C.POINTER(_vp), stp, _vp]
+        L.yupvq_encode_hdr_batch_sharded.argtypes = [_vp, C.POINTER(_vp), C.c_size_t, C.c_uint32, C.c_uint32, C.c_int, C.c_size_t,
+                                                     C.c_size_t, cfgp, C.POINTER(_vp), C.POINTER(_vp), stp]
+        L.yupvq_encode_hdr_sharded.argtypes = [_vp, _vp, C.c_uint32, C.c_uint32, C.c_int, C.c_size_t, C.c_size_t, cfgp, _vp, _vp, stp]
         _lib = L
     return _lib
 
@@ -214,6 +217,32 @@ class Encoder:
                                                         C.byref(cfg), arr(out_centroids), arr(out_indices), C.byref(st),
                                                         _ptr(flags)),
                  "yupvq_encode_bcn_batch_sharded")
+        return out_centroids, out_indices, st
+
+    def encode_hdr_batch_sharded(self, images, width, height, ch, first, n_local, cfg, out_centroids=None, out_indices=None):
+        """HDR images over the ranks (config 4): every rank passes every image whole (numpy arrays or raw device pointers)."""
+        t_n = len(images)
+        images = [x if isinstance(x, int) else _c(x, np.float32) for x in images]
+        if out_centroids is None:
+            out_centroids = [np.empty((cfg.codebook_size, 16 * ch), np.float32) for _ in range(t_n)]
+        if out_indices is None:
+            out_indices = [np.empty(n_local, np.uint32) for _ in range(t_n)]
+        arr = lambda xs: (_vp * t_n)(*[None if x is None else _ptr(x).value for x in xs])
+        st = Stats()
+        self._ck(self._L.yupvq_encode_hdr_batch_sharded(self._ctx, arr(images), t_n, width, height, ch, first, n_local, C.byref(cfg),
+                                                        arr(out_centroids), arr(out_indices), C.byref(st)),
+                 "yupvq_encode_hdr_batch_sharded")
+        return out_centroids, out_indices, st
+
+    def encode_hdr_sharded(self, image, width, height, ch, first, n_local, cfg, out_centroids=None, out_indices=None):
+        image = _c(image, np.float32)
+        if out_centroids is None:
+            out_centroids = np.empty((cfg.codebook_size, 16 * ch), np.float32)
+        if out_indices is None:
+            out_indices = np.empty(n_local, np.uint32)
+        st = Stats()
+        self._ck(self._L.yupvq_encode_hdr_sharded(self._ctx, _ptr(image), width, height, ch, first, n_local, C.byref(cfg),
+                                                  _ptr(out_centroids), _ptr(out_indices), C.byref(st)), "yupvq_encode_hdr_sharded")
         return out_centroids, out_indices, st
 
     # ---- the four VQEncoder calls

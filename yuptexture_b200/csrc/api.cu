@@ -101,6 +101,7 @@ struct yupvq_ctx {
     DevBuf tc_chg, delta_ctl;  // delta update: (row, previous centroid) lists; counter / mode words
     // lock-step batch (yupvq_encode_bcn_batch_sharded): per-texture slices of one buffer each
     DevBuf bt_feat, bt_tca, bt_xnorm, bt_tcsmall, bt_assign, bt_errors, bt_cent, bt_acc, bt_misc, bt_centpx, bt_cent0, bt_acc_local;
+    DevBuf bt_planes, bt_in, bt_rows;   // general lock-step batch: SAD pixel planes, device-resident inputs, row lists
     const float* tc_feat = nullptr;                    // block set the A' buffer was built from
     int tc_rgb = 0;                                    // 1: channels are 1 or 3 (alpha feature constant): 48-column tensor operands
     size_t tc_n = 0;
@@ -872,7 +873,7 @@ void yupvq_destroy(yupvq_ctx* ctx) {
                       &ctx->errors, &ctx->cent, &ctx->acc, &ctx->cent_px, &ctx->cent_feat, &ctx->out_idx,
                       &ctx->tc_a, &ctx->tc_xnorm, &ctx->tc_small, &ctx->tc_b, &ctx->tc_bx, &ctx->tc_cand, &ctx->tc_amb,
                       &ctx->bt_feat, &ctx->bt_tca, &ctx->bt_xnorm, &ctx->bt_tcsmall, &ctx->bt_assign, &ctx->bt_errors,
-                      &ctx->bt_cent, &ctx->bt_acc, &ctx->bt_misc, &ctx->bt_centpx, &ctx->bt_cent0, &ctx->tc_chg, &ctx->delta_ctl, &ctx->bt_acc_local, &ctx->pal5, &ctx->tail_scratch};
+                      &ctx->bt_cent, &ctx->bt_acc, &ctx->bt_misc, &ctx->bt_centpx, &ctx->bt_cent0, &ctx->tc_chg, &ctx->delta_ctl, &ctx->bt_acc_local, &ctx->pal5, &ctx->tail_scratch, &ctx->bt_planes, &ctx->bt_in, &ctx->bt_rows};
     for (DevBuf* b : bufs) b->release();
     if (ctx->h_small) cudaFreeHost(ctx->h_small);
     for (auto& ev : ctx->ev)
@@ -1556,6 +1557,375 @@ int yupvq_encode_bcn_sharded(yupvq_ctx* ctx, const uint8_t* bc_blocks, size_t n_
 }
 
 
+}  // extern "C" (reopened below)
+
+namespace {
+
+// Input of a lock-step batch: T BCn block arrays (LDR) or T float images (HDR), host or device pointers.
+struct BatchSrc {
+    bool hdr = false;
+    const void* const* data = nullptr;
+    int bc_format = 0;
+    uint32_t width = 0, height = 0;
+};
+
+// The lock-step batch for the variants of the path: fast-mode sampling (src/vq_encoder.cpp:262-284), the SAD metric
+// (:380-430) and HDR input (:493-622).  Same protocol as the Oklab LDR batch below -- texture t is seeded on rank
+// t % R, the K seed rows of all textures go out with one all-reduce, all textures advance one Lloyd pass at a time and
+// ONE all-reduce per pass carries the [K x 64 sums | K counts | changed] words of the whole batch; the convergence test
+// runs on the device, a rank-sharded empty-cluster reseed falls back to the host-driven loop -- but written with the
+// per-texture kernels (these variants are not the headline configuration):
+//   * every rank needs every texture WHOLE (a sampled Lloyd row can be any block; an HDR tile any part of the image);
+//   * with sampling the ranks split the SAMPLE list (in sample order, so "first maximum" keeps its meaning for the
+//     reseed), not the texture; the list is drawn on the seeding rank and broadcast; the final index map is still this
+//     rank's block range [first_block, first_block + n_local);
+//   * SAD: integer sums with shift 0 (exact), sad_assign / sad_finalize instead of the Oklab kernels;
+//   * HDR: the reference's `iter > 1` break rule, float centroids out.
+// Results equal the single-GPU yupvq_encode_bcn / yupvq_encode_hdr with seed + t bit for bit (integer or fixed-point
+// sums are order independent), HDR seeding as stated in DESIGN.md 4.3.
+int batch_sharded_general(yupvq_ctx* ctx, const BatchSrc& src, size_t T, size_t n_total, size_t first_block, size_t n_local, int channels,
+                          const yupvq_config* cfg, void* const* out_centroids, uint32_t* const* out_indices, yupvq_stats* stats) {
+    const bool hdr = src.hdr;
+    const bool sad = !hdr && cfg->metric == YUPVQ_METRIC_SAD;
+    const bool sampling = cfg->sample_ratio < 1.0f && cfg->sample_ratio > 0.0f;
+    const uint32_t break_after = hdr ? 1u : 0u;
+    const uint32_t K = cfg->codebook_size;
+    const int R = ctx->comm ? ctx->n_ranks : 1, rank = ctx->comm ? ctx->rank : 0;
+    const size_t in_bytes = hdr ? (size_t)src.width * src.height * channels * 4 : n_total * bc_block_bytes(src.bc_format);
+    const size_t cpx_bytes = (size_t)K * 16 * channels * (hdr ? 4 : 1);
+    const size_t acc_words = (size_t)K * 65 + 1;
+    // the Lloyd row set of this rank: its block range, or its slice of the sample list
+    size_t n_used = n_total;
+    if (sampling) n_used = std::min(std::max((size_t)K, (size_t)(n_total * cfg->sample_ratio)), n_total);   // make_draws
+    size_t row_first = first_block, n_rows = n_local;
+    if (sampling) {
+        const size_t per = (n_used + (size_t)R - 1) / (size_t)R;
+        row_first = std::min((size_t)rank * per, n_used);
+        n_rows = std::min(per, n_used - row_first);
+    }
+    const size_t nl = std::max<size_t>(1, n_rows);
+    const bool tensor = !sad && use_tensor(cfg->assign_mode, n_rows, K);
+    Timer tm(ctx);
+    const int t0 = tm.mark();
+
+    CK(ctx->bt_feat.ensure(T * nl * 256));
+    CK(ctx->bt_assign.ensure(T * nl * 4));
+    CK(ctx->bt_errors.ensure(T * nl * 4));
+    CK(ctx->bt_cent.ensure(T * (size_t)K * 256));
+    CK(ctx->bt_acc.ensure(T * acc_words * 8));
+    CK(ctx->bt_misc.ensure(T * 56 + 512));
+    CK(ctx->bt_centpx.ensure(T * cpx_bytes));
+    if (sad) CK(ctx->bt_planes.ensure(T * nl * 16 * channels));
+    if (tensor) {
+        CK(ctx->bt_tca.ensure(T * nl * 256));
+        CK(ctx->bt_xnorm.ensure(T * nl * 4));
+        CK(ctx->bt_tcsmall.ensure(T * TC_SMALL_BYTES));
+    }
+    auto feat_t = [&](size_t t) { return ctx->bt_feat.as<float>() + t * nl * 64; };
+    auto planes_t = [&](size_t t) { return sad ? ctx->bt_planes.as<uint4>() + t * nl * channels : nullptr; };
+    auto assign_t = [&](size_t t) { return ctx->bt_assign.as<uint32_t>() + t * nl; };
+    auto errors_t = [&](size_t t) { return ctx->bt_errors.as<float>() + t * nl; };
+    auto cent_t = [&](size_t t) { return ctx->bt_cent.as<float>() + t * (size_t)K * 64; };
+    auto acc_t = [&](size_t t) { return ctx->bt_acc.as<long long>() + t * acc_words; };
+    auto centpx_t = [&](size_t t) { return ctx->bt_centpx.as<uint8_t>() + t * cpx_bytes; };
+    uint32_t* maxabs_d = ctx->bt_misc.as<uint32_t>();
+    uint32_t* empty_d = maxabs_d + T;
+    std::vector<TcView> views(T);
+    for (size_t t = 0; t < T && tensor; ++t) {
+        views[t].a = ctx->bt_tca.as<float>() + t * nl * 64;
+        views[t].xnorm = ctx->bt_xnorm.as<float>() + t * nl;
+        views[t].small = ctx->bt_tcsmall.as<uint8_t>() + t * TC_SMALL_BYTES;
+    }
+
+    // ---- inputs: device resident for the whole call (the final index map decodes them a second time when sampling) ----
+    std::vector<const void*> in_dev(T);
+    {
+        size_t host_count = 0;
+        for (size_t t = 0; t < T; ++t) host_count += is_device_ptr(src.data[t]) ? 0 : 1;
+        if (host_count) CK(ctx->bt_in.ensure(host_count * in_bytes));
+        size_t slot = 0;
+        for (size_t t = 0; t < T; ++t) {
+            if (is_device_ptr(src.data[t])) {
+                in_dev[t] = src.data[t];
+            } else {
+                uint8_t* d = ctx->bt_in.as<uint8_t>() + slot++ * in_bytes;
+                CK(cudaMemcpyAsync(d, src.data[t], in_bytes, cudaMemcpyHostToDevice, ctx->stream));
+                in_dev[t] = d;
+            }
+        }
+    }
+    // whole texture -> ctx->planes (LDR) and ctx->feat (Oklab features; SAD: the pixel bytes as fp32 rows)
+    auto decode_whole = [&](size_t t) -> int {
+        CK(ctx->feat.ensure(n_total * 256));
+        if (hdr) {
+            LAUNCH(launch_image_to_features(reinterpret_cast<const float*>(in_dev[t]), src.width, src.height, channels, ctx->feat.as<float>(),
+                                            nullptr, ctx->stream));
+        } else {
+            CK(ctx->planes.ensure(n_total * 16 * channels));
+            LAUNCH(launch_decode_bcn(reinterpret_cast<const uint8_t*>(in_dev[t]), n_total, src.bc_format, channels, ctx->planes.as<uint4>(),
+                                     n_total, sad ? nullptr : ctx->feat.as<float>(), nullptr, ctx->stream));
+            if (sad) LAUNCH(launch_sad_expand(ctx->planes.as<uint4>(), n_total, n_total, channels, ctx->feat.as<float>(), ctx->stream));
+        }
+        return 0;
+    };
+    // row lists: [0, n_local) -> first_block + i (shared by all textures); with sampling each texture's own list in s_rows
+    CK(ctx->bt_rows.ensure(std::max<size_t>(1, n_local) * 4));
+    {
+        std::vector<uint32_t> iota(n_local);
+        for (size_t i = 0; i < n_local; ++i) iota[i] = (uint32_t)(first_block + i);
+        if (n_local) CK(cudaMemcpyAsync(ctx->bt_rows.p, iota.data(), n_local * 4, cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));  // iota is stack-owned
+    }
+    if (sampling) CK(ctx->s_rows.ensure(n_used * 4));
+
+    // ---- phases A + B, texture by texture: decode, (sample,) seed on the owning rank, gather this rank's Lloyd rows -------
+    uint32_t seed_rounds = 0;
+    CK(cudaMemsetAsync(ctx->bt_cent.p, 0, T * (size_t)K * 256, ctx->stream));
+    CK(cudaMemsetAsync(maxabs_d, 0, T * 8, ctx->stream));
+    for (size_t t = 0; t < T; ++t) {
+        const int owner = (int)(t % (size_t)R);
+        if (decode_whole(t)) return 1;
+        Blocks all;
+        all.n = n_total;
+        all.ch = channels;
+        all.planes = hdr ? nullptr : ctx->planes.as<uint4>();
+        all.stride = hdr ? 0 : n_total;
+        all.feat = ctx->feat.as<float>();
+        Draws dr;
+        if (owner == rank) {
+            size_t used = 0;
+            dr = make_draws(n_total, K, cfg->sample_ratio, cfg->seed ? cfg->seed + t : 0, &used);
+            if (sampling) CK(cudaMemcpyAsync(ctx->s_rows.p, dr.sample.data(), n_used * 4, cudaMemcpyHostToDevice, ctx->stream));
+        }
+        if (sampling && ctx->comm && ctx->nccl.broadcast_bytes(ctx->comm, ctx->s_rows.p, n_used * 4, owner, ctx->stream))
+            return ctx->fail("ncclBroadcast(sample list) failed");
+        if (owner == rank) {
+            Blocks b = all;
+            if (sampling) {
+                CK(ctx->s_feat.ensure(n_used * 256));
+                if (!hdr) CK(ctx->s_planes.ensure(n_used * 16 * channels));
+                LAUNCH(launch_gather_blocks(all.planes, all.stride, all.feat, ctx->s_rows.as<uint32_t>(), n_used, channels,
+                                            hdr ? nullptr : ctx->s_planes.as<uint4>(), n_used, ctx->s_feat.as<float>(), ctx->stream));
+                b.n = n_used;
+                b.planes = hdr ? nullptr : ctx->s_planes.as<uint4>();
+                b.stride = hdr ? 0 : n_used;
+                b.feat = ctx->s_feat.as<float>();
+            } else if (!hdr && attach_palette_form(ctx, b, in_dev[t], src.bc_format, channels)) {
+                return 1;
+            }
+            uint32_t rounds = 0;
+            if (run_seeding(ctx, b, K, dr, hdr, stats ? &rounds : nullptr)) return 1;
+            seed_rounds += rounds;
+            // seeds -> centroid rows: the feature row (SAD: the pixel row) of the chosen block (:324-326, :388-389, :556-558)
+            LAUNCH(launch_gather_rows_f32(b.feat, ctx->seed_idx.as<uint32_t>(), K, 64, cent_t(t), ctx->stream));
+        }
+        if (n_rows) {
+            const uint32_t* rows = sampling ? ctx->s_rows.as<uint32_t>() + row_first : ctx->bt_rows.as<uint32_t>();
+            LAUNCH(launch_gather_blocks(all.planes, all.stride, all.feat, rows, n_rows, channels, planes_t(t), nl, feat_t(t), ctx->stream));
+            if (!sad) LAUNCH(launch_max_abs(feat_t(t), n_rows * 64, maxabs_d + t, ctx->stream));
+        }
+    }
+    if (ctx->comm && ctx->nccl.all_reduce_sum_i64(ctx->comm, ctx->bt_cent.as<long long>(), T * (size_t)K * 32, ctx->stream))
+        return ctx->fail("ncclAllReduce(seed rows) failed");
+    if (ctx->comm && ctx->nccl.all_reduce_max_u32(ctx->comm, maxabs_d, T, ctx->stream)) return ctx->fail("ncclAllReduce(max) failed");
+    uint32_t* h_words = ctx->h_small + 64;
+    CK(cudaMemcpyAsync(h_words, maxabs_d, T * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    std::vector<int> shift(T, 0);   // SAD: exact integer sums
+    for (size_t t = 0; t < T && !sad; ++t) {
+        float m;
+        std::memcpy(&m, h_words + t, 4);
+        shift[t] = fixed_shift(n_used, m);
+    }
+    for (size_t t = 0; t < T && tensor; ++t)
+        if (tc_prepare_view(ctx, feat_t(t), n_rows, views[t])) return 1;
+    const int t1 = tm.mark();
+
+    // ---- Lloyd, all textures in lock step ------------------------------------------------------------------------
+    uint32_t* flags = ctx->small.as<uint32_t>();
+    uint32_t* ctl_d = maxabs_d + ((2 * T + 31) & ~(size_t)31);   // [T][3]: stop, passes, empty clusters
+    uint32_t* tflags_d = ctl_d + 3 * T;                          // [T][4]: changed, empty, reseeds, spare
+    uint32_t* sticky_d = tflags_d + 4 * T;
+    std::vector<uint32_t> passes(T, 0);
+    uint32_t reseeds_async = 0;
+    if (ctx->comm) {  // the seeds, should the pass loop have to be redone synchronously
+        CK(ctx->bt_cent0.ensure(T * (size_t)K * 256));
+        CK(cudaMemcpyAsync(ctx->bt_cent0.p, ctx->bt_cent.p, T * (size_t)K * 256, cudaMemcpyDeviceToDevice, ctx->stream));
+    }
+    auto reset_state = [&]() -> int {
+        CK(cudaMemsetAsync(ctx->bt_assign.p, 0, T * nl * 4, ctx->stream));  // assignments(numBlocks, 0)
+        CK(cudaMemsetAsync(flags + F_RESEEDS, 0, 4, ctx->stream));
+        CK(cudaMemsetAsync(flags + F_PAIRS, 0, 8, ctx->stream));
+        CK(cudaMemsetAsync(ctl_d, 0, (7 * T + 1) * 4, ctx->stream));
+        CK(cudaMemsetAsync(flags + F_AMB, 0, 8, ctx->stream));
+        ctx->reseeds_sharded = 0;
+        return 0;
+    };
+    // one texture's assignment + partial sums of a pass
+    auto assign_and_sum = [&](size_t t, uint32_t* fl, const uint32_t* stop) -> int {
+        if (sad) {
+            LAUNCH(launch_sad_pack(cent_t(t), K, channels, centpx_t(t), ctx->stream));
+            LAUNCH(launch_sad_assign(planes_t(t), nl, n_rows, channels, centpx_t(t), K, assign_t(t), errors_t(t), fl, stop, ctx->stream));
+        } else if (assign_blocks(ctx, feat_t(t), n_rows, cent_t(t), K, cfg->assign_mode, assign_t(t), tensor ? nullptr : errors_t(t), fl, stop,
+                                 tensor ? &views[t] : nullptr)) {
+            return 1;
+        }
+        LAUNCH(launch_accumulate(feat_t(t), n_rows, assign_t(t), K, shift[t], acc_t(t), fl, stop, ctx->stream));
+        return 0;
+    };
+    auto finalize = [&](size_t t, uint32_t* fl, const uint32_t* stop) -> int {
+        if (sad) LAUNCH(launch_sad_finalize(acc_t(t), K, cent_t(t), fl, stop, ctx->stream));
+        else LAUNCH(launch_finalize_centroids(acc_t(t), K, shift[t], cent_t(t), fl, stop, ctx->stream));
+        return 0;
+    };
+    auto run_async = [&](bool* redo) -> int {
+        *redo = false;
+        if (reset_state()) return 1;
+        for (uint32_t iter = 0; iter < cfg->max_iterations; ++iter) {
+            CK(cudaMemsetAsync(ctx->bt_acc.p, 0, T * acc_words * 8, ctx->stream));
+            for (size_t t = 0; t < T; ++t)
+                if (assign_and_sum(t, tflags_d + 4 * t, ctl_d + 3 * t)) return 1;
+            if (ctx->comm && ctx->nccl.all_reduce_sum_i64(ctx->comm, ctx->bt_acc.as<long long>(), T * acc_words, ctx->stream))
+                return ctx->fail("ncclAllReduce(sum) failed");
+            LAUNCH(launch_lloyd_control_batch(ctx->bt_acc.as<long long>(), acc_words, (uint32_t)T, K, iter, break_after, tflags_d, 4u, ctl_d,
+                                              ctx->comm ? sticky_d : nullptr, ctx->stream));
+            for (size_t t = 0; t < T; ++t) {
+                const uint32_t* stop = ctl_d + 3 * t;
+                if (tensor && !ctx->comm)
+                    LAUNCH(launch_exact_errors(feat_t(t), n_rows, cent_t(t), assign_t(t), errors_t(t), stop, ctl_d + 3 * t + 2, ctx->stream));
+                if (finalize(t, tflags_d + 4 * t, stop)) return 1;
+                if (!ctx->comm)
+                    LAUNCH(launch_reseed_empty(feat_t(t), n_rows, errors_t(t), acc_t(t), K, cent_t(t), tflags_d + 4 * t, stop, ctx->stream));
+            }
+            if ((iter == 3 || iter == 7 || iter == 15) && iter + 1 < cfg->max_iterations) {  // all converged / redo needed?
+                CK(cudaMemcpyAsync(h_words, ctl_d, (7 * T + 1) * 4, cudaMemcpyDeviceToHost, ctx->stream));
+                CK(cudaStreamSynchronize(ctx->stream));
+                bool all_stopped = true;
+                for (size_t t = 0; t < T; ++t) all_stopped = all_stopped && h_words[3 * t] != 0;
+                if (all_stopped || h_words[7 * T]) break;
+            }
+        }
+        CK(cudaMemcpyAsync(h_words, ctl_d, (7 * T + 1) * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+        if (h_words[7 * T]) {
+            *redo = true;
+            return 0;
+        }
+        for (size_t t = 0; t < T; ++t) {
+            passes[t] = h_words[3 * t + 1];
+            reseeds_async += h_words[3 * T + 4 * t + 2];
+        }
+        return 0;
+    };
+    // host-driven loop (an empty cluster on a rank-sharded row set: the reseed needs the global first maximum)
+    auto run_sync = [&]() -> int {
+        if (reset_state()) return 1;
+        if (ctx->comm) CK(cudaMemcpyAsync(ctx->bt_cent.p, ctx->bt_cent0.p, T * (size_t)K * 256, cudaMemcpyDeviceToDevice, ctx->stream));
+        CK(cudaMemsetAsync(ctx->bt_acc.p, 0, T * acc_words * 8, ctx->stream));
+        std::vector<char> active(T, 1);
+        std::fill(passes.begin(), passes.end(), 0u);
+        size_t n_active = T;
+        for (uint32_t iter = 0; iter < cfg->max_iterations && n_active; ++iter) {
+            for (size_t t = 0; t < T; ++t) {
+                if (!active[t]) continue;
+                CK(cudaMemsetAsync(flags, 0, 8, ctx->stream));  // changed, empty
+                CK(cudaMemsetAsync(acc_t(t), 0, acc_words * 8, ctx->stream));
+                if (assign_and_sum(t, flags, nullptr)) return 1;
+                ++passes[t];
+            }
+            if (ctx->comm && ctx->nccl.all_reduce_sum_i64(ctx->comm, ctx->bt_acc.as<long long>(), T * acc_words, ctx->stream))
+                return ctx->fail("ncclAllReduce(sum) failed");
+            for (size_t t = 0; t < T; ++t)
+                if (active[t]) LAUNCH(launch_count_empty(acc_t(t), K, empty_d + t, ctx->stream));
+            CK(cudaMemcpy2DAsync(h_words, 8, ctx->bt_acc.as<long long>() + (size_t)K * 65, acc_words * 8, 8, T, cudaMemcpyDeviceToHost,
+                                 ctx->stream));
+            CK(cudaMemcpyAsync(h_words + 2 * T, empty_d, T * 4, cudaMemcpyDeviceToHost, ctx->stream));
+            CK(cudaStreamSynchronize(ctx->stream));
+            for (size_t t = 0; t < T; ++t) {
+                if (!active[t]) continue;
+                long long changed;
+                std::memcpy(&changed, h_words + 2 * t, 8);
+                const uint32_t n_empty = h_words[2 * T + t];
+                if (!changed && iter > break_after) {  // src/vq_encoder.cpp:341, :395, :572
+                    active[t] = 0;
+                    --n_active;
+                    continue;
+                }
+                if (tensor && n_empty)  // errors[i] = distance to the assigned centroid, before the update
+                    LAUNCH(launch_exact_errors(feat_t(t), n_rows, cent_t(t), assign_t(t), errors_t(t), nullptr, nullptr, ctx->stream));
+                CK(cudaMemsetAsync(flags + F_EMPTY, 0, 4, ctx->stream));
+                if (finalize(t, flags, nullptr)) return 1;
+                if (!n_empty) continue;
+                if (!ctx->comm) {
+                    LAUNCH(launch_reseed_empty(feat_t(t), n_rows, errors_t(t), acc_t(t), K, cent_t(t), flags, nullptr, ctx->stream));
+                } else {
+                    Blocks mine;
+                    mine.n = n_rows;
+                    mine.ch = channels;
+                    mine.feat = feat_t(t);
+                    if (reseed_sharded(ctx, mine, row_first, K, cent_t(t), errors_t(t), acc_t(t), flags)) return 1;
+                }
+            }
+        }
+        return 0;
+    };
+    bool redo = debug_opts().lloyd_sync;
+    if (!redo && run_async(&redo)) return 1;
+    if (redo && run_sync()) return 1;
+    const int t2 = tm.mark();
+
+    // ---- centroids -> pixels / floats, final index map of this rank's block range (QuantizeBlocks[HDR]) ----------------
+    for (size_t t = 0; t < T; ++t) {
+        if (sad) LAUNCH(launch_sad_pack(cent_t(t), K, channels, centpx_t(t), ctx->stream));   // the centroids are pixel blocks already
+        else if (hdr) LAUNCH(launch_oklab_to_floats(cent_t(t), K, channels, reinterpret_cast<float*>(centpx_t(t)), ctx->stream));
+        else LAUNCH(launch_oklab_to_pixels(cent_t(t), K, channels, centpx_t(t), ctx->stream));
+        Blocks shard;
+        shard.n = n_local;
+        shard.ch = channels;
+        if (!sampling) {   // the Lloyd rows are this rank's blocks
+            shard.planes = planes_t(t);
+            shard.stride = nl;
+            shard.feat = feat_t(t);
+        } else if (n_local) {
+            if (decode_whole(t)) return 1;
+            CK(ctx->s_feat.ensure(n_local * 256));
+            if (sad) CK(ctx->s_planes.ensure(n_local * 16 * channels));
+            LAUNCH(launch_gather_blocks(hdr ? nullptr : ctx->planes.as<uint4>(), n_total, ctx->feat.as<float>(), ctx->bt_rows.as<uint32_t>(), n_local,
+                                        channels, sad ? ctx->s_planes.as<uint4>() : nullptr, n_local, ctx->s_feat.as<float>(), ctx->stream));
+            shard.planes = sad ? ctx->s_planes.as<uint4>() : nullptr;
+            shard.stride = n_local;
+            shard.feat = ctx->s_feat.as<float>();
+        }
+        ctx->tc_feat = nullptr;   // the operand cache is keyed on the feature pointer: these rows are new
+        if (n_local && quantize_device(ctx, shard, centpx_t(t), K, hdr, cfg->assign_mode, sad ? YUPVQ_METRIC_SAD : YUPVQ_METRIC_OKLAB)) return 1;
+        if (out_centroids && from_device(ctx, out_centroids[t], centpx_t(t), cpx_bytes)) return 1;
+        if (out_indices && n_local && from_device(ctx, out_indices[t], ctx->out_idx.p, n_local * 4)) return 1;
+    }
+    const int t3 = tm.mark();
+    CK(cudaMemcpyAsync(ctx->h_small, flags + F_RESEEDS, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(ctx->h_small + 1, flags + F_PAIRS, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (stats) {
+        stats->n_blocks = (uint32_t)(n_rows * T);
+        stats->codebook_size = K;
+        stats->seed_rounds = seed_rounds;
+        for (size_t t = 0; t < T; ++t) stats->lloyd_passes += passes[t];
+        stats->reseeds = ctx->h_small[0] + ctx->reseeds_sharded + reseeds_async;
+        stats->rerank_blocks = ctx->h_small[1];
+        stats->rerank_overflow = ctx->h_small[2];
+        stats->ms_seed = tm.ms(t0, t1);      // upload, whole decode, seeding of the owned textures, row gather
+        stats->ms_lloyd = tm.ms(t1, t2);
+        stats->ms_quantize = tm.ms(t2, t3);  // incl. centroid conversion and the D2H of the results
+        stats->ms_total = tm.ms(t0, t3);
+        stats->gpu_launches = ctx->launches;
+    }
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
 // Lock-step batch over block shards: T textures of n_total blocks each, this rank
 // holds blocks [first_block, first_block + n_local) of EVERY texture.
 //   phase A  texture-parallel seeding: texture t is decoded whole and seeded on rank t % R only (K-Means++
@@ -1583,8 +1953,16 @@ int yupvq_encode_bcn_batch_sharded(yupvq_ctx* ctx, const uint8_t* const* bc_bloc
     if (n_textures > 4096) return ctx->fail("too many textures in one batch (%zu > 4096)", n_textures);
     if (!bc_supported(bc_format)) return ctx->fail("BC format %d is not supported on the LDR VQ path", bc_format);
     if (first_block + n_local > n_total) return ctx->fail("shard [%zu, %zu) exceeds %zu blocks", first_block, first_block + n_local, n_total);
-    if (cfg->sample_ratio < 1.0f && cfg->sample_ratio > 0.0f) return ctx->fail("fast-mode sampling is not supported on the sharded path");
-    if (cfg->metric != YUPVQ_METRIC_OKLAB) return ctx->fail("the SAD metric is not supported on the sharded path");
+    if ((cfg->sample_ratio < 1.0f && cfg->sample_ratio > 0.0f) || cfg->metric != YUPVQ_METRIC_OKLAB) {
+        // fast-mode sampling / SAD metric: the general lock-step batch (whole textures on every rank)
+        for (size_t t = 0; t < n_textures && shard_only; ++t)
+            if (shard_only[t]) return ctx->fail("fast-mode sampling and the SAD metric need the whole texture on every rank (shard_only[%zu] is set)", t);
+        BatchSrc src;
+        src.data = reinterpret_cast<const void* const*>(bc_blocks);
+        src.bc_format = bc_format;
+        return batch_sharded_general(ctx, src, n_textures, n_total, first_block, n_local, channels, cfg,
+                                     reinterpret_cast<void* const*>(out_pixel_centroids), out_indices, stats);
+    }
     const uint32_t K = cfg->codebook_size;
     const size_t T = n_textures;
     const int R = ctx->comm ? ctx->n_ranks : 1, rank = ctx->comm ? ctx->rank : 0;
@@ -2055,6 +2433,39 @@ int yupvq_encode_bcn_batch_sharded(yupvq_ctx* ctx, const uint8_t* const* bc_bloc
         stats->gpu_launches = ctx->launches;
     }
     return 0;
+}
+
+// HDR images (BASELINE config 4) over the ranks of the communicator: the general lock-step batch above.
+int yupvq_encode_hdr_batch_sharded(yupvq_ctx* ctx, const float* const* images, size_t n_images, uint32_t width, uint32_t height,
+                                   int channels, size_t first_block, size_t n_local, const yupvq_config* cfg,
+                                   float* const* out_float_centroids, uint32_t* const* out_indices, yupvq_stats* stats) {
+    if (!ctx) return 1;
+    Scope scope(ctx->device);
+    init_stats(stats);
+    ctx->launches = 0;
+    ctx->tc_feat = nullptr;
+    ctx->tc_rgb = rgb_layout(channels);
+    const size_t n_total = (size_t)((width + 3) / 4) * ((height + 3) / 4);
+    if (check_cfg(ctx, cfg, n_total, channels)) return 1;
+    if (!images || n_images == 0) return ctx->fail("no images");
+    if (n_images > 4096) return ctx->fail("too many images in one batch (%zu > 4096)", n_images);
+    if (first_block + n_local > n_total) return ctx->fail("shard [%zu, %zu) exceeds %zu blocks", first_block, first_block + n_local, n_total);
+    BatchSrc src;
+    src.hdr = true;
+    src.data = reinterpret_cast<const void* const*>(images);
+    src.width = width;
+    src.height = height;
+    return batch_sharded_general(ctx, src, n_images, n_total, first_block, n_local, channels, cfg,
+                                 reinterpret_cast<void* const*>(out_float_centroids), out_indices, stats);
+}
+
+int yupvq_encode_hdr_sharded(yupvq_ctx* ctx, const float* image, uint32_t width, uint32_t height, int channels, size_t first_block,
+                             size_t n_local, const yupvq_config* cfg, float* out_float_centroids, uint32_t* out_indices,
+                             yupvq_stats* stats) {
+    const float* img[1] = {image};
+    float* cents[1] = {out_float_centroids};
+    uint32_t* idx[1] = {out_indices};
+    return yupvq_encode_hdr_batch_sharded(ctx, img, 1, width, height, channels, first_block, n_local, cfg, cents, idx, stats);
 }
 
 }  // extern "C"
