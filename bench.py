@@ -423,6 +423,7 @@ def run_ours(args, rank, world, local_rank):
                                              f"BuildCodebook+QuantizeBlocks {dt:.2f} s"}
             if world == 1:
                 out["decompress_gather"] = gather_report(solo, torch, dev, pk)
+                out["bcn_encode_gpu"] = bcn_encode_report(solo, torch, dev, pk)
                 out["compress_breakdown"] = compress_report()
             solo.close()
         print(json.dumps(out))
@@ -474,6 +475,47 @@ def compress_report():
     for _ in range(2):   # the second call has a warm device arena
         rep["stages_ms"] = hostapi.compress_timed(img, bc_format=1, quality=QUALITY, max_iterations=MAX_ITER, use_zstd=True,
                                                   threads=threads, seed=SEED)
+    rep["pre_pass_encoder"] = hostapi.last_encoder_name()
+    # the same call with the BC1 pre-pass on the GPU (BCnCompressor::SetGpuEncode(kGpuOn)); host buffers, so
+    # bcn_encode_ms includes the 48 MB image upload and the 8 MB block download
+    hostapi.set_gpu_bcn_encode(1)
+    for _ in range(2):
+        rep["stages_ms_gpu_pre_pass"] = hostapi.compress_timed(img, bc_format=1, quality=QUALITY, max_iterations=MAX_ITER, use_zstd=True,
+                                                               threads=threads, seed=SEED)
+    rep["pre_pass_encoder_gpu"] = hostapi.last_encoder_name()
+    hostapi.set_gpu_bcn_encode(-1)
+    return rep
+
+
+def bcn_encode_report(enc, torch, dev, pk):
+    """the whole-texture BCn pre-pass (src/vq_bcn_compressor.cpp:94 -> src/bcn_compressor.cpp:45) as a CUDA kernel,
+    image and blocks resident in HBM; PSNR of the decoded blocks against Compressonator's on a 1024^2 crop."""
+    from yuptexture_b200 import synth
+    rep = {}
+    for name, fmt, ch, bs in (("bc1_rgb_4096", 1, 3, 8), ("bc3_rgba_4096", 3, 4, 16)):
+        img = synth.ldr_rgb(TEX, TEX, seed=1000) if ch == 3 else synth.ldr_rgba(TEX, TEX, seed=1000)
+        d_img = torch.from_numpy(img).to(dev)
+        d_out = torch.empty(((TEX // 4) ** 2, bs), dtype=torch.uint8, device=dev)
+        best = min(enc.bcn_encode_image_raw(d_img.data_ptr(), TEX, TEX, ch, fmt, int(ch == 3), 128, d_out.data_ptr()) for _ in range(5))
+        gb = (img.nbytes + d_out.numel()) / 1e9
+        rep[name] = {"kernel_ms": best, "gbs": gb / (best * 1e-3), "frac_of_hbm_peak": gb / (best * 1e-3) / pk["hbm_gbs"],
+                     "note": "ALU-bound (endpoint search), not HBM-bound"}
+        try:
+            from oracle import orcbind, refbind
+            if refbind.available():
+                crop = np.ascontiguousarray(img[:1024, :1024])
+                src = synth.image_to_blocks(crop).reshape(-1, 16 * ch)
+                if ch == 3:
+                    src = src.reshape(-1, 16, 3)[:, :, ::-1].reshape(-1, 48)   # Compressonator reads RGB_888 red/blue-swapped
+                ours, _ = enc.bcn_encode_image(crop, fmt)
+                t0 = time.perf_counter()
+                theirs = refbind.bcn_encode(crop, fmt, quality=1.0, threads=os.cpu_count() or 1)
+                t_cmp = time.perf_counter() - t0
+                rep[name]["psnr_db_gpu_1024_crop"] = float(synth.psnr_u8(orcbind.decode_bcn(ours, fmt, ch), src))
+                rep[name]["psnr_db_compressonator_1024_crop"] = float(synth.psnr_u8(orcbind.decode_bcn(theirs, fmt, ch), src))
+                rep[name]["compressonator_ms_1024_crop"] = t_cmp * 1e3
+        except Exception as e:   # the checker is optional here
+            rep[name]["psnr_check"] = "unavailable: %s" % e
     return rep
 
 

@@ -183,6 +183,29 @@ YUPVQ_API int yupvq_update_centroids(yupvq_ctx* ctx, const float* features, size
 YUPVQ_API int yupvq_gather_codebook(yupvq_ctx* ctx, const uint8_t* codebook, uint32_t n_entries, uint32_t block_size,
                                     const uint32_t* indices, size_t n_blocks, uint8_t* out_bc_blocks);
 
+/* ---- N4: the whole-texture BCn pre-pass on the GPU ---------------------------------------------- */
+
+/* BCnCompressor::Compress, src/bcn_compressor.cpp:45-116 (called at src/vq_bcn_compressor.cpp:94), for BC1, BC3, BC4
+ * and BC5: image (height x width x channels bytes, row-major, host or device) -> ceil(w/4) * ceil(h/4) blocks in
+ * row-major block order (host or device).  The reference hands this stage to the closed-source Compressonator
+ * encoders; the blocks written here are not bit-identical to its output but decode to at least its PSNR
+ * (tests/test_gpu_bcn_encode.py).  swap_rb != 0 encodes a red/blue-swapped view of a 3- or 4-channel source:
+ * Compressonator reads CMP_FORMAT_RGB_888 sources that way, so the reference's VQ path (flipRGB == false) corresponds
+ * to swap_rb = (channels == 3) and its bypass path (flipRGB == true, :61-76) to swap_rb = 0.  alpha_threshold: BC1 with
+ * a 4-channel source puts texels with alpha below it on the transparent entry (CMP_CompressOptions::nAlphaThreshold,
+ * :103-107).  out_ms_kernel (may be NULL): CUDA-event time of the encode kernel. */
+YUPVQ_API int yupvq_bcn_encode_supported(int bc_format);
+YUPVQ_API int yupvq_bcn_encode_image(yupvq_ctx* ctx, const uint8_t* image, uint32_t width, uint32_t height, int channels,
+                                     int bc_format, int swap_rb, int alpha_threshold, uint8_t* out_bc_blocks,
+                                     float* out_ms_kernel);
+/* Pre-pass + VQ in one call (VQBCnCompressor::Compress, src/vq_bcn_compressor.cpp:94-150, without the host-side
+ * centroid encodes and container): the BCn blocks stay in HBM between the encoder and yupvq_encode_bcn's decode.
+ * out_bc_blocks may be NULL (the VQ path does not need them on the host). */
+YUPVQ_API int yupvq_compress_image(yupvq_ctx* ctx, const uint8_t* image, uint32_t width, uint32_t height, int channels,
+                                   int bc_format, int swap_rb, int alpha_threshold, const yupvq_config* cfg,
+                                   uint8_t* out_bc_blocks, uint8_t* out_pixel_centroids, uint32_t* out_indices,
+                                   yupvq_stats* stats, float* out_ms_bcn_encode);
+
 /* ---- multi-GPU (one process per GPU) -------------------------------------------- */
 
 /* NCCL bootstrap: rank 0 calls yupvq_comm_unique_id, the host runtime (torch.distributed, MPI, a

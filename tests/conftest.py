@@ -8,6 +8,10 @@ ROOT = os.path.normpath(os.path.join(os.path.dirname(os.path.abspath(__file__)),
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
+HERE = os.path.dirname(os.path.abspath(__file__))
+if HERE not in sys.path:
+    sys.path.insert(0, HERE)   # test-side helpers (bcnenc_host.py)
+
 GOLDEN = os.path.join(ROOT, "tests", "golden")
 
 

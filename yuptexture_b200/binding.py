@@ -74,6 +74,10 @@ def lib():
         L.yupvq_seed_hdr.argtypes = [_vp, _vp, C.c_size_t, C.c_uint32, C.c_uint64, _vp, C.POINTER(C.c_uint32)]
         L.yupvq_update_centroids.argtypes = [_vp, _vp, C.c_size_t, _vp, _vp, C.c_uint32, _vp, _vp]
         L.yupvq_gather_codebook.argtypes = [_vp, _vp, C.c_uint32, C.c_uint32, _vp, C.c_size_t, _vp]
+        L.yupvq_bcn_encode_supported.argtypes = [C.c_int]
+        L.yupvq_bcn_encode_image.argtypes = [_vp, _vp, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.c_int, C.c_int, _vp, C.POINTER(C.c_float)]
+        L.yupvq_compress_image.argtypes = [_vp, _vp, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.c_int, C.c_int, cfgp, _vp, _vp, _vp, stp,
+                                           C.POINTER(C.c_float)]
         L.yupvq_profile.argtypes = [_vp, C.c_int]
         L.yupvq_profile_read.argtypes = [_vp, C.POINTER(C.c_float), C.POINTER(C.c_uint32)]
         L.yupvq_comm_unique_id.argtypes = [_vp, _vp]
@@ -369,6 +373,44 @@ class Encoder:
         """yupvq_gather_codebook on raw (device or host) pointers."""
         self._ck(self._L.yupvq_gather_codebook(self._ctx, _vp(codebook_ptr), n_entries, block_size, _vp(indices_ptr), n_blocks,
                                                _vp(out_ptr)), "yupvq_gather_codebook")
+
+    # ---- N4: whole-texture BCn pre-pass on the GPU
+    def bcn_encode_image(self, img, fmt, swap_rb=None, alpha_threshold=128):
+        """img: (H, W, ch) uint8 -> (BCn bytes as (n_blocks, blockSize) uint8, kernel ms).  swap_rb defaults to the
+        reference's VQ-path behaviour (3-channel sources are read red/blue-swapped by Compressonator)."""
+        img = _c(img, np.uint8)
+        h, w, ch = img.shape
+        swap = (ch == 3) if swap_rb is None else bool(swap_rb)
+        bs = 8 if fmt in (BC["BC1"], BC["BC4"]) else 16
+        out = np.empty((((w + 3) // 4) * ((h + 3) // 4), bs), np.uint8)
+        ms = C.c_float(0)
+        self._ck(self._L.yupvq_bcn_encode_image(self._ctx, _ptr(img), w, h, ch, fmt, int(swap), alpha_threshold, _ptr(out), C.byref(ms)),
+                 "yupvq_bcn_encode_image")
+        return out, ms.value
+
+    def bcn_encode_image_raw(self, img_ptr, w, h, ch, fmt, swap_rb, alpha_threshold, out_ptr):
+        """yupvq_bcn_encode_image on raw (device or host) pointers; returns the kernel's CUDA-event time in ms."""
+        ms = C.c_float(0)
+        self._ck(self._L.yupvq_bcn_encode_image(self._ctx, _vp(img_ptr), w, h, ch, fmt, int(swap_rb), alpha_threshold, _vp(out_ptr),
+                                                C.byref(ms)), "yupvq_bcn_encode_image")
+        return ms.value
+
+    def compress_image(self, img, fmt, cfg, swap_rb=None, alpha_threshold=128, want_bc=False):
+        """Pre-pass + VQ in one call: -> (pixel centroids, indices, stats, BCn encode ms, BCn bytes or None)."""
+        img = _c(img, np.uint8)
+        h, w, ch = img.shape
+        swap = (ch == 3) if swap_rb is None else bool(swap_rb)
+        n = ((w + 3) // 4) * ((h + 3) // 4)
+        bs = 8 if fmt in (BC["BC1"], BC["BC4"]) else 16
+        bc = np.empty((n, bs), np.uint8) if want_bc else None
+        cent = np.empty((cfg.codebook_size, 16 * ch), np.uint8)
+        idx = np.empty(n, np.uint32)
+        st = Stats()
+        ms = C.c_float(0)
+        self._ck(self._L.yupvq_compress_image(self._ctx, _ptr(img), w, h, ch, fmt, int(swap), alpha_threshold, C.byref(cfg),
+                                              _ptr(bc) if want_bc else None, _ptr(cent), _ptr(idx), C.byref(st), C.byref(ms)),
+                 "yupvq_compress_image")
+        return cent, idx, st, ms.value, bc
 
     # ---- multi-GPU
     def comm_unique_id(self):

@@ -32,7 +32,7 @@ const DebugOpts& debug_opts() {
         o.seed_no_tri = on("YUPVQ_SEED_NO_TRI");
         o.seed_no_pal = on("YUPVQ_SEED_NO_PAL");
         o.seed_no_smem = on("YUPVQ_SEED_NO_SMEM");
-        o.seed_no_cluster = on("YUPVQ_SEED_NO_CLUSTER");
+        o.seed_leader = on("YUPVQ_SEED_LEADER") || !on("YUPVQ_SEED_ALLSCAN");   // all-scan is opt-in until its GPU validation lands
         o.lloyd_sync = on("YUPVQ_LLOYD_SYNC");
         o.no_delta = on("YUPVQ_NO_DELTA");
         o.no_rgb48 = on("YUPVQ_NO_RGB48");
@@ -88,6 +88,7 @@ struct yupvq_ctx {
 
     // device arena (grow-only, reused across calls)
     DevBuf in_bytes;    // staged input (BCn bytes / pixel blocks / float image or blocks)
+    DevBuf img_in, bc_enc;  // N4: staged source image and the BCn blocks the GPU encoder writes
     DevBuf planes;      // uint8 pixel planes (ch planes of uint4)
     DevBuf pal5;        // BC1 input, 3 channels: palette form of the blocks for the seeding (5 planes of uint32)
     DevBuf feat;        // N x 64 fp32 features
@@ -873,7 +874,7 @@ void yupvq_destroy(yupvq_ctx* ctx) {
                       &ctx->errors, &ctx->cent, &ctx->acc, &ctx->cent_px, &ctx->cent_feat, &ctx->out_idx,
                       &ctx->tc_a, &ctx->tc_xnorm, &ctx->tc_small, &ctx->tc_b, &ctx->tc_bx, &ctx->tc_cand, &ctx->tc_amb,
                       &ctx->bt_feat, &ctx->bt_tca, &ctx->bt_xnorm, &ctx->bt_tcsmall, &ctx->bt_assign, &ctx->bt_errors,
-                      &ctx->bt_cent, &ctx->bt_acc, &ctx->bt_misc, &ctx->bt_centpx, &ctx->bt_cent0, &ctx->tc_chg, &ctx->delta_ctl, &ctx->bt_acc_local, &ctx->pal5, &ctx->tail_scratch, &ctx->bt_planes, &ctx->bt_in, &ctx->bt_rows};
+                      &ctx->bt_cent, &ctx->bt_acc, &ctx->bt_misc, &ctx->bt_centpx, &ctx->bt_cent0, &ctx->tc_chg, &ctx->delta_ctl, &ctx->bt_acc_local, &ctx->pal5, &ctx->tail_scratch, &ctx->bt_planes, &ctx->bt_in, &ctx->bt_rows, &ctx->img_in, &ctx->bc_enc};
     for (DevBuf* b : bufs) b->release();
     if (ctx->h_small) cudaFreeHost(ctx->h_small);
     for (auto& ev : ctx->ev)
@@ -1518,6 +1519,72 @@ int yupvq_gather_codebook(yupvq_ctx* ctx, const uint8_t* codebook, uint32_t n_en
     if (!out_is_dev && from_device(ctx, out_bc_blocks, out_dev, n_blocks * block_size)) return 1;
     CK(cudaStreamSynchronize(ctx->stream));
     return 0;
+}
+
+// ---- N4: whole-texture BCn encode on the GPU (bcn_encode.cu) ---------------------------------------------------
+int yupvq_bcn_encode_supported(int bc_format) { return bcn_encode_supported(bc_format) ? 1 : 0; }
+
+namespace {
+// image (host or device) -> BCn blocks in `out_dev` (device); CUDA-event time of the kernel alone in *out_ms
+int bcn_encode_to_device(yupvq_ctx* ctx, const uint8_t* image, uint32_t width, uint32_t height, int channels, int bc_format,
+                         int swap_rb, int alpha_threshold, uint8_t* out_dev, float* out_ms) {
+    if (!image) return ctx->fail("image is null");
+    if (width == 0 || height == 0) return ctx->fail("empty image");
+    if (channels < 1 || channels > 4) return ctx->fail("channels must be 1..4 (got %d)", channels);
+    if (!bcn_encode_supported(bc_format)) return ctx->fail("BC format %d has no GPU encoder (BC1, BC3, BC4, BC5 do)", bc_format);
+    const void* img_dev = nullptr;
+    if (to_device(ctx, image, (size_t)width * height * channels, ctx->img_in, &img_dev)) return 1;
+    Timer tm(ctx);
+    const int t0 = tm.mark();
+    LAUNCH(launch_bcn_encode(reinterpret_cast<const uint8_t*>(img_dev), width, height, (uint32_t)channels, bc_format, swap_rb ? 1 : 0,
+                             (uint32_t)std::min(std::max(alpha_threshold, 0), 256), out_dev, ctx->stream));
+    const int t1 = tm.mark();
+    if (out_ms) {
+        CK(cudaStreamSynchronize(ctx->stream));
+        *out_ms = tm.ms(t0, t1);
+    }
+    return 0;
+}
+}  // namespace
+
+int yupvq_bcn_encode_image(yupvq_ctx* ctx, const uint8_t* image, uint32_t width, uint32_t height, int channels, int bc_format,
+                           int swap_rb, int alpha_threshold, uint8_t* out_bc_blocks, float* out_ms_kernel) {
+    if (!ctx) return 1;
+    Scope scope(ctx->device);
+    ctx->launches = 0;
+    if (!out_bc_blocks) return ctx->fail("out_bc_blocks is null");
+    const size_t bytes = (size_t)((width + 3) / 4) * ((height + 3) / 4) * bc_block_bytes(bc_format);
+    uint8_t* out_dev = out_bc_blocks;
+    const bool out_is_dev = is_device_ptr(out_bc_blocks);
+    if (!out_is_dev) {
+        CK(ctx->bc_enc.ensure(std::max<size_t>(bytes, 16)));
+        out_dev = ctx->bc_enc.as<uint8_t>();
+    }
+    if (bcn_encode_to_device(ctx, image, width, height, channels, bc_format, swap_rb, alpha_threshold, out_dev, out_ms_kernel)) return 1;
+    if (!out_is_dev && from_device(ctx, out_bc_blocks, out_dev, bytes)) return 1;
+    CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+int yupvq_compress_image(yupvq_ctx* ctx, const uint8_t* image, uint32_t width, uint32_t height, int channels, int bc_format,
+                         int swap_rb, int alpha_threshold, const yupvq_config* cfg, uint8_t* out_bc_blocks,
+                         uint8_t* out_pixel_centroids, uint32_t* out_indices, yupvq_stats* stats, float* out_ms_bcn_encode) {
+    if (!ctx) return 1;
+    {
+        Scope scope(ctx->device);
+        const size_t bytes = (size_t)((width + 3) / 4) * ((height + 3) / 4) * bc_block_bytes(bc_format);
+        CK(ctx->bc_enc.ensure(std::max<size_t>(bytes, 16)));
+        ctx->launches = 0;
+        if (bcn_encode_to_device(ctx, image, width, height, channels, bc_format, swap_rb, alpha_threshold, ctx->bc_enc.as<uint8_t>(),
+                                 out_ms_bcn_encode))
+            return 1;
+        if (out_bc_blocks && from_device(ctx, out_bc_blocks, ctx->bc_enc.p, bytes)) return 1;
+    }
+    // the blocks stay in HBM: the VQ stage reads them where the encoder wrote them
+    const size_t n_blocks = (size_t)((width + 3) / 4) * ((height + 3) / 4);
+    const int rc = yupvq_encode_bcn(ctx, ctx->bc_enc.as<uint8_t>(), n_blocks, bc_format, channels, cfg, out_pixel_centroids, out_indices, stats);
+    if (rc == 0 && stats) stats->gpu_launches += 1;
+    return rc;
 }
 
 // ---- multi-GPU -------------------------------------------------------------------------------------------

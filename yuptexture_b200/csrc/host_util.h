@@ -17,7 +17,7 @@ struct DebugOpts {
     bool seed_no_tri = false;        // YUPVQ_SEED_NO_TRI         HDR triangle-inequality skip off
     bool seed_no_pal = false;        // YUPVQ_SEED_NO_PAL         BC1 palette-form seeding off (pixel-plane kernel)
     bool seed_no_smem = false;       // YUPVQ_SEED_NO_SMEM        no shared-memory resident segments in the pixel-plane kernel
-    bool seed_no_cluster = false;    // YUPVQ_SEED_NO_CLUSTER     palette seeding without the thread-block-cluster exchange
+    bool seed_leader = false;        // YUPVQ_SEED_LEADER         palette seeding with the leader-CTA / mailbox protocol (round 1)
     bool lloyd_sync = false;         // YUPVQ_LLOYD_SYNC          host-synchronous Lloyd loop
     bool no_delta = false;           // YUPVQ_NO_DELTA            full accumulate on every pass
     bool no_rgb48 = false;           // YUPVQ_NO_RGB48            64-column tensor operands for textures without alpha

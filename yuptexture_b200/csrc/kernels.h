@@ -235,6 +235,13 @@ struct TailArgs {
 };
 cudaError_t launch_lloyd_tail(const TailArgs& args, cudaStream_t s);
 
+// ---- bcn_encode.cu : N4, whole-texture BCn encoders (BC1, BC3, BC4, BC5) ---------------------------------------
+// image: height x width x channels bytes, row-major; out: ceil(w/4) * ceil(h/4) blocks in row-major block order.
+// swap_rb: encode a red/blue-swapped view (3- and 4-channel sources); alpha_threshold: BC1 punch-through (4 channels).
+bool bcn_encode_supported(int fmt);
+cudaError_t launch_bcn_encode(const uint8_t* image, uint32_t width, uint32_t height, uint32_t channels, int fmt, int swap_rb,
+                              uint32_t alpha_threshold, uint8_t* out, cudaStream_t s);
+
 // ---- sad.cu : A21, SAD-metric Lloyd (all integer, bit-exact) ---------------------------------------------
 // argmin over K pixel-block centroids (K x 16*ch bytes) of sum |a - b|; errors[i] = the minimum (as float)
 cudaError_t launch_sad_assign(const uint4* planes, size_t stride, size_t n, int ch, const uint8_t* cent_px, uint32_t K,

@@ -7,6 +7,7 @@
 #include <dlfcn.h>
 
 #include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <cmath>
 #include <cstdio>
@@ -289,10 +290,51 @@ const char* BCnCompressor::CodecName() {
     return name.c_str();
 }
 
+namespace {
+std::atomic<int> g_gpu_encode{BCnCompressor::kGpuAuto};
+thread_local const char* t_last_encoder = "none";
+
+bool gpu_encode_wanted(bool have_codec) {
+    int mode = g_gpu_encode.load(std::memory_order_relaxed);
+    if (mode == BCnCompressor::kGpuAuto) {
+        static const int env_mode = [] {
+            const char* e = std::getenv("YUPTEXTURE_GPU_BCN");
+            return e ? (std::atoi(e) != 0 ? (int)BCnCompressor::kGpuOn : (int)BCnCompressor::kGpuOff) : (int)BCnCompressor::kGpuAuto;
+        }();
+        mode = env_mode;
+    }
+    return mode == BCnCompressor::kGpuOn || (mode == BCnCompressor::kGpuAuto && !have_codec);
+}
+
+yupvq_ctx* codec_ctx();
+extern std::mutex g_codec_ctx_mutex;
+}  // namespace
+
+void BCnCompressor::SetGpuEncode(GpuEncode mode) { g_gpu_encode.store((int)mode, std::memory_order_relaxed); }
+const char* BCnCompressor::LastEncoderName() { return t_last_encoder; }
+
 std::vector<uint8_t> BCnCompressor::Compress(const uint8_t* inData, uint32_t width, uint32_t height, uint32_t channelCount,
                                              BCFormat format, int numThreads, float quality, uint8_t alphaThreshold, bool flipRGB) {
-    if (const Codec c = current_codec(); c.compress)
+    const Codec c = current_codec();
+    // N4: the pre-pass on the GPU.  Compressonator reads 3-channel sources red/blue-swapped (the reference compensates
+    // only on its VQ-bypass path, flipRGB == true: src/bcn_compressor.cpp:61-76), so the same view is encoded here.
+    if (inData && width && height && channelCount >= 1 && channelCount <= 4 && yupvq_bcn_encode_supported((int)format) &&
+        gpu_encode_wanted((bool)c.compress)) {
+        const size_t bytes = (size_t)((width + 3) / 4) * ((height + 3) / 4) * BCBlockSize::GetSize(format);
+        std::vector<uint8_t> out(bytes);
+        std::lock_guard<std::mutex> lock(g_codec_ctx_mutex);
+        if (yupvq_bcn_encode_image(codec_ctx(), inData, width, height, (int)channelCount, (int)format, channelCount == 3 && !flipRGB ? 1 : 0,
+                                   alphaThreshold, out.data(), nullptr) == 0) {
+            t_last_encoder = "gpu (yupvq_bcn_encode_image)";
+            return out;
+        }
+        return {};   // the reference returns an empty vector on failure (src/bcn_compressor.cpp:111)
+    }
+    if (c.compress) {
+        t_last_encoder = "codec";
         return c.compress(inData, width, height, channelCount, format, numThreads, quality, alphaThreshold, flipRGB);
+    }
+    t_last_encoder = "built-in (cpu)";
     if (!inData || width == 0 || height == 0 || channelCount < 1 || channelCount > 4) return {};
     if (format != BCFormat::BC1 && format != BCFormat::BC3 && format != BCFormat::BC4 && format != BCFormat::BC5 && format != BCFormat::BC7)
         return {};  // the reference returns an empty vector on failure (src/bcn_compressor.cpp:111)
@@ -350,7 +392,7 @@ yupvq_ctx* create_ctx(int device) {
     throw std::runtime_error(std::string(what) + ": " + yupvq_last_error(c));
 }
 
-// one process-wide context for the stateless BCnCompressor::Decompress
+// one process-wide context for the stateless BCnCompressor::Compress (GPU pre-pass) / Decompress
 yupvq_ctx* codec_ctx() {
     static yupvq_ctx* c = create_ctx(default_device());
     return c;
@@ -785,6 +827,11 @@ extern "C" {
 YUPTEXTURE_API const char* yuptexture_codec_name(void) { return BCnCompressor::CodecName(); }
 
 YUPTEXTURE_API int yuptexture_load_codec(const char* path) { return BCnCompressor::LoadCodecLibrary(path) ? 0 : 1; }
+// -1 auto, 0 off, 1 on (BCnCompressor::SetGpuEncode); the encoder the calling thread's last Compress used
+YUPTEXTURE_API void yuptexture_set_gpu_bcn_encode(int mode) {
+    BCnCompressor::SetGpuEncode(mode < 0 ? BCnCompressor::kGpuAuto : (mode ? BCnCompressor::kGpuOn : BCnCompressor::kGpuOff));
+}
+YUPTEXTURE_API const char* yuptexture_last_encoder_name(void) { return BCnCompressor::LastEncoderName(); }
 
 YUPTEXTURE_API int yuptexture_compress_timed(const void* image, int is_hdr, uint32_t width, uint32_t height, uint32_t channels,
                                              const CompressionParams* params, uint64_t seed, double out_ms[5], size_t* out_bytes,

@@ -32,6 +32,8 @@ def lib():
         L = C.CDLL(LIB_PATH)
         L.yuptexture_codec_name.restype = C.c_char_p
         L.yuptexture_load_codec.argtypes = [C.c_char_p]
+        L.yuptexture_set_gpu_bcn_encode.argtypes = [C.c_int]
+        L.yuptexture_last_encoder_name.restype = C.c_char_p
         L.yuptexture_compress_timed.argtypes = [C.c_void_p, C.c_int, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(CompressionParams),
                                                 C.c_uint64, C.POINTER(C.c_double), C.POINTER(C.c_size_t), C.c_void_p, C.c_size_t,
                                                 C.c_char_p, C.c_size_t]
@@ -43,6 +45,15 @@ def lib():
 
 def codec_name():
     return lib().yuptexture_codec_name().decode()
+
+
+def set_gpu_bcn_encode(mode):
+    """-1: auto (GPU pre-pass only without a codec), 0: off, 1: on (BCnCompressor::SetGpuEncode)."""
+    lib().yuptexture_set_gpu_bcn_encode(int(mode))
+
+
+def last_encoder_name():
+    return lib().yuptexture_last_encoder_name().decode()
 
 
 def make_params(bc_format=7, quality=0.5, max_iterations=32, use_zstd=True, threads=16, bc_quality=1.0, metric=1, sample_ratio=1.0):
