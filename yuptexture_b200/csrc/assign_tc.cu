@@ -305,6 +305,8 @@ struct MovedList {
     }
 };
 
+static_assert(512 * 96 + 256 * 48 == kThreadsTc2 * 80, "v2 register budgets must add up to the launch allocation (80 per thread)");
+
 template <bool BATCH, bool MW>
 __global__ void __launch_bounds__(MW ? kThreadsTc2 : kThreadsTc, 1)
 assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
@@ -371,8 +373,9 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
     // v2: registers follow the work (setmaxnreg at the head of each role's branch, so the role's code is compiled against
-    // its own budget): 16 epilogue warps hold two 32-column score tiles each (104), the control and merge warpgroups need
-    // little (48 each): 512 x 104 + 256 x 48 = 65536
+    // its own budget): 16 epilogue warps hold two 32-column score tiles each (96), the control and merge warpgroups need
+    // little (48 each).  The pool setmaxnreg moves registers inside is what the CTA got at launch -- 768 threads x 80 --
+    // so the budgets must add up to it: 512 x 96 + 256 x 48 = 61440 (an .inc beyond the pool would wait forever).
     uint16_t* const lists = reinterpret_cast<uint16_t*>(base_ptr + OFF_LIST);   // [2 parity][4 slices][128][kListCap]
     float* const s_max = reinterpret_cast<float*>(base_ptr + OFF_MAX);          // [2 parity][4 slices][128]
     uint8_t* const s_cnt = reinterpret_cast<uint8_t*>(base_ptr + OFF_CNT);      // [2 parity][4 slices][128]
@@ -578,7 +581,7 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
         constexpr int kCols = BN / kSplit;           // columns per thread per stage
         constexpr int kTiles = kCols / 32;           // 32-column register tiles per pass
         static_assert(kTiles == 2, "the unrolled load schedule below is written for two tiles per pass");
-        if (MW) setmaxnreg_inc<104>();
+        if (MW) setmaxnreg_inc<96>();
         const int ew = warp - kEpiBase;
         const int quad = warp & 3;          // TMEM lane quadrant this warp may access (kEpiBase is a multiple of 4 or 2: see r)
         const int slice = ew >> 2;          // which kCols of the stage's 256 columns
