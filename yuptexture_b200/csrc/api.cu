@@ -32,15 +32,15 @@ const DebugOpts& debug_opts() {
         o.seed_no_tri = on("YUPVQ_SEED_NO_TRI");
         o.seed_no_pal = on("YUPVQ_SEED_NO_PAL");
         o.seed_no_smem = on("YUPVQ_SEED_NO_SMEM");
-        o.seed_leader = on("YUPVQ_SEED_LEADER") || !on("YUPVQ_SEED_ALLSCAN");   // all-scan is opt-in until its GPU validation lands
         o.lloyd_sync = on("YUPVQ_LLOYD_SYNC");
         o.no_delta = on("YUPVQ_NO_DELTA");
         o.no_rgb48 = on("YUPVQ_NO_RGB48");
         o.no_split_decode = on("YUPVQ_NO_SPLIT_DECODE");
+        o.no_decode_fuse = on("YUPVQ_NO_DECODE_FUSE");
         o.batch_per_texture = on("YUPVQ_BATCH_PER_TEXTURE");
         o.no_tail_fuse = on("YUPVQ_NO_TAIL_FUSE");
         o.no_overlap = on("YUPVQ_NO_OVERLAP");
-        o.tc_v1 = on("YUPVQ_TC_V1") || !on("YUPVQ_TC_V2");   // v2 is opt-in until its GPU validation lands
+        o.tc_v1 = on("YUPVQ_TC_V1");   // v2 (merge warps) is the default since r02c: 0.143 against 0.177 ms per pass, bit-identical
         if (const char* v = getenv("YUPVQ_ASYNC_DBG")) o.async_dbg = atoi(v);
         return o;
     }();
@@ -104,6 +104,7 @@ struct yupvq_ctx {
     DevBuf bt_feat, bt_tca, bt_xnorm, bt_tcsmall, bt_assign, bt_errors, bt_cent, bt_acc, bt_misc, bt_centpx, bt_cent0, bt_acc_local;
     DevBuf bt_planes, bt_in, bt_rows;   // general lock-step batch: SAD pixel planes, device-resident inputs, row lists
     const float* tc_feat = nullptr;                    // block set the A' buffer was built from
+    const float* maxabs_feat = nullptr;                // block set whose max |x| already sits in small[F_MAXABS] (fused feature pass)
     int tc_rgb = 0;                                    // 1: channels are 1 or 3 (alpha feature constant): 48-column tensor operands
     size_t tc_n = 0;
     uint64_t rerank_pairs = 0;
@@ -479,8 +480,11 @@ int run_lloyd(yupvq_ctx* ctx, const Blocks& b, size_t n_total, uint32_t K, uint3
     ctx->reseeds_sharded = 0;
 
     // fixed-point scale from the data range (deterministic function of the data)
-    CK(cudaMemsetAsync(flags + F_MAXABS, 0, 4, ctx->stream));
-    LAUNCH(launch_max_abs(b.feat, n * 64, flags + F_MAXABS, ctx->stream));
+    if (ctx->maxabs_feat != b.feat) {   // else: the fused feature pass of this call already reduced it (same maximum, same bits)
+        CK(cudaMemsetAsync(flags + F_MAXABS, 0, 4, ctx->stream));
+        LAUNCH(launch_max_abs(b.feat, n * 64, flags + F_MAXABS, ctx->stream));
+    }
+    ctx->maxabs_feat = nullptr;
     CK(cudaMemcpyAsync(ctx->h_small, flags + F_MAXABS, 4, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     float max_abs;
@@ -945,6 +949,7 @@ int yupvq_encode_bcn(yupvq_ctx* ctx, const uint8_t* bc_blocks, size_t n_blocks, 
     init_stats(stats);
     ctx->launches = 0;
     ctx->tc_feat = nullptr;
+    ctx->maxabs_feat = nullptr;
     ctx->tc_rgb = rgb_layout(channels);
     if (check_cfg(ctx, cfg, n_blocks, channels)) return 1;
     if (!bc_supported(bc_format)) return ctx->fail("BC format %d is not supported on the LDR VQ path", bc_format);
@@ -967,12 +972,49 @@ int yupvq_encode_bcn(yupvq_ctx* ctx, const uint8_t* bc_blocks, size_t n_blocks, 
     float ms_late = 0.f;
     int tl0 = -1, tl1e = -1;
     std::function<int()> late;
+    // Fused feature pass (tensor engine): the decode that writes the Oklab features also writes the front-end's A' operand,
+    // |x'| and max |x| -- otherwise three more passes over the 256 MB feature matrix (col_sums, max_abs, prep_blocks).  The
+    // centring row mu must exist before that pass, so it is the mean of the K seed blocks' features instead of the mean of
+    // all blocks: any mu gives the same distances (translation invariance); it only conditions the bf16 split.
+    const bool fuse_operands = split && !sad && !debug_opts().no_decode_fuse && use_tensor(cfg->assign_mode, n_blocks, cfg->codebook_size) &&
+                               (reinterpret_cast<uintptr_t>(bc_dev) & 15u) == 0;
     if (split)
         late = [&]() -> int {
             tl0 = tm.mark();
-            if (sad) LAUNCH(launch_sad_expand(ctx->planes.as<uint4>(), n_blocks, n_blocks, channels, ctx->feat.as<float>(), ctx->stream));
-            else LAUNCH(launch_decode_bcn(reinterpret_cast<const uint8_t*>(bc_dev), n_blocks, bc_format, channels, nullptr, 0,
-                                          ctx->feat.as<float>(), nullptr, ctx->stream));
+            if (sad) {
+                LAUNCH(launch_sad_expand(ctx->planes.as<uint4>(), n_blocks, n_blocks, channels, ctx->feat.as<float>(), ctx->stream));
+            } else if (fuse_operands) {
+                const uint32_t K = cfg->codebook_size;
+                const size_t bs = bc_block_bytes(bc_format);
+                CK(ctx->s_rows.ensure((size_t)K * bs));
+                CK(ctx->cent.ensure((size_t)K * 256));
+                CK(ctx->tc_small.ensure(TC_SMALL_BYTES));
+                CK(ctx->tc_a.ensure(n_blocks * 256));
+                CK(ctx->tc_xnorm.ensure(n_blocks * 4));
+                uint8_t* sm = ctx->tc_small.as<uint8_t>();
+                uint32_t* flags = ctx->small.as<uint32_t>();
+                // the K seed blocks -> their feature rows -> mu
+                LAUNCH(launch_gather_codebook(reinterpret_cast<const uint8_t*>(bc_dev), (uint32_t)n_blocks, (uint32_t)bs, ctx->seed_idx.as<uint32_t>(), K,
+                                              ctx->s_rows.as<uint8_t>(), ctx->stream));
+                LAUNCH(launch_decode_bcn(ctx->s_rows.as<uint8_t>(), K, bc_format, channels, nullptr, 0, ctx->cent.as<float>(), nullptr, ctx->stream));
+                LAUNCH(launch_tc_mean(ctx->cent.as<float>(), K, reinterpret_cast<double*>(sm + TC_SUMS), reinterpret_cast<float*>(sm + TC_MU), ctx->stream));
+                ++ctx->launches;
+                CK(cudaMemsetAsync(flags + F_MAXABS, 0, 4, ctx->stream));
+                DecodeFuse fu;
+                fu.mu = reinterpret_cast<const float*>(sm + TC_MU);
+                fu.a_prime = ctx->tc_a.as<float>();
+                fu.xnorm = ctx->tc_xnorm.as<float>();
+                fu.max_abs_bits = flags + F_MAXABS;
+                fu.rgb = ctx->tc_rgb;
+                LAUNCH(launch_decode_bcn(reinterpret_cast<const uint8_t*>(bc_dev), n_blocks, bc_format, channels, nullptr, 0,
+                                         ctx->feat.as<float>(), nullptr, ctx->stream, &fu));
+                ctx->tc_feat = ctx->feat.as<float>();     // tc_prepare_blocks and run_lloyd's max_abs find their work done
+                ctx->tc_n = n_blocks;
+                ctx->maxabs_feat = ctx->feat.as<float>();
+            } else {
+                LAUNCH(launch_decode_bcn(reinterpret_cast<const uint8_t*>(bc_dev), n_blocks, bc_format, channels, nullptr, 0,
+                                         ctx->feat.as<float>(), nullptr, ctx->stream));
+            }
             tl1e = tm.mark();
             return 0;
         };
@@ -1015,6 +1057,7 @@ int yupvq_encode_hdr(yupvq_ctx* ctx, const float* image, uint32_t width, uint32_
     init_stats(stats);
     ctx->launches = 0;
     ctx->tc_feat = nullptr;
+    ctx->maxabs_feat = nullptr;
     ctx->tc_rgb = rgb_layout(channels);
     const size_t n_blocks = (size_t)((width + 3) / 4) * ((height + 3) / 4);
     if (check_cfg(ctx, cfg, n_blocks, channels)) return 1;
@@ -1091,6 +1134,7 @@ int yupvq_build_codebook(yupvq_ctx* ctx, const uint8_t* pixel_blocks, size_t n_b
     init_stats(stats);
     ctx->launches = 0;
     ctx->tc_feat = nullptr;
+    ctx->maxabs_feat = nullptr;
     ctx->tc_rgb = rgb_layout(channels);
     if (check_cfg(ctx, cfg, n_blocks, channels)) return 1;
     Timer tm(ctx);
@@ -1146,6 +1190,7 @@ int yupvq_quantize_blocks(yupvq_ctx* ctx, const uint8_t* pixel_blocks, size_t n_
     init_stats(stats);
     ctx->launches = 0;
     ctx->tc_feat = nullptr;
+    ctx->maxabs_feat = nullptr;
     ctx->tc_rgb = rgb_layout(channels);
     if (n_blocks == 0) return 0;  // reference returns {} (:449)
     if (channels < 1 || channels > 4) return ctx->fail("channels must be 1..4");
@@ -1192,6 +1237,7 @@ int yupvq_build_codebook_hdr(yupvq_ctx* ctx, const float* float_blocks, size_t n
     init_stats(stats);
     ctx->launches = 0;
     ctx->tc_feat = nullptr;
+    ctx->maxabs_feat = nullptr;
     ctx->tc_rgb = rgb_layout(channels);
     if (n_blocks == 0) return 0;  // reference returns {} (:517)
     if (check_cfg(ctx, cfg, n_blocks, channels)) return 1;
@@ -1230,6 +1276,7 @@ int yupvq_quantize_blocks_hdr(yupvq_ctx* ctx, const float* float_blocks, size_t 
     init_stats(stats);
     ctx->launches = 0;
     ctx->tc_feat = nullptr;
+    ctx->maxabs_feat = nullptr;
     ctx->tc_rgb = rgb_layout(channels);
     if (n_blocks == 0) return 0;  // :631
     if (channels < 1 || channels > 4) return ctx->fail("channels must be 1..4");
@@ -1358,6 +1405,7 @@ int yupvq_assign(yupvq_ctx* ctx, const float* features, size_t n_blocks, const f
     init_stats(stats);
     ctx->launches = 0;
     ctx->tc_feat = nullptr;
+    ctx->maxabs_feat = nullptr;
     ctx->tc_rgb = 0;
     if (n_blocks == 0) return 0;
     const void* f_dev = nullptr;
@@ -1394,6 +1442,7 @@ int yupvq_seed_ldr(yupvq_ctx* ctx, const uint8_t* pixel_blocks, size_t n_blocks,
     Scope scope(ctx->device);
     ctx->launches = 0;
     ctx->tc_feat = nullptr;
+    ctx->maxabs_feat = nullptr;
     ctx->tc_rgb = 0;
     if (channels < 1 || channels > 4) return ctx->fail("channels must be 1..4");
     if (n_blocks == 0 || codebook_size == 0) return ctx->fail("empty input");
@@ -1423,6 +1472,7 @@ int yupvq_seed_hdr(yupvq_ctx* ctx, const float* features, size_t n_blocks, uint3
     Scope scope(ctx->device);
     ctx->launches = 0;
     ctx->tc_feat = nullptr;
+    ctx->maxabs_feat = nullptr;
     ctx->tc_rgb = 0;
     if (n_blocks == 0 || codebook_size == 0) return ctx->fail("empty input");
     const void* f_dev = nullptr;
@@ -1447,6 +1497,7 @@ int yupvq_update_centroids(yupvq_ctx* ctx, const float* features, size_t n_block
     Scope scope(ctx->device);
     ctx->launches = 0;
     ctx->tc_feat = nullptr;
+    ctx->maxabs_feat = nullptr;
     ctx->tc_rgb = 0;
     const uint32_t K = codebook_size;
     if (n_blocks == 0 || K == 0) return ctx->fail("empty input");
@@ -1501,6 +1552,7 @@ int yupvq_gather_codebook(yupvq_ctx* ctx, const uint8_t* codebook, uint32_t n_en
     Scope scope(ctx->device);
     ctx->launches = 0;
     ctx->tc_feat = nullptr;
+    ctx->maxabs_feat = nullptr;
     ctx->tc_rgb = 0;
     if (block_size != 8 && block_size != 16) return ctx->fail("block_size must be 8 or 16");
     if (n_blocks == 0) return 0;
@@ -2014,6 +2066,7 @@ int yupvq_encode_bcn_batch_sharded(yupvq_ctx* ctx, const uint8_t* const* bc_bloc
     init_stats(stats);
     ctx->launches = 0;
     ctx->tc_feat = nullptr;
+    ctx->maxabs_feat = nullptr;
     ctx->tc_rgb = rgb_layout(channels);
     if (check_cfg(ctx, cfg, n_total, channels)) return 1;
     if (!bc_blocks || n_textures == 0) return ctx->fail("no textures");
@@ -2511,6 +2564,7 @@ int yupvq_encode_hdr_batch_sharded(yupvq_ctx* ctx, const float* const* images, s
     init_stats(stats);
     ctx->launches = 0;
     ctx->tc_feat = nullptr;
+    ctx->maxabs_feat = nullptr;
     ctx->tc_rgb = rgb_layout(channels);
     const size_t n_total = (size_t)((width + 3) / 4) * ((height + 3) / 4);
     if (check_cfg(ctx, cfg, n_total, channels)) return 1;

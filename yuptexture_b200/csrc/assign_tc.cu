@@ -178,6 +178,18 @@ __device__ __forceinline__ float fmax3(float a, float b, float c) {
     asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
     return d;
 }
+// two-input maxima for the -DYUPVQ_EPI_MAX2 A/B build (nvcc and ptxas both fold max(max(a, b), c) into FMNMX3; a plain
+// max under a NaN-propagating one cannot be folded)
+__device__ __forceinline__ float fmax2(float a, float b) {
+    float d;
+    asm volatile("max.f32 %0, %1, %2;" : "=f"(d) : "f"(a), "f"(b));
+    return d;
+}
+__device__ __forceinline__ float fmax2n(float a, float b) {   // NaN-propagating form: cannot be folded with a plain max
+    float d;
+    asm volatile("max.NaN.f32 %0, %1, %2;" : "=f"(d) : "f"(a), "f"(b));
+    return d;
+}
 __device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, %0;" ::"n"(kEpiWarps * 32) : "memory"); }
 
 // K-major shared-memory matrix descriptor (cute::UMMA::SmemDescriptor, version 1 == Blackwell).
@@ -642,13 +654,22 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                 const uint32_t taddr = lane_taddr + acc * BN;
                 uint32_t va[32], vb[32];
                 float m0 = -INFINITY, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
+                // FMNMX3 issues at FMNMX's rate (0.42 warp instructions / clk / SMSP, tools/micro/fp_alu_rate.cu), so the
+                // three-input form halves the ALU-pipe time of this pass (-DYUPVQ_EPI_MAX2: two-input form, measured 4 % slower).
                 auto reduce_max = [&](const uint32_t (&v)[32]) {
 #pragma unroll
                     for (int i = 0; i < 32; i += 8) {
+#ifndef YUPVQ_EPI_MAX2
                         m0 = fmax3(m0, __uint_as_float(v[i]), __uint_as_float(v[i + 1]));
                         m1 = fmax3(m1, __uint_as_float(v[i + 2]), __uint_as_float(v[i + 3]));
                         m2 = fmax3(m2, __uint_as_float(v[i + 4]), __uint_as_float(v[i + 5]));
                         m3 = fmax3(m3, __uint_as_float(v[i + 6]), __uint_as_float(v[i + 7]));
+#else
+                        m0 = fmax2n(fmax2(m0, __uint_as_float(v[i])), __uint_as_float(v[i + 1]));
+                        m1 = fmax2n(fmax2(m1, __uint_as_float(v[i + 2])), __uint_as_float(v[i + 3]));
+                        m2 = fmax2n(fmax2(m2, __uint_as_float(v[i + 4])), __uint_as_float(v[i + 5]));
+                        m3 = fmax2n(fmax2(m3, __uint_as_float(v[i + 6])), __uint_as_float(v[i + 7]));
+#endif
                     }
                 };
                 // ---- one read of the accumulator: both 32-column register tiles of this thread's slice are loaded,

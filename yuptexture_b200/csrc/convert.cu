@@ -13,6 +13,7 @@
 #include "bcn_decode.cuh"
 #include "colour.cuh"
 #include "kernels.h"
+#include "tc_prep.cuh"
 
 namespace yupvq {
 
@@ -176,14 +177,72 @@ __device__ __forceinline__ void store_features_tile(const float4 (&f)[16], bool 
     }
 }
 
+// Optional second product of a feature pass (DecodeFuse, kernels.h): the tensor front-end's A' operand row, |x'| and the
+// running max |x| of the block this thread just converted -- what col_sums / max_abs / prep_blocks otherwise re-read
+// the 256 MB feature matrix for.  Same arithmetic as assign_tc.cu prep_blocks_kernel and update.cu max_abs_kernel.
+// The thread's row goes through the shared-memory tile again so the 256-byte rows leave as coalesced 16-byte stores.
+__device__ __forceinline__ void store_operands_tile(const float4 (&f)[16], bool valid, float4* tile, const float* s_mu, const DecodeFuse& fu,
+                                                    size_t tile_first, size_t blk, size_t n) {
+    __syncthreads();   // the feature tile has been streamed out
+    float ss = 0.0f, mx = 0.0f;
+    if (valid) {
+        uint32_t* row = reinterpret_cast<uint32_t*>(tile + threadIdx.x * kPitch4);   // 64 words = 128 bf16
+        auto absmax = [&](float v) {
+            const float a = fabsf(v);
+            if (a != a) mx = INFINITY;
+            else if (a > mx) mx = a;
+        };
+#pragma unroll
+        for (int q = 0; q < 16; ++q) {
+            const float4 x = f[q];
+            absmax(x.x); absmax(x.y); absmax(x.z); absmax(x.w);
+            const float4 m = reinterpret_cast<const float4*>(s_mu)[q];
+            const float o0 = 2.0f * (x.x - m.x), o1 = x.y - m.y, o2 = x.z - m.z, o3 = x.w - m.w;
+            ss += o0 * o0 + o1 * o1 + o2 * o2 + o3 * o3;
+            uint16_t h0, h1, h2, h3, l0, l1, l2, l3;
+            split_bf16(o0, h0, l0);
+            split_bf16(o1, h1, l1);
+            split_bf16(o2, h2, l2);
+            split_bf16(o3, h3, l3);
+            if (fu.rgb) {
+                uint16_t* r16 = reinterpret_cast<uint16_t*>(row);
+                r16[3 * q] = h0; r16[3 * q + 1] = h1; r16[3 * q + 2] = h2;
+                r16[64 + 3 * q] = l0; r16[64 + 3 * q + 1] = l1; r16[64 + 3 * q + 2] = l2;
+                r16[48 + q] = q < 3 ? (uint16_t)0x3f80u : (uint16_t)0u;
+                r16[112 + q] = 0;
+            } else {
+                row[2 * q] = (uint32_t)h0 | ((uint32_t)h1 << 16);
+                row[2 * q + 1] = (uint32_t)h2 | ((uint32_t)h3 << 16);
+                row[32 + 2 * q] = (uint32_t)l0 | ((uint32_t)l1 << 16);
+                row[32 + 2 * q + 1] = (uint32_t)l2 | ((uint32_t)l3 << 16);
+            }
+        }
+        fu.xnorm[blk] = sqrtf(ss) * 1.0001f;
+    }
+    __syncthreads();
+    const size_t rows = (n - tile_first) < (size_t)kTile ? (n - tile_first) : (size_t)kTile;
+    float4* dst = reinterpret_cast<float4*>(fu.a_prime) + tile_first * 16;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        const int idx = threadIdx.x + kTile * k;
+        const int r = idx >> 4, col = idx & 15;
+        if ((size_t)r < rows) dst[idx] = tile[r * kPitch4 + col];
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if ((threadIdx.x & 31) == 0) atomicMax(fu.max_abs_bits, __float_as_uint(mx));
+}
+
 // ---- K1: BCn -> pixel planes + features ----------------------------------------------------------
 
 template <int FMT, int CH>
 __global__ void __launch_bounds__(kTile) decode_bcn_kernel(const uint8_t* __restrict__ bc, size_t n,
                                                            uint4* __restrict__ planes, size_t stride,
                                                            float* __restrict__ feat, uint8_t* __restrict__ px_blocks,
-                                                           int vec16) {
+                                                           int vec16, DecodeFuse fu) {
     __shared__ float4 tile[kTile * kPitch4];
+    __shared__ __align__(16) float s_mu[64];
+    if (fu.a_prime && threadIdx.x < 64) s_mu[threadIdx.x] = fu.mu[threadIdx.x];   // visible after the tile barrier below
     const size_t tile_first = (size_t)blockIdx.x * kTile;
     const size_t blk = tile_first + threadIdx.x;
     const bool valid = blk < n;
@@ -269,6 +328,7 @@ __global__ void __launch_bounds__(kTile) decode_bcn_kernel(const uint8_t* __rest
         }
     }
     if (feat) store_features_tile(f, valid, tile, feat, tile_first, n);
+    if (feat && fu.a_prime) store_operands_tile(f, valid, tile, s_mu, fu, tile_first, blk, n);
 }
 
 // ---- uint8 pixel blocks (reference layout) -> planes + features ---------------------------------
@@ -527,28 +587,29 @@ cudaError_t colour_tables_init() {
 
 template <int FMT>
 static cudaError_t decode_fmt(const uint8_t* bc, size_t n, int ch, uint4* planes, size_t stride, float* feat,
-                              uint8_t* px, int vec16, cudaStream_t s) {
+                              uint8_t* px, int vec16, cudaStream_t s, const DecodeFuse& fu) {
     const unsigned g = grid_for(n, kTile);
     switch (ch) {
-        case 1: decode_bcn_kernel<FMT, 1><<<g, kTile, 0, s>>>(bc, n, planes, stride, feat, px, vec16); break;
-        case 2: decode_bcn_kernel<FMT, 2><<<g, kTile, 0, s>>>(bc, n, planes, stride, feat, px, vec16); break;
-        case 3: decode_bcn_kernel<FMT, 3><<<g, kTile, 0, s>>>(bc, n, planes, stride, feat, px, vec16); break;
-        case 4: decode_bcn_kernel<FMT, 4><<<g, kTile, 0, s>>>(bc, n, planes, stride, feat, px, vec16); break;
+        case 1: decode_bcn_kernel<FMT, 1><<<g, kTile, 0, s>>>(bc, n, planes, stride, feat, px, vec16, fu); break;
+        case 2: decode_bcn_kernel<FMT, 2><<<g, kTile, 0, s>>>(bc, n, planes, stride, feat, px, vec16, fu); break;
+        case 3: decode_bcn_kernel<FMT, 3><<<g, kTile, 0, s>>>(bc, n, planes, stride, feat, px, vec16, fu); break;
+        case 4: decode_bcn_kernel<FMT, 4><<<g, kTile, 0, s>>>(bc, n, planes, stride, feat, px, vec16, fu); break;
         default: return cudaErrorInvalidValue;
     }
     return cudaGetLastError();
 }
 
 cudaError_t launch_decode_bcn(const uint8_t* bc, size_t n, int fmt, int ch, uint4* planes, size_t plane_stride,
-                              float* feat, uint8_t* px_blocks, cudaStream_t s) {
+                              float* feat, uint8_t* px_blocks, cudaStream_t s, const DecodeFuse* fuse) {
     if (n == 0) return cudaSuccess;
     const int vec16 = ((reinterpret_cast<uintptr_t>(bc) & 15u) == 0) ? 1 : 0;
+    const DecodeFuse fu = fuse ? *fuse : DecodeFuse{};
     switch (fmt) {
-        case YUPVQ_FMT_BC1: return decode_fmt<YUPVQ_FMT_BC1>(bc, n, ch, planes, plane_stride, feat, px_blocks, vec16, s);
-        case YUPVQ_FMT_BC3: return decode_fmt<YUPVQ_FMT_BC3>(bc, n, ch, planes, plane_stride, feat, px_blocks, vec16, s);
-        case YUPVQ_FMT_BC4: return decode_fmt<YUPVQ_FMT_BC4>(bc, n, ch, planes, plane_stride, feat, px_blocks, vec16, s);
-        case YUPVQ_FMT_BC5: return decode_fmt<YUPVQ_FMT_BC5>(bc, n, ch, planes, plane_stride, feat, px_blocks, vec16, s);
-        case YUPVQ_FMT_BC7: return decode_fmt<YUPVQ_FMT_BC7>(bc, n, ch, planes, plane_stride, feat, px_blocks, vec16, s);
+        case YUPVQ_FMT_BC1: return decode_fmt<YUPVQ_FMT_BC1>(bc, n, ch, planes, plane_stride, feat, px_blocks, vec16, s, fu);
+        case YUPVQ_FMT_BC3: return decode_fmt<YUPVQ_FMT_BC3>(bc, n, ch, planes, plane_stride, feat, px_blocks, vec16, s, fu);
+        case YUPVQ_FMT_BC4: return decode_fmt<YUPVQ_FMT_BC4>(bc, n, ch, planes, plane_stride, feat, px_blocks, vec16, s, fu);
+        case YUPVQ_FMT_BC5: return decode_fmt<YUPVQ_FMT_BC5>(bc, n, ch, planes, plane_stride, feat, px_blocks, vec16, s, fu);
+        case YUPVQ_FMT_BC7: return decode_fmt<YUPVQ_FMT_BC7>(bc, n, ch, planes, plane_stride, feat, px_blocks, vec16, s, fu);
         default: return cudaErrorInvalidValue;
     }
 }

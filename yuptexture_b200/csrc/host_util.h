@@ -17,11 +17,11 @@ struct DebugOpts {
     bool seed_no_tri = false;        // YUPVQ_SEED_NO_TRI         HDR triangle-inequality skip off
     bool seed_no_pal = false;        // YUPVQ_SEED_NO_PAL         BC1 palette-form seeding off (pixel-plane kernel)
     bool seed_no_smem = false;       // YUPVQ_SEED_NO_SMEM        no shared-memory resident segments in the pixel-plane kernel
-    bool seed_leader = false;        // YUPVQ_SEED_LEADER         palette seeding with the leader-CTA / mailbox protocol (round 1)
     bool lloyd_sync = false;         // YUPVQ_LLOYD_SYNC          host-synchronous Lloyd loop
     bool no_delta = false;           // YUPVQ_NO_DELTA            full accumulate on every pass
     bool no_rgb48 = false;           // YUPVQ_NO_RGB48            64-column tensor operands for textures without alpha
     bool no_split_decode = false;    // YUPVQ_NO_SPLIT_DECODE     one decode before the seeding
+    bool no_decode_fuse = false;     // YUPVQ_NO_DECODE_FUSE      separate mean / max |x| / operand passes after the feature decode
     bool batch_per_texture = false;  // YUPVQ_BATCH_PER_TEXTURE   lock-step batch with per-texture launches
     bool no_tail_fuse = false;       // YUPVQ_NO_TAIL_FUSE        separate control / errors / finalize / reseed / prep launches
     bool tc_v1 = false;              // YUPVQ_TC_V1               tensor front-end with the one-barrier-per-tile epilogue (no merge warps)

@@ -10,8 +10,18 @@ namespace yupvq {
 // Pixel blocks live in HBM as `ch` planes of uint4: plane p holds bytes [16p, 16p+16) of every
 // block's 16*ch-byte pixel block, planes[p * plane_stride + block].  Seeding reads them coalesced.
 cudaError_t colour_tables_init();
+// DecodeFuse (optional, with feat != null): the same pass also writes the tensor front-end's per-block operands for the
+// given mean row -- a_prime (n x 128 bf16), xnorm (n) -- and max-reduces |x| into *max_abs_bits (float bits; zero it
+// first): the work of launch_tc_mean / launch_tc_prep_blocks / launch_max_abs without re-reading the features.
+struct DecodeFuse {
+    const float* mu = nullptr;        // 64 floats
+    float* a_prime = nullptr;
+    float* xnorm = nullptr;
+    unsigned int* max_abs_bits = nullptr;
+    int rgb = 0;
+};
 cudaError_t launch_decode_bcn(const uint8_t* bc, size_t n, int fmt, int ch, uint4* planes, size_t plane_stride,
-                              float* feat, uint8_t* px_blocks, cudaStream_t s);
+                              float* feat, uint8_t* px_blocks, cudaStream_t s, const DecodeFuse* fuse = nullptr);
 cudaError_t launch_pixels_to_features(const uint8_t* px_blocks, size_t n, int ch, uint4* planes, size_t plane_stride,
                                       float* feat, cudaStream_t s);
 cudaError_t launch_floats_to_features(const float* float_blocks, size_t n, int ch, float* feat, cudaStream_t s);

@@ -786,12 +786,8 @@ seed_persistent_kernel(SeedState st, const uint4* __restrict__ planes, size_t st
 //      TOGETHER with the seed's 20 bytes taken from its shared memory.  Three round trips, every message a
 //      self-validating tagged 64-bit word (16-bit round tag + 48-bit payload): no fences, no min_dist array.
 constexpr int kQMailbox = 256, kQMailStride = 16, kQPick = 4096;  // u64 offsets in SeedState::partial (CTA words at 0)
-//  (3) ALLSCAN (default): there is no leader.  EVERY CTA's first warp polls all CTA totals and computes S, the target
-//      and the owning CTA itself (the same integer arithmetic on the same words, so all CTAs agree); the owner starts
-//      its search at once and the others wait for the pick: two L2 exchanges per round instead of three (no mailbox).
-constexpr unsigned int kEvtPick = 1, kEvtOwner = 2, kEvtWait = 3, kEvtStop = 4;
+constexpr unsigned int kEvtPick = 1, kEvtOwner = 2;
 
-template <bool ALLSCAN>
 __global__ void __launch_bounds__(kPThreads, 1)
 seed_palette_kernel(SeedState st, const uint32_t* __restrict__ pal5, size_t pstride, size_t n, size_t bpw, uint32_t K) {
     extern __shared__ uint4 s_cache[];                 // [warp][8 segments][5 words][32 lanes]
@@ -845,7 +841,7 @@ seed_palette_kernel(SeedState st, const uint32_t* __restrict__ pal5, size_t pstr
         t0 = clock64();
 #endif
         const unsigned long long tag = (unsigned long long)round << kTagShift;
-        const double canon_u = ((ALLSCAN || leader) && wid == 0) ? st.canon[round - 1] : 0.0;  // fetched early: off the critical path
+        const double canon_u = (leader && wid == 0) ? st.canon[round - 1] : 0.0;  // fetched early: off the critical path
         // ---- (1) the new seed's pixels, channel-planar: sp[q] = channel q of texels 0-3, 4-7, 8-11, 12-15
         uint4 sp[3];
         {
@@ -888,8 +884,8 @@ seed_palette_kernel(SeedState st, const uint32_t* __restrict__ pal5, size_t pstr
             const unsigned long long cta_total = ((unsigned long long)__reduce_add_sync(0xffffffffu, (unsigned int)(wv >> 20)) << 20) +
                                                  (unsigned long long)__reduce_add_sync(0xffffffffu, (unsigned int)(wv & 0xfffffu));
             if (lane == 0) st_relaxed_u64(cta_words + blockIdx.x, tag | cta_total);
-            if (ALLSCAN || leader) {
-                // ---- (3) leader warp (ALLSCAN: the first warp of every CTA): all CTA totals -> S, target, owning CTA, residual
+            if (leader) {
+                // ---- (3) leader warp: all CTA totals -> S, target, owning CTA, residual
                 unsigned long long v[kPPer];
                 for (;;) {
                     bool ok = true;
@@ -909,15 +905,9 @@ seed_palette_kernel(SeedState st, const uint32_t* __restrict__ pal5, size_t pstr
                 const unsigned long long incl = warp_incl_scan<unsigned long long>(thread_tot, lane);
                 const unsigned long long S = __shfl_sync(0xffffffffu, incl, 31);
                 if (S == 0) {  // reference :299-302: fill the rest with seed 0 and stop
-                    if (leader) {
-                        for (uint32_t rr = round + lane; rr < K; rr += 32) st.seed_idx[rr] = st.seed_idx[0];
-                        if (lane == 0) st.status[0] = round;
-                    }
-                    if (ALLSCAN) {
-                        if (lane == 0) s_evt = kEvtStop;   // every CTA sees S == 0 itself
-                    } else if (lane < 5) {
-                        st_relaxed_u64(pickw + lane, tag | kStopBit);
-                    }
+                    for (uint32_t rr = round + lane; rr < K; rr += 32) st.seed_idx[rr] = st.seed_idx[0];
+                    if (lane == 0) st.status[0] = round;
+                    if (lane < 5) st_relaxed_u64(pickw + lane, tag | kStopBit);
                 } else {
                     const double p = __dadd_rn(__dmul_rn(canon_u, (double)S), 0.0);
                     // first j with prefix_j >= p  <=>  prefix_j >= ceil(p) on exact integers
@@ -938,136 +928,97 @@ seed_palette_kernel(SeedState st, const uint32_t* __restrict__ pal5, size_t pstr
                     const unsigned long long before = __shfl_sync(0xffffffffu, cum, f);
                     const unsigned long long resid = target > before ? target - before : 0ull;
                     if (lane == 0) {
-                        if (leader) st.status[1] = round;                        // rounds that drew a sample
-                        if (ALLSCAN) {
-                            s_resid = resid;
-                            s_evt = (f * kPPer + hk) == (int)blockIdx.x ? kEvtOwner : kEvtWait;
-                        } else {
-                            st_relaxed_u64(st.partial + kQMailbox + (size_t)(f * kPPer + hk) * kQMailStride, tag | resid);
-                        }
+                        st.status[1] = round;                                    // rounds that drew a sample
+                        st_relaxed_u64(st.partial + kQMailbox + (size_t)(f * kPPer + hk) * kQMailStride, tag | resid);
                     }
                 }
             }
         }
         TICK(q_lead);
-        // owner: first block (in block order) whose inclusive prefix inside this CTA reaches the residual; the pick goes to
-        // the exchange words and, for this CTA itself, straight to shared memory
-        auto owner_search = [&]() {
-            const unsigned long long resid = s_resid;
-            const unsigned long long wtot = s_w[lane];
-            const unsigned long long wincl = warp_incl_scan<unsigned long long>(wtot, lane);
-            const unsigned int wb = __ballot_sync(0xffffffffu, wincl >= resid);
-            const int ow = wb ? __ffs(wb) - 1 : kPWarps - 1;
-            const unsigned long long before_w = __shfl_sync(0xffffffffu, wincl - wtot, ow);
-            if (wid == ow) {
-                const unsigned long long r = resid - before_w;
-                // segment totals by hardware reduction (independent, pipelined), then ONE scan inside the segment
-                // that holds the residual
-                uint32_t v32[8];
-                unsigned long long run = 0;
-                int si = -1;
-#pragma unroll
-                for (int i = 0; i < 8; ++i) v32[i] = ((vmask >> i) & 1u) ? sq_of(ms[i]) : 0u;
-#pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    const unsigned long long tot = ((unsigned long long)__reduce_add_sync(0xffffffffu, v32[i] >> 16) << 16) +
-                                                   (unsigned long long)__reduce_add_sync(0xffffffffu, v32[i] & 0xffffu);
-                    if (si < 0) {
-                        if (run + tot >= r) si = i;
-                        else run += tot;
-                    }
+        // ---- (4) wait for the pick; the CTA whose mailbox is posted first finds the block and publishes it
+        bool owner_done = false;
+        for (;;) {
+            if (wid == 0) {
+                unsigned long long w = 0;
+                unsigned int b;
+                for (;;) {
+                    if (lane < 5) w = ld_relaxed_u64(pickw + lane);
+                    else if (lane == 5 && !owner_done) w = ld_relaxed_u64(mailbox);
+                    const bool ok = lane < 6 && (w >> kTagShift) == (unsigned long long)round;
+                    b = __ballot_sync(0xffffffffu, ok);
+                    if ((b & 0x1fu) == 0x1fu || (b & 0x20u)) break;
                 }
-                bool found = false;
-                if (si >= 0) {
-                    uint32_t v = 0;
+                if ((b & 0x1fu) == 0x1fu) {
+                    if (lane < 5) s_pickw[lane] = w;
+                    if (lane == 0) s_evt = kEvtPick;
+                } else {
+                    if (lane == 5) s_resid = w & kPayloadMask;
+                    if (lane == 0) s_evt = kEvtOwner;
+                    owner_done = true;
+                }
+            }
+            __syncthreads();
+            TICK(q_poll);
+            if (s_evt == kEvtPick) break;
+            {   // owner: first block (in block order) whose inclusive prefix inside this CTA reaches the residual
+                const unsigned long long resid = s_resid;
+                const unsigned long long wtot = s_w[lane];
+                const unsigned long long wincl = warp_incl_scan<unsigned long long>(wtot, lane);
+                const unsigned int wb = __ballot_sync(0xffffffffu, wincl >= resid);
+                const int ow = wb ? __ffs(wb) - 1 : kPWarps - 1;
+                const unsigned long long before_w = __shfl_sync(0xffffffffu, wincl - wtot, ow);
+                if (wid == ow) {
+                    const unsigned long long r = resid - before_w;
+                    // segment totals by hardware reduction (independent, pipelined), then ONE scan inside the segment
+                    // that holds the residual
+                    uint32_t v32[8];
+                    unsigned long long run = 0;
+                    int si = -1;
 #pragma unroll
-                    for (int i = 0; i < 8; ++i)
-                        if (i == si) v = v32[i];
-                    const unsigned long long incl = warp_incl_scan<unsigned long long>((unsigned long long)v, lane);
-                    const unsigned int hb = __ballot_sync(0xffffffffu, run + incl >= r);
-                    if (hb) {
-                        found = true;
-                        if (lane == __ffs(hb) - 1) {
-                            const size_t chosen = wbase + (size_t)si * 32 + lane;
-                            uint32_t e[5];
+                    for (int i = 0; i < 8; ++i) v32[i] = ((vmask >> i) & 1u) ? sq_of(ms[i]) : 0u;
 #pragma unroll
-                            for (int q = 0; q < 5; ++q) e[q] = pc[(si * 5 + q) * 32];
-                            st.seed_idx[round] = (uint32_t)chosen;
-                            st_relaxed_u64(pickw + 0, tag | (unsigned long long)chosen);
-                            st_relaxed_u64(pickw + 1, tag | (unsigned long long)e[0] | ((unsigned long long)(e[1] & 0xffffu) << 32));
-                            st_relaxed_u64(pickw + 2, tag | (unsigned long long)(e[1] >> 16) | ((unsigned long long)e[2] << 16));
-                            st_relaxed_u64(pickw + 3, tag | (unsigned long long)e[3] | ((unsigned long long)(e[4] & 0xffffu) << 32));
-                            st_relaxed_u64(pickw + 4, tag | (unsigned long long)(e[4] >> 16));
-                            if (ALLSCAN) {
-                                s_pickw[0] = tag | (unsigned long long)chosen;
-                                s_pickw[1] = tag | (unsigned long long)e[0] | ((unsigned long long)(e[1] & 0xffffu) << 32);
-                                s_pickw[2] = tag | (unsigned long long)(e[1] >> 16) | ((unsigned long long)e[2] << 16);
-                                s_pickw[3] = tag | (unsigned long long)e[3] | ((unsigned long long)(e[4] & 0xffffu) << 32);
-                                s_pickw[4] = tag | (unsigned long long)(e[4] >> 16);
+                    for (int i = 0; i < 8; ++i) {
+                        const unsigned long long tot = ((unsigned long long)__reduce_add_sync(0xffffffffu, v32[i] >> 16) << 16) +
+                                                       (unsigned long long)__reduce_add_sync(0xffffffffu, v32[i] & 0xffffu);
+                        if (si < 0) {
+                            if (run + tot >= r) si = i;
+                            else run += tot;
+                        }
+                    }
+                    bool found = false;
+                    if (si >= 0) {
+                        uint32_t v = 0;
+#pragma unroll
+                        for (int i = 0; i < 8; ++i)
+                            if (i == si) v = v32[i];
+                        const unsigned long long incl = warp_incl_scan<unsigned long long>((unsigned long long)v, lane);
+                        const unsigned int hb = __ballot_sync(0xffffffffu, run + incl >= r);
+                        if (hb) {
+                            found = true;
+                            if (lane == __ffs(hb) - 1) {
+                                const size_t chosen = wbase + (size_t)si * 32 + lane;
+                                uint32_t e[5];
+#pragma unroll
+                                for (int q = 0; q < 5; ++q) e[q] = pc[(si * 5 + q) * 32];
+                                st.seed_idx[round] = (uint32_t)chosen;
+                                st_relaxed_u64(pickw + 0, tag | (unsigned long long)chosen);
+                                st_relaxed_u64(pickw + 1, tag | (unsigned long long)e[0] | ((unsigned long long)(e[1] & 0xffffu) << 32));
+                                st_relaxed_u64(pickw + 2, tag | (unsigned long long)(e[1] >> 16) | ((unsigned long long)e[2] << 16));
+                                st_relaxed_u64(pickw + 3, tag | (unsigned long long)e[3] | ((unsigned long long)(e[4] & 0xffffu) << 32));
+                                st_relaxed_u64(pickw + 4, tag | (unsigned long long)(e[4] >> 16));
                             }
                         }
                     }
-                }
-                if (!found && lane == 0) {  // cannot happen (r <= warp total); never leave the grid waiting
-                    st.seed_idx[round] = (uint32_t)(n - 1);
+                    if (!found && lane == 0) {  // cannot happen (r <= warp total); never leave the grid waiting
+                        st.seed_idx[round] = (uint32_t)(n - 1);
 #pragma unroll
-                    for (int q = 0; q < 5; ++q) {
-                        st_relaxed_u64(pickw + q, tag | kStopBit);
-                        if (ALLSCAN) s_pickw[q] = tag | kStopBit;
+                        for (int q = 0; q < 5; ++q) st_relaxed_u64(pickw + q, tag | kStopBit);
+                        st.status[0] = round;
                     }
-                    st.status[0] = round;
                 }
-            }
-        };
-        if (ALLSCAN) {
-            // ---- (4) the owning CTA searches its registers and publishes the pick; every other CTA waits for it
-            __syncthreads();
-            TICK(q_poll);
-            const unsigned int evt = s_evt;
-            if (evt == kEvtStop) return;
-            if (evt == kEvtOwner) {
-                owner_search();
-            } else if (wid == 0) {
-                unsigned long long w = 0;
-                for (;;) {
-                    if (lane < 5) w = ld_relaxed_u64(pickw + lane);
-                    const bool ok = lane >= 5 || (w >> kTagShift) == (unsigned long long)round;
-                    if (__all_sync(0xffffffffu, ok)) break;
-                }
-                if (lane < 5) s_pickw[lane] = w;
             }
             __syncthreads();
             TICK(q_own);
-        } else {
-            // ---- (4) wait for the pick; the CTA whose mailbox is posted first finds the block and publishes it
-            bool owner_done = false;
-            for (;;) {
-                if (wid == 0) {
-                    unsigned long long w = 0;
-                    unsigned int b;
-                    for (;;) {
-                        if (lane < 5) w = ld_relaxed_u64(pickw + lane);
-                        else if (lane == 5 && !owner_done) w = ld_relaxed_u64(mailbox);
-                        const bool ok = lane < 6 && (w >> kTagShift) == (unsigned long long)round;
-                        b = __ballot_sync(0xffffffffu, ok);
-                        if ((b & 0x1fu) == 0x1fu || (b & 0x20u)) break;
-                    }
-                    if ((b & 0x1fu) == 0x1fu) {
-                        if (lane < 5) s_pickw[lane] = w;
-                        if (lane == 0) s_evt = kEvtPick;
-                    } else {
-                        if (lane == 5) s_resid = w & kPayloadMask;
-                        if (lane == 0) s_evt = kEvtOwner;
-                        owner_done = true;
-                    }
-                }
-                __syncthreads();
-                TICK(q_poll);
-                if (s_evt == kEvtPick) break;
-                owner_search();
-                __syncthreads();
-                TICK(q_own);
-            }
         }
         const unsigned long long p0 = s_pickw[0], p1 = s_pickw[1], p2 = s_pickw[2], p3 = s_pickw[3], p4 = s_pickw[4];
         if (p0 & kStopBit) return;
@@ -1176,17 +1127,14 @@ cudaError_t launch_seed_persistent(const SeedState& st, const uint4* planes, siz
     const bool no_pal = debug_opts().seed_no_pal;
     if (pal5 != nullptr && !hdr && ch == 3 && mdreg && !tri && !no_pal && K <= 0xffffu) {
         const size_t smem_pal = (size_t)kPWarps * 8 * 5 * 32 * 4;  // 160 KiB
-        // YUPVQ_SEED_LEADER=1: the round-1 protocol (one leader CTA and a mailbox hop) for A/B
-        const bool allscan = !debug_opts().seed_leader;
-        const void* pfn = allscan ? (const void*)seed_palette_kernel<true> : (const void*)seed_palette_kernel<false>;
-        static std::atomic<uint64_t> attr_pal[2];
-        if (cudaError_t e = once_per_device(attr_pal[allscan ? 1 : 0], [&] {
-                return cudaFuncSetAttribute(pfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_pal);
+        static std::atomic<uint64_t> attr_pal{0};
+        if (cudaError_t e = once_per_device(attr_pal, [&] {
+                return cudaFuncSetAttribute(seed_palette_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_pal);
             }); e != cudaSuccess)
             return e;
         SeedState st_pal = st;
         void* pargs[] = {&st_pal, (void*)&pal5, &pal_stride, &n, &bpw, &K};
-        return cudaLaunchCooperativeKernel(pfn, dim3((unsigned)g), dim3(kPThreads), pargs, smem_pal, s);
+        return cudaLaunchCooperativeKernel((const void*)seed_palette_kernel, dim3((unsigned)g), dim3(kPThreads), pargs, smem_pal, s);
     }
     // shared-memory resident segments per warp: as many as fit in ~200 KB (after the seed table of the TRI variant)
     int cseg = 0;

@@ -488,6 +488,23 @@ VQCodebook VQEncoder::EncodeCentroids(const std::vector<std::vector<uint8_t>>& p
     const double t0 = now_ms();
     VQCodebook cb((uint32_t)BCBlockSize::GetSize(bcFormat), config.codebookSize);
     cb.entries.resize(pixelCentroids.size());
+    // GPU encoders active (BCnCompressor::SetGpuEncode): the K blocks stacked into one 4 x 4K image are one kernel launch
+    // instead of K single-block calls -- the same encoder, the same bytes as K calls of BCnCompressor::Compress(4, 4).
+    if (!pixelCentroids.empty() && yupvq_bcn_encode_supported((int)bcFormat) && gpu_encode_wanted((bool)current_codec().compress)) {
+        const size_t per = 16 * (size_t)channels, bs = BCBlockSize::GetSize(bcFormat), K = pixelCentroids.size();
+        const std::vector<uint8_t> flat = flatten(pixelCentroids, per);
+        std::vector<uint8_t> out(K * bs);
+        int rc;
+        {
+            std::lock_guard<std::mutex> lock(g_codec_ctx_mutex);
+            rc = yupvq_bcn_encode_image(codec_ctx(), flat.data(), 4, (uint32_t)(4 * K), (int)channels, (int)bcFormat, channels == 3 ? 1 : 0, 128,
+                                        out.data(), nullptr);
+        }
+        if (rc) throw std::runtime_error("GPU centroid encode failed");
+        for (size_t i = 0; i < K; ++i) cb.entries[i].assign(out.begin() + i * bs, out.begin() + (i + 1) * bs);
+        lastCentroidMs = now_ms() - t0;
+        return cb;
+    }
     // CompressSingleBlock passes (numThreads, bcQuality) only, so the default alphaThreshold (128) applies, not params'.
     // One thread per 4x4 call (the result of a single-block encode does not depend on it), the K calls
     // spread over params.numThreads as in the reference's loop.
