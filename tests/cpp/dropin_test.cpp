@@ -138,7 +138,12 @@ static void ldr_case(const Ref& ref, const std::string& out, const std::string& 
     dump(out + "/" + tag + "_indices.u32", idx);
     // (4) a stream written by the reference's own Compress (its seed is random) decodes to the same bytes with both decoders
     std::vector<uint8_t> rs(stream.size() * 2 + (1u << 20));
-    const long long rn = ref.compress(img.data(), 0, W, H, CH, &p, rs.data(), rs.size(), nullptr);
+    // (the container does not depend on how long the reference's CPU clustering ran: one Lloyd pass on a 5 % sample keeps
+    // this leg to seconds instead of minutes of host time per case)
+    CompressionParams pr = p;
+    pr.vq_maxIterations = 1;
+    pr.vq_FastModeSampleRatio = 0.05f;
+    const long long rn = ref.compress(img.data(), 0, W, H, CH, &pr, rs.data(), rs.size(), nullptr);
     CHECK(rn > 24);
     if (rn > 24) {
         rs.resize((size_t)rn);
