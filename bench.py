@@ -326,6 +326,7 @@ def run_ours(args, rank, world, local_rank):
     enc.profile(True)
     step(True)
     ms_fe, n_fe = enc.profile_read()
+    stage_ms, stage_passes = enc.profile_stages()
     enc.profile(False)
 
     # ---- multi-GPU parity, carried by every N > 1 line: this rank's outputs of the first and the last texture it holds are
@@ -401,7 +402,9 @@ def run_ours(args, rank, world, local_rank):
                        "l2": "no explicit flush: each step streams a 330 MB working set (features + pixel planes) > 126 MB L2",
                        "lloyd_passes": last.lloyd_passes, "ms_per_texture": ms_dev / args.steps / n_tex,
                        "phases_ms": {p: getattr(last, "ms_" + p) for p in phases},
-                       "wall_ms_per_step": wall_dev / args.steps},
+                       "wall_ms_per_step": wall_dev / args.steps,
+                       "lloyd_stage_ms": {"passes": stage_passes, **stage_ms,
+                                          "note": "rank 0, one profiled step: CUDA events between the four launches of every pass"}},
             "e2e": {"value": e2e, "unit": "blocks/s", "h2d_bytes_per_step": bytes_in, "d2h_bytes_per_step": bytes_out,
                     "ms_per_step": ms_e2e / args.steps, "wall_ms_per_step": wall_e2e / args.steps,
                     "note": "rank 0's bytes; pinned host buffers, copies inside the timed region"},

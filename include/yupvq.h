@@ -87,6 +87,10 @@ YUPVQ_API int yupvq_timer_stop(yupvq_ctx* ctx, float* out_ms);
  * timed region of the bench runs with profiling off). */
 YUPVQ_API int yupvq_profile(yupvq_ctx* ctx, int enable);
 YUPVQ_API int yupvq_profile_read(yupvq_ctx* ctx, float* out_ms_front_end, uint32_t* out_launches);
+/* Stage times of the Lloyd passes run while profiling was on (CUDA events between the launches of a pass), summed over the
+ * passes: out_ms = { tensor front-end, exact re-rank, update (full or delta), tail (with the exchange step when the
+ * blocks are sharded) }.  Used by bench.py to explain where a multi-GPU step spends its time. */
+YUPVQ_API int yupvq_profile_stages(yupvq_ctx* ctx, float out_ms[4], uint32_t* out_passes);
 
 /* CompressionConfig::SetQuality, src/vq_encoder.cpp:12-18 (powers hard-wired 4..10). */
 YUPVQ_API uint32_t yupvq_codebook_size(float quality);

@@ -43,7 +43,11 @@ def main():
     # K = 512 (resident centroid operand), Oklab metric, all rows
     cfg = binding.make_config(quality=0.8, max_iterations=8, seed=43)
     cent, idx, _ = case("bc1 K=512 oklab", lambda: enc.encode_bcn(bc1, n1, 1, 3, cfg))
-    case("gather codebook", lambda: enc.gather_codebook(cent, idx))
+    entries = np.random.default_rng(3).integers(0, 256, (len(cent), 8), dtype=np.uint8)   # BC1-sized codebook entries
+    case("gather codebook", lambda: enc.gather_codebook(entries, idx))
+    case("bcn encode bc1", lambda: enc.bcn_encode_image(rgb, 1))
+    case("bcn encode bc3", lambda: enc.bcn_encode_image(rgba, 3))
+    case("compress image (encode + vq)", lambda: enc.compress_image(rgb, 1, cfg)[:3])
     case("bc3 rgba K=512 oklab", lambda: enc.encode_bcn(bc3, n3, 3, 4, cfg))
     # small codebook (single chunk), K = 1024 (streamed operand)
     case("bc1 K=64", lambda: enc.encode_bcn(bc1, n1, 1, 3, binding.make_config(codebook=64, max_iterations=6, seed=5)))

@@ -80,6 +80,7 @@ def lib():
                                            C.POINTER(C.c_float)]
         L.yupvq_profile.argtypes = [_vp, C.c_int]
         L.yupvq_profile_read.argtypes = [_vp, C.POINTER(C.c_float), C.POINTER(C.c_uint32)]
+        L.yupvq_profile_stages.argtypes = [_vp, C.POINTER(C.c_float), C.POINTER(C.c_uint32)]
         L.yupvq_comm_unique_id.argtypes = [_vp, _vp]
         L.yupvq_comm_init.argtypes = [_vp, _vp, C.c_int, C.c_int]
         L.yupvq_encode_bcn_sharded.argtypes = [_vp, _vp, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int, C.c_int, cfgp,
@@ -196,6 +197,13 @@ class Encoder:
 
     def profile(self, enable):
         self._ck(self._L.yupvq_profile(self._ctx, 1 if enable else 0), "yupvq_profile")
+
+    def profile_stages(self):
+        """-> ({front_end, rerank, update, tail: ms summed over the profiled passes}, passes)"""
+        ms = (C.c_float * 4)()
+        n = C.c_uint32(0)
+        self._ck(self._L.yupvq_profile_stages(self._ctx, ms, C.byref(n)), "yupvq_profile_stages")
+        return {"front_end": ms[0], "rerank": ms[1], "update": ms[2], "tail_and_exchange": ms[3]}, n.value
 
     def profile_read(self):
         """(summed ms of the tensor front-end launches since the last read, number of launches)"""

@@ -39,7 +39,8 @@ const DebugOpts& debug_opts() {
         o.no_decode_fuse = on("YUPVQ_NO_DECODE_FUSE");
         o.batch_per_texture = on("YUPVQ_BATCH_PER_TEXTURE");
         o.no_tail_fuse = on("YUPVQ_NO_TAIL_FUSE");
-        o.no_overlap = on("YUPVQ_NO_OVERLAP");
+        o.no_peer_xchg = on("YUPVQ_NO_PEER_XCHG");
+        if (const char* v = getenv("YUPVQ_XCHG_MODE")) o.xchg_mode = atoi(v);
         o.tc_v1 = on("YUPVQ_TC_V1");   // v2 (merge warps) is the default since r02c: 0.143 against 0.177 ms per pass, bit-identical
         if (const char* v = getenv("YUPVQ_ASYNC_DBG")) o.async_dbg = atoi(v);
         return o;
@@ -113,11 +114,27 @@ struct yupvq_ctx {
     bool profile = false;
     std::vector<cudaEvent_t> pev;
     size_t pev_used = 0;
+    // stage marks of the fused Lloyd pass while profiling (yupvq_profile_stages): event + the stage that ended at it
+    std::vector<cudaEvent_t> sev;
+    std::vector<uint8_t> sev_stage;
+    size_t sev_used = 0;
+    void stage_mark(int stage) {   // 255 = start of a pass; 0 front-end, 1 re-rank, 2 update, 3 exchange + tail
+        if (!profile || sev_used >= sev.size()) return;
+        cudaEventRecord(sev[sev_used], stream);
+        sev_stage[sev_used++] = (uint8_t)stage;
+    }
 
     // multi-GPU
     NcclApi nccl;
     void* comm = nullptr;
     int n_ranks = 1, rank = 0;
+    // peer exchange (XchgArgs, kernels.h): one device buffer per rank -- [flags 4 KB | 2 x staging | 2 x result] -- mapped into
+    // every peer with CUDA IPC; xchg_state: 0 = not tried, 1 = usable, -1 = unavailable (the NCCL path is used)
+    void* xchg_base = nullptr;
+    void* xchg_peer[kXchgMaxRanks] = {};
+    size_t xchg_cap = 0;              // capacity in int64 words
+    uint32_t xchg_epoch = 0;
+    int xchg_state = 0;
 
     int fail(const char* fmt, ...) {
         char buf[512];
@@ -371,6 +388,115 @@ int reseed_sharded(yupvq_ctx* ctx, const Blocks& b, size_t first_block, uint32_t
     return 0;
 }
 
+// ---- peer exchange buffers ------------------------------------------------------------------------
+constexpr size_t kXchgFlagBytes = 4096;
+size_t xchg_slot_stride(size_t cap, int) { return cap; }   // a slot holds a whole vector (one-shot mode); a slice in two-shot mode
+size_t xchg_bytes(size_t cap, int R) { return kXchgFlagBytes + 2 * (size_t)R * xchg_slot_stride(cap, R) * 8 + 2 * cap * 8; }
+
+void xchg_release(yupvq_ctx* ctx) {
+    for (int r = 0; r < kXchgMaxRanks; ++r) {
+        if (ctx->xchg_peer[r] && r != ctx->rank) cudaIpcCloseMemHandle(ctx->xchg_peer[r]);
+        ctx->xchg_peer[r] = nullptr;
+    }
+    if (ctx->xchg_base) cudaFree(ctx->xchg_base);
+    ctx->xchg_base = nullptr;
+    ctx->xchg_cap = 0;
+}
+
+// Collective over the communicator (every rank calls it with the same `words`): makes sure each rank owns an exchange
+// buffer of at least `words` int64 and has every peer's buffer mapped.  Returns 0 and sets *ok; *ok == false (on all ranks
+// alike) means peer mapping is not available here and the caller keeps the NCCL all-reduce.
+int xchg_ensure(yupvq_ctx* ctx, size_t words, bool* ok) {
+    *ok = false;
+    const int R = ctx->n_ranks;
+    if (!ctx->comm || R < 2 || R > kXchgMaxRanks || ctx->xchg_state < 0 || debug_opts().no_peer_xchg) return 0;
+    if (ctx->xchg_state == 1 && words <= ctx->xchg_cap) {
+        *ok = true;
+        return 0;
+    }
+    // (re)allocate: all ranks decide alike (same words, same history).  The collectives below double as the barrier that
+    // makes it safe to drop the old mapping: nobody is still inside a kernel that touches it.
+    CK(cudaStreamSynchronize(ctx->stream));
+    size_t cap = 1;
+    while (cap < words) cap <<= 1;
+    uint32_t status = 0;   // 1 = this rank failed
+    void* base = nullptr;
+    if (cudaMalloc(&base, xchg_bytes(cap, R)) != cudaSuccess || cudaMemset(base, 0, xchg_bytes(cap, R)) != cudaSuccess) {
+        cudaGetLastError();
+        status = 1;
+    }
+    cudaIpcMemHandle_t mine;
+    std::memset(&mine, 0, sizeof(mine));
+    if (!status && cudaIpcGetMemHandle(&mine, base) != cudaSuccess) {
+        cudaGetLastError();
+        status = 1;
+    }
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle size");
+    CK(ctx->s_rows.ensure((size_t)(R + 1) * 64 + 64));
+    uint8_t* hbuf = ctx->s_rows.as<uint8_t>();          // [R handles | mine | status word]
+    CK(cudaMemcpyAsync(hbuf + (size_t)R * 64, &mine, 64, cudaMemcpyHostToDevice, ctx->stream));
+    if (ctx->nccl.all_gather_bytes(ctx->comm, hbuf + (size_t)R * 64, hbuf, 64, ctx->stream)) return ctx->fail("ncclAllGather failed");
+    std::vector<cudaIpcMemHandle_t> all(R);
+    CK(cudaMemcpyAsync(all.data(), hbuf, (size_t)R * 64, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    xchg_release(ctx);   // every rank has passed the all-gather: the old buffers are idle everywhere
+    void* peer[kXchgMaxRanks] = {};
+    for (int r = 0; r < R && !status; ++r) {
+        if (r == ctx->rank) {
+            peer[r] = base;
+        } else if (cudaIpcOpenMemHandle(&peer[r], all[r], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+            cudaGetLastError();
+            peer[r] = nullptr;
+            status = 1;
+        }
+    }
+    // agree on the outcome
+    uint32_t* st_d = reinterpret_cast<uint32_t*>(hbuf + (size_t)(R + 1) * 64);
+    CK(cudaMemcpyAsync(st_d, &status, 4, cudaMemcpyHostToDevice, ctx->stream));
+    if (ctx->nccl.all_reduce_max_u32(ctx->comm, st_d, 1, ctx->stream)) return ctx->fail("ncclAllReduce(max) failed");
+    uint32_t any = 0;
+    CK(cudaMemcpyAsync(&any, st_d, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (any) {
+        for (int r = 0; r < R; ++r)
+            if (peer[r] && r != ctx->rank) cudaIpcCloseMemHandle(peer[r]);
+        if (base) cudaFree(base);
+        ctx->xchg_state = -1;
+        return 0;
+    }
+    ctx->xchg_base = base;
+    for (int r = 0; r < R; ++r) ctx->xchg_peer[r] = peer[r];
+    ctx->xchg_cap = cap;
+    ctx->xchg_epoch = 0;   // fresh counters on every rank
+    ctx->xchg_state = 1;
+    *ok = true;
+    return 0;
+}
+
+// XchgArgs of the next exchange of `words` int64 from `src`; *result receives this rank's result buffer (the tail's acc)
+void xchg_args(yupvq_ctx* ctx, const long long* src, size_t words, XchgArgs* x, const long long** result) {
+    const int R = ctx->n_ranks;
+    const size_t stride = xchg_slot_stride(ctx->xchg_cap, R);
+    x->n_ranks = R;
+    x->rank = ctx->rank;
+    x->epoch = ++ctx->xchg_epoch;
+    const uint32_t par = x->epoch & 1u;
+    x->words = words;
+    // one shot while the (R - 1) copies of the vector are a few MB (their NVLink time stays below a second phase's latency)
+    const int forced = debug_opts().xchg_mode;
+    x->one_shot = forced ? (forced == 1) : ((size_t)(R - 1) * words * 8 <= (4u << 20));
+    x->slice = (words + R - 1) / R;
+    x->slot_stride = stride;
+    x->src = src;
+    for (int r = 0; r < R; ++r) {
+        uint8_t* b = static_cast<uint8_t*>(ctx->xchg_peer[r]);
+        x->peer_flags[r] = reinterpret_cast<uint32_t*>(b);
+        x->peer_stage[r] = reinterpret_cast<long long*>(b + kXchgFlagBytes) + (size_t)par * R * stride;
+        x->peer_result[r] = reinterpret_cast<long long*>(b + kXchgFlagBytes) + 2 * (size_t)R * stride + (size_t)par * ctx->xchg_cap;
+    }
+    *result = x->peer_result[R > 0 ? ctx->rank : 0];
+}
+
 // ---- K3 dispatch: exact engine or tcgen05 front-end + exact re-rank -----------------------------------
 bool use_tensor(int mode, size_t n, uint32_t K) {
     if (mode == YUPVQ_ASSIGN_EXACT) return false;
@@ -563,15 +689,20 @@ int run_lloyd(yupvq_ctx* ctx, const Blocks& b, size_t n_total, uint32_t K, uint3
                 const float* cmax = reinterpret_cast<const float*>(sm + TC_CMAX) + (iter & 1u);
                 const bool prof = ctx->profile && ctx->pev_used + 2 <= ctx->pev.size();
                 if (prof) cudaEventRecord(ctx->pev[ctx->pev_used++], ctx->stream);
+                ctx->stage_mark(255);
                 LAUNCH(launch_assign_tc(ctx->tc_a.as<float>(), ctx->tc_xnorm.as<float>(), n, ctx->tc_b.as<float>(), ctx->tc_bx.as<float>(), K, cmax,
                                         ctx->tc_cand.as<uint4>(), assign, flags, ctx->tc_amb.as<uint32_t>(), flags + F_AMB, stopk, ctx->stream, &dl));
                 if (prof) cudaEventRecord(ctx->pev[ctx->pev_used++], ctx->stream);
+                ctx->stage_mark(0);
                 prep.force_full = iter == 0 ? 1u : 0u;
                 LAUNCH(launch_rerank_sparse(b.feat, cent, K, ctx->tc_cand.as<uint4>(), ctx->tc_amb.as<uint32_t>(), flags + F_AMB, flags + F_AMB + 1,
                                             assign, flags, flags + F_PAIRS, ctx->stream, &dl, &prep));
+                ctx->stage_mark(1);
                 LAUNCH(launch_accumulate_auto(b.feat, n, assign, K, shift, acc, dl.chg_rows, dl.chg_old, dctl, flags, stopk, ctx->stream));
+                ctx->stage_mark(2);
                 ta.iter = iter;
                 LAUNCH(launch_lloyd_tail(ta, ctx->stream));
+                ctx->stage_mark(3);
                 if (dbg.async_dbg & 1) CK(cudaStreamSynchronize(ctx->stream));
                 if ((iter == 3 || iter == 7 || iter == 15) && iter + 1 < max_iter) {
                     CK(cudaMemcpyAsync(ctx->h_small, ctl, 4, cudaMemcpyDeviceToHost, ctx->stream));
@@ -872,6 +1003,7 @@ void yupvq_destroy(yupvq_ctx* ctx) {
     if (!ctx) return;
     Scope scope(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    xchg_release(ctx);
     if (ctx->comm) ctx->nccl.destroy(ctx->comm);
     DevBuf* bufs[] = {&ctx->in_bytes, &ctx->planes, &ctx->feat, &ctx->s_planes, &ctx->s_feat, &ctx->s_rows,
                       &ctx->min_dist, &ctx->partial, &ctx->seed_idx, &ctx->canon, &ctx->small, &ctx->assign,
@@ -887,6 +1019,8 @@ void yupvq_destroy(yupvq_ctx* ctx) {
         if (ev) cudaEventDestroy(ev);
     for (auto& ev : ctx->pev)
         if (ev) cudaEventDestroy(ev);
+    for (auto& ev : ctx->sev)
+        if (ev) cudaEventDestroy(ev);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -897,9 +1031,13 @@ int yupvq_profile(yupvq_ctx* ctx, int enable) {
     if (enable && ctx->pev.empty()) {
         ctx->pev.resize(256);
         for (auto& e : ctx->pev) CK(cudaEventCreate(&e));
+        ctx->sev.resize(512);
+        ctx->sev_stage.assign(512, 255);
+        for (auto& e : ctx->sev) CK(cudaEventCreate(&e));
     }
     ctx->profile = enable != 0;
     ctx->pev_used = 0;
+    ctx->sev_used = 0;
     return 0;
 }
 
@@ -918,6 +1056,30 @@ int yupvq_profile_read(yupvq_ctx* ctx, float* out_ms_front_end, uint32_t* out_la
     ctx->pev_used = 0;
     if (out_ms_front_end) *out_ms_front_end = total;
     if (out_launches) *out_launches = n;
+    return 0;
+}
+
+int yupvq_profile_stages(yupvq_ctx* ctx, float out_ms[4], uint32_t* out_passes) {
+    if (!ctx) return 1;
+    Scope scope(ctx->device);
+    CK(cudaStreamSynchronize(ctx->stream));
+    float ms[4] = {0.f, 0.f, 0.f, 0.f};
+    uint32_t passes = 0;
+    for (size_t i = 0; i < ctx->sev_used; ++i) {
+        const int st = ctx->sev_stage[i];
+        if (st == 255) {
+            ++passes;
+            continue;
+        }
+        if (i == 0 || st > 3) continue;
+        float v = 0.f;
+        CK(cudaEventElapsedTime(&v, ctx->sev[i - 1], ctx->sev[i]));
+        ms[st] += v;
+    }
+    ctx->sev_used = 0;
+    for (int i = 0; i < 4; ++i)
+        if (out_ms) out_ms[i] = ms[i];
+    if (out_passes) *out_passes = passes;
     return 0;
 }
 
@@ -1652,6 +1814,9 @@ int yupvq_comm_init(yupvq_ctx* ctx, const uint8_t id[128], int n_ranks, int rank
     Scope scope(ctx->device);
     if (ctx->nccl.load()) return ctx->fail("cannot load NCCL: %s", ctx->nccl.error.c_str());
     if (ctx->comm) {
+        CK(cudaStreamSynchronize(ctx->stream));
+        xchg_release(ctx);
+        ctx->xchg_state = 0;
         ctx->nccl.destroy(ctx->comm);
         ctx->comm = nullptr;
     }
@@ -2156,6 +2321,7 @@ int yupvq_encode_bcn_batch_sharded(yupvq_ctx* ctx, const uint8_t* const* bc_bloc
     const int t1 = tm.mark();
 
     // ---- phase B: this rank's shard of every texture -> features, fixed-point scale, tensor operands --------
+    const bool fuse_operands = tensor && !debug_opts().no_decode_fuse;
     CK(cudaMemsetAsync(maxabs_d, 0, T * 8, ctx->stream));
     for (size_t t = 0; t < T; ++t) {
         const uint8_t* shard_dev = nullptr;
@@ -2168,7 +2334,19 @@ int yupvq_encode_bcn_batch_sharded(yupvq_ctx* ctx, const uint8_t* const* bc_bloc
             if (to_device(ctx, shard_src, nl * bb, ctx->in_bytes, &p)) return 1;
             shard_dev = reinterpret_cast<const uint8_t*>(p);
         }
-        if (n_local) {
+        if (n_local && fuse_operands) {
+            // fused feature pass (see yupvq_encode_bcn): mu = the mean of this texture's K seed rows (identical on every rank)
+            uint8_t* sm = views[t].small;
+            LAUNCH(launch_tc_mean(cent_t(t), K, reinterpret_cast<double*>(sm + TC_SUMS), reinterpret_cast<float*>(sm + TC_MU), ctx->stream));
+            ++ctx->launches;
+            DecodeFuse fu;
+            fu.mu = reinterpret_cast<const float*>(sm + TC_MU);
+            fu.a_prime = views[t].a;
+            fu.xnorm = views[t].xnorm;
+            fu.max_abs_bits = maxabs_d + t;
+            fu.rgb = ctx->tc_rgb;
+            LAUNCH(launch_decode_bcn(shard_dev, n_local, bc_format, channels, nullptr, 0, feat_t(t), nullptr, ctx->stream, &fu));
+        } else if (n_local) {
             LAUNCH(launch_decode_bcn(shard_dev, n_local, bc_format, channels, nullptr, 0, feat_t(t), nullptr, ctx->stream));
             LAUNCH(launch_max_abs(feat_t(t), n_local * 64, maxabs_d + t, ctx->stream));
         }
@@ -2183,7 +2361,7 @@ int yupvq_encode_bcn_batch_sharded(yupvq_ctx* ctx, const uint8_t* const* bc_bloc
         std::memcpy(&m, h_words + t, 4);
         shift[t] = fixed_shift(n_total, m);
     }
-    for (size_t t = 0; t < T && tensor; ++t)
+    for (size_t t = 0; t < T && tensor && !fuse_operands; ++t)
         if (tc_prepare_view(ctx, feat_t(t), n_local, views[t])) return 1;
     const int t2 = tm.mark();
 
@@ -2401,6 +2579,9 @@ int yupvq_encode_bcn_batch_sharded(yupvq_ctx* ctx, const uint8_t* const* bc_bloc
         // Fused pass for the block-sharded batch (no device reseed there): front-end, re-rank (+ update prologue), one update
         // kernel, [copy + all-reduce], one tail kernel for all textures (control, finalize, next operands).
         const bool fuse_tail = ctx->comm && delta && !debug_opts().no_tail_fuse && accumulate_auto_supported(n_local, K, (uint32_t)T);
+        // the exchange step inside the tail kernel, over peer memory (no copy, no NCCL launch); else copy + ncclAllReduce
+        bool peer_xchg = false;
+        if (fuse_tail && xchg_ensure(ctx, T * acc_words, &peer_xchg)) return 1;
         if (fuse_tail) {
             uint8_t* sm = ctx->bt_tcsmall.as<uint8_t>();
             CK(cudaMemset2DAsync(sm + TC_CMAX, TC_SMALL_BYTES, 0, 8, T, ctx->stream));
@@ -2433,21 +2614,30 @@ int yupvq_encode_bcn_batch_sharded(yupvq_ctx* ctx, const uint8_t* const* bc_bloc
                 const float* cmax = reinterpret_cast<const float*>(sm + TC_CMAX) + (iter & 1u);
                 const bool prof = ctx->profile && ctx->pev_used + 2 <= ctx->pev.size();
                 if (prof) cudaEventRecord(ctx->pev[ctx->pev_used++], ctx->stream);
+                ctx->stage_mark(255);
                 LAUNCH(launch_assign_tc(ctx->bt_tca.as<float>(), ctx->bt_xnorm.as<float>(), T * n_local, ctx->tc_b.as<float>(), ctx->tc_bx.as<float>(), K,
                                         cmax, ctx->tc_cand.as<uint4>(), ctx->bt_assign.as<uint32_t>(), tflags_d, ctx->tc_amb.as<uint32_t>(),
                                         flags + F_AMB, ctl_d, ctx->stream, &b));
                 if (prof) cudaEventRecord(ctx->pev[ctx->pev_used++], ctx->stream);
+                ctx->stage_mark(0);
                 prep.force_full = iter == 0 ? 1u : 0u;
                 LAUNCH(launch_rerank_sparse(ctx->bt_feat.as<float>(), ctx->bt_cent.as<float>(), K, ctx->tc_cand.as<uint4>(), ctx->tc_amb.as<uint32_t>(),
                                             flags + F_AMB, flags + F_AMB + 1, ctx->bt_assign.as<uint32_t>(), tflags_d, flags + F_PAIRS, ctx->stream,
                                             &b, &prep));
+                ctx->stage_mark(1);
                 LAUNCH(launch_accumulate_auto(ctx->bt_feat.as<float>(), n_local, ctx->bt_assign.as<uint32_t>(), K, 0, acc_loc, tb.chg_rows, tb.chg_old,
                                               dctl, tflags_d, ctl_d, ctx->stream, &ab));
-                CK(cudaMemcpyAsync(ctx->bt_acc.p, acc_loc, T * acc_words * 8, cudaMemcpyDeviceToDevice, ctx->stream));
-                if (ctx->nccl.all_reduce_sum_i64(ctx->comm, ctx->bt_acc.as<long long>(), T * acc_words, ctx->stream))
-                    return ctx->fail("ncclAllReduce(sum) failed");
+                ctx->stage_mark(2);
+                if (peer_xchg) {
+                    xchg_args(ctx, acc_loc, T * acc_words, &ta.x, &ta.acc);
+                } else {
+                    CK(cudaMemcpyAsync(ctx->bt_acc.p, acc_loc, T * acc_words * 8, cudaMemcpyDeviceToDevice, ctx->stream));
+                    if (ctx->nccl.all_reduce_sum_i64(ctx->comm, ctx->bt_acc.as<long long>(), T * acc_words, ctx->stream))
+                        return ctx->fail("ncclAllReduce(sum) failed");
+                }
                 ta.iter = iter;
                 LAUNCH(launch_lloyd_tail(ta, ctx->stream));
+                ctx->stage_mark(3);
                 if ((iter == 3 || iter == 7 || iter == 15) && iter + 1 < cfg->max_iterations) {  // all converged / redo needed?
                     CK(cudaMemcpyAsync(h_words, ctl_d, (7 * T + 1) * 4, cudaMemcpyDeviceToHost, ctx->stream));
                     CK(cudaStreamSynchronize(ctx->stream));

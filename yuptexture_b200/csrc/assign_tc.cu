@@ -182,6 +182,11 @@ __device__ __forceinline__ void tc_wait_ld(uint32_t (&v)[32]) {
                  :
                  : "memory");
 }
+// Read-only global load that neither nvcc nor ptxas can schedule above the computation of `after`: the address carries
+// the sign bit of `after`, which is zero at run time (after = kDotErr * |x'| * Cmax >= 0) but not provably so.
+__device__ __forceinline__ float ldg_f32_pinned(const float* p, float after) {
+    return __ldg(p + (__float_as_uint(after) >> 31));
+}
 __device__ __forceinline__ float fmax3(float a, float b, float c) {
     float d;
     asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
@@ -577,17 +582,19 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
             const size_t row = (size_t)t * BM + r;
             const float xn = xn_next;
             const uint32_t old_c = old_next;
-            {   // prefetch the next tile's |x'| and previous assignment
+            const float e_dot = kDotErr * xn * cmax;
+            {   // prefetch the next tile's |x'| and previous assignment -- AFTER the last use of this tile's values: loads issued
+                // before it share its scoreboard, and the use then waits for the new loads' DRAM latency (r02e capture)
                 const size_t nrow = (size_t)t_next * BM + r;
                 const bool has = t_next < num_tiles && nrow < n;
-                xn_next = has ? __ldg(xnorm + nrow) : 0.0f;
+                xn_next = has ? ldg_f32_pinned(xnorm + nrow, e_dot) : 0.0f;
                 if (assign) old_next = has ? assign[nrow] : 0u;
             }
             const uint32_t tpar = ti & 1u;
             mbar_wait(bar(BAR_MFULL + tpar * 4 + m), (ti >> 1) & 1u);
             bool moved = false;
             if (row < n)
-                moved = merge_row(lists, s_max, s_cnt, tpar, r, row, xn, kDotErr * xn * cmax, old_c, tex, cand, assign, flags, amb_list,
+                moved = merge_row(lists, s_max, s_cnt, tpar, r, row, xn, e_dot, old_c, tex, cand, assign, flags, amb_list,
                                   amb_count, bt);
             __syncwarp();
             if (lane == 0) mbar_arrive(bar(BAR_MEMPTY + tpar * 4 + m));
@@ -651,13 +658,14 @@ assign_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
             const size_t row = (size_t)t * BM + r;
             const float xn = xn_next;
             const uint32_t old_c = old_next;
-            {   // prefetch the next tile's |x'| (and previous assignment) so its DRAM latency hides behind this tile
+            const float e_dot = kDotErr * xn * cmax;
+            {   // prefetch the next tile's |x'| (and previous assignment) so its DRAM latency hides behind this tile; issued after
+                // e_dot, the only use of this tile's |x'| (see the merge warps)
                 const size_t nrow = (size_t)t_next * BM + r;
                 const bool has = t_next < num_tiles && nrow < n;
-                xn_next = has ? __ldg(xnorm + nrow) : 0.0f;
+                xn_next = has ? ldg_f32_pinned(xnorm + nrow, e_dot) : 0.0f;
                 if (!MW && slice == 0 && assign) old_next = has ? assign[nrow] : 0u;
             }
-            const float e_dot = kDotErr * xn * cmax;
             float m_run = -INFINITY;
             uint32_t cnt = 0;
             bool local_bad = false;  // ignored: a slice of padding columns is not an error; the merge decides
@@ -1220,7 +1228,13 @@ cudaError_t launch_assign_tc(const float* a_prime, const float* xnorm, size_t n,
     assign_tc_kernel<B, M><<<grid, (M) ? kThreadsTc2 : kThreadsTc, SMEM_TC, s>>>(tm_a, tm_b, tm_bx, xnorm, cmax, (uint32_t)n, num_tiles, \
                                                                                 num_chunks, res_b, cand, assign, flags, amb_list,       \
                                                                                 amb_count, stop, bt)
-    if (batch && n_tex > 1) {
+    static const bool force_batch = getenv("YUPVQ_TC_FORCE_BATCH") != nullptr;   // diagnostic only (codegen A/B on one texture)
+    if (force_batch && !(batch && n_tex > 1)) {
+        bt.tiles_per_tex = num_tiles;
+        bt.n_textures = 1;
+        bt.rows_per_tex = (uint32_t)n;
+    }
+    if ((batch && n_tex > 1) || force_batch) {
         if (v1) YUPVQ_TC_LAUNCH(true, false);
         else YUPVQ_TC_LAUNCH(true, true);
     } else {

@@ -219,7 +219,27 @@ cudaError_t launch_max_abs(const float* x, size_t n, uint32_t* out_bits, cudaStr
 // parity: the front-end of pass p reads small[cmax_off + 4 * (p & 1)], this kernel max-reduces the next pass' value into slot
 // (iter + 1) & 1 and zeroes slot iter & 1 for the tail after it.  errors == null (or n_textures > 1): no device reseed;
 // `sticky` (may be null) is raised when a running texture has an empty cluster.
+// Exchange step of a block-sharded pass as part of the tail kernel: a two-shot all-reduce of the int64
+// partial sums over NVLink peer memory instead of copy + ncclAllReduce.  Every rank pushes slice j of its partial sums into
+// rank j's staging area, rank j adds the R contributions (integer adds: any order gives the same bits) and pushes the
+// totals of its slice into every rank's result buffer; monotonic counters (one per phase and source rank, bumped with
+// red.release.sys by every CTA, polled with ld.acquire.sys) order the two phases -- no grid-wide barrier, no host round trip.
+// The data buffers alternate with the parity of a per-context epoch.  n_ranks == 0: off.
+constexpr int kXchgMaxRanks = 16;
+struct XchgArgs {
+    int n_ranks = 0, rank = 0;
+    int one_shot = 0;                         // 1: every rank receives every peer's whole vector and adds on read (small vectors)
+    uint32_t epoch = 0;                       // number of this exchange (1, 2, ...): counters reach epoch * grid size; parity = epoch & 1
+    size_t words = 0;                         // int64 words exchanged
+    size_t slice = 0;                         // words per owner slice (ceil(words / n_ranks))
+    size_t slot_stride = 0;                   // words between the per-source-rank slots of a staging area
+    const long long* src = nullptr;           // this rank's partial sums
+    long long* peer_stage[kXchgMaxRanks];     // rank j's staging area of this parity (n_ranks slots), mapped into this process
+    long long* peer_result[kXchgMaxRanks];    // rank j's result buffer of this parity
+    uint32_t* peer_flags[kXchgMaxRanks];      // rank j's counters: [2 phases][kXchgMaxRanks sources]
+};
 struct TailArgs {
+    XchgArgs x;                // n_ranks > 1: `acc` is this rank's result buffer, filled by the exchange at the head of the kernel
     const long long* acc;      // (all-reduced) accumulators
     size_t acc_stride;         // int64 words between textures
     uint32_t n_textures, K, k_pad, iter, break_after;

@@ -28,6 +28,15 @@ namespace {
 
 constexpr int kTailThreads = 256;
 
+__device__ __forceinline__ void red_release_sys_add_u32(uint32_t* p, uint32_t v) {
+    asm volatile("red.release.sys.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys_u32(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
 __global__ void __launch_bounds__(kTailThreads) lloyd_tail_kernel(TailArgs a) {
     cg::grid_group grid = cg::this_grid();
     __shared__ unsigned int s_empty;
@@ -35,9 +44,64 @@ __global__ void __launch_bounds__(kTailThreads) lloyd_tail_kernel(TailArgs a) {
     __shared__ unsigned long long s_idx[kTailThreads / 32];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const uint32_t K = a.K;
+    // ---- 0. block-sharded batch: the exchange step (XchgArgs, kernels.h) -- after it the sums of all ranks can be read.
+    // No grid-wide barrier: every CTA pushes its part, bumps a counter on each peer (release, system scope) and waits on
+    // this rank's own counters, which are monotonic: exchange number `epoch` is complete once a counter has reached
+    // epoch * gridDim.x.  (The data buffers alternate with the epoch's parity; the counters need not.)
+    const XchgArgs& x = a.x;
+    const bool sum_on_read = x.n_ranks > 1 && x.one_shot != 0;
+    if (x.n_ranks > 1) {
+        const int R = x.n_ranks;
+        const size_t gtid = (size_t)blockIdx.x * kTailThreads + tid, gsz = (size_t)gridDim.x * kTailThreads;
+        const uint32_t target = x.epoch * gridDim.x;
+        auto signal_and_wait = [&](int phase) {
+            __syncthreads();
+            if (tid < R) {   // release: cumulative over the CTA's stores ordered before it by the barrier
+                red_release_sys_add_u32(x.peer_flags[tid] + phase * kXchgMaxRanks + x.rank, 1u);
+                const uint32_t* mine = x.peer_flags[x.rank] + phase * kXchgMaxRanks + tid;
+                while ((int32_t)(ld_acquire_sys_u32(mine) - target) < 0) {}
+            }
+            __syncthreads();
+        };
+        if (x.one_shot) {
+            // one shot: the whole vector goes to every peer's slot for this rank; readers add the R vectors as they go
+            for (int j = 0; j < R; ++j) {
+                if (j == x.rank) continue;
+                long long* dst = x.peer_stage[j] + (size_t)x.rank * x.slot_stride;
+                for (size_t w = gtid; w < x.words; w += gsz) dst[w] = x.src[w];
+            }
+            signal_and_wait(0);
+        } else {
+            // two shots: slice j of this rank's partial sums goes to rank j's slot for this rank ...
+            for (size_t w = gtid; w < x.words; w += gsz) {
+                const size_t j = w / x.slice;
+                x.peer_stage[j][(size_t)x.rank * x.slot_stride + (w - j * x.slice)] = x.src[w];
+            }
+            signal_and_wait(0);
+            // ... rank j adds the R contributions of its slice and pushes the totals to every rank
+            const size_t s0 = (size_t)x.rank * x.slice;
+            const size_t s1 = s0 + x.slice < x.words ? s0 + x.slice : x.words;
+            const long long* stage = x.peer_stage[x.rank];
+            for (size_t w = s0 + gtid; w < s1; w += gsz) {
+                long long t = 0;
+                for (int r = 0; r < R; ++r) t += __ldcg(stage + (size_t)r * x.slot_stride + (w - s0));
+                for (int j = 0; j < R; ++j) x.peer_result[j][w] = t;
+            }
+            signal_and_wait(1);
+        }
+    }
+    // word w of the (all-reduced) accumulator vector
+    auto ld_acc = [&](size_t w) -> long long {
+        if (!sum_on_read) return __ldcg(a.acc + w);
+        long long t = __ldcg(x.src + w);
+        const long long* stage = x.peer_stage[x.rank];
+        for (int r = 0; r < x.n_ranks; ++r)
+            if (r != x.rank) t += __ldcg(stage + (size_t)r * x.slot_stride + w);
+        return t;
+    };
     bool any_rare = false;   // uniform across the grid: every CTA evaluates the same words
     for (uint32_t tex = 0; tex < a.n_textures; ++tex) {
-        const long long* acc = a.acc + (size_t)tex * a.acc_stride;
+        const size_t acc0 = (size_t)tex * a.acc_stride;   // this texture's words in the accumulator vector
         uint32_t* ctl = a.ctl + (size_t)tex * 3;
         uint32_t* flags = a.flags + (size_t)tex * a.flags_stride;
         // ---- 1. control (every CTA computes the same decision; CTA 0 publishes it)
@@ -46,12 +110,12 @@ __global__ void __launch_bounds__(kTailThreads) lloyd_tail_kernel(TailArgs a) {
         __syncthreads();
         unsigned int local = 0;
         if (!stopped)
-            for (uint32_t c = tid; c < K; c += kTailThreads) local += __ldcg(acc + (size_t)K * 64 + c) == 0 ? 1u : 0u;
+            for (uint32_t c = tid; c < K; c += kTailThreads) local += ld_acc(acc0 + (size_t)K * 64 + c) == 0 ? 1u : 0u;
         local = warp_sum(local);
         if (lane == 0 && local) atomicAdd(&s_empty, local);
         __syncthreads();
         const unsigned int n_empty = s_empty;
-        const bool changed = __ldcg(acc + (size_t)K * 65) != 0;
+        const bool changed = ld_acc(acc0 + (size_t)K * 65) != 0;
         const bool stop_now = !stopped && !changed && a.iter > a.break_after;
         __syncthreads();
         if (stopped || stop_now) {
@@ -100,12 +164,12 @@ __global__ void __launch_bounds__(kTailThreads) lloyd_tail_kernel(TailArgs a) {
                 const bool real = c < K;
                 float x0 = 0.0f, x1 = 0.0f;
                 if (real) {
-                    const uint32_t cnt = (uint32_t)__ldcg(acc + (size_t)K * 64 + c);
+                    const uint32_t cnt = (uint32_t)ld_acc(acc0 + (size_t)K * 64 + c);
                     if (empties_only && cnt != 0) continue;
                     if (cnt > 0) {
                         const float inv = __fdiv_rn(1.0f, (float)cnt);                                 // 1.0f / counts[c]
-                        x0 = __fmul_rn((float)((double)__ldcg(acc + (size_t)c * 64 + lane) * inv_scale), inv);   // the sum, rounded to fp32 once
-                        x1 = __fmul_rn((float)((double)__ldcg(acc + (size_t)c * 64 + 32 + lane) * inv_scale), inv);
+                        x0 = __fmul_rn((float)((double)ld_acc(acc0 + (size_t)c * 64 + lane) * inv_scale), inv);   // the sum, rounded to fp32 once
+                        x1 = __fmul_rn((float)((double)ld_acc(acc0 + (size_t)c * 64 + 32 + lane) * inv_scale), inv);
                         cent[(size_t)c * 64 + lane] = x0;
                         cent[(size_t)c * 64 + 32 + lane] = x1;
                     } else {   // empty: the old centroid stays (or the reseeded row, second call)
@@ -126,7 +190,7 @@ __global__ void __launch_bounds__(kTailThreads) lloyd_tail_kernel(TailArgs a) {
             const size_t stripe = (a.n_rows + gridDim.x - 1) / gridDim.x;
             const size_t r0 = (size_t)blockIdx.x * stripe, r1 = r0 + stripe < a.n_rows ? r0 + stripe : a.n_rows;
             for (uint32_t c = 0; c < K; ++c) {
-                if (__ldcg(acc + (size_t)K * 64 + c) != 0) continue;
+                if (ld_acc(acc0 + (size_t)K * 64 + c) != 0) continue;
                 // this CTA's stripe: (max, first index)
                 float bv = -FLT_MAX;
                 unsigned long long bi = ~0ull;
