@@ -424,3 +424,30 @@ def test_config4_reference_psnr_on_crop(enc, reflib):
     i_on_ref, _ = enc.quantize_blocks_hdr(px, 3, c_ref)
     assert (i_on_ref == i_ref).mean() >= 0.9999
     assert abs(_hdr_psnr_delta_db(px, cent, idx, c_ref, i_ref)) <= PSNR_TOL_DB
+
+
+@pytest.mark.parametrize("switch", ["YUPVQ_TC_V1", "YUPVQ_NO_DECODE_FUSE", "YUPVQ_NO_TAIL_FUSE", "YUPVQ_NO_DELTA", "YUPVQ_NO_SPLIT_DECODE",
+                                    "YUPVQ_BATCH_PER_TEXTURE", "YUPVQ_SEED_NO_PAL"])
+def test_implementation_switches_do_not_change_results(switch):
+    """Every A/B switch of csrc/host_util.h selects between two implementations of the same arithmetic (merge-warp front-end
+    vs one barrier per tile, fused feature pass vs separate operand passes, fused pass tail vs separate kernels, delta vs full
+    update, split decode, whole-batch vs per-texture launches, palette-form vs pixel-plane seeding): the outputs of a fixed
+    set of encodes are bit-identical either way."""
+    import subprocess
+    import sys
+    root = os.path.normpath(os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
+    script = os.path.join(root, "tools", "variant_hash.py")
+
+    def run(extra):
+        env = {k: v for k, v in os.environ.items() if not k.startswith("YUPVQ_")}
+        env.update(extra)
+        r = subprocess.run([sys.executable, script], capture_output=True, text=True, timeout=600, env=env)
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+        return [ln for ln in r.stdout.splitlines() if ln.startswith("VARIANT_HASH")][0]
+
+    global _BASE_HASH
+    try:
+        base = _BASE_HASH
+    except NameError:
+        base = _BASE_HASH = run({})
+    assert run({switch: "1"}) == base

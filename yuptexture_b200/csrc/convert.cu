@@ -365,27 +365,71 @@ __global__ void __launch_bounds__(kTile) pixels_kernel(const uint8_t* __restrict
 
 // ---- K1h: float tiles / raw float image -> features ----------------------------------------------
 
-// VQEncoder::RgbaFloatBlockToOklabBlock, src/vq_encoder.cpp:179-185, with a one-entry cache (the
-// synthetic HDR skybox and real skies are piecewise constant).
+// VQEncoder::RgbaFloatBlockToOklabBlock, src/vq_encoder.cpp:179-185.  The conversion (fp64 cbrt / pow) is the cost, and HDR
+// blocks are often piecewise constant (skies, the synthetic skybox), so it is de-duplicated the way block_features does it
+// for LDR blocks, in three steps that keep the warp converged through the fp64 code: (1) compares only: every texel gets
+// the slot of its (r, g, b) bit pattern in a 4-entry key list, or an overflow bit once the block has shown a fifth colour;
+// (2) slot j is converted by all lanes together while any lane of the warp has more than j colours; (3) texels pick their
+// slot, overflow texels are converted one by one (blocks with many colours: no worse than a plain loop).  The r01 version
+// kept a one-entry cache inside the 16-texel loop: lanes missed at different texels and the warp walked the fp64 code at
+// every position where any lane missed.  Same function on the same bits: identical features.
 template <int CH>
 __device__ __forceinline__ void float_block_features(const float (&v)[16 * CH], float4 (&f)[16]) {
-    float kr = __int_as_float(0x7fc00001), kg = kr, kb = kr;  // NaN keys never compare equal
-    float3 last = make_float3(0.f, 0.f, 0.f);
+    auto rgb_of = [&](int p, float& r, float& g, float& b) {
+        if (CH == 1) r = g = b = v[p];
+        else if (CH == 2) r = g = b = v[2 * p];
+        else { r = v[p * CH]; g = v[p * CH + 1]; b = v[p * CH + 2]; }
+    };
+    uint32_t kr[4], kg[4], kb[4];
+    uint32_t slots = 0, overflow = 0;
+    int count = 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) kr[j] = kg[j] = kb[j] = 0u;
 #pragma unroll
     for (int p = 0; p < 16; ++p) {
-        float r, g, b, alpha = 1.0f;
-        if (CH == 1) r = g = b = v[p];
-        else if (CH == 2) { r = g = b = v[2 * p]; alpha = v[2 * p + 1]; }
-        else {
-            r = v[p * CH]; g = v[p * CH + 1]; b = v[p * CH + 2];
-            if (CH == 4) alpha = v[p * CH + 3];
+        float r, g, b;
+        rgb_of(p, r, g, b);
+        const uint32_t ur = __float_as_uint(r), ug = __float_as_uint(g), ub = __float_as_uint(b);
+        uint32_t s = 4;
+#pragma unroll
+        for (int j = 3; j >= 0; --j)
+            if (j < count && ur == kr[j] && ug == kg[j] && ub == kb[j]) s = (uint32_t)j;
+        if (s == 4) {
+            if (count < 4) {
+                s = (uint32_t)count;
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    if (j == count) { kr[j] = ur; kg[j] = ug; kb[j] = ub; }
+                ++count;
+            } else {
+                s = 0;
+                overflow |= 1u << p;
+            }
         }
-        if (!(__float_as_uint(r) == __float_as_uint(kr) && __float_as_uint(g) == __float_as_uint(kg) &&
-              __float_as_uint(b) == __float_as_uint(kb))) {
-            last = float_to_oklab(r, g, b);
-            kr = r; kg = g; kb = b;
+        slots |= s << (2 * p);
+    }
+    float3 val[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        val[j] = make_float3(0.f, 0.f, 0.f);
+        if (__any_sync(__activemask(), count > j)) {
+            const bool has = count > j;
+            val[j] = float_to_oklab(has ? __uint_as_float(kr[j]) : 0.0f, has ? __uint_as_float(kg[j]) : 0.0f, has ? __uint_as_float(kb[j]) : 0.0f);
         }
-        f[p] = make_float4(last.x, last.y, last.z, alpha);
+    }
+#pragma unroll
+    for (int p = 0; p < 16; ++p) {
+        const uint32_t s = (slots >> (2 * p)) & 3u;
+        float3 o = s == 0 ? val[0] : s == 1 ? val[1] : s == 2 ? val[2] : val[3];
+        if (overflow & (1u << p)) {
+            float r, g, b;
+            rgb_of(p, r, g, b);
+            o = float_to_oklab(r, g, b);
+        }
+        float alpha = 1.0f;
+        if (CH == 2) alpha = v[2 * p + 1];
+        if (CH == 4) alpha = v[p * CH + 3];
+        f[p] = make_float4(o.x, o.y, o.z, alpha);
     }
 }
 
