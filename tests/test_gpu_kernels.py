@@ -277,3 +277,27 @@ def test_gather_codebook(enc):
         want = cb[np.minimum(idx, 511)]
         want[5] = 0
         assert bits_equal(out, want)
+
+
+def test_assign_tensor_adversarial_near_ties(enc, oracle):
+    """the margin's accumulation term is established by test.  Rows with large |x'||c'| whose two best centroids
+    differ by a few ulps of the score, components of alternating sign and mixed magnitude (worst case for the fp32 accumulation
+    inside the tensor core): the tensor engine must return the exact engine's (= the oracle's) indices and errors."""
+    rng = np.random.default_rng(77)
+    k, n = 512, 40000
+    base = rng.uniform(-1.0, 1.0, (k // 2, 64)).astype(np.float32)
+    base *= (1.0 + 6.0 * (rng.uniform(size=(k // 2, 64)) < 0.2)).astype(np.float32)          # a few large components
+    base *= np.where(np.arange(64) % 2 == 0, 1.0, -1.0).astype(np.float32)                    # alternating signs
+    twin = base.copy()
+    j = rng.integers(0, 64, k // 2)
+    twin[np.arange(k // 2), j] = np.nextafter(twin[np.arange(k // 2), j], np.float32(np.inf))  # one ulp apart in one column
+    cent = np.concatenate([base, twin]).astype(np.float32)
+    pick = rng.integers(0, k // 2, n)
+    # rows close to the midpoint of a twin pair: both centroids are candidates, the exact re-rank must decide
+    feat = (0.5 * (base[pick] + twin[pick]) + rng.normal(0, 1e-4, (n, 64))).astype(np.float32)
+    i_e, e_e, _ = enc.assign(feat, cent, assign_mode=1)
+    i_t, e_t, st = enc.assign(feat, cent, assign_mode=2)
+    i_r, e_r = oracle.assign(feat, cent)
+    assert np.array_equal(i_e, i_r) and bits_equal(e_e, e_r)
+    assert np.array_equal(i_t, i_e) and bits_equal(e_t, e_e)
+    assert st.rerank_blocks > n     # the twins really were ambiguous for the front-end

@@ -22,7 +22,7 @@
 //   D  = 128 lanes x 256 columns fp32 in TMEM, two accumulator stages (512 columns).
 // The epilogue (16 warps, one TMEM lane == one block per thread, four column slices) makes two passes over each
 // accumulator stage: max3 reduction, then a sign-bit sweep that collects every centroid whose score
-// is within a proven error margin of the running maximum.  Blocks end up with a short candidate list
+// is within the error margin (header comment below) of the running maximum.  Blocks end up with a short candidate list
 // (uint16 x 7 + count in one uint4); rerank_kernel evaluates those candidates with the reference's
 // exact operation order (common.cuh DistAcc) and resolves ties to the lowest index.
 //
