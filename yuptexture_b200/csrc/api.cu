@@ -40,6 +40,7 @@ const DebugOpts& debug_opts() {
         o.batch_per_texture = on("YUPVQ_BATCH_PER_TEXTURE");
         o.no_tail_fuse = on("YUPVQ_NO_TAIL_FUSE");
         o.no_peer_xchg = on("YUPVQ_NO_PEER_XCHG");
+        o.tc_force_batch = on("YUPVQ_TC_FORCE_BATCH");
         if (const char* v = getenv("YUPVQ_XCHG_MODE")) o.xchg_mode = atoi(v);
         o.tc_v1 = on("YUPVQ_TC_V1");   // v2 (merge warps) is the default since r02c: 0.143 against 0.177 ms per pass, bit-identical
         if (const char* v = getenv("YUPVQ_ASYNC_DBG")) o.async_dbg = atoi(v);

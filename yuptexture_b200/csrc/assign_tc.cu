@@ -1228,7 +1228,7 @@ cudaError_t launch_assign_tc(const float* a_prime, const float* xnorm, size_t n,
     assign_tc_kernel<B, M><<<grid, (M) ? kThreadsTc2 : kThreadsTc, SMEM_TC, s>>>(tm_a, tm_b, tm_bx, xnorm, cmax, (uint32_t)n, num_tiles, \
                                                                                 num_chunks, res_b, cand, assign, flags, amb_list,       \
                                                                                 amb_count, stop, bt)
-    static const bool force_batch = getenv("YUPVQ_TC_FORCE_BATCH") != nullptr;   // diagnostic only (codegen A/B on one texture)
+    const bool force_batch = debug_opts().tc_force_batch;   // diagnostic only (codegen A/B on one texture)
     if (force_batch && !(batch && n_tex > 1)) {
         bt.tiles_per_tex = num_tiles;
         bt.n_textures = 1;

@@ -25,6 +25,7 @@ struct DebugOpts {
     bool batch_per_texture = false;  // YUPVQ_BATCH_PER_TEXTURE   lock-step batch with per-texture launches
     bool no_tail_fuse = false;       // YUPVQ_NO_TAIL_FUSE        separate control / errors / finalize / reseed / prep launches
     bool tc_v1 = false;              // YUPVQ_TC_V1               tensor front-end with the one-barrier-per-tile epilogue (no merge warps)
+    bool tc_force_batch = false;     // YUPVQ_TC_FORCE_BATCH      single texture through the batch instantiation of the front-end (codegen A/B)
     bool no_peer_xchg = false;       // YUPVQ_NO_PEER_XCHG        sharded batch: copy + ncclAllReduce instead of the in-kernel peer exchange
     int xchg_mode = 0;               // YUPVQ_XCHG_MODE           peer exchange: 1 = one shot, 2 = two shots (default: by size)
     int async_dbg = 0;               // YUPVQ_ASYNC_DBG           bit 0: sync after every pass, bit 3: per-pass delta statistics on stderr

@@ -42,3 +42,41 @@ def partial_sums(features, assign, k, shift):
     np.add.at(acc[:k * 64].reshape(k, 64), assign, fx)
     np.add.at(acc[k * 64:], assign, 1)
     return acc
+
+
+# ---- the exchange step of a sharded pass (csrc/tail.cu, XchgArgs in csrc/kernels.h) ----------------------
+ONE_SHOT_LIMIT_BYTES = 4 << 20
+
+
+def exchange_plan(words, world):
+    """How the in-kernel exchange moves a vector of `words` int64: (one_shot, slice_words).  One shot while the world - 1
+    copies of the vector stay within a few MB, else two shots over owner slices of ceil(words / world) (csrc/api.cu
+    xchg_args)."""
+    one_shot = (world - 1) * words * 8 <= ONE_SHOT_LIMIT_BYTES
+    return one_shot, (words + world - 1) // world
+
+
+def exchange_push(partial, world, rank, one_shot, slice_words):
+    """What rank `rank` stores into the peers' staging slots: a list of `world` arrays, entry j going to rank j's slot for
+    `rank` (one shot: the whole vector to everyone else; two shots: slice j to its owner j)."""
+    partial = np.asarray(partial, np.int64)
+    if one_shot:
+        return [partial if j != rank else partial[:0] for j in range(world)]
+    return [partial[j * slice_words:(j + 1) * slice_words] for j in range(world)]
+
+
+def exchange_reduce_slice(slots):
+    """Two shots, phase 1: the owner adds the `world` contributions of its slice (integer adds: order-free)."""
+    out = np.zeros_like(slots[0])
+    for s in slots:
+        out = out + s
+    return out
+
+
+def exchange_sum_on_read(own, slots, rank):
+    """One shot: a reader adds its own vector and the other ranks' slots as it goes (csrc/tail.cu ld_acc)."""
+    out = np.asarray(own, np.int64).copy()
+    for r, s in enumerate(slots):
+        if r != rank:
+            out = out + s
+    return out
