@@ -85,6 +85,7 @@ struct yupvq_ctx {
     std::string err;
     cudaEvent_t ev[12] = {};
     cudaEvent_t ev_user[2] = {};
+    cudaEvent_t ev_poll = nullptr;   // lagged convergence poll of the fused Lloyd loops
     uint32_t launches = 0;
     uint32_t reseeds_sharded = 0;
 
@@ -705,9 +706,15 @@ int run_lloyd(yupvq_ctx* ctx, const Blocks& b, size_t n_total, uint32_t K, uint3
                 LAUNCH(launch_lloyd_tail(ta, ctx->stream));
                 ctx->stage_mark(3);
                 if (dbg.async_dbg & 1) CK(cudaStreamSynchronize(ctx->stream));
+                // Lagged poll: the stop word after passes 3 / 7 / 15 is read back while the NEXT pass is already queued, so the
+                // GPU never drains for it (a blocking read cost three pipeline bubbles per texture); a texture that has
+                // converged runs one more no-op pass than it would need to.
                 if ((iter == 3 || iter == 7 || iter == 15) && iter + 1 < max_iter) {
                     CK(cudaMemcpyAsync(ctx->h_small, ctl, 4, cudaMemcpyDeviceToHost, ctx->stream));
-                    CK(cudaStreamSynchronize(ctx->stream));
+                    CK(cudaEventRecord(ctx->ev_poll, ctx->stream));
+                }
+                if (iter == 4 || iter == 8 || iter == 16) {
+                    CK(cudaEventSynchronize(ctx->ev_poll));
                     if (ctx->h_small[0]) break;
                 }
             }
@@ -987,6 +994,7 @@ int yupvq_create(int device, yupvq_ctx** out) {
     bool ok = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) == cudaSuccess;
     for (auto& ev : ctx->ev) ok = ok && cudaEventCreate(&ev) == cudaSuccess;
     for (auto& ev : ctx->ev_user) ok = ok && cudaEventCreate(&ev) == cudaSuccess;
+    ok = ok && cudaEventCreateWithFlags(&ctx->ev_poll, cudaEventDisableTiming) == cudaSuccess;
     ok = ok && cudaMallocHost(reinterpret_cast<void**>(&ctx->h_small), 65536) == cudaSuccess;
     ok = ok && ctx->small.ensure(F_WORDS * 4) == cudaSuccess;
     ok = ok && cudaMemset(ctx->small.p, 0, F_WORDS * 4) == cudaSuccess;
@@ -1018,6 +1026,7 @@ void yupvq_destroy(yupvq_ctx* ctx) {
         if (ev) cudaEventDestroy(ev);
     for (auto& ev : ctx->ev_user)
         if (ev) cudaEventDestroy(ev);
+    if (ctx->ev_poll) cudaEventDestroy(ctx->ev_poll);
     for (auto& ev : ctx->pev)
         if (ev) cudaEventDestroy(ev);
     for (auto& ev : ctx->sev)
@@ -2639,9 +2648,13 @@ int yupvq_encode_bcn_batch_sharded(yupvq_ctx* ctx, const uint8_t* const* bc_bloc
                 ta.iter = iter;
                 LAUNCH(launch_lloyd_tail(ta, ctx->stream));
                 ctx->stage_mark(3);
-                if ((iter == 3 || iter == 7 || iter == 15) && iter + 1 < cfg->max_iterations) {  // all converged / redo needed?
+                // all converged / redo needed?  Lagged poll (see run_lloyd): read back behind the next pass, no drain
+                if ((iter == 3 || iter == 7 || iter == 15) && iter + 1 < cfg->max_iterations) {
                     CK(cudaMemcpyAsync(h_words, ctl_d, (7 * T + 1) * 4, cudaMemcpyDeviceToHost, ctx->stream));
-                    CK(cudaStreamSynchronize(ctx->stream));
+                    CK(cudaEventRecord(ctx->ev_poll, ctx->stream));
+                }
+                if (iter == 4 || iter == 8 || iter == 16) {
+                    CK(cudaEventSynchronize(ctx->ev_poll));
                     bool all_stopped = true;
                     for (size_t t = 0; t < T; ++t) all_stopped = all_stopped && h_words[3 * t] != 0;
                     if (all_stopped || h_words[7 * T]) break;
