@@ -7,14 +7,16 @@ One "step" = one pass of the whole VQ hot path over one synthetic 4096^2 BC1 tex
 blocks, K = 512, 32 Lloyd iterations max, Oklab metric): BCn decode -> Oklab features, K-Means++
 seeding, Lloyd iterations, centroid conversion, final assignment.  N > 1 (torchrun, one rank per
 GPU): weak scaling -- N textures per step in lock step (BASELINE config 5's shape), every texture's blocks
-sharded over the N GPUs, seeding texture-parallel (texture t on rank t % N), and ONE NCCL all-reduce per
-Lloyd pass carrying the K x 65 fixed-point sums/counts of all N textures (the exchange step north_star names).
+sharded over the N GPUs, seeding texture-parallel (texture t on rank t % N), and ONE exchange per Lloyd pass
+carrying the K x 65 fixed-point sums/counts of all N textures (the exchange step north_star names): inside the pass-tail
+kernel over NVLink peer memory, or one NCCL all-reduce where peers cannot be mapped (YUPVQ_NO_PEER_XCHG=1 forces it).
+--textures T / --placement texture: BASELINE config 5 as stated (64 textures) and the zero-collective placement.
 
 `value`  : blocks/s with the BCn bytes already resident in HBM and outputs left in HBM.
 `e2e`    : the same through the C ABI with HOST (pinned) buffers: H2D of the BCn bytes and D2H of the
            centroids + indices inside the timed region.
---impl reference : the unmodified reference (oracle/_ref, else the CPU port) on the host cores, on
-           a bounded sample (a crop of the same texture) per step.
+--impl reference : the unmodified reference (oracle/_ref) on all host cores, one full pass over the same 4096^2
+           texture per timed step (8.6 s on 16 cores); the scalar CPU port on a crop where oracle/_ref is not built.
 """
 import argparse
 import json
@@ -391,8 +393,9 @@ def run_ours(args, rank, world, local_rank):
         cfgd = workload_config(n_tex)
         par = "1 GPU" if world == 1 and n_tex == 1 else (
             f"{n_tex} textures, texture-parallel placement: whole textures on rank t % {world}, zero collectives" if texture_parallel else
-            f"{n_tex} textures in lock step, blocks sharded over {world} GPU(s), seeding texture-parallel, one NCCL all-reduce of "
-            f"{n_tex} x K x 65 int64 per pass; a rank receives whole only the textures it seeds and its block shard of the others")
+            f"{n_tex} textures in lock step, blocks sharded over {world} GPU(s), seeding texture-parallel, one exchange of "
+            f"{n_tex} x K x 65 int64 per pass (inside the pass-tail kernel over NVLink peer memory; ncclAllReduce where peers cannot be "
+            f"mapped or the batch exceeds the fused path); a rank receives whole only the textures it seeds and its block shard of the others")
         out = {
             "metric": "vq_blocks_per_sec", "value": value, "unit": "blocks/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(3, args.warmup), "ms_per_step": ms_dev / args.steps, "higher_is_better": True,
