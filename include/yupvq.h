@@ -187,6 +187,33 @@ YUPVQ_API int yupvq_update_centroids(yupvq_ctx* ctx, const float* features, size
 YUPVQ_API int yupvq_gather_codebook(yupvq_ctx* ctx, const uint8_t* codebook, uint32_t n_entries, uint32_t block_size,
                                     const uint32_t* indices, size_t n_blocks, uint8_t* out_bc_blocks);
 
+/* The same update for callers that cannot allocate GPU memory.  No counterpart in the reference (its update works in
+ * std::vector on the host); this exists because every other entry point needs a yupvq_ctx, and creating or growing a
+ * context calls cudaMalloc / cudaMallocHost.  That rules the library out for a pipeline embedded in an engine or tool
+ * whose own allocator already owns the whole device, for code in a frame loop that cannot afford the process-wide stall
+ * of a driver allocation, and for plugins whose host application hands them buffers and forbids them device memory of
+ * their own.  This call takes no context and allocates nothing: its working memory (fixed-point sums, counts and a few
+ * flag words) is an array built into the library, 520 KiB, which every GPU that loads libyupvq.so carries until the
+ * process exits.
+ *   - every buffer is DEVICE (or managed) memory owned by the caller, valid on `device`; host pointers are refused
+ *     (staging them would need an allocation).  cuda_stream is a cudaStream_t of that device (NULL = default stream).
+ *   - codebook_size <= YUPVQ_STATIC_MAX_CODEBOOK (what the array was sized for); larger values are an error.
+ *     assignments[i] must be < codebook_size, as for yupvq_update_centroids.
+ *   - inout_errors is modified IN PLACE by the empty-cluster reseed (the error of each block taken as a new centroid
+ *     becomes 0, src/vq_encoder.cpp:373); yupvq_update_centroids works on a private copy instead.
+ *   - out_counts (may be NULL): codebook_size uint32 in device memory.
+ *   - centroids and counts are bit-identical to yupvq_update_centroids on the same inputs.
+ *   - all calls on a device share the one array.  It keeps the previous call's contents, so each call first clears the
+ *     words it uses; two calls whose GPU work overlaps (e.g. two host threads) overwrite each other's sums -- serialise
+ *     them.  The call returns after its work on cuda_stream has finished.
+ *   - the first call on each device also resolves the array's device address and sets a kernel attribute; make that
+ *     first call outside any stream capture.
+ *   - returns 0, or non-zero with a message in err_text (caller's buffer of err_len bytes; may be NULL). */
+#define YUPVQ_STATIC_MAX_CODEBOOK 1024
+YUPVQ_API int yupvq_update_centroids_static(int device, void* cuda_stream, const float* features, size_t n_blocks,
+                                            const uint32_t* assignments, float* inout_errors, uint32_t codebook_size,
+                                            float* inout_centroids, uint32_t* out_counts, char* err_text, size_t err_len);
+
 /* ---- N4: the whole-texture BCn pre-pass on the GPU ---------------------------------------------- */
 
 /* BCnCompressor::Compress, src/bcn_compressor.cpp:45-116 (called at src/vq_bcn_compressor.cpp:94), for BC1, BC3, BC4
