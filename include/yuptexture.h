@@ -93,6 +93,8 @@ struct CompressionParams {
 // integrator.  This build decodes on the GPU (bit-exact with Compressonator 4.3 for
 // BC1/BC3/BC4/BC5/BC7) and ships small bounding-box encoders for BC1/BC3/BC4/BC5 and a mode-6 BC7
 // encoder so the API is usable stand-alone; an integrator installs the real encoders with SetCodec().
+// The stand-ins are not silent: the first time one of them writes blocks the library prints one line on stderr naming the
+// fallback (YUPTEXTURE_QUIET=1 suppresses it); LastEncoderName() reports which encoder a call used.
 class YUPTEXTURE_API BCnCompressor {
 public:
     struct Codec {  // any member left empty keeps the built-in behaviour

@@ -224,7 +224,9 @@ YUPVQ_API int yupvq_update_centroids_static(int device, void* cuda_stream, const
  * Compressonator reads CMP_FORMAT_RGB_888 sources that way, so the reference's VQ path (flipRGB == false) corresponds
  * to swap_rb = (channels == 3) and its bypass path (flipRGB == true, :61-76) to swap_rb = 0.  alpha_threshold: BC1 with
  * a 4-channel source puts texels with alpha below it on the transparent entry (CMP_CompressOptions::nAlphaThreshold,
- * :103-107).  out_ms_kernel (may be NULL): CUDA-event time of the encode kernel. */
+ * :103-107).  out_ms_kernel (may be NULL): CUDA-event time of the encode kernel.  A device out_bc_blocks aligned to the
+ * block size (8 or 16 bytes) is written in place; any other pointer (host memory, or a misaligned slice of a device
+ * buffer) is filled through a staging copy. */
 YUPVQ_API int yupvq_bcn_encode_supported(int bc_format);
 YUPVQ_API int yupvq_bcn_encode_image(yupvq_ctx* ctx, const uint8_t* image, uint32_t width, uint32_t height, int channels,
                                      int bc_format, int swap_rb, int alpha_threshold, uint8_t* out_bc_blocks,

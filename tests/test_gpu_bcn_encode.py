@@ -71,6 +71,25 @@ def test_compress_image_equals_encode_then_vq(enc):
     assert st.lloyd_passes >= 1 and ms > 0.0
 
 
+@pytest.mark.parametrize("fmt,ch", [(1, 3), (3, 4)])
+def test_misaligned_device_output_is_staged(enc, fmt, ch):
+    """a device output pointer that is not aligned to the block size (a slice of a larger buffer) must not reach
+    the kernel's uint2 / uint4 stores; the call stages it and the bytes equal the aligned call's."""
+    import torch
+    img = (synth.ldr_rgba(128, 64, seed=5) if ch == 4 else synth.ldr_rgb(128, 64, seed=5)).copy()
+    want, _ = enc.bcn_encode_image(img, fmt)
+    d_img = torch.from_numpy(img).cuda()
+    d_buf = torch.full((want.size + 64,), 0xAB, dtype=torch.uint8, device="cuda")
+    off = 4 if fmt == 1 else 8                      # multiple of 4 (fine for any copy), not of the block size
+    assert (d_buf.data_ptr() + off) % want.shape[1] != 0
+    torch.cuda.synchronize()
+    enc.bcn_encode_image_raw(d_img.data_ptr(), 128, 64, ch, fmt, int(ch == 3), 128, d_buf.data_ptr() + off)
+    torch.cuda.synchronize()
+    got = d_buf.cpu().numpy()
+    assert np.array_equal(got[off:off + want.size].reshape(want.shape), want)
+    assert (got[:off] == 0xAB).all() and (got[off + want.size:] == 0xAB).all()
+
+
 def test_full_size_properties(enc):
     """BASELINE config 2 size: every block decodes close to its source texels; device-resident input and output."""
     import torch

@@ -271,6 +271,24 @@ def test_multi_gpu_sharded_matches_single_gpu():
     assert "multi_gpu_check ok" in r.stdout
 
 
+def test_peer_exchange_times_out_instead_of_hanging():
+    """ADVICE r02 (tail.cu): ranks that fall out of step must get an error from the in-kernel exchange, not spin for ever;
+    afterwards the same contexts work over NCCL (tools/xchg_timeout_check.py)."""
+    import os
+    import subprocess
+    import sys
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    root = os.path.normpath(os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
+    env = dict(os.environ, YUPVQ_XCHG_DESYNC_RANK="1", YUPVQ_XCHG_TIMEOUT_MS="300")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
+                        "127.0.0.1", "--master-port", "29534", os.path.join(root, "tools", "xchg_timeout_check.py")],
+                       capture_output=True, text=True, timeout=300, env=env)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "xchg_timeout_check ok" in r.stdout
+
+
 # ---- A21: the SAD metric (vq_Metric == SAD), all-integer: bit-exact end to end -------------------------------
 
 def test_sad_metric_golden(enc, golden_pipeline):

@@ -1,0 +1,49 @@
+"""GPU search (one-off helper for tools/variant_hash.py): which small synthetic textures make the Lloyd loop hit empty
+clusters AFTER pass 0 (so the reseed sees non-zero errors) on the tensor path?  Prints reseeds per candidate."""
+import os
+import sys
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from yuptexture_b200 import binding, synth  # noqa: E402
+
+
+def palette_texture(w, h, m, seed, jitter):
+    """m random 4x4 blocks with Zipf-like frequencies; `jitter` of the blocks get +-2 levels of noise (so D >> m)."""
+    rng = np.random.default_rng(seed)
+    pal = rng.integers(0, 256, (m, 4, 4, 3), dtype=np.uint8)
+    nb = (w // 4) * (h // 4)
+    p = 1.0 / np.arange(1, m + 1)
+    pick = rng.choice(m, nb, p=p / p.sum())
+    blocks = pal[pick].astype(np.int16)
+    noisy = rng.random(nb) < jitter
+    blocks[noisy] += rng.integers(-2, 3, (int(noisy.sum()), 4, 4, 3), dtype=np.int16)
+    blocks = np.clip(blocks, 0, 255).astype(np.uint8)
+    img = blocks.reshape(h // 4, w // 4, 4, 4, 3).transpose(0, 2, 1, 3, 4).reshape(h, w, 3)
+    return np.ascontiguousarray(img)
+
+
+def posterised(w, h, seed, step):
+    img = synth.ldr_rgb(w, h, seed=seed)
+    return ((img // step) * step).astype(np.uint8)
+
+
+enc = binding.Encoder(0)
+w, h = 1024, 512
+cands = []
+for seed in range(1, 5):
+    for m, jit in ((40, 0.02), (80, 0.01), (200, 0.0), (30, 0.2)):
+        cands.append((f"palette m={m} jitter={jit} seed={seed}", palette_texture(w, h, m, seed, jit)))
+    for step in (32, 64):
+        cands.append((f"posterised step={step} seed={seed}", posterised(w, h, seed, step)))
+for name, img in cands:
+    bc = synth.bc1_encode(img)
+    px = enc.decode_bcn(bc, 1, 3)
+    distinct = len(np.unique(px, axis=0))
+    for k in (64, 128):
+        for s in (3, 4):
+            cfg = binding.make_config(codebook=k, max_iterations=12, seed=s, assign_mode=binding.ASSIGN_TENSOR)
+            _, _, st = enc.encode_bcn(bc, len(bc), 1, 3, cfg)
+            print(f"{name:40s} distinct={distinct:6d} K={k:4d} seed={s} passes={st.lloyd_passes:2d} reseeds={st.reseeds}", flush=True)
+enc.close()

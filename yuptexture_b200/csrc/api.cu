@@ -43,6 +43,8 @@ const DebugOpts& debug_opts() {
         o.tc_force_batch = on("YUPVQ_TC_FORCE_BATCH");
         if (const char* v = getenv("YUPVQ_XCHG_MODE")) o.xchg_mode = atoi(v);
         o.tc_v1 = on("YUPVQ_TC_V1");   // v2 (merge warps) is the default since r02c: 0.143 against 0.177 ms per pass, bit-identical
+        if (const char* v = getenv("YUPVQ_XCHG_TIMEOUT_MS")) o.xchg_timeout_ms = std::max(1, atoi(v));
+        if (const char* v = getenv("YUPVQ_XCHG_DESYNC_RANK")) o.xchg_desync_rank = atoi(v);
         if (const char* v = getenv("YUPVQ_ASYNC_DBG")) o.async_dbg = atoi(v);
         return o;
     }();
@@ -423,37 +425,76 @@ int xchg_ensure(yupvq_ctx* ctx, size_t words, bool* ok) {
     while (cap < words) cap <<= 1;
     uint32_t status = 0;   // 1 = this rank failed
     void* base = nullptr;
-    if (cudaMalloc(&base, xchg_bytes(cap, R)) != cudaSuccess || cudaMemset(base, 0, xchg_bytes(cap, R)) != cudaSuccess) {
+    // The zeroing (counters included) must be complete before any peer can learn the handle: cudaMemset runs on the legacy
+    // default stream, which the context's non-blocking stream and the collectives below do not wait for, hence the
+    // device-wide synchronize.
+    if (cudaMalloc(&base, xchg_bytes(cap, R)) != cudaSuccess || cudaMemset(base, 0, xchg_bytes(cap, R)) != cudaSuccess ||
+        cudaDeviceSynchronize() != cudaSuccess) {
         cudaGetLastError();
         status = 1;
     }
-    cudaIpcMemHandle_t mine;
+    // what every rank tells the others: the handle of its buffer, the grid its tail kernel runs with (the counters reach
+    // epoch * grid, so all ranks must use the same grid) and where its GPU sits (to ask about native peer atomics)
+    struct XchgHello {
+        cudaIpcMemHandle_t handle;
+        int32_t tail_grid;
+        char pci[28];
+    };
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64 && sizeof(XchgHello) == 96, "record size");
+    XchgHello mine;
     std::memset(&mine, 0, sizeof(mine));
-    if (!status && cudaIpcGetMemHandle(&mine, base) != cudaSuccess) {
+    if (!status && cudaIpcGetMemHandle(&mine.handle, base) != cudaSuccess) {
         cudaGetLastError();
         status = 1;
     }
-    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle size");
-    CK(ctx->s_rows.ensure((size_t)(R + 1) * 64 + 64));
-    uint8_t* hbuf = ctx->s_rows.as<uint8_t>();          // [R handles | mine | status word]
-    CK(cudaMemcpyAsync(hbuf + (size_t)R * 64, &mine, 64, cudaMemcpyHostToDevice, ctx->stream));
-    if (ctx->nccl.all_gather_bytes(ctx->comm, hbuf + (size_t)R * 64, hbuf, 64, ctx->stream)) return ctx->fail("ncclAllGather failed");
-    std::vector<cudaIpcMemHandle_t> all(R);
-    CK(cudaMemcpyAsync(all.data(), hbuf, (size_t)R * 64, cudaMemcpyDeviceToHost, ctx->stream));
+    {
+        int sms = 0;
+        if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device) != cudaSuccess) cudaGetLastError();
+        mine.tail_grid = sms;   // launch_lloyd_tail: one CTA per SM
+        if (cudaDeviceGetPCIBusId(mine.pci, (int)sizeof(mine.pci), ctx->device) != cudaSuccess) {
+            cudaGetLastError();
+            mine.pci[0] = 0;
+        }
+    }
+    constexpr size_t kRec = sizeof(XchgHello);
+    CK(ctx->s_rows.ensure((size_t)(R + 1) * kRec + 64));
+    uint8_t* hbuf = ctx->s_rows.as<uint8_t>();          // [R records | mine | status word]
+    CK(cudaMemcpyAsync(hbuf + (size_t)R * kRec, &mine, kRec, cudaMemcpyHostToDevice, ctx->stream));
+    if (ctx->nccl.all_gather_bytes(ctx->comm, hbuf + (size_t)R * kRec, hbuf, kRec, ctx->stream)) return ctx->fail("ncclAllGather failed");
+    std::vector<XchgHello> all(R);
+    CK(cudaMemcpyAsync(all.data(), hbuf, (size_t)R * kRec, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     xchg_release(ctx);   // every rank has passed the all-gather: the old buffers are idle everywhere
     void* peer[kXchgMaxRanks] = {};
     for (int r = 0; r < R && !status; ++r) {
         if (r == ctx->rank) {
             peer[r] = base;
-        } else if (cudaIpcOpenMemHandle(&peer[r], all[r], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+            continue;
+        }
+        if (all[r].tail_grid != mine.tail_grid || mine.tail_grid <= 0) {   // different SM counts: the counters would never meet
+            status = 1;
+            break;
+        }
+        // red.release.sys on a peer's counters needs native atomics over the link; ask when the peer's GPU is visible to this
+        // process (it is under torchrun; when it is not, the mapping below is the only test there is)
+        all[r].pci[sizeof(all[r].pci) - 1] = 0;
+        int peer_dev = -1, native = 1;
+        if (all[r].pci[0] && cudaDeviceGetByPCIBusId(&peer_dev, all[r].pci) == cudaSuccess && peer_dev != ctx->device) {
+            if (cudaDeviceGetP2PAttribute(&native, cudaDevP2PAttrNativeAtomicSupported, ctx->device, peer_dev) != cudaSuccess) native = 1;
+        }
+        cudaGetLastError();
+        if (!native) {
+            status = 1;
+            break;
+        }
+        if (cudaIpcOpenMemHandle(&peer[r], all[r].handle, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
             cudaGetLastError();
             peer[r] = nullptr;
             status = 1;
         }
     }
     // agree on the outcome
-    uint32_t* st_d = reinterpret_cast<uint32_t*>(hbuf + (size_t)(R + 1) * 64);
+    uint32_t* st_d = reinterpret_cast<uint32_t*>(hbuf + (size_t)(R + 1) * kRec);
     CK(cudaMemcpyAsync(st_d, &status, 4, cudaMemcpyHostToDevice, ctx->stream));
     if (ctx->nccl.all_reduce_max_u32(ctx->comm, st_d, 1, ctx->stream)) return ctx->fail("ncclAllReduce(max) failed");
     uint32_t any = 0;
@@ -496,7 +537,23 @@ void xchg_args(yupvq_ctx* ctx, const long long* src, size_t words, XchgArgs* x, 
         x->peer_stage[r] = reinterpret_cast<long long*>(b + kXchgFlagBytes) + (size_t)par * R * stride;
         x->peer_result[r] = reinterpret_cast<long long*>(b + kXchgFlagBytes) + 2 * (size_t)R * stride + (size_t)par * ctx->xchg_cap;
     }
+    x->err = x->peer_flags[ctx->rank] + kXchgErrWord;
+    x->timeout_ns = (unsigned long long)debug_opts().xchg_timeout_ms * 1000000ull;
     *result = x->peer_result[R > 0 ? ctx->rank : 0];
+}
+
+// After the passes of a call have been synchronised: did one of its exchanges give up waiting?  Then the sums it read were
+// not the peers' and the call fails; the peer path stays off for this communicator (a new yupvq_comm_init starts afresh).
+int xchg_check(yupvq_ctx* ctx) {
+    if (ctx->xchg_state != 1 || !ctx->xchg_base) return 0;
+    uint32_t err = 0;
+    CK(cudaMemcpyAsync(&err, static_cast<uint32_t*>(ctx->xchg_base) + kXchgErrWord, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (!err) return 0;
+    ctx->xchg_state = -1;
+    return ctx->fail("peer exchange timed out after %d ms waiting for rank %u (phase %u, exchange %u): a peer failed, exited or "
+                     "launched a different sequence of passes",
+                     debug_opts().xchg_timeout_ms, (err - 1u) % kXchgMaxRanks, (err - 1u) / kXchgMaxRanks, ctx->xchg_epoch);
 }
 
 // ---- K3 dispatch: exact engine or tcgen05 front-end + exact re-rank -----------------------------------
@@ -1779,13 +1836,15 @@ int yupvq_bcn_encode_image(yupvq_ctx* ctx, const uint8_t* image, uint32_t width,
     if (!out_bc_blocks) return ctx->fail("out_bc_blocks is null");
     const size_t bytes = (size_t)((width + 3) / 4) * ((height + 3) / 4) * bc_block_bytes(bc_format);
     uint8_t* out_dev = out_bc_blocks;
-    const bool out_is_dev = is_device_ptr(out_bc_blocks);
-    if (!out_is_dev) {
+    // the encoder stores whole blocks as uint2 / uint4: it writes in place only into device memory aligned to the block size;
+    // host buffers and misaligned device pointers (a slice of a larger buffer) are staged and copied
+    const bool in_place = is_device_ptr(out_bc_blocks) && reinterpret_cast<uintptr_t>(out_bc_blocks) % bc_block_bytes(bc_format) == 0;
+    if (!in_place) {
         CK(ctx->bc_enc.ensure(std::max<size_t>(bytes, 16)));
         out_dev = ctx->bc_enc.as<uint8_t>();
     }
     if (bcn_encode_to_device(ctx, image, width, height, channels, bc_format, swap_rb, alpha_threshold, out_dev, out_ms_kernel)) return 1;
-    if (!out_is_dev && from_device(ctx, out_bc_blocks, out_dev, bytes)) return 1;
+    if (!in_place && from_device(ctx, out_bc_blocks, out_dev, bytes)) return 1;
     CK(cudaStreamSynchronize(ctx->stream));
     return 0;
 }
@@ -2639,6 +2698,7 @@ int yupvq_encode_bcn_batch_sharded(yupvq_ctx* ctx, const uint8_t* const* bc_bloc
                                               dctl, tflags_d, ctl_d, ctx->stream, &ab));
                 ctx->stage_mark(2);
                 if (peer_xchg) {
+                    if (iter == 2 && debug_opts().xchg_desync_rank == ctx->rank) ++ctx->xchg_epoch;   // test hook
                     xchg_args(ctx, acc_loc, T * acc_words, &ta.x, &ta.acc);
                 } else {
                     CK(cudaMemcpyAsync(ctx->bt_acc.p, acc_loc, T * acc_words * 8, cudaMemcpyDeviceToDevice, ctx->stream));
@@ -2698,6 +2758,7 @@ int yupvq_encode_bcn_batch_sharded(yupvq_ctx* ctx, const uint8_t* const* bc_bloc
         }
         CK(cudaMemcpyAsync(h_words, ctl_d, (7 * T + 1) * 4, cudaMemcpyDeviceToHost, ctx->stream));
         CK(cudaStreamSynchronize(ctx->stream));
+        if (peer_xchg && xchg_check(ctx)) return 1;   // before anything is believed: a timed-out exchange left garbage behind
         if (h_words[7 * T]) {
             *redo = true;
             return 0;

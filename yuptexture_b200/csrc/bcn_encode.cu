@@ -3,8 +3,12 @@
 // image to the closed-source Compressonator encoders: 5.3 s for a 4096^2 RGB texture).
 //
 // Compressonator's bit patterns cannot be reproduced (binary-only); what can be matched is the QUALITY of the blocks,
-// measured the way the VQ stage sees them: PSNR of the decoded texels against the source (tests/test_gpu_bcn_encode.py
-// gates every format against Compressonator's own output).  One thread encodes one 4x4 block:
+// measured the way the VQ stage sees them: PSNR of the decoded texels against the source.  Gated against Compressonator's
+// own output: BC1 (RGB, and RGBA punch-through), BC3 and BC4 on the host-compiled build of this block code
+// (tests/test_bcn_encode_cpu.py), BC1 again on the GPU at 4096^2 (tests/test_gpu_bcn_encode.py), and the kernel's bytes
+// equal that host build's for all four formats.  BC5 has no gate of its own: it is two BC4 halves from the gated scalar
+// encoder (the reference library aborts on 2-channel sources here, so there is nothing to compare with).
+// One thread encodes one 4x4 block:
 //   colour (BC1 / the colour half of BC3): principal axis of the 16 texels by power iteration on the covariance matrix,
 //     endpoints = the extreme projections, then least-squares refits of the endpoints for the current selectors; each
 //     candidate is scored with the DECODER's integer palette ((2a+b)/3 truncating, bcn_decode.cuh) and the best kept.

@@ -28,6 +28,8 @@ struct DebugOpts {
     bool tc_force_batch = false;     // YUPVQ_TC_FORCE_BATCH      single texture through the batch instantiation of the front-end (codegen A/B)
     bool no_peer_xchg = false;       // YUPVQ_NO_PEER_XCHG        sharded batch: copy + ncclAllReduce instead of the in-kernel peer exchange
     int xchg_mode = 0;               // YUPVQ_XCHG_MODE           peer exchange: 1 = one shot, 2 = two shots (default: by size)
+    int xchg_timeout_ms = 30000;     // YUPVQ_XCHG_TIMEOUT_MS     peer exchange: how long a CTA waits for a peer's counter before the call fails
+    int xchg_desync_rank = -1;       // YUPVQ_XCHG_DESYNC_RANK    test hook: that rank skips one exchange number at pass 2 (its wait must time out)
     int async_dbg = 0;               // YUPVQ_ASYNC_DBG           bit 0: sync after every pass, bit 3: per-pass delta statistics on stderr
 };
 const DebugOpts& debug_opts();       // defined in api.cu

@@ -237,7 +237,15 @@ struct XchgArgs {
     long long* peer_stage[kXchgMaxRanks];     // rank j's staging area of this parity (n_ranks slots), mapped into this process
     long long* peer_result[kXchgMaxRanks];    // rank j's result buffer of this parity
     uint32_t* peer_flags[kXchgMaxRanks];      // rank j's counters: [2 phases][kXchgMaxRanks sources]
+    // Bounded wait: a counter that has not reached its target timeout_ns after a CTA began to spin on it (a peer died, failed
+    // on the host or launched a different sequence) raises *err (this rank's own memory, sticky) and the kernel goes on
+    // with whatever the buffers hold -- every access stays in bounds -- so that it ends and the host can fail the call.  Once
+    // *err is set the exchange is skipped altogether.  err == null: wait for ever.
+    uint32_t* err = nullptr;
+    unsigned long long timeout_ns = 0;
 };
+// word offset of the error word inside a rank's counter area (behind the [2][kXchgMaxRanks] counters)
+constexpr int kXchgErrWord = 2 * kXchgMaxRanks;
 struct TailArgs {
     XchgArgs x;                // n_ranks > 1: `acc` is this rank's result buffer, filled by the exchange at the head of the kernel
     const long long* acc;      // (all-reduced) accumulators

@@ -36,6 +36,11 @@ __device__ __forceinline__ uint32_t ld_acquire_sys_u32(const uint32_t* p) {
     asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
 
 __global__ void __launch_bounds__(kTailThreads) lloyd_tail_kernel(TailArgs a) {
     cg::grid_group grid = cg::this_grid();
@@ -50,7 +55,7 @@ __global__ void __launch_bounds__(kTailThreads) lloyd_tail_kernel(TailArgs a) {
     // epoch * gridDim.x.  (The data buffers alternate with the epoch's parity; the counters need not.)
     const XchgArgs& x = a.x;
     const bool sum_on_read = x.n_ranks > 1 && x.one_shot != 0;
-    if (x.n_ranks > 1) {
+    if (x.n_ranks > 1 && !(x.err && __ldcg(x.err) != 0u)) {   // a timed-out exchange earlier in this call: do not wait again
         const int R = x.n_ranks;
         const size_t gtid = (size_t)blockIdx.x * kTailThreads + tid, gsz = (size_t)gridDim.x * kTailThreads;
         const uint32_t target = x.epoch * gridDim.x;
@@ -59,7 +64,20 @@ __global__ void __launch_bounds__(kTailThreads) lloyd_tail_kernel(TailArgs a) {
             if (tid < R) {   // release: cumulative over the CTA's stores ordered before it by the barrier
                 red_release_sys_add_u32(x.peer_flags[tid] + phase * kXchgMaxRanks + x.rank, 1u);
                 const uint32_t* mine = x.peer_flags[x.rank] + phase * kXchgMaxRanks + tid;
-                while ((int32_t)(ld_acquire_sys_u32(mine) - target) < 0) {}
+                // the clock is looked at once per 1024 polls: the common case (counter already there, or a few microseconds
+                // away) never reads it
+                uint32_t polls = 0;
+                unsigned long long t0 = 0;
+                while ((int32_t)(ld_acquire_sys_u32(mine) - target) < 0) {
+                    if (x.err == nullptr || (++polls & 1023u) != 0u) continue;
+                    const unsigned long long now = global_timer_ns();
+                    if (t0 == 0) {
+                        t0 = now;
+                    } else if (now - t0 > x.timeout_ns || __ldcg(x.err) != 0u) {
+                        atomicMax(x.err, 1u + (uint32_t)phase * kXchgMaxRanks + (uint32_t)tid);   // which counter: phase, source rank
+                        break;
+                    }
+                }
             }
             __syncthreads();
         };

@@ -335,6 +335,19 @@ std::vector<uint8_t> BCnCompressor::Compress(const uint8_t* inData, uint32_t wid
         return c.compress(inData, width, height, channelCount, format, numThreads, quality, alphaThreshold, flipRGB);
     }
     t_last_encoder = "built-in (cpu)";
+    {
+        // Not silent: these stand-in encoders (bounding-box BC1/3/4/5, mode-6-only BC7) are below Compressonator's quality.
+        // One line per process the first time they write blocks; YUPTEXTURE_QUIET=1 turns it off.
+        static std::once_flag warned;
+        std::call_once(warned, [format] {
+            if (getenv("YUPTEXTURE_QUIET")) return;
+            fprintf(stderr,
+                    "yuptexture: no BCn codec installed -- %s blocks come from the built-in stand-in encoder (lower quality than the "
+                    "reference's Compressonator). Put libyupcodec_cmp.so next to libyuptexture.so, set YUPTEXTURE_CODEC, or call "
+                    "BCnCompressor::SetCodec().\n",
+                    format == BCFormat::BC7 ? "BC7 (mode 6 only)" : "BCn");
+        });
+    }
     if (!inData || width == 0 || height == 0 || channelCount < 1 || channelCount > 4) return {};
     if (format != BCFormat::BC1 && format != BCFormat::BC3 && format != BCFormat::BC4 && format != BCFormat::BC5 && format != BCFormat::BC7)
         return {};  // the reference returns an empty vector on failure (src/bcn_compressor.cpp:111)
