@@ -319,6 +319,7 @@ def run_ours(args, rank, world, local_rank):
     for _ in range(2):
         step(False)
     ms_e2e, wall_e2e, _, last_e2e = timed(False, args.steps)
+    exchange_path = enc.exchange_path()   # of the last timed step, before any checking call below
 
     total_blocks = n * n_tex
     value = total_blocks * args.steps / (ms_dev * 1e-3)
@@ -402,6 +403,8 @@ def run_ours(args, rank, world, local_rank):
             "scaling": "weak" if not args.textures else "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": cfgd,
             "detail": {"parallelism": par,
+                       # what the library says it did on rank 0's last timed step (yupvq_exchange_path), not a static claim
+                       "exchange_path": exchange_path,
                        "l2": "no explicit flush: each step streams a 330 MB working set (features + pixel planes) > 126 MB L2",
                        "lloyd_passes": last.lloyd_passes, "ms_per_texture": ms_dev / args.steps / n_tex,
                        "phases_ms": {p: getattr(last, "ms_" + p) for p in phases},

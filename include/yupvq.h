@@ -248,6 +248,13 @@ YUPVQ_API int yupvq_comm_init(yupvq_ctx* ctx, const uint8_t id[128], int n_ranks
 /* Only the *_sharded entry points below use the communicator.  Every other call on a context that has one
  * (yupvq_encode_bcn, yupvq_build_codebook[_hdr], yupvq_encode_bcn_batch, ...) stays rank-local: ranks may encode
  * unrelated textures with them at the same time. */
+/* How the last *_sharded call on this context exchanged the per-pass partial sums (no reference equivalent: the reference
+ * has one encoder per Compress call, src/vq_bcn_compressor.cpp:136).  PEER_*: inside the pass-tail kernel over NVLink peer
+ * memory (one shot = every rank reads all vectors, two shots = reduce-scatter then all-gather); NCCL: copy +
+ * ncclAllReduce (peers not mappable, grids differ, batch beyond the fused path, or after a timed-out peer exchange);
+ * NONE: no communicator or no sharded call yet. */
+enum { YUPVQ_XCHG_NONE = 0, YUPVQ_XCHG_PEER_ONE_SHOT = 1, YUPVQ_XCHG_PEER_TWO_SHOT = 2, YUPVQ_XCHG_NCCL = 3 };
+YUPVQ_API int yupvq_exchange_path(const yupvq_ctx* ctx);
 /* Block-sharded LDR VQ of ONE texture: this rank holds blocks [first_block, first_block + n_local) of a texture
  * of n_total blocks; the whole texture's BCn bytes are passed on every rank.  It is the lock-step batch below with a
  * single texture: rank 0 runs the K-Means++ seeding (with cfg->seed == 0 it alone draws from std::random_device) and

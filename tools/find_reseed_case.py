@@ -37,6 +37,19 @@ for seed in range(1, 5):
         cands.append((f"palette m={m} jitter={jit} seed={seed}", palette_texture(w, h, m, seed, jit)))
     for step in (32, 64):
         cands.append((f"posterised step={step} seed={seed}", posterised(w, h, seed, step)))
+# tiny clusters: few blocks per centroid, where a centroid can lose its last member after pass 0
+small = []
+for seed in range(1, 4):
+    small.append((f"ldr 512x256 seed={seed}", synth.ldr_rgb(512, 256, seed=seed)))
+    small.append((f"palette m=600 seed={seed}", palette_texture(512, 256, 600, seed, 0.0)))
+    small.append((f"palette m=1100 seed={seed}", palette_texture(512, 256, 1100, seed, 0.0)))
+for name, img in small:
+    bc = synth.bc1_encode(img)
+    for k in (512, 1024):
+        for s in (3, 4, 5):
+            cfg = binding.make_config(codebook=k, max_iterations=32, seed=s, assign_mode=binding.ASSIGN_TENSOR)
+            _, _, st = enc.encode_bcn(bc, len(bc), 1, 3, cfg)
+            print(f"{name:40s} n={len(bc)} K={k:4d} seed={s} passes={st.lloyd_passes:2d} reseeds={st.reseeds}", flush=True)
 for name, img in cands:
     bc = synth.bc1_encode(img)
     px = enc.decode_bcn(bc, 1, 3)

@@ -57,6 +57,7 @@ def main():
     # the contexts stay usable: the peer path is off now, the NCCL path gives the single-GPU answer
     cent, idx, _ = enc.encode_bcn_sharded(bc, n, first, n_local, 1, 3, cfg)
     same = np.array_equal(cent, want_cent) and np.array_equal(idx, want_idx[first:first + n_local])
+    same = same and enc.exchange_path() == "nccl"
     flag = torch.tensor([int(timed_out and same and took < 30.0)], device=dev)
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     print(f"rank {rank}: error={msg!r} after {took:.2f} s; next call identical to single GPU: {same}", flush=True)

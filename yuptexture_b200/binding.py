@@ -81,6 +81,7 @@ def lib():
         L.yupvq_profile.argtypes = [_vp, C.c_int]
         L.yupvq_profile_read.argtypes = [_vp, C.POINTER(C.c_float), C.POINTER(C.c_uint32)]
         L.yupvq_profile_stages.argtypes = [_vp, C.POINTER(C.c_float), C.POINTER(C.c_uint32)]
+        L.yupvq_exchange_path.argtypes = [_vp]
         L.yupvq_comm_unique_id.argtypes = [_vp, _vp]
         L.yupvq_comm_init.argtypes = [_vp, _vp, C.c_int, C.c_int]
         L.yupvq_encode_bcn_sharded.argtypes = [_vp, _vp, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int, C.c_int, cfgp,
@@ -194,6 +195,10 @@ class Encoder:
                                                   _ptr(out_centroids), _ptr(out_indices), C.byref(st)),
                  "yupvq_encode_bcn_sharded")
         return out_centroids, out_indices, st
+
+    def exchange_path(self):
+        """How the last *_sharded call exchanged its partial sums: 'none', 'peer_one_shot', 'peer_two_shot' or 'nccl'."""
+        return ("none", "peer_one_shot", "peer_two_shot", "nccl")[self._L.yupvq_exchange_path(self._ctx)]
 
     def profile(self, enable):
         self._ck(self._L.yupvq_profile(self._ctx, 1 if enable else 0), "yupvq_profile")

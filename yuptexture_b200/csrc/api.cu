@@ -139,6 +139,7 @@ struct yupvq_ctx {
     size_t xchg_cap = 0;              // capacity in int64 words
     uint32_t xchg_epoch = 0;
     int xchg_state = 0;
+    int xchg_path = YUPVQ_XCHG_NONE;  // how the last sharded call exchanged its partial sums (yupvq_exchange_path)
 
     int fail(const char* fmt, ...) {
         char buf[512];
@@ -1125,6 +1126,8 @@ int yupvq_profile_read(yupvq_ctx* ctx, float* out_ms_front_end, uint32_t* out_la
     if (out_launches) *out_launches = n;
     return 0;
 }
+
+int yupvq_exchange_path(const yupvq_ctx* ctx) { return ctx ? ctx->xchg_path : YUPVQ_XCHG_NONE; }
 
 int yupvq_profile_stages(yupvq_ctx* ctx, float out_ms[4], uint32_t* out_passes) {
     if (!ctx) return 1;
@@ -2302,6 +2305,7 @@ int yupvq_encode_bcn_batch_sharded(yupvq_ctx* ctx, const uint8_t* const* bc_bloc
     ctx->tc_feat = nullptr;
     ctx->maxabs_feat = nullptr;
     ctx->tc_rgb = rgb_layout(channels);
+    ctx->xchg_path = ctx->comm ? YUPVQ_XCHG_NCCL : YUPVQ_XCHG_NONE;   // the peer path overwrites it where it runs
     if (check_cfg(ctx, cfg, n_total, channels)) return 1;
     if (!bc_blocks || n_textures == 0) return ctx->fail("no textures");
     if (n_textures > 4096) return ctx->fail("too many textures in one batch (%zu > 4096)", n_textures);
@@ -2700,6 +2704,7 @@ int yupvq_encode_bcn_batch_sharded(yupvq_ctx* ctx, const uint8_t* const* bc_bloc
                 if (peer_xchg) {
                     if (iter == 2 && debug_opts().xchg_desync_rank == ctx->rank) ++ctx->xchg_epoch;   // test hook
                     xchg_args(ctx, acc_loc, T * acc_words, &ta.x, &ta.acc);
+                    ctx->xchg_path = ta.x.one_shot ? YUPVQ_XCHG_PEER_ONE_SHOT : YUPVQ_XCHG_PEER_TWO_SHOT;
                 } else {
                     CK(cudaMemcpyAsync(ctx->bt_acc.p, acc_loc, T * acc_words * 8, cudaMemcpyDeviceToDevice, ctx->stream));
                     if (ctx->nccl.all_reduce_sum_i64(ctx->comm, ctx->bt_acc.as<long long>(), T * acc_words, ctx->stream))
@@ -2832,6 +2837,7 @@ int yupvq_encode_hdr_batch_sharded(yupvq_ctx* ctx, const float* const* images, s
     ctx->maxabs_feat = nullptr;
     ctx->tc_rgb = rgb_layout(channels);
     const size_t n_total = (size_t)((width + 3) / 4) * ((height + 3) / 4);
+    ctx->xchg_path = ctx->comm ? YUPVQ_XCHG_NCCL : YUPVQ_XCHG_NONE;
     if (check_cfg(ctx, cfg, n_total, channels)) return 1;
     if (!images || n_images == 0) return ctx->fail("no images");
     if (n_images > 4096) return ctx->fail("too many images in one batch (%zu > 4096)", n_images);
