@@ -135,6 +135,41 @@ def cpu_sample_pixels(bc, size=None):
     return orcbind.decode_bcn(bc[rows.reshape(-1)], 1, 3)
 
 
+def variant_parity(enc, solo, world, rank):
+    """The sharded variants next to the headline path (include/yupvq.h: fast-mode sampling, SAD metric, HDR images over the
+    ranks), each compared bit for bit with the communicator-less single-GPU call -- so that every N > 1 bench line, the driver's
+    included, carries their multi-GPU parity and not only the builder's tools/multi_gpu_check.py run.  Collective: every rank
+    calls it."""
+    from yuptexture_b200 import binding, sharding, synth
+    res = {}
+    small = [synth.bc1_encode(synth.ldr_rgb(512, 512, seed=300 + t)) for t in range(world + 1)]
+    small.append(synth.bc1_encode(synth.checker_rgb(512, 512)))     # few distinct blocks: empty clusters, sharded reseed
+    ns = len(small[0])
+    f2, nl2 = sharding.shard_range(ns, world, rank)
+    for name, kw in (("sampled", dict(sample_ratio=0.35)), ("sad", dict(metric=binding.METRIC_SAD)),
+                     ("sad_sampled", dict(metric=binding.METRIC_SAD, sample_ratio=0.5))):
+        good = True
+        cents, idxs, stv = enc.encode_bcn_batch_sharded(small, ns, f2, nl2, 1, 3, binding.make_config(codebook=128, max_iterations=8, seed=40, **kw))
+        passes = 0
+        for t, bc in enumerate(small):
+            cent, idx, s1 = solo.encode_bcn(bc, ns, 1, 3, binding.make_config(codebook=128, max_iterations=8, seed=40 + t, **kw))
+            good = good and np.array_equal(cents[t], cent) and np.array_equal(idxs[t], idx[f2:f2 + nl2])
+            passes += s1.lloyd_passes
+        res[name] = bool(good and stv.lloyd_passes == passes)
+    w, h = 512, 256
+    imgs = [synth.hdr_rgb(w, h, seed=400 + t) for t in range(world + 1)]
+    nh = (w // 4) * (h // 4)
+    f3, nl3 = sharding.shard_range(nh, world, rank)
+    for name, kw in (("hdr", dict()), ("hdr_sampled", dict(sample_ratio=0.5))):
+        good = True
+        cents, idxs, _ = enc.encode_hdr_batch_sharded(imgs, w, h, 3, f3, nl3, binding.make_config(codebook=600, max_iterations=8, seed=50, **kw))
+        for t, img in enumerate(imgs):
+            cent, idx, _ = solo.encode_hdr(img, w, h, 3, binding.make_config(codebook=600, max_iterations=8, seed=50 + t, **kw))
+            good = good and np.array_equal(cents[t].view(np.uint32), cent.view(np.uint32)) and np.array_equal(idxs[t], idx[f3:f3 + nl3])
+        res[name] = bool(good)
+    return res
+
+
 def workload_config(n_tex):
     """The `config` object both arms print (identical keys and values for the same N, so the driver's same_config holds)."""
     return {"workload": f"BC1 VQ compress of {n_tex} synthetic 4096x4096 texture(s) (BASELINE config 2 per GPU): "
@@ -346,6 +381,7 @@ def run_ours(args, rank, world, local_rank):
             ok = ok and np.array_equal(dev_cent[t].cpu().numpy().reshape(k, 48), cent_s)
             ok = ok and np.array_equal(dev_idx[t].cpu().numpy().view(np.uint32)[:n_local], idx_s[first:first + n_local])
             checked += 1
+        variants = None if (args.no_extras or texture_parallel) else variant_parity(enc, solo, world, rank)
         solo.close()
         tt = torch.tensor([1.0 if ok else 0.0, float(checked), 1.0 if checked else 0.0], dtype=torch.float64, device=dev)
         mn = tt.clone()
@@ -354,6 +390,13 @@ def run_ours(args, rank, world, local_rank):
         multi = {"multi_gpu_identical": bool(mn[0] == 1.0), "ranks_checked": int(tt[2]), "comparisons": int(tt[1]),
                  "what": "centroids and this rank's index shard of textures 0 and T-1 vs a single-GPU yupvq_encode_bcn of the "
                          "same texture and seed, bit for bit, on every rank that holds them"}
+        if variants is not None:
+            names = sorted(variants)
+            vt = torch.tensor([1.0 if variants[v] else 0.0 for v in names], dtype=torch.float64, device=dev)
+            dist.all_reduce(vt, op=dist.ReduceOp.MIN)      # a variant counts only if every rank found it identical
+            multi["variants_identical"] = {v: bool(vt[i] == 1.0) for i, v in enumerate(names)}
+            multi["variants_what"] = ("the other sharded entry points on small inputs (512^2 BC1 x (N+2) textures incl. a checker texture "
+                                      "with empty clusters; 512x256 float images), each vs its single-GPU call with seed + t, bit for bit")
 
     out = None
     if rank == 0:
@@ -373,15 +416,23 @@ def run_ours(args, rank, world, local_rank):
         sec = ms_a * 1e-3
         ach_alg = flop_alg / sec / 1e12 if sec > 0 else 0.0
         ach_exec = flop_exec / sec / 1e12 if sec > 0 else 0.0
-        traffic = None
+        # DRAM bytes per launch come from an ncu capture, which cannot be taken inside a timed run.  The committed figure is
+        # used only while it describes THIS kernel: the capture file names the sha256 of csrc/assign_tc.cu it was taken from,
+        # and a capture of any other source (or of another config) leaves traffic null rather than quoting a stale number.
+        traffic, traffic_source = None, None
         import glob
-        tfiles = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_traffic.json")))
-        tpath = tfiles[-1] if tfiles else ""
-        if world == 1 and n_tex == 1 and tpath:  # DRAM bytes per launch of the same kernel on the same config, from the committed ncu capture
-            traffic = json.load(open(tpath))["assign_tc_kernel"]["dram_bytes_per_launch"]
+        import hashlib
+        src_path = os.path.join(ROOT, "yuptexture_b200", "csrc", "assign_tc.cu")
+        src_sha = hashlib.sha256(open(src_path, "rb").read()).hexdigest()[:16] if os.path.exists(src_path) else None
+        for tpath in sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_traffic.json")), reverse=True):
+            tj = json.load(open(tpath))
+            if world == 1 and n_tex == 1 and src_sha and tj.get("kernel_source_sha16") == src_sha:
+                traffic = tj["assign_tc_kernel"]["dram_bytes_per_launch"]
+                traffic_source = os.path.relpath(tpath, ROOT)
+                break
         peak = pk["bf16_tflops_sustained"]
         roofline = {"bound": "tensor", "kernel": "assign_tc_kernel (N x K x 64 contraction as bf16 partial products + argmax epilogue)",
-                    "achieved": ach_alg, "peak": peak, "unit": "TFLOP/s", "frac": ach_alg / peak, "traffic": traffic,
+                    "achieved": ach_alg, "peak": peak, "unit": "TFLOP/s", "frac": ach_alg / peak, "traffic": traffic, "traffic_source": traffic_source,
                     "frac_algorithmic": ach_alg / peak, "achieved_executed": ach_exec, "frac_executed": ach_exec / peak,
                     "executed_over_algorithmic": 16.0 * ksteps / 64.0,
                     "peak_source": pk["src"] + " bf16 sustained (kernel timed inside a step)",

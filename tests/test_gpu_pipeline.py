@@ -483,6 +483,41 @@ def test_config4_reference_psnr_on_crop(enc, reflib):
     assert abs(_hdr_psnr_delta_db(px, cent, idx, c_ref, i_ref)) <= PSNR_TOL_DB
 
 
+def test_fused_tail_rare_path(enc, oracle):
+    """the reseed inside the fused pass tail (csrc/tail.cu: errors, grid.sync, first-maximum arg-max over the CTA
+    stripes, operand rows again) at sizes that take the tensor path.
+    (a) 8x8 checker: two distinct blocks, 62 of 64 clusters empty on every pass, every error ties at exactly 0 (our sums are
+    exact), so block 0 -- the first row of the first stripe -- must win every time (src/vq_encoder.cpp:369-374,
+    std::max_element).  The reference's fp32 sums leave ulp-sized errors on the big cluster and so duplicate the OTHER block;
+    what both must agree on is the reconstruction, block for block.
+    (b) 1100-block palette texture at K = 1024: clusters run empty after pass 0, errors are real distances.
+    In both, the exact engine (separate assign kernel computing errors[] on every pass) and the tensor engine (errors only
+    when a cluster came out empty, inside the tail) must agree bit for bit."""
+    from yuptexture_b200 import binding
+    bc = synth.bc1_encode(synth.checker_rgb(1024, 512))
+    n = len(bc)
+    px = oracle.decode_bcn(bc, 1, 3)
+    runs = {}
+    for mode in (binding.ASSIGN_TENSOR, binding.ASSIGN_EXACT):
+        cent, idx, st = enc.encode_bcn(bc, n, 1, 3, binding.make_config(codebook=64, max_iterations=6, seed=8, assign_mode=mode))
+        assert st.reseeds > 0
+        runs[mode] = (cent, idx, st.lloyd_passes)
+    (cent, idx, passes), (cent_e, idx_e, passes_e) = runs[binding.ASSIGN_TENSOR], runs[binding.ASSIGN_EXACT]
+    assert bits_equal(cent, cent_e) and bits_equal(idx, idx_e) and passes == passes_e
+    assert all(bits_equal(cent[c], px[0]) for c in range(2, 64))          # first maximum of an all-zero error array: block 0
+    c_ref, _ = oracle.build_codebook(px, 3, 64, 6, 8)
+    assert bits_equal(cent[idx], c_ref[oracle.quantize_blocks(px, 3, c_ref)])   # same reconstruction as the CPU restatement
+    assert bits_equal(cent[idx], px)                                      # and it is lossless here
+    pal = synth.bc1_encode(synth.palette_rgb(512, 256, 1100, 1))
+    runs = {}
+    for mode in (binding.ASSIGN_TENSOR, binding.ASSIGN_EXACT):
+        cent, idx, st = enc.encode_bcn(pal, len(pal), 1, 3, binding.make_config(codebook=1024, max_iterations=8, seed=3, assign_mode=mode))
+        assert st.reseeds > 0 and st.lloyd_passes > 2
+        runs[mode] = (cent, idx, st.lloyd_passes, st.reseeds)
+    a, b = runs[binding.ASSIGN_TENSOR], runs[binding.ASSIGN_EXACT]
+    assert bits_equal(a[0], b[0]) and bits_equal(a[1], b[1]) and a[2:] == b[2:]
+
+
 @pytest.mark.parametrize("switch", ["YUPVQ_TC_V1", "YUPVQ_NO_DECODE_FUSE", "YUPVQ_NO_TAIL_FUSE", "YUPVQ_NO_DELTA", "YUPVQ_NO_SPLIT_DECODE",
                                     "YUPVQ_BATCH_PER_TEXTURE", "YUPVQ_SEED_NO_PAL"])
 def test_implementation_switches_do_not_change_results(switch):

@@ -9,19 +9,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from yuptexture_b200 import binding, synth  # noqa: E402
 
 
-def palette_texture(w, h, m, seed, jitter):
-    """m random 4x4 blocks with Zipf-like frequencies; `jitter` of the blocks get +-2 levels of noise (so D >> m)."""
-    rng = np.random.default_rng(seed)
-    pal = rng.integers(0, 256, (m, 4, 4, 3), dtype=np.uint8)
-    nb = (w // 4) * (h // 4)
-    p = 1.0 / np.arange(1, m + 1)
-    pick = rng.choice(m, nb, p=p / p.sum())
-    blocks = pal[pick].astype(np.int16)
-    noisy = rng.random(nb) < jitter
-    blocks[noisy] += rng.integers(-2, 3, (int(noisy.sum()), 4, 4, 3), dtype=np.int16)
-    blocks = np.clip(blocks, 0, 255).astype(np.uint8)
-    img = blocks.reshape(h // 4, w // 4, 4, 4, 3).transpose(0, 2, 1, 3, 4).reshape(h, w, 3)
-    return np.ascontiguousarray(img)
+palette_texture = synth.palette_rgb
 
 
 def posterised(w, h, seed, step):

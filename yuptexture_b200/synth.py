@@ -66,6 +66,24 @@ def checker_rgb(width, height, a=(30, 60, 200), b=(220, 200, 40), cell=8):
     return img
 
 
+def palette_rgb(width, height, m, seed, jitter=0.0):
+    """Texture assembled from m random 4x4 blocks with Zipf-like frequencies (heavy duplicates, m distinct blocks);
+    `jitter` of the blocks get +-2 levels of noise.  With m a little above K and few blocks per centroid, Lloyd passes
+    AFTER the first one lose clusters, so the empty-cluster reseed runs with non-zero errors (found with
+    tools/find_reseed_case.py: 512x256, m = 1100, seed 1, K = 1024 reseeds on every pass)."""
+    rng = np.random.default_rng(seed)
+    pal = rng.integers(0, 256, (m, 4, 4, 3), dtype=np.uint8)
+    nb = (width // 4) * (height // 4)
+    p = 1.0 / np.arange(1, m + 1)
+    pick = rng.choice(m, nb, p=p / p.sum())
+    blocks = pal[pick].astype(np.int16)
+    noisy = rng.random(nb) < jitter
+    blocks[noisy] += rng.integers(-2, 3, (int(noisy.sum()), 4, 4, 3), dtype=np.int16)
+    blocks = np.clip(blocks, 0, 255).astype(np.uint8)
+    img = blocks.reshape(height // 4, width // 4, 4, 4, 3).transpose(0, 2, 1, 3, 4).reshape(height, width, 3)
+    return np.ascontiguousarray(img)
+
+
 def image_to_blocks(img):
     """(H, W, ch) -> (n_blocks, 16*ch) 4x4 tiles, edge-clamped, row-major blocks and pixels
     (the gather of reference src/vq_bcn_compressor.cpp:235-252)."""
